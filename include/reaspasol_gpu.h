@@ -1,0 +1,177 @@
+/*
+ * reaspasol_gpu.h -- C ABI of libreaspasol_gpu: B200-native CSR SpMV, ILU0 and L/U SpTRSV.
+ *
+ * The reference (yex33/ReSpaSol) has no plugin layer: its hot path is the set of cuSPARSE
+ * calls inside two main()s.  Each entry point below replaces one of those call groups and
+ * takes the same raw device CSR arrays (int32 indices, base 0 or 1) the reference harness
+ * uploads.  Citations are relative to /root/reference.
+ *
+ *   spmv_csr_d / spmv_csr_s      cusparseSpMV fp64 / fp32           GPU/spmv.cu:184-186 / 179-181
+ *                                (+ descriptors & workspace)         GPU/spmv.cu:122-164
+ *   spmv_csr_mixed               (no reference equivalent; north_star: fp32 A, fp64 x/y/accumulate)
+ *   rsg_ilu0_analysis            cusparse?csrilu02_analysis + zeroPivot   GPU/ilu0.cu:196-226
+ *   ilu0_factor_d / _s           cusparse?csrilu02 + zeroPivot            GPU/ilu0.cu:257-282
+ *   rsg_sptrsv_analysis          cusparse?csrsv2_analysis x2              GPU/ilu0.cu:229-252
+ *   sptrsv_lu_d / _s             cusparse?csrsv2_solve x2                 GPU/ilu0.cu:284-310
+ *                                (second solve = the INTENDED U solve; the reference's call is an
+ *                                 L^T solve left over from an IC0 example -- SURVEY.md 9-D3)
+ *   *_host wrappers              cudaMalloc + cudaMemcpy H2D/D2H          GPU/spmv.cu:91-119,216
+ *                                                                         GPU/ilu0.cu:78-118
+ *
+ * Conventions
+ *   - All pointers named rowptr/colidx/values/x/y/b/z are DEVICE pointers unless the function
+ *     name ends in _host.  Calls are asynchronous on the handle's stream (rsg_set_stream);
+ *     analysis functions and anything returning a value through a host pointer synchronise.
+ *   - The caller owns every array; the library owns only plans/workspace inside the handle
+ *     (the analogue of dBuffer / pBuffer, spmv.cu:164, ilu0.cu:193-194).
+ *   - `nnz` is advisory: the stored-entry count is rowptr[m]-rowptr[0].  When they disagree
+ *     (the reference loader's symmetric-file defect) the rowptr value is used.
+ *   - One handle = one device + one stream; calls on a handle are not re-entrant.
+ *   - Every function returns an rsg_status (0 = OK).  The library never exit()s or prints.
+ */
+#ifndef REASPASOL_GPU_H
+#define REASPASOL_GPU_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rsg_context *rsg_handle_t;
+typedef struct rsg_matrix *rsg_matrix_t;
+
+typedef enum {
+    RSG_OK = 0,
+    RSG_BAD_ARG = 1,
+    RSG_CUDA_ERROR = 2,
+    RSG_ALLOC_FAILED = 3,
+    RSG_NOT_ANALYSED = 4,
+    RSG_ZERO_PIVOT_STRUCTURAL = 5, /* A(j,j) missing  -- ilu0.cu:221-226 */
+    RSG_ZERO_PIVOT_NUMERIC = 6,    /* U(j,j) == 0     -- ilu0.cu:278-282 */
+    RSG_DEPENDENCY_TIMEOUT = 7,    /* watchdog in a dependency-flag wait fired (malformed input) */
+    RSG_UNSUPPORTED = 8
+} rsg_status;
+
+/* ---- handle ---------------------------------------------------------------------------- */
+int rsg_create(rsg_handle_t *handle, int device);
+int rsg_destroy(rsg_handle_t handle);
+int rsg_set_stream(rsg_handle_t handle, void *cuda_stream); /* cudaStream_t; NULL = default */
+int rsg_synchronize(rsg_handle_t handle);
+const char *rsg_status_string(int status);
+int rsg_version(void);
+
+/* ---- tuning / introspection ------------------------------------------------------------- */
+typedef enum {
+    RSG_OPT_SPMV_ALGO = 0,      /* rsg_spmv_algo; default AUTO */
+    RSG_OPT_SPMV_REDUCE = 1,    /* row-block kernel's in-tile reduction: 0 auto, 1 thread/row, 2 warp/row */
+    RSG_OPT_SPMV_LONG_ROW = 2,  /* rows longer than this get a CTA each (0 = default, tile/4) */
+    RSG_OPT_SPMV_VARIANT = 3,   /* compiled tile/CTA shape variant index (0 = default) */
+    RSG_OPT_SPMV_CACHE_HINT = 4,/* 0: plain ld.global.nc; 1: L1::no_allocate streams; 2: + L2 evict_first streams */
+    RSG_OPT_TRSV_ALGO = 5,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
+    RSG_OPT_ILU0_ALGO = 6,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
+    RSG_OPT_SPMV_X_PERSIST = 7, /* 1: pin x in L2 with an access-policy window on the stream */
+    RSG_OPT_COUNT_
+} rsg_option;
+
+typedef enum {
+    RSG_SPMV_AUTO = 0,
+    RSG_SPMV_ROWBLOCK = 1, /* row-length-binned row blocks: thread-, warp- and CTA-per-row paths */
+    RSG_SPMV_MERGE = 2,    /* merge-path, for skewed row lengths */
+    RSG_SPMV_VECTOR = 3,   /* plain sub-warp-per-row, scalar loads (any alignment) */
+    RSG_SPMV_SCALAR = 4    /* plain thread-per-row, scalar loads */
+} rsg_spmv_algo;
+
+typedef enum {
+    RSG_INFO_KERNEL_LAUNCHES = 0, /* kernels of this library launched on the handle so far */
+    RSG_INFO_SPMV_ALGO_USED = 1,  /* rsg_spmv_algo of the last spmv call */
+    RSG_INFO_SPMV_ROW_BLOCKS = 2, /* CTAs in the last spmv plan */
+    RSG_INFO_SPMV_MAX_ROW = 3,    /* longest row seen by the last spmv analysis */
+    RSG_INFO_LEVELS_L = 4,
+    RSG_INFO_LEVELS_U = 5,
+    RSG_INFO_SM_COUNT = 6,
+    RSG_INFO_WORKSPACE_BYTES = 7
+} rsg_info;
+
+int rsg_set_option(rsg_handle_t handle, int option, int value);
+int rsg_get_info(rsg_handle_t handle, int info, long long *value);
+
+/* ---- SpMV:  y = alpha*A*x + beta*y  (beta == 0 never reads y) ---------------------------- */
+int rsg_spmv_analysis(rsg_handle_t handle, int m, int n, int nnz, int base,
+                      const int *rowptr, const int *colidx);
+int spmv_csr_d(rsg_handle_t handle, int m, int n, int nnz, int base,
+               const int *rowptr, const int *colidx, const double *values,
+               double alpha, const double *x, double beta, double *y);
+int spmv_csr_s(rsg_handle_t handle, int m, int n, int nnz, int base,
+               const int *rowptr, const int *colidx, const float *values,
+               float alpha, const float *x, float beta, float *y);
+int spmv_csr_mixed(rsg_handle_t handle, int m, int n, int nnz, int base,
+                   const int *rowptr, const int *colidx, const float *values,
+                   double alpha, const double *x, double beta, double *y);
+
+/* ---- ILU0 -------------------------------------------------------------------------------- */
+/* "Symbolic": diagonal positions, structural zero-pivot check, level sets of the lower pattern
+ * (shared by the factorization and the L solve).  *zero_pivot_row = -1 or the first row with no
+ * diagonal entry (then the status is RSG_ZERO_PIVOT_STRUCTURAL). */
+int rsg_ilu0_analysis(rsg_handle_t handle, int n, int nnz, int base,
+                      const int *rowptr, const int *colidx, int *zero_pivot_row);
+/* "Numeric": in-place ILU(0), natural order, no pivoting; runs the analysis itself if needed.
+ * zero_pivot_row may be NULL (then the call stays asynchronous and pivots are not reported). */
+int ilu0_factor_d(rsg_handle_t handle, int n, int nnz, int base,
+                  const int *rowptr, const int *colidx, double *values_inout, int *zero_pivot_row);
+int ilu0_factor_s(rsg_handle_t handle, int n, int nnz, int base,
+                  const int *rowptr, const int *colidx, float *values_inout, int *zero_pivot_row);
+
+/* ---- SpTRSV:  L z = b (unit lower), U y = z (non-unit upper) on the in-place LU values ---- */
+int rsg_sptrsv_analysis(rsg_handle_t handle, int n, int nnz, int base,
+                        const int *rowptr, const int *colidx);
+int sptrsv_lu_d(rsg_handle_t handle, int n, int nnz, int base,
+                const int *rowptr, const int *colidx, const double *lu_values,
+                const double *b, double *tmp_z, double *y);
+int sptrsv_lu_s(rsg_handle_t handle, int n, int nnz, int base,
+                const int *rowptr, const int *colidx, const float *lu_values,
+                const float *b, float *tmp_z, float *y);
+
+/* ---- parity introspection (integers must be bit-exact against the oracle) ----------------- */
+/* which: 0 = L (lower pattern), 1 = U (upper pattern).  HOST output buffers: level_ptr needs
+ * nlevels+1 ints, level_rows n ints; pass NULL for both to query *nlevels only. */
+int rsg_get_levels(rsg_handle_t handle, int which, int *nlevels, int *level_ptr, int *level_rows);
+/* row_starts: HOST buffer of ngpu+1 ints.  balanced=1: nnz-balanced split points
+ * start[g] = first row r with rowptr[r]-rowptr[0] >= floor(g*nnz/ngpu); 0: ceil(g*m/ngpu). */
+int rsg_get_row_partition(rsg_handle_t handle, int m, int base, const int *rowptr,
+                          int ngpu, int balanced, int *row_starts);
+
+/* ---- host-pointer convenience wrappers (allocate, H2D, run, D2H, free; synchronous) ------- */
+int spmv_csr_d_host(rsg_handle_t handle, int m, int n, int nnz, int base,
+                    const int *rowptr, const int *colidx, const double *values,
+                    double alpha, const double *x, double beta, double *y);
+int spmv_csr_s_host(rsg_handle_t handle, int m, int n, int nnz, int base,
+                    const int *rowptr, const int *colidx, const float *values,
+                    float alpha, const float *x, float beta, float *y);
+int spmv_csr_mixed_host(rsg_handle_t handle, int m, int n, int nnz, int base,
+                        const int *rowptr, const int *colidx, const float *values,
+                        double alpha, const double *x, double beta, double *y);
+int ilu0_factor_d_host(rsg_handle_t handle, int n, int nnz, int base,
+                       const int *rowptr, const int *colidx, double *values_inout, int *zero_pivot_row);
+int ilu0_factor_s_host(rsg_handle_t handle, int n, int nnz, int base,
+                       const int *rowptr, const int *colidx, float *values_inout, int *zero_pivot_row);
+int sptrsv_lu_d_host(rsg_handle_t handle, int n, int nnz, int base,
+                     const int *rowptr, const int *colidx, const double *lu_values,
+                     const double *b, double *y);
+int sptrsv_lu_s_host(rsg_handle_t handle, int n, int nnz, int base,
+                     const int *rowptr, const int *colidx, const float *lu_values,
+                     const float *b, float *y);
+
+/* ---- device-resident matrix for repeated host-vector products (x in, y out per call) ------ */
+/* precision: 'd' (fp64), 's' (fp32: values cast on upload, like spmv.cu:63-67), 'm' (mixed).
+ * values_host is always fp64, as in the reference CSR struct. */
+int rsg_matrix_upload(rsg_handle_t handle, char precision, int m, int n, int nnz, int base,
+                      const int *rowptr_host, const int *colidx_host, const double *values_host,
+                      rsg_matrix_t *matrix);
+/* x_host / y_host are fp64 for 'd' and 'm', fp32 for 's' (passed as void*). */
+int rsg_matrix_spmv_host(rsg_handle_t handle, rsg_matrix_t matrix, double alpha,
+                         const void *x_host, double beta, void *y_host);
+int rsg_matrix_free(rsg_handle_t handle, rsg_matrix_t matrix);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* REASPASOL_GPU_H */

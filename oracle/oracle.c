@@ -1,0 +1,316 @@
+/*
+ * oracle.c -- CPU restatement of the ReSpaSol SpMV / ILU0 / SpTRSV hot path.
+ *
+ * THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs may load it.  The product
+ * (libreaspasol_gpu.so) never links, loads or calls anything in this directory.
+ *
+ * Parity status (see DESIGN.md "Oracle"):
+ *   - Matrix Market -> CSR: PINNED against the reference loader itself, compiled
+ *     from /root/reference/ReadMatrixMarket into oracle/_ref/ (oracle/Makefile).
+ *   - dlarnv(1,{0,0,0,1}) vector: PINNED (bit-identical to LAPACK dlaruv).
+ *   - SpMV / ILU0 / SpTRSV arithmetic: the reference delegates these to closed
+ *     third-party libraries that are absent from /root/reference (cuSPARSE: un-pinned
+ *     "CUDA 10 or recent", README.md:20; MKL "2020 or recent", README.md:19; SuperLU 5.2.1,
+ *     README.md:18).  The restatement follows the published algorithms and the
+ *     reference's call sites; the reference holds no golden vectors for them, so
+ *     for these functions PARITY IS UNPINNED beyond the KATs of SURVEY.md 10
+ *     (K2 SpMV values, K4 ILU0/levels/solves), which tests/ check.
+ *
+ * Reference call sites restated (paths relative to /root/reference):
+ *   SpMV   y = alpha*A*x + beta*y, NON_TRANSPOSE, CSR int32    GPU/spmv.cu:77-78,174-186
+ *                                                               test_spmv.c:168-180
+ *   ILU0   in place, natural order, no pivoting, unit L         GPU/ilu0.cu:203-209,264-268
+ *   zero pivots (structural / numerical)                        GPU/ilu0.cu:221-226,278-282
+ *   L solve (unit lower), U solve (non-unit upper, intended)    GPU/ilu0.cu:129-141,284-310
+ *   x = dlarnv(idist=1, seed {0,0,0,1})                         test_spmv.c:75-76
+ *
+ * Build: gcc -O2 -ffp-contract=off -fopenmp -shared -fPIC (oracle/Makefile).
+ * -ffp-contract=off: every fused multiply-add in this file is an explicit fma().
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define ORC_OK 0
+#define ORC_BAD_ARG 1
+#define ORC_ZERO_PIVOT_STRUCTURAL 5
+#define ORC_ZERO_PIVOT_NUMERIC 6
+
+/* ---------------------------------------------------------------- dlarnv ---
+ * LAPACK dlaruv as used by LAPACKE_dlarnv(1, {0,0,0,1}, n, x), test_spmv.c:75-76:
+ * 48-bit multiplicative congruential generator s <- s*33952834046453 mod 2^48,
+ * u = s * 2^-48, starting from s0 = 1; output i uses s_{i+1}.            */
+void orc_dlarnv_u01(int64_t n, double *x)
+{
+    const uint64_t mult = 33952834046453ULL, mask = (1ULL << 48) - 1;
+    uint64_t s = 1;
+    for (int64_t i = 0; i < n; ++i) {
+        s = (s * mult) & mask;
+        x[i] = (double)s * (1.0 / 281474976710656.0);
+    }
+}
+
+/* ------------------------------------------------------------------ SpMV ---
+ * Rows summed left to right in stored order, in the working precision
+ * (SURVEY.md 8c).  beta == 0 never reads y (cuSPARSE semantics, spmv.cu:78). */
+#define SPMV_BODY(TV, TX, TA)                                                   \
+    const int *rp = rowptr;                                                     \
+    for (int i = 0; i < m; ++i) {                                               \
+        TA acc = 0;                                                             \
+        for (int k = rp[i] - base; k < rp[i + 1] - base; ++k)                   \
+            acc += (TA)values[k] * (TA)x[colidx[k] - base];                     \
+        y[i] = (beta == 0) ? (TX)(alpha * acc) : (TX)(alpha * acc + beta * y[i]); \
+    }
+
+void orc_spmv_csr_d(int m, int base, const int *rowptr, const int *colidx,
+                    const double *values, double alpha, const double *x,
+                    double beta, double *y)
+{
+    SPMV_BODY(double, double, double)
+}
+
+void orc_spmv_csr_s(int m, int base, const int *rowptr, const int *colidx,
+                    const float *values, float alpha, const float *x,
+                    float beta, float *y)
+{
+    SPMV_BODY(float, float, float)
+}
+
+/* mixed: A stored fp32, x / y / accumulation fp64 (north_star; not in the reference) */
+void orc_spmv_csr_mixed(int m, int base, const int *rowptr, const int *colidx,
+                        const float *values, double alpha, const double *x,
+                        double beta, double *y)
+{
+    SPMV_BODY(float, double, double)
+}
+
+/* Row-parallel OpenMP forms: the stand-in for mkl_sparse_{d,s}_mv
+ * (test_spmv.c:168-180, bench_spmv.cc:45-48), used only as the timed CPU baseline. */
+#define SPMV_OMP_BODY(TX, TA)                                                   \
+    _Pragma("omp parallel for schedule(static) num_threads(nthreads)")          \
+    for (int i = 0; i < m; ++i) {                                               \
+        TA acc = 0;                                                             \
+        for (int k = rowptr[i] - base; k < rowptr[i + 1] - base; ++k)           \
+            acc += (TA)values[k] * (TA)x[colidx[k] - base];                     \
+        y[i] = (beta == 0) ? (TX)(alpha * acc) : (TX)(alpha * acc + beta * y[i]); \
+    }
+
+void orc_spmv_csr_d_omp(int nthreads, int m, int base, const int *rowptr, const int *colidx,
+                        const double *values, double alpha, const double *x,
+                        double beta, double *y)
+{
+    SPMV_OMP_BODY(double, double)
+}
+
+void orc_spmv_csr_s_omp(int nthreads, int m, int base, const int *rowptr, const int *colidx,
+                        const float *values, float alpha, const float *x,
+                        float beta, float *y)
+{
+    SPMV_OMP_BODY(float, float)
+}
+
+void orc_spmv_csr_mixed_omp(int nthreads, int m, int base, const int *rowptr, const int *colidx,
+                            const float *values, double alpha, const double *x,
+                            double beta, double *y)
+{
+    SPMV_OMP_BODY(double, double)
+}
+
+int orc_max_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* ------------------------------------------------------------------ ILU0 ---
+ * csrilu02 as called at GPU/ilu0.cu:264-268: IKJ, natural order, zero fill,
+ * in place; L unit-lower (diagonal not stored), U upper incl. diagonal.
+ *   for i: for k<i in row i ascending: a_ik /= a_kk;
+ *          for j>k in row k, (i,j) in pattern: a_ij = fma(-a_ik, a_kj, a_ij)
+ * Zero pivots mirror cusparseXcsrilu02_zeroPivot (ilu0.cu:222,278): structural =
+ * missing diagonal entry (smallest such row), numerical = smallest row whose
+ * finished pivot u_ii is exactly 0 (the factorization still runs to the end).  Columns must be sorted and unique within a row.               */
+#define ILU0_BODY(T, FMA)                                                       \
+    int *diag = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));           \
+    int *pos = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1));            \
+    if (!diag || !pos) { free(diag); free(pos); return ORC_BAD_ARG; }           \
+    *pivot_row = -1;                                                            \
+    for (int i = 0; i < n; ++i) {                                               \
+        diag[i] = -1;                                                           \
+        for (int k = rowptr[i] - base; k < rowptr[i + 1] - base; ++k)           \
+            if (colidx[k] - base == i) { diag[i] = k; break; }                  \
+        if (diag[i] < 0) { *pivot_row = i; free(diag); free(pos);               \
+                           return ORC_ZERO_PIVOT_STRUCTURAL; }                  \
+    }                                                                           \
+    for (int j = 0; j < n; ++j) pos[j] = -1;                                    \
+    int status = ORC_OK;                                                        \
+    for (int i = 0; i < n; ++i) {                                               \
+        int rs = rowptr[i] - base, re = rowptr[i + 1] - base;                   \
+        for (int k = rs; k < re; ++k) pos[colidx[k] - base] = k;                \
+        for (int kk = rs; kk < re; ++kk) {                                      \
+            int k = colidx[kk] - base;                                          \
+            if (k >= i) break;                                                  \
+            T lik = a[kk] / a[diag[k]];                                         \
+            a[kk] = lik;                                                        \
+            for (int jj = diag[k] + 1; jj < rowptr[k + 1] - base; ++jj) {       \
+                int p = pos[colidx[jj] - base];                                 \
+                if (p >= 0) a[p] = FMA(-lik, a[jj], a[p]);                      \
+            }                                                                   \
+        }                                                                       \
+        for (int k = rs; k < re; ++k) pos[colidx[k] - base] = -1;               \
+        if (a[diag[i]] == (T)0 && status == ORC_OK) {                           \
+            status = ORC_ZERO_PIVOT_NUMERIC; *pivot_row = i; }                  \
+    }                                                                           \
+    free(diag); free(pos);                                                      \
+    return status;
+
+int orc_ilu0_d(int n, int base, const int *rowptr, const int *colidx, double *a, int *pivot_row)
+{
+    ILU0_BODY(double, fma)
+}
+
+int orc_ilu0_s(int n, int base, const int *rowptr, const int *colidx, float *a, int *pivot_row)
+{
+    ILU0_BODY(float, fmaf)
+}
+
+/* ---------------------------------------------------------------- SpTRSV ---
+ * L z = b : L = strictly-lower part of the in-place LU values, unit diagonal
+ *           (desc_L, GPU/ilu0.cu:129-134; csrsv2_solve ilu0.cu:296-298).
+ * U y = z : U = upper part incl. diagonal, non-unit (desc_U fill/diag modes,
+ *           ilu0.cu:136-141 -- the INTENDED second solve).
+ * Sequential left-to-right sums with explicit fma.                          */
+#define TRSV_L_BODY(T, FMA)                                                     \
+    for (int i = 0; i < n; ++i) {                                               \
+        T s = b[i];                                                             \
+        for (int k = rowptr[i] - base; k < rowptr[i + 1] - base; ++k) {         \
+            int j = colidx[k] - base;                                           \
+            if (j >= i) break;                                                  \
+            s = FMA(-lu[k], z[j], s);                                           \
+        }                                                                       \
+        z[i] = s;                                                               \
+    }
+
+#define TRSV_U_BODY(T, FMA)                                                     \
+    for (int i = n - 1; i >= 0; --i) {                                          \
+        T s = z[i]; T d = 0; int have = 0;                                      \
+        for (int k = rowptr[i] - base; k < rowptr[i + 1] - base; ++k) {         \
+            int j = colidx[k] - base;                                           \
+            if (j < i) continue;                                                \
+            if (j == i) { d = lu[k]; have = 1; continue; }                      \
+            s = FMA(-lu[k], y[j], s);                                           \
+        }                                                                       \
+        if (!have) return ORC_ZERO_PIVOT_STRUCTURAL;                            \
+        y[i] = s / d;                                                           \
+    }                                                                           \
+    return ORC_OK;
+
+void orc_sptrsv_l_d(int n, int base, const int *rowptr, const int *colidx,
+                    const double *lu, const double *b, double *z)
+{
+    TRSV_L_BODY(double, fma)
+}
+void orc_sptrsv_l_s(int n, int base, const int *rowptr, const int *colidx,
+                    const float *lu, const float *b, float *z)
+{
+    TRSV_L_BODY(float, fmaf)
+}
+int orc_sptrsv_u_d(int n, int base, const int *rowptr, const int *colidx,
+                   const double *lu, const double *z, double *y)
+{
+    TRSV_U_BODY(double, fma)
+}
+int orc_sptrsv_u_s(int n, int base, const int *rowptr, const int *colidx,
+                   const float *lu, const float *z, float *y)
+{
+    TRSV_U_BODY(float, fmaf)
+}
+int orc_sptrsv_lu_d(int n, int base, const int *rowptr, const int *colidx,
+                    const double *lu, const double *b, double *z, double *y)
+{
+    orc_sptrsv_l_d(n, base, rowptr, colidx, lu, b, z);
+    return orc_sptrsv_u_d(n, base, rowptr, colidx, lu, z, y);
+}
+int orc_sptrsv_lu_s(int n, int base, const int *rowptr, const int *colidx,
+                    const float *lu, const float *b, float *z, float *y)
+{
+    orc_sptrsv_l_s(n, base, rowptr, colidx, lu, b, z);
+    return orc_sptrsv_u_s(n, base, rowptr, colidx, lu, z, y);
+}
+
+/* ---------------------------------------------------------------- levels ---
+ * Canonical level sets (what csrilu02_analysis / csrsv2_analysis,
+ * ilu0.cu:203-209,232-251, compute internally):
+ *   which = 0 (L): lev[i] = 1 + max{lev[j] : j < i, a_ij stored}, 0 if none
+ *   which = 1 (U): lev[i] = 1 + max{lev[j] : j > i, a_ij stored}, 0 if none
+ * level_ptr has nlevels+1 entries; level_rows lists rows ascending inside a level. */
+int orc_levels(int n, int base, const int *rowptr, const int *colidx, int which,
+               int *lev, int *nlevels, int *level_ptr, int *level_rows)
+{
+    int nl = 0;
+    if (which == 0) {
+        for (int i = 0; i < n; ++i) {
+            int l = 0;
+            for (int k = rowptr[i] - base; k < rowptr[i + 1] - base; ++k) {
+                int j = colidx[k] - base;
+                if (j < i && lev[j] + 1 > l) l = lev[j] + 1;
+            }
+            lev[i] = l;
+            if (l + 1 > nl) nl = l + 1;
+        }
+    } else {
+        for (int i = n - 1; i >= 0; --i) {
+            int l = 0;
+            for (int k = rowptr[i] - base; k < rowptr[i + 1] - base; ++k) {
+                int j = colidx[k] - base;
+                if (j > i && j < n && lev[j] + 1 > l) l = lev[j] + 1;
+            }
+            lev[i] = l;
+            if (l + 1 > nl) nl = l + 1;
+        }
+    }
+    *nlevels = nl;
+    if (level_ptr && level_rows) {
+        for (int l = 0; l <= nl; ++l) level_ptr[l] = 0;
+        for (int i = 0; i < n; ++i) level_ptr[lev[i] + 1]++;
+        for (int l = 0; l < nl; ++l) level_ptr[l + 1] += level_ptr[l];
+        int *cur = (int *)malloc(sizeof(int) * (size_t)(nl + 1));
+        if (!cur) return ORC_BAD_ARG;
+        memcpy(cur, level_ptr, sizeof(int) * (size_t)(nl + 1));
+        for (int i = 0; i < n; ++i) level_rows[cur[lev[i]]++] = i;
+        free(cur);
+    }
+    return ORC_OK;
+}
+
+/* ------------------------------------------------------------- partition ---
+ * nnz-balanced contiguous row blocks for the multi-GPU SpMV:
+ * start[g] = first row r with rowptr[r]-base >= floor(g*nnz/P); start[0]=0, start[P]=m.
+ * balanced = 0 gives the equal-rows variant ceil(g*m/P).                      */
+void orc_row_partition(int m, int base, const int *rowptr, int P, int balanced, int *start)
+{
+    int64_t nnz = (int64_t)rowptr[m] - rowptr[0];
+    start[0] = 0;
+    start[P] = m;
+    for (int g = 1; g < P; ++g) {
+        if (!balanced) {
+            start[g] = (int)(((int64_t)g * m + P - 1) / P);
+            continue;
+        }
+        int64_t target = (int64_t)g * nnz / P + (rowptr[0] - base);
+        int lo = 0, hi = m;
+        while (lo < hi) {
+            int mid = lo + (hi - lo) / 2;
+            if ((int64_t)rowptr[mid] - base < target) lo = mid + 1; else hi = mid;
+        }
+        start[g] = lo;
+    }
+}

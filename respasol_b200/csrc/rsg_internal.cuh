@@ -1,0 +1,128 @@
+// rsg_internal.cuh -- shared declarations of libreaspasol_gpu (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../include/reaspasol_gpu.h"
+
+#define RSG_CUDA_TRY(expr)                                         \
+    do {                                                           \
+        cudaError_t e__ = (expr);                                  \
+        if (e__ != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; } \
+    } while (0)
+
+#define RSG_TRY(expr)                      \
+    do {                                   \
+        int s__ = (expr);                  \
+        if (s__ != RSG_OK) return s__;     \
+    } while (0)
+
+namespace rsg {
+
+// ------------------------------------------------------------------ SpMV plan
+// Built once per sparsity pattern by rsg_spmv_analysis (device kernels + one small D2H of
+// the statistics), cached in the handle; the analogue of cusparseSpMV_bufferSize/preprocess.
+struct SpmvPlan {
+    // key
+    const int *rowptr = nullptr;
+    const int *colidx = nullptr;
+    int m = 0, n = 0, base = 0;
+    int opt_sig = 0;       // hash of the options that shape the plan
+    // statistics
+    int nnz = 0;           // stored entries, rowptr[m]-rowptr[0]
+    int first = 0;         // rowptr[0]-base (non-zero for a row-slab view into a larger CSR)
+    int max_row = 0;
+    int algo = 0;          // resolved rsg_spmv_algo
+    // row-block kernel
+    int tile = 0;          // nnz capacity of a CTA tile
+    int long_row = 0;      // rows longer than this are CTA-per-row blocks
+    int nblk = 0;
+    int *blk_row = nullptr;    // nblk+1 row indices
+    // merge-path kernel
+    int merge_items = 0;   // rows+nnz per CTA
+    int ntiles = 0;
+    int2 *coords = nullptr;    // ntiles+1 (row, nnz) start coordinates
+    int *carry_row = nullptr;  // ntiles
+    void *carry_val = nullptr; // ntiles * 8 B
+    size_t bytes = 0;
+};
+
+// ------------------------------------------------ triangular / ILU0 plan
+struct TriPlan {
+    const int *rowptr = nullptr;
+    const int *colidx = nullptr;
+    int n = 0, base = 0, nnz = 0;
+    int *diag_pos = nullptr;       // position of a_ii in colidx/values, -1 if missing
+    int missing_diag_row = -1;     // first row without a diagonal entry
+    bool have[2] = {false, false}; // [0]=L (lower pattern), [1]=U (upper pattern)
+    int nlevels[2] = {0, 0};
+    int *lev[2] = {nullptr, nullptr};       // level of every row
+    int *order[2] = {nullptr, nullptr};     // rows sorted by (level, row): "level_rows"
+    int *level_ptr[2] = {nullptr, nullptr}; // nlevels+1 offsets into order (device)
+    std::vector<int> level_ptr_host[2];
+    int *done = nullptr;           // per-row dependency flags (epoch-stamped)
+    int epoch = 0;
+    int *ctl = nullptr;            // [0] ticket counter, [1] error flag, [2] min zero-pivot row
+    size_t bytes = 0;
+};
+
+} // namespace rsg
+
+struct rsg_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    int l2_bytes = 0;
+    int opts[RSG_OPT_COUNT_] = {0};
+    long long launches = 0;
+    int last_spmv_algo = 0;
+    int last_spmv_blocks = 0;
+    int last_spmv_maxrow = 0;
+    std::vector<rsg::SpmvPlan> spmv_plans;
+    std::vector<rsg::TriPlan> tri_plans;
+    int last_tri = -1;
+    void *cub_tmp = nullptr;
+    size_t cub_tmp_bytes = 0;
+    int *scratch_i = nullptr; // small device scratch (stats), 64 ints
+    int *pinned_i = nullptr;  // small pinned host mirror, 64 ints
+};
+
+struct rsg_matrix {
+    char precision;
+    int m, n, nnz, base;
+    int *rowptr;
+    int *colidx;
+    void *values;
+    void *x;
+    void *y;
+    void *pin_x; // pinned staging
+    void *pin_y;
+};
+
+namespace rsg {
+
+int ensure_cub_tmp(rsg_context *h, size_t bytes);
+
+// spmv.cu
+int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
+                  bool aligned16, SpmvPlan **out);
+void spmv_free_plan(SpmvPlan &p);
+template <typename TV, typename TX>
+int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
+             const TV *values, TX alpha, const TX *x, TX beta, TX *y);
+
+// levels.cu
+int tri_get_plan(rsg_context *h, int n, int base, const int *rowptr, const int *colidx, TriPlan **out);
+int tri_build_levels(rsg_context *h, TriPlan *p, int which);
+void tri_free_plan(TriPlan &p);
+
+// ilu0_trsv.cu
+template <typename T>
+int ilu0_run(rsg_context *h, TriPlan *p, T *values, int *zero_pivot_row);
+template <typename T>
+int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y);
+
+} // namespace rsg
