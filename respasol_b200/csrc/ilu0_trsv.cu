@@ -1,0 +1,381 @@
+// ilu0_trsv.cu -- "Numeric" ILU(0) factorization and the L/U triangular solves for sm_100a,
+// replacing cusparse?csrilu02 and the two cusparse?csrsv2_solve calls of the reference harness
+// (/root/reference/GPU/ilu0.cu:257-310).  Semantics: in place, natural order, no pivoting, zero
+// fill; L unit-lower (diagonal not stored), U upper incl. diagonal; the second solve is the
+// INTENDED U solve (the reference's call is an L^T solve left over from an IC0 example).
+//
+// Both phases are driven by the level-set schedule built on device (levels.cu): rows are handed
+// out through an atomic ticket in level order, so rows of one level run side by side and their
+// dependencies -- all in earlier levels -- have almost always finished; correctness does not
+// rest on that: every dependency is still guarded by a per-row flag (factorization) or by the
+// solution entry itself carrying a not-yet-written sentinel (solves).  A row only waits on rows
+// whose ticket was drawn earlier by a warp that is resident, hence no deadlock and no grid-wide
+// barrier per level.  Waiting never spins inside a divergent branch: a warp sweeps all its rows,
+// those that are ready advance, then the warp votes and sweeps again.
+//
+// Arithmetic follows the oracle exactly (k ascending, explicit fma, IEEE division), so the
+// factors and the thread-per-row solves are bit-identical to the CPU restatement.
+#include "rsg_internal.cuh"
+
+namespace rsg {
+
+#define RSG_SPIN_LIMIT (1 << 22) // sweeps before a waiting row gives up (malformed schedule)
+
+// ------------------------------------------------------------------ flags / sentinels
+__device__ __forceinline__ int ld_acquire(const int *p)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int *p, int v)
+{
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// A solution entry that has not been written yet holds a quiet NaN with a payload no
+// arithmetic instruction produces (hardware NaN results are canonical).
+template <typename T> struct Pending;
+template <> struct Pending<double> {
+    typedef unsigned long long bits_t;
+    static constexpr bits_t kBits = 0xFFF8DEADBEEF0001ULL;
+    static __device__ __forceinline__ bits_t load(const double *p)
+    {
+        bits_t v;
+        asm volatile("ld.relaxed.gpu.global.b64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+        return v;
+    }
+    static __device__ __forceinline__ void store(double *p, double x)
+    {
+        asm volatile("st.relaxed.gpu.global.b64 [%0], %1;" ::"l"(p), "l"(__double_as_longlong(x)) : "memory");
+    }
+    static __device__ __forceinline__ double value(bits_t b) { return __longlong_as_double((long long)b); }
+};
+template <> struct Pending<float> {
+    typedef unsigned int bits_t;
+    static constexpr bits_t kBits = 0xFFC0DEADu;
+    static __device__ __forceinline__ bits_t load(const float *p)
+    {
+        bits_t v;
+        asm volatile("ld.relaxed.gpu.global.b32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+        return v;
+    }
+    static __device__ __forceinline__ void store(float *p, float x)
+    {
+        asm volatile("st.relaxed.gpu.global.b32 [%0], %1;" ::"l"(p), "r"(__float_as_uint(x)) : "memory");
+    }
+    static __device__ __forceinline__ float value(bits_t b) { return __uint_as_float(b); }
+};
+
+template <typename T> __device__ __forceinline__ T fma_t(T a, T b, T c);
+template <> __device__ __forceinline__ double fma_t(double a, double b, double c) { return fma(a, b, c); }
+template <> __device__ __forceinline__ float fma_t(float a, float b, float c) { return fmaf(a, b, c); }
+template <typename T> __device__ __forceinline__ T div_t(T a, T b);
+template <> __device__ __forceinline__ double div_t(double a, double b) { return __ddiv_rn(a, b); }
+template <> __device__ __forceinline__ float div_t(float a, float b) { return __fdiv_rn(a, b); }
+
+// ------------------------------------------------------------------ ILU(0), warp per row
+// ctl[0] ticket, ctl[1] timeout flag, ctl[2] smallest row with a zero pivot
+template <typename T, int WARPS, int WCAP>
+__global__ void __launch_bounds__(WARPS * 32)
+ilu0_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx, T *values,
+            const int *__restrict__ diag_pos, const int *__restrict__ order, int *done, int epoch, int *ctl)
+{
+    __shared__ int s_col[WARPS][WCAP];
+    __shared__ T s_val[WARPS][WCAP];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = (*(volatile int *)(ctl + 1)) ? n : atomicAdd(ctl, 1); // stop drawing rows after a timeout
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= n) break;
+        const int i = order[t];
+        const int rs = rowptr[i] - base, len = rowptr[i + 1] - base - rs;
+        const int nl = diag_pos[i] - rs; // lower entries are [0,nl) of the row (columns sorted)
+        const bool staged = len <= WCAP;
+        const int *rc;
+        volatile T *rv;
+        if (staged) {
+            for (int l = lane; l < len; l += 32) { s_col[w][l] = colidx[rs + l]; s_val[w][l] = values[rs + l]; }
+            rc = s_col[w];
+            rv = s_val[w];
+        } else {
+            rc = colidx + rs;
+            rv = values + rs;
+        }
+        __syncwarp();
+        for (int c0 = 0; c0 < nl; c0 += 32) {
+            // lane <-> lower entry c0+lane: wait for its row, fetch that row's pivot and extent
+            const int lk = c0 + lane;
+            const bool mine = lk < nl;
+            int k = 0, dpk = 0, rek = 0;
+            T ukk = 1;
+            if (mine) k = rc[lk] - base;
+            bool ready = !mine;
+            int spins = 0;
+            while (!__all_sync(0xffffffffu, ready)) {
+                if (!ready) ready = (ld_acquire(done + k) == epoch);
+                if (++spins > RSG_SPIN_LIMIT) { if (lane == 0) atomicExch(ctl + 1, 1); break; }
+            }
+            __threadfence();
+            __syncwarp();
+            if (mine) {
+                dpk = diag_pos[k];
+                rek = rowptr[k + 1] - base;
+                ukk = __ldcg(values + dpk);
+            }
+            const int cnt = min(32, nl - c0);
+            for (int u = 0; u < cnt; ++u) {
+                const int dk = __shfl_sync(0xffffffffu, dpk, u);
+                const int ek = __shfl_sync(0xffffffffu, rek, u);
+                const T pk = __shfl_sync(0xffffffffu, ukk, u);
+                T lik = 0;
+                if (lane == 0) {
+                    lik = div_t<T>(rv[c0 + u], pk);
+                    rv[c0 + u] = lik;
+                }
+                lik = __shfl_sync(0xffffffffu, lik, 0);
+                for (int jj = dk + 1 + lane; jj < ek; jj += 32) {
+                    const int jraw = colidx[jj];
+                    const T ukj = __ldcg(values + jj);
+                    int lo = c0 + u + 1, hi = len;
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        if (rc[mid] < jraw) lo = mid + 1; else hi = mid;
+                    }
+                    if (lo < len && rc[lo] == jraw) rv[lo] = fma_t<T>(-lik, ukj, rv[lo]);
+                }
+                __syncwarp();
+            }
+        }
+        if (staged)
+            for (int l = lane; l < len; l += 32) values[rs + l] = s_val[w][l];
+        if (lane == 0 && rv[nl] == (T)0) atomicMin(ctl + 2, i);
+        __threadfence();
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence();
+            st_release(done + i, epoch);
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------ solves, thread per row
+template <typename T> __global__ void fill_pending_kernel(int n, T *a, T *b)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const T s = Pending<T>::value(Pending<T>::kBits);
+    a[i] = s;
+    if (b) b[i] = s;
+}
+
+// UPPER = false:  z_i = b_i - sum_{j<i} l_ij z_j            (unit diagonal)
+// UPPER = true :  y_i = (z_i - sum_{j>i} u_ij y_j) / u_ii
+// `sol` is pre-filled with the pending sentinel; rhs is b (lower) or z (upper).
+template <typename T, bool UPPER>
+__global__ void __launch_bounds__(256)
+trsv_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+            const T *__restrict__ lu, const int *__restrict__ diag_pos, const int *__restrict__ order,
+            const T *__restrict__ rhs, T *sol, int *ctl)
+{
+    typedef Pending<T> P;
+    constexpr int B = 4; // dependencies fetched per round trip
+    const int lane = threadIdx.x & 31;
+    for (;;) {
+        int t0 = 0;
+        if (lane == 0) t0 = (*(volatile int *)(ctl + 1)) ? n : atomicAdd(ctl, 32);
+        t0 = __shfl_sync(0xffffffffu, t0, 0);
+        if (t0 >= n) break;
+        const int t = t0 + lane;
+        const bool have = t < n;
+        int i = 0, k = 0, ke = 0, kd = 0;
+        T s = 0;
+        if (have) {
+            i = order[t];
+            kd = diag_pos[i];
+            if (UPPER) { k = kd + 1; ke = rowptr[i + 1] - base; }
+            else { k = rowptr[i] - base; ke = kd; }
+            s = rhs[i];
+        }
+        bool done = !have;
+        int spins = 0;
+        while (!__all_sync(0xffffffffu, done)) {
+            if (!done) {
+                while (k < ke) {
+                    const int nb = min(B, ke - k);
+                    typename P::bits_t v[B];
+                    T a[B];
+#pragma unroll
+                    for (int u = 0; u < B; ++u)
+                        if (u < nb) {
+                            v[u] = P::load(sol + (colidx[k + u] - base));
+                            a[u] = lu[k + u];
+                        }
+                    int adv = 0;
+#pragma unroll
+                    for (int u = 0; u < B; ++u)
+                        if (u < nb && adv == u && v[u] != P::kBits) {
+                            s = fma_t<T>(-a[u], P::value(v[u]), s);
+                            adv = u + 1;
+                        }
+                    k += adv;
+                    if (adv < nb) break; // a dependency is still pending: next sweep
+                }
+                if (k >= ke) {
+                    P::store(sol + i, UPPER ? div_t<T>(s, lu[kd]) : s);
+                    done = true;
+                }
+            }
+            if (++spins > RSG_SPIN_LIMIT) { atomicExch(ctl + 1, 1); break; }
+        }
+    }
+}
+
+// Level-by-level variant (RSG_OPT_TRSV_ALGO = 2): rows [lo,hi) of the schedule belong to levels
+// that are all complete on entry, plain loads, one launch per run of levels.  A run of thin
+// levels is chewed by ONE CTA with a block barrier between levels instead of a launch each.
+template <typename T, bool UPPER>
+__device__ __forceinline__ void trsv_row_plain(int i, int base, const int *__restrict__ rowptr,
+                                               const int *__restrict__ colidx, const T *__restrict__ lu,
+                                               const int *__restrict__ diag_pos, const T *rhs, volatile T *sol)
+{
+    const int kd = diag_pos[i];
+    int k, ke;
+    if (UPPER) { k = kd + 1; ke = rowptr[i + 1] - base; }
+    else { k = rowptr[i] - base; ke = kd; }
+    T s = rhs[i];
+    for (; k < ke; ++k) s = fma_t<T>(-lu[k], sol[colidx[k] - base], s);
+    sol[i] = UPPER ? div_t<T>(s, lu[kd]) : s;
+}
+
+template <typename T, bool UPPER>
+__global__ void trsv_level_kernel(int lo, int hi, int base, const int *__restrict__ rowptr,
+                                  const int *__restrict__ colidx, const T *__restrict__ lu,
+                                  const int *__restrict__ diag_pos, const int *__restrict__ order, const T *rhs, T *sol)
+{
+    const int t = lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < hi) trsv_row_plain<T, UPPER>(order[t], base, rowptr, colidx, lu, diag_pos, rhs, sol);
+}
+
+template <typename T, bool UPPER>
+__global__ void __launch_bounds__(1024)
+trsv_thin_levels_kernel(int l0, int l1, const int *__restrict__ level_ptr, int base, const int *__restrict__ rowptr,
+                        const int *__restrict__ colidx, const T *__restrict__ lu, const int *__restrict__ diag_pos,
+                        const int *__restrict__ order, const T *rhs, T *sol)
+{
+    __shared__ int s_rows[1024]; // this level's rows, staged while the previous level drains
+    int lo = level_ptr[l0];
+    for (int l = l0; l < l1; ++l) {
+        const int hi = level_ptr[l + 1];
+        const int t = lo + threadIdx.x;
+        if (t < hi) s_rows[threadIdx.x] = order[t];
+        __syncthreads();
+        if (t < hi) trsv_row_plain<T, UPPER>(s_rows[threadIdx.x], base, rowptr, colidx, lu, diag_pos, rhs, sol);
+        __threadfence_block();
+        __syncthreads();
+        lo = hi;
+    }
+}
+
+// ------------------------------------------------------------------ host side
+template <typename T>
+int ilu0_run(rsg_context *h, TriPlan *p, T *values, int *zero_pivot_row)
+{
+    if (zero_pivot_row) *zero_pivot_row = -1;
+    if (p->missing_diag_row >= 0) {
+        if (zero_pivot_row) *zero_pivot_row = p->missing_diag_row;
+        return RSG_ZERO_PIVOT_STRUCTURAL;
+    }
+    if (p->n == 0) return RSG_OK;
+    RSG_TRY(tri_build_levels(h, p, 0));
+    cudaStream_t st = h->stream;
+    p->epoch++;
+    if (p->epoch == 0x7fffffff) { // flags are compared for equality: restart the stamp
+        RSG_CUDA_TRY(cudaMemsetAsync(p->done, 0, sizeof(int) * (size_t)p->n, st));
+        p->epoch = 1;
+    }
+    h->pinned_i[8] = 0; h->pinned_i[9] = 0; h->pinned_i[10] = 0x7fffffff; h->pinned_i[11] = 0;
+    RSG_CUDA_TRY(cudaMemcpyAsync(p->ctl, h->pinned_i + 8, 4 * sizeof(int), cudaMemcpyHostToDevice, st));
+    constexpr int WARPS = 8, WCAP = 128;
+    auto kern = ilu0_kernel<T, WARPS, WCAP>;
+    int per_sm = 0;
+    RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, 0));
+    const int grid = std::max(1, std::min(h->sm_count * std::max(per_sm, 1), (p->n + WARPS - 1) / WARPS));
+    kern<<<grid, WARPS * 32, 0, st>>>(p->n, p->base, p->rowptr, p->colidx, values, p->diag_pos, p->order[0], p->done,
+                                      p->epoch, p->ctl);
+    h->launches++;
+    RSG_CUDA_TRY(cudaGetLastError());
+    if (!zero_pivot_row) return RSG_OK;
+    RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i + 12, p->ctl, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaStreamSynchronize(st));
+    if (h->pinned_i[13]) return RSG_DEPENDENCY_TIMEOUT;
+    if (h->pinned_i[14] != 0x7fffffff) {
+        *zero_pivot_row = h->pinned_i[14];
+        return RSG_ZERO_PIVOT_NUMERIC;
+    }
+    return RSG_OK;
+}
+
+template <typename T, bool UPPER>
+static int trsv_levels_launches(rsg_context *h, TriPlan *p, const T *lu, const T *rhs, T *sol)
+{
+    const int which = UPPER ? 1 : 0;
+    const std::vector<int> &lp = p->level_ptr_host[which];
+    const int nl = p->nlevels[which];
+    cudaStream_t st = h->stream;
+    int l = 0;
+    while (l < nl) {
+        const int width = lp[l + 1] - lp[l];
+        if (width > 1024) {
+            trsv_level_kernel<T, UPPER><<<(width + 255) / 256, 256, 0, st>>>(lp[l], lp[l + 1], p->base, p->rowptr, p->colidx,
+                                                                             lu, p->diag_pos, p->order[which], rhs, sol);
+            h->launches++;
+            ++l;
+        } else {
+            int e = l + 1;
+            while (e < nl && lp[e + 1] - lp[e] <= 1024) ++e;
+            trsv_thin_levels_kernel<T, UPPER><<<1, 1024, 0, st>>>(l, e, p->level_ptr[which], p->base, p->rowptr, p->colidx, lu,
+                                                                  p->diag_pos, p->order[which], rhs, sol);
+            h->launches++;
+            l = e;
+        }
+    }
+    return RSG_OK;
+}
+
+template <typename T>
+int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
+{
+    if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
+    if (p->n == 0) return RSG_OK;
+    if (!lu || !b || !z || !y || b == z || z == y || b == y) return RSG_BAD_ARG;
+    RSG_TRY(tri_build_levels(h, p, 0));
+    RSG_TRY(tri_build_levels(h, p, 1));
+    cudaStream_t st = h->stream;
+    const int n = p->n;
+    if (h->opts[RSG_OPT_TRSV_ALGO] == 2) {
+        RSG_TRY((trsv_levels_launches<T, false>(h, p, lu, b, z)));
+        RSG_TRY((trsv_levels_launches<T, true>(h, p, lu, z, y)));
+        RSG_CUDA_TRY(cudaGetLastError());
+        return RSG_OK;
+    }
+    RSG_CUDA_TRY(cudaMemsetAsync(p->ctl, 0, 8 * sizeof(int), st));
+    fill_pending_kernel<T><<<(n + 255) / 256, 256, 0, st>>>(n, z, y);
+    int per_sm = 0;
+    RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trsv_kernel<T, false>, 256, 0));
+    const int grid = std::max(1, std::min(h->sm_count * std::max(per_sm, 1), (n + 255) / 256));
+    trsv_kernel<T, false><<<grid, 256, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[0], b, z, p->ctl);
+    trsv_kernel<T, true><<<grid, 256, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[1], z, y, p->ctl + 4);
+    h->launches += 3;
+    RSG_CUDA_TRY(cudaGetLastError());
+    return RSG_OK;
+}
+
+template int ilu0_run<double>(rsg_context *, TriPlan *, double *, int *);
+template int ilu0_run<float>(rsg_context *, TriPlan *, float *, int *);
+template int trsv_run<double>(rsg_context *, TriPlan *, const double *, const double *, double *, double *);
+template int trsv_run<float>(rsg_context *, TriPlan *, const float *, const float *, float *, float *);
+
+} // namespace rsg

@@ -36,15 +36,15 @@ struct SpmvPlan {
     int first = 0;         // rowptr[0]-base (non-zero for a row-slab view into a larger CSR)
     int max_row = 0;
     int algo = 0;          // resolved rsg_spmv_algo
+    int variant = 0;       // resolved tile/CTA shape
     // row-block kernel
-    int tile = 0;          // nnz capacity of a CTA tile
-    int long_row = 0;      // rows longer than this are CTA-per-row blocks
+    int tile = 0;          // merged items (rows + entries) per CTA
     int nblk = 0;
     int *blk_row = nullptr;    // nblk+1 row indices
     // merge-path kernel
-    int merge_items = 0;   // rows+nnz per CTA
+    int merge_items = 0;   // rows+entries per CTA
     int ntiles = 0;
-    int2 *coords = nullptr;    // ntiles+1 (row, nnz) start coordinates
+    int2 *coords = nullptr;    // ntiles+1 (row, entry) start coordinates
     int *carry_row = nullptr;  // ntiles
     void *carry_val = nullptr; // ntiles * 8 B
     size_t bytes = 0;
@@ -55,8 +55,9 @@ struct TriPlan {
     const int *rowptr = nullptr;
     const int *colidx = nullptr;
     int n = 0, base = 0, nnz = 0;
-    int *diag_pos = nullptr;       // position of a_ii in colidx/values, -1 if missing
+    int *diag_pos = nullptr;       // zero-based position of a_ii in colidx/values, -1 if missing
     int missing_diag_row = -1;     // first row without a diagonal entry
+    int max_row = 0;
     bool have[2] = {false, false}; // [0]=L (lower pattern), [1]=U (upper pattern)
     int nlevels[2] = {0, 0};
     int *lev[2] = {nullptr, nullptr};       // level of every row
@@ -65,7 +66,7 @@ struct TriPlan {
     std::vector<int> level_ptr_host[2];
     int *done = nullptr;           // per-row dependency flags (epoch-stamped)
     int epoch = 0;
-    int *ctl = nullptr;            // [0] ticket counter, [1] error flag, [2] min zero-pivot row
+    int *ctl = nullptr;            // [0] ticket counter, [1] error flag, [2] min zero-pivot row, [3] 2nd ticket
     size_t bytes = 0;
 };
 
@@ -76,6 +77,7 @@ struct rsg_context {
     cudaStream_t stream = nullptr;
     int sm_count = 148;
     int l2_bytes = 0;
+    int max_smem_optin = 0;
     int opts[RSG_OPT_COUNT_] = {0};
     long long launches = 0;
     int last_spmv_algo = 0;
@@ -88,6 +90,8 @@ struct rsg_context {
     size_t cub_tmp_bytes = 0;
     int *scratch_i = nullptr; // small device scratch (stats), 64 ints
     int *pinned_i = nullptr;  // small pinned host mirror, 64 ints
+    const void *persist_ptr = nullptr; // x currently covered by the L2 access-policy window
+    size_t persist_bytes = 0;
 };
 
 struct rsg_matrix {
@@ -108,14 +112,17 @@ int ensure_cub_tmp(rsg_context *h, size_t bytes);
 
 // spmv.cu
 int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
-                  bool aligned16, SpmvPlan **out);
+                  bool force_rebuild, SpmvPlan **out);
 void spmv_free_plan(SpmvPlan &p);
 template <typename TV, typename TX>
 int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
              const TV *values, TX alpha, const TX *x, TX beta, TX *y);
+int row_partition(rsg_context *h, int m, int base, const int *rowptr, int ngpu, int balanced,
+                  int *row_starts_host);
 
 // levels.cu
-int tri_get_plan(rsg_context *h, int n, int base, const int *rowptr, const int *colidx, TriPlan **out);
+int tri_get_plan(rsg_context *h, int n, int base, const int *rowptr, const int *colidx,
+                 bool force_rebuild, TriPlan **out);
 int tri_build_levels(rsg_context *h, TriPlan *p, int which);
 void tri_free_plan(TriPlan &p);
 

@@ -1,0 +1,719 @@
+// spmv.cu -- CSR SpMV  y = alpha*A*x + beta*y  for sm_100a (B200), replacing the cusparseSpMV
+// call group of the reference harness (/root/reference/GPU/spmv.cu:122-186).
+//
+// Kernels (no tensor cores: 2 flop per 12 B, the bound is HBM):
+//   rowblock  The matrix is cut on device into CTA tiles of ~TILE merged items (rows + entries)
+//             rounded to row boundaries.  A CTA streams its entries with aligned 128-bit
+//             loads indexed on the GLOBAL entry index (row starts are arbitrary, the stream is
+//             not), multiplies by the gathered x (read-only path, L1/L2 resident) and parks the
+//             products in shared memory; rows are then reduced out of shared memory by a
+//             per-tile row-length bin: thread-per-row (short rows), 4/8/16/32-lane
+//             sub-warp-per-row with shuffle reduction (medium rows).  A row that does not fit
+//             the tile is reduced CTA-per-row straight from global memory.
+//   merge     Merge-path (rows+entries split evenly over CTAs and threads, carry fix-up):
+//             for skewed row lengths, where one dense row would pin a single CTA.
+//   vector    plain sub-warp-per-row, scalar loads, any alignment (fallback / cross-check)
+//   scalar    plain thread-per-row (fallback / cross-check)
+// TX is the vector / accumulation type, TV the stored-value type: (double,double) fp64,
+// (float,float) fp32, (float,double) the mixed variant.
+#include "rsg_internal.cuh"
+
+#include <cub/block/block_scan.cuh>
+
+namespace rsg {
+
+// ------------------------------------------------------------------ streaming loads
+// HINT 0: ld.global.nc   1: + L1::no_allocate   2: + L2 evict_first policy
+template <int HINT> __device__ __forceinline__ int4 ld_stream(const int4 *p, uint64_t pol)
+{
+    int4 r;
+    if (HINT == 0) {
+        asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    } else if (HINT == 1) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.s32 {%0,%1,%2,%3}, [%4], %5;"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+    }
+    return r;
+}
+template <int HINT> __device__ __forceinline__ float4 ld_stream(const float4 *p, uint64_t pol)
+{
+    int4 r = ld_stream<HINT>(reinterpret_cast<const int4 *>(p), pol);
+    return make_float4(__int_as_float(r.x), __int_as_float(r.y), __int_as_float(r.z), __int_as_float(r.w));
+}
+template <int HINT> __device__ __forceinline__ double2 ld_stream(const double2 *p, uint64_t pol)
+{
+    double2 r;
+    if (HINT == 0) {
+        asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    } else if (HINT == 1) {
+        asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;"
+                     : "=d"(r.x), "=d"(r.y) : "l"(p), "l"(pol));
+    }
+    return r;
+}
+__device__ __forceinline__ uint64_t make_evict_first_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
+// four consecutive stored values starting at an index that is a multiple of 4
+template <int HINT> __device__ __forceinline__ void ld_values4(const double *p, uint64_t pol, double (&v)[4])
+{
+    double2 a = ld_stream<HINT>(reinterpret_cast<const double2 *>(p), pol);
+    double2 b = ld_stream<HINT>(reinterpret_cast<const double2 *>(p) + 1, pol);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+template <int HINT> __device__ __forceinline__ void ld_values4(const float *p, uint64_t pol, float (&v)[4])
+{
+    float4 a = ld_stream<HINT>(reinterpret_cast<const float4 *>(p), pol);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+__device__ __forceinline__ void st_shared4(double *p, const double (&v)[4])
+{
+    reinterpret_cast<double2 *>(p)[0] = make_double2(v[0], v[1]);
+    reinterpret_cast<double2 *>(p)[1] = make_double2(v[2], v[3]);
+}
+__device__ __forceinline__ void st_shared4(float *p, const float (&v)[4])
+{
+    *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+// ------------------------------------------------------------------ entry staging
+// Products a_k * x[col_k] for the entries [k0,k1) go to s_prod[k - (k0 & ~3)].  VEC: whole
+// aligned quads use one 128-bit colidx load + 128/256 bits of values per thread, two quads in
+// flight per thread; the ragged head and tail quads are done with guarded scalar loads.
+template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
+__device__ __forceinline__ void stage_products(int k0, int k1, const int *__restrict__ colidx,
+                                               const TV *__restrict__ values, const TX *__restrict__ x,
+                                               int base, TX *s_prod, uint64_t pol)
+{
+    const int tid = threadIdx.x;
+    if (VEC) {
+        const int sb = k0 & ~3;
+        const int qf0 = (k0 + 3) >> 2, qf1 = k1 >> 2; // whole quads [qf0,qf1)
+        if (qf0 <= qf1) {
+            const int he = qf0 << 2, tb = qf1 << 2;
+            if (tid < 4) { // head
+                const int k = k0 + tid;
+                if (k < he) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+            } else if (tid >= 32 && tid < 36) { // tail
+                const int k = tb + (tid - 32);
+                if (k < k1) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+            }
+            for (int q = qf0 + tid; q < qf1; q += 2 * THREADS) {
+                const int qb = q + THREADS;
+                const bool hb = qb < qf1;
+                int4 ca, cb = make_int4(base, base, base, base);
+                TV va[4], vb[4] = {0, 0, 0, 0};
+                ca = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
+                ld_values4<HINT>(values + (q << 2), pol, va);
+                if (hb) {
+                    cb = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (qb << 2)), pol);
+                    ld_values4<HINT>(values + (qb << 2), pol, vb);
+                }
+                TX pa[4], pb[4];
+                pa[0] = __ldg(x + (ca.x - base)); pa[1] = __ldg(x + (ca.y - base));
+                pa[2] = __ldg(x + (ca.z - base)); pa[3] = __ldg(x + (ca.w - base));
+                if (hb) {
+                    pb[0] = __ldg(x + (cb.x - base)); pb[1] = __ldg(x + (cb.y - base));
+                    pb[2] = __ldg(x + (cb.z - base)); pb[3] = __ldg(x + (cb.w - base));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) pa[j] *= (TX)va[j];
+                st_shared4(s_prod + ((q << 2) - sb), pa);
+                if (hb) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) pb[j] *= (TX)vb[j];
+                    st_shared4(s_prod + ((qb << 2) - sb), pb);
+                }
+            }
+        } else { // [k0,k1) lies inside one quad
+            const int k = k0 + tid;
+            if (k < k1) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+        }
+    } else {
+        const int sb = k0 & ~3;
+        for (int k = k0 + tid; k < k1; k += THREADS)
+            s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+    }
+}
+
+// CTA-wide sum of a_k*x[col_k] over [k0,k1), result valid in thread 0 (CTA-per-row path).
+template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
+__device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict__ colidx,
+                                          const TV *__restrict__ values, const TX *__restrict__ x,
+                                          int base, TX *s_red, uint64_t pol)
+{
+    const int tid = threadIdx.x;
+    TX acc = 0;
+    int ks = k0, ke = k1;
+    if (VEC) {
+        const int qf0 = (k0 + 3) >> 2, qf1 = k1 >> 2;
+        if (qf0 < qf1) {
+            ks = qf0 << 2; ke = qf1 << 2;
+            TX acc2 = 0;
+            for (int q = qf0 + tid; q < qf1; q += THREADS) {
+                int4 c = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
+                TV v[4];
+                ld_values4<HINT>(values + (q << 2), pol, v);
+                acc += (TX)v[0] * __ldg(x + (c.x - base));
+                acc2 += (TX)v[1] * __ldg(x + (c.y - base));
+                acc += (TX)v[2] * __ldg(x + (c.z - base));
+                acc2 += (TX)v[3] * __ldg(x + (c.w - base));
+            }
+            acc += acc2;
+            // ragged ends
+            for (int k = k0 + tid; k < ks; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+            for (int k = ke + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+        } else {
+            for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+        }
+    } else {
+        for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __syncthreads();
+    if ((tid & 31) == 0) s_red[tid >> 5] = acc;
+    __syncthreads();
+    TX tot = 0;
+    if (tid == 0)
+        for (int w = 0; w < THREADS / 32; ++w) tot += s_red[w];
+    __syncthreads();
+    return tot;
+}
+
+template <typename TX> __device__ __forceinline__ void store_y(TX *y, int r, TX sum, TX alpha, TX beta)
+{
+    y[r] = (beta == (TX)0) ? alpha * sum : alpha * sum + beta * y[r];
+}
+
+// rows [row_lo,row_lo+nrows) of the tile, entries already staged; G lanes per row
+template <typename TX, int THREADS, int G>
+__device__ __forceinline__ void reduce_rows(const TX *s_prod, const int *s_rp, int sb, int nrows, int row_glob,
+                                            TX *__restrict__ y, TX alpha, TX beta)
+{
+    const int tid = threadIdx.x;
+    if (G == 1) {
+        for (int i = tid; i < nrows; i += THREADS) {
+            const int a = s_rp[i] - sb, b = s_rp[i + 1] - sb;
+            TX s = 0;
+            for (int k = a; k < b; ++k) s += s_prod[k];
+            store_y(y, row_glob + i, s, alpha, beta);
+        }
+    } else {
+        constexpr int GROUPS = THREADS / G;
+        const int gid = tid / G, lane = tid % G;
+        const int iters = (nrows + GROUPS - 1) / GROUPS;
+        for (int it = 0; it < iters; ++it) {
+            const int i = it * GROUPS + gid;
+            TX s = 0;
+            if (i < nrows) {
+                const int a = s_rp[i] - sb, b = s_rp[i + 1] - sb;
+                for (int k = a + lane; k < b; k += G) s += s_prod[k];
+            }
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ row-block kernel
+template <int TILE> struct RowBlockShape {
+    static constexpr int CAP = TILE + TILE / 8; // staged entries per pass
+};
+
+template <typename TV, typename TX, int THREADS, int TILE, int HINT, bool VEC>
+__global__ void __launch_bounds__(THREADS)
+spmv_rowblock_kernel(int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                     const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
+                     TX alpha, TX beta, const int *__restrict__ blk_row, int reduce_opt)
+{
+    constexpr int CAP = RowBlockShape<TILE>::CAP;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    TX *s_prod = reinterpret_cast<TX *>(smem_raw);            // CAP + 4
+    int *s_rp = reinterpret_cast<int *>(s_prod + CAP + 4);    // TILE + 1
+    const int b = blockIdx.x;
+    const int r0 = blk_row[b], r1 = blk_row[b + 1];
+    const int nr = r1 - r0;
+    if (nr <= 0) return;
+    uint64_t pol = 0;
+    if (HINT == 2) pol = make_evict_first_policy();
+    for (int i = threadIdx.x; i <= nr; i += THREADS) s_rp[i] = rowptr[r0 + i] - base;
+    __syncthreads();
+    int cur = 0;
+    while (cur < nr) {
+        const int k0 = s_rp[cur];
+        const int sb = k0 & ~3;
+        int pe;
+        if (s_rp[nr] - sb <= CAP) {
+            pe = nr;
+        } else { // largest pe in [cur,nr] with s_rp[pe]-sb <= CAP
+            int lo = cur, hi = nr;
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (s_rp[mid] - sb <= CAP) lo = mid; else hi = mid - 1;
+            }
+            pe = lo;
+        }
+        if (pe == cur) { // this row alone exceeds the staging capacity: CTA-per-row
+            const TX tot = cta_row_sum<TV, TX, THREADS, HINT, VEC>(k0, s_rp[cur + 1], colidx, values, x, base, s_prod, pol);
+            if (threadIdx.x == 0) store_y(y, r0 + cur, tot, alpha, beta);
+            cur += 1;
+            continue;
+        }
+        const int k1 = s_rp[pe];
+        stage_products<TV, TX, THREADS, HINT, VEC>(k0, k1, colidx, values, x, base, s_prod, pol);
+        __syncthreads();
+        const int nrows = pe - cur;
+        int g = reduce_opt;
+        if (g == 0) { // row-length bin of this tile
+            const int avg = (k1 - k0) / nrows;
+            g = avg <= 12 ? 1 : avg <= 48 ? 4 : avg <= 96 ? 8 : avg <= 256 ? 16 : 32;
+        }
+        const int *rp = s_rp + cur;
+        switch (g) {
+        case 1: reduce_rows<TX, THREADS, 1>(s_prod, rp, sb, nrows, r0 + cur, y, alpha, beta); break;
+        case 2: reduce_rows<TX, THREADS, 2>(s_prod, rp, sb, nrows, r0 + cur, y, alpha, beta); break;
+        case 4: reduce_rows<TX, THREADS, 4>(s_prod, rp, sb, nrows, r0 + cur, y, alpha, beta); break;
+        case 8: reduce_rows<TX, THREADS, 8>(s_prod, rp, sb, nrows, r0 + cur, y, alpha, beta); break;
+        case 16: reduce_rows<TX, THREADS, 16>(s_prod, rp, sb, nrows, r0 + cur, y, alpha, beta); break;
+        default: reduce_rows<TX, THREADS, 32>(s_prod, rp, sb, nrows, r0 + cur, y, alpha, beta); break;
+        }
+        cur = pe;
+        if (cur < nr) __syncthreads();
+    }
+}
+
+// first row r in [0,m] with (rowptr[r]-rowptr[0]) + r >= target  (merged-item coordinate)
+__device__ __forceinline__ int first_row_at_item(const int *__restrict__ rowptr, int m, long long target)
+{
+    const int rp0 = rowptr[0];
+    int lo = 0, hi = m;
+    while (lo < hi) {
+        const int mid = lo + ((hi - lo) >> 1);
+        if ((long long)(rowptr[mid] - rp0) + mid < target) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void rowblock_partition_kernel(int m, const int *__restrict__ rowptr, int tile, int nblk, int *blk_row)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > nblk) return;
+    blk_row[b] = (b == nblk) ? m : first_row_at_item(rowptr, m, (long long)b * tile);
+}
+
+// ------------------------------------------------------------------ merge-path kernel
+template <typename TX> struct CarryPair {
+    int f; // 1: a row ended inside this thread's span (v restarts there)
+    TX v;
+};
+template <typename TX> struct CarryOp {
+    __device__ __forceinline__ CarryPair<TX> operator()(const CarryPair<TX> &a, const CarryPair<TX> &b) const
+    {
+        CarryPair<TX> r;
+        r.f = a.f | b.f;
+        r.v = b.f ? b.v : a.v + b.v;
+        return r;
+    }
+};
+
+// coords[t] = (rows consumed, absolute entry index) where diagonal t*items crosses the merge of
+// row-end offsets A[i] = rowptr[i+1]-base and entry indices B[j] = first+j.
+__global__ void merge_coords_kernel(int m, int nnz, int base, const int *__restrict__ rowptr, int items,
+                                    int ntiles, int2 *coords)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > ntiles) return;
+    const int first = rowptr[0] - base;
+    long long d = (long long)t * items;
+    const long long total = (long long)m + nnz;
+    if (d > total) d = total;
+    int lo = (int)(d > nnz ? d - nnz : 0), hi = (int)(d < m ? d : m);
+    while (lo < hi) {
+        const int mid = lo + ((hi - lo) >> 1);
+        if ((long long)(rowptr[mid + 1] - base) <= (long long)first + (d - 1 - mid)) lo = mid + 1; else hi = mid;
+    }
+    coords[t] = make_int2(lo, first + (int)(d - lo));
+}
+
+template <typename TV, typename TX, int THREADS, int IPT, int HINT, bool VEC>
+__global__ void __launch_bounds__(THREADS)
+spmv_merge_kernel(int m, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                  const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
+                  const int2 *__restrict__ coords, int *__restrict__ carry_row, TX *__restrict__ carry_val)
+{
+    constexpr int ITEMS = THREADS * IPT;
+    typedef cub::BlockScan<CarryPair<TX>, THREADS> Scan;
+    __shared__ __align__(16) TX s_prod[ITEMS + 4];
+    __shared__ int s_end[ITEMS + 1];
+    __shared__ typename Scan::TempStorage s_scan;
+    const int tid = threadIdx.x, b = blockIdx.x;
+    const int2 c0 = coords[b], c1 = coords[b + 1];
+    const int row0 = c0.x, nz0 = c0.y, nr = c1.x - c0.x, nn = c1.y - c0.y;
+    uint64_t pol = 0;
+    if (HINT == 2) pol = make_evict_first_policy();
+    for (int i = tid; i < nr; i += THREADS) s_end[i] = rowptr[row0 + 1 + i] - base;
+    stage_products<TV, TX, THREADS, HINT, VEC>(nz0, nz0 + nn, colidx, values, x, base, s_prod, pol);
+    __syncthreads();
+    const TX *prod = s_prod + (nz0 & 3); // entry nz0+j sits at s_prod[(nz0&3)+j]
+    // this thread's start on the tile-local merge path
+    int d = tid * IPT;
+    const int total = nr + nn;
+    if (d > total) d = total;
+    int lo = d > nn ? d - nn : 0, hi = d < nr ? d : nr;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (s_end[mid] <= nz0 + (d - 1 - mid)) lo = mid + 1; else hi = mid;
+    }
+    int i = lo, j = d - lo;
+    TX sum = 0, head_val = 0;
+    int head_row = -1;
+    const int steps = min(IPT, total - d);
+    for (int it = 0; it < steps; ++it) {
+        if (j < nn && (i >= nr || s_end[i] > nz0 + j)) {
+            sum += prod[j];
+            ++j;
+        } else { // row row0+i ends here
+            if (head_row < 0) { head_row = row0 + i; head_val = sum; }
+            else store_y(y, row0 + i, sum, alpha, beta);
+            sum = 0;
+            ++i;
+        }
+    }
+    CarryPair<TX> in, ex, agg, init;
+    in.f = head_row >= 0; in.v = sum;
+    init.f = 0; init.v = 0;
+    Scan(s_scan).ExclusiveScan(in, ex, init, CarryOp<TX>(), agg);
+    if (head_row >= 0) store_y(y, head_row, ex.v + head_val, alpha, beta);
+    if (tid == 0) { // the row still open at the end of the tile is row0+nr
+        const int open = row0 + nr;
+        carry_row[b] = open < m ? open : -1;
+        carry_val[b] = agg.v;
+    }
+}
+
+// adds the carried partial sums: one thread per run of equal carry_row, fixed order
+template <typename TX>
+__global__ void merge_fixup_kernel(int ntiles, const int *__restrict__ carry_row, const TX *__restrict__ carry_val,
+                                   TX *__restrict__ y, TX alpha)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    const int r = carry_row[t];
+    if (r < 0 || (t > 0 && carry_row[t - 1] == r)) return;
+    TX s = carry_val[t];
+    for (int u = t + 1; u < ntiles && carry_row[u] == r; ++u) s += carry_val[u];
+    y[r] += alpha * s;
+}
+
+// ------------------------------------------------------------------ plain kernels
+template <typename TV, typename TX>
+__global__ void spmv_scalar_kernel(int m, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
+                                   TX alpha, TX beta)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= m) return;
+    TX s = 0;
+    for (int k = rowptr[r] - base; k < rowptr[r + 1] - base; ++k) s += (TX)values[k] * __ldg(x + (colidx[k] - base));
+    store_y(y, r, s, alpha, beta);
+}
+
+template <typename TV, typename TX, int G>
+__global__ void spmv_vector_kernel(int m, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
+                                   TX alpha, TX beta)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = t / G, lane = t % G;
+    TX s = 0;
+    if (r < m)
+        for (int k = rowptr[r] - base + lane; k < rowptr[r + 1] - base; k += G)
+            s += (TX)values[k] * __ldg(x + (colidx[k] - base));
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (r < m && lane == 0) store_y(y, r, s, alpha, beta);
+}
+
+// ------------------------------------------------------------------ statistics
+// out[0] = max row length, out[1] = rowptr[0], out[2] = rowptr[m]
+__global__ void row_stats_kernel(int m, const int *__restrict__ rowptr, int *out)
+{
+    int mx = 0;
+    for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < m; r += gridDim.x * blockDim.x)
+        mx = max(mx, rowptr[r + 1] - rowptr[r]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(out, mx);
+    if (blockIdx.x == 0 && threadIdx.x == 0) { out[1] = rowptr[0]; out[2] = rowptr[m]; }
+}
+
+__global__ void row_partition_kernel(int m, int base, const int *__restrict__ rowptr, int ngpu, int balanced, int *starts)
+{
+    const int g = threadIdx.x;
+    if (g > ngpu) return;
+    if (g == 0) { starts[0] = 0; return; }
+    if (g == ngpu) { starts[g] = m; return; }
+    if (!balanced) { starts[g] = (int)(((long long)g * m + ngpu - 1) / ngpu); return; }
+    const long long nnz = (long long)rowptr[m] - rowptr[0];
+    const long long target = (long long)g * nnz / ngpu + (rowptr[0] - base);
+    int lo = 0, hi = m;
+    while (lo < hi) {
+        const int mid = lo + ((hi - lo) >> 1);
+        if ((long long)rowptr[mid] - base < target) lo = mid + 1; else hi = mid;
+    }
+    starts[g] = lo;
+}
+
+// ------------------------------------------------------------------ host side
+struct Variant { int threads, tile; };
+static const Variant kVariants[] = {{256, 4096}, {128, 2048}, {256, 2048}, {512, 8192}, {128, 1024}};
+static const int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
+static const int kMergeThreads = 256, kMergeIpt = 8;
+
+void spmv_free_plan(SpmvPlan &p)
+{
+    cudaFree(p.blk_row); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
+    p = SpmvPlan();
+}
+
+static int plan_signature(const rsg_context *h)
+{
+    return h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW];
+}
+
+int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
+                  bool force_rebuild, SpmvPlan **out)
+{
+    const int sig = plan_signature(h);
+    for (size_t i = 0; i < h->spmv_plans.size(); ++i) {
+        SpmvPlan &p = h->spmv_plans[i];
+        if (p.rowptr == rowptr && p.colidx == colidx && p.m == m && p.n == n && p.base == base && p.opt_sig == sig) {
+            if (!force_rebuild) { *out = &p; return RSG_OK; }
+            spmv_free_plan(p);
+            h->spmv_plans.erase(h->spmv_plans.begin() + (long)i);
+            break;
+        }
+    }
+    if (h->spmv_plans.size() >= 16) { // bounded cache: drop the oldest
+        spmv_free_plan(h->spmv_plans.front());
+        h->spmv_plans.erase(h->spmv_plans.begin());
+    }
+    SpmvPlan p;
+    p.rowptr = rowptr; p.colidx = colidx; p.m = m; p.n = n; p.base = base; p.opt_sig = sig;
+    cudaStream_t st = h->stream;
+    RSG_CUDA_TRY(cudaMemsetAsync(h->scratch_i, 0, 4 * sizeof(int), st));
+    if (m > 0) {
+        const int blocks = std::min((m + 255) / 256, h->sm_count * 8);
+        row_stats_kernel<<<blocks, 256, 0, st>>>(m, rowptr, h->scratch_i);
+        h->launches++;
+    } else {
+        RSG_CUDA_TRY(cudaMemcpyAsync(h->scratch_i + 1, rowptr, sizeof(int), cudaMemcpyDeviceToDevice, st));
+        RSG_CUDA_TRY(cudaMemcpyAsync(h->scratch_i + 2, rowptr, sizeof(int), cudaMemcpyDeviceToDevice, st));
+    }
+    RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i, h->scratch_i, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaStreamSynchronize(st));
+    p.max_row = h->pinned_i[0];
+    p.first = h->pinned_i[1] - base;
+    p.nnz = h->pinned_i[2] - h->pinned_i[1];
+    if (p.nnz < 0 || p.first < 0) return RSG_BAD_ARG;
+
+    int algo = h->opts[RSG_OPT_SPMV_ALGO];
+    int variant = h->opts[RSG_OPT_SPMV_VARIANT];
+    if (variant < 0 || variant >= kNumVariants) variant = 0;
+    p.variant = variant;
+    p.tile = kVariants[variant].tile;
+    if (algo == RSG_SPMV_AUTO) {
+        // A row reduced by one CTA streams at one SM's share of the bandwidth (~1/148); past
+        // roughly nnz/64 entries that single row outlasts the rest of the product: merge-path.
+        const int cap = RowBlockShape<4096>::CAP;
+        const long long skew = std::max<long long>(cap, (long long)p.nnz / 64);
+        algo = (p.max_row > skew) ? RSG_SPMV_MERGE : RSG_SPMV_ROWBLOCK;
+    }
+    p.algo = algo;
+    const long long items = (long long)m + p.nnz;
+    if (algo == RSG_SPMV_ROWBLOCK && m > 0) {
+        p.nblk = (int)((items + p.tile - 1) / p.tile);
+        RSG_CUDA_TRY(cudaMalloc(&p.blk_row, sizeof(int) * ((size_t)p.nblk + 1)));
+        p.bytes += sizeof(int) * ((size_t)p.nblk + 1);
+        rowblock_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, rowptr, p.tile, p.nblk, p.blk_row);
+        h->launches++;
+    } else if (algo == RSG_SPMV_MERGE && m > 0) {
+        p.merge_items = kMergeThreads * kMergeIpt;
+        p.ntiles = (int)((items + p.merge_items - 1) / p.merge_items);
+        RSG_CUDA_TRY(cudaMalloc(&p.coords, sizeof(int2) * ((size_t)p.ntiles + 1)));
+        RSG_CUDA_TRY(cudaMalloc(&p.carry_row, sizeof(int) * (size_t)p.ntiles));
+        RSG_CUDA_TRY(cudaMalloc(&p.carry_val, sizeof(double) * (size_t)p.ntiles));
+        p.bytes += (sizeof(int2) + sizeof(int) + sizeof(double)) * ((size_t)p.ntiles + 1);
+        merge_coords_kernel<<<(p.ntiles + 1 + 255) / 256, 256, 0, st>>>(m, p.nnz, base, rowptr, p.merge_items, p.ntiles, p.coords);
+        h->launches++;
+    }
+    RSG_CUDA_TRY(cudaGetLastError());
+    h->spmv_plans.push_back(p);
+    *out = &h->spmv_plans.back();
+    return RSG_OK;
+}
+
+template <typename TV, typename TX, int THREADS, int TILE, int HINT, bool VEC>
+static int launch_rowblock_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    auto kern = spmv_rowblock_kernel<TV, TX, THREADS, TILE, HINT, VEC>;
+    const size_t smem = sizeof(TX) * (RowBlockShape<TILE>::CAP + 4) + sizeof(int) * (TILE + 1);
+    static bool configured = false; // per instantiation
+    if (!configured) {
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    kern<<<p->nblk, THREADS, smem, h->stream>>>(p->base, p->rowptr, p->colidx, values, x, y, alpha, beta, p->blk_row,
+                                               h->opts[RSG_OPT_SPMV_REDUCE]);
+    h->launches++;
+    return RSG_OK;
+}
+
+template <typename TV, typename TX, int THREADS, int TILE>
+static int launch_rowblock_shape(rsg_context *h, const SpmvPlan *p, bool vec, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    const int hint = h->opts[RSG_OPT_SPMV_CACHE_HINT];
+    if (!vec) return launch_rowblock_one<TV, TX, THREADS, TILE, 0, false>(h, p, values, alpha, x, beta, y);
+    switch (hint) {
+    case 0: return launch_rowblock_one<TV, TX, THREADS, TILE, 0, true>(h, p, values, alpha, x, beta, y);
+    case 2: return launch_rowblock_one<TV, TX, THREADS, TILE, 2, true>(h, p, values, alpha, x, beta, y);
+    default: return launch_rowblock_one<TV, TX, THREADS, TILE, 1, true>(h, p, values, alpha, x, beta, y);
+    }
+}
+
+template <typename TV, typename TX>
+static int launch_rowblock(rsg_context *h, const SpmvPlan *p, bool vec, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    switch (p->variant) {
+    case 1: return launch_rowblock_shape<TV, TX, 128, 2048>(h, p, vec, values, alpha, x, beta, y);
+    case 2: return launch_rowblock_shape<TV, TX, 256, 2048>(h, p, vec, values, alpha, x, beta, y);
+    case 3: return launch_rowblock_shape<TV, TX, 512, 8192>(h, p, vec, values, alpha, x, beta, y);
+    case 4: return launch_rowblock_shape<TV, TX, 128, 1024>(h, p, vec, values, alpha, x, beta, y);
+    default: return launch_rowblock_shape<TV, TX, 256, 4096>(h, p, vec, values, alpha, x, beta, y);
+    }
+}
+
+template <typename TV, typename TX>
+static int launch_merge(rsg_context *h, const SpmvPlan *p, bool vec, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    const int hint = h->opts[RSG_OPT_SPMV_CACHE_HINT];
+    TX *cv = reinterpret_cast<TX *>(p->carry_val);
+#define RSG_MERGE(H, V)                                                                                          \
+    spmv_merge_kernel<TV, TX, 256, 8, H, V><<<p->ntiles, 256, 0, h->stream>>>(p->m, p->base, p->rowptr, p->colidx, \
+                                                                              values, x, y, alpha, beta, p->coords, \
+                                                                              p->carry_row, cv)
+    if (!vec) RSG_MERGE(0, false);
+    else if (hint == 0) RSG_MERGE(0, true);
+    else if (hint == 2) RSG_MERGE(2, true);
+    else RSG_MERGE(1, true);
+#undef RSG_MERGE
+    merge_fixup_kernel<TX><<<(p->ntiles + 255) / 256, 256, 0, h->stream>>>(p->ntiles, p->carry_row, cv, y, alpha);
+    h->launches += 2;
+    return RSG_OK;
+}
+
+static int set_x_persistence(rsg_context *h, const void *x, size_t bytes)
+{
+    if (!h->opts[RSG_OPT_SPMV_X_PERSIST]) {
+        if (h->persist_ptr) {
+            cudaStreamAttrValue attr = {};
+            attr.accessPolicyWindow.num_bytes = 0;
+            cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &attr);
+            h->persist_ptr = nullptr; h->persist_bytes = 0;
+        }
+        return RSG_OK;
+    }
+    if (h->persist_ptr == x && h->persist_bytes == bytes) return RSG_OK;
+    cudaDeviceProp prop;
+    RSG_CUDA_TRY(cudaGetDeviceProperties(&prop, h->device));
+    const size_t win = std::min(bytes, (size_t)prop.accessPolicyMaxWindowSize);
+    if (win == 0) return RSG_OK;
+    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min((size_t)prop.persistingL2CacheMaxSize, win));
+    cudaStreamAttrValue attr = {};
+    attr.accessPolicyWindow.base_ptr = const_cast<void *>(x);
+    attr.accessPolicyWindow.num_bytes = win;
+    attr.accessPolicyWindow.hitRatio = 1.0f;
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    RSG_CUDA_TRY(cudaStreamSetAttribute(h->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+    h->persist_ptr = x; h->persist_bytes = bytes;
+    return RSG_OK;
+}
+
+template <typename TV, typename TX>
+int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx, const TV *values,
+             TX alpha, const TX *x, TX beta, TX *y)
+{
+    if (m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || (m > 0 && !y)) return RSG_BAD_ARG;
+    if (m == 0) return RSG_OK;
+    SpmvPlan *p = nullptr;
+    RSG_TRY(spmv_get_plan(h, m, n, base, rowptr, colidx, false, &p));
+    if (p->nnz > 0 && (!colidx || !values || !x)) return RSG_BAD_ARG;
+    h->last_spmv_algo = p->algo;
+    h->last_spmv_maxrow = p->max_row;
+    RSG_TRY(set_x_persistence(h, x, sizeof(TX) * (size_t)n));
+    const bool vec = (((uintptr_t)colidx | (uintptr_t)values) & 15) == 0;
+    switch (p->algo) {
+    case RSG_SPMV_ROWBLOCK:
+        h->last_spmv_blocks = p->nblk;
+        RSG_TRY((launch_rowblock<TV, TX>(h, p, vec, values, alpha, x, beta, y)));
+        break;
+    case RSG_SPMV_MERGE:
+        h->last_spmv_blocks = p->ntiles;
+        RSG_TRY((launch_merge<TV, TX>(h, p, vec, values, alpha, x, beta, y)));
+        break;
+    case RSG_SPMV_VECTOR: {
+        const int avg = p->nnz / std::max(m, 1);
+        const int threads = 256;
+#define RSG_VEC(G)                                                                                          \
+    spmv_vector_kernel<TV, TX, G><<<(int)(((long long)m * G + threads - 1) / threads), threads, 0, h->stream>>>( \
+        m, base, rowptr, colidx, values, x, y, alpha, beta)
+        if (avg <= 6) RSG_VEC(4); else if (avg <= 24) RSG_VEC(8); else if (avg <= 64) RSG_VEC(16); else RSG_VEC(32);
+#undef RSG_VEC
+        h->last_spmv_blocks = 0;
+        h->launches++;
+        break;
+    }
+    case RSG_SPMV_SCALAR:
+        spmv_scalar_kernel<TV, TX><<<(m + 255) / 256, 256, 0, h->stream>>>(m, base, rowptr, colidx, values, x, y, alpha, beta);
+        h->last_spmv_blocks = (m + 255) / 256;
+        h->launches++;
+        break;
+    default:
+        return RSG_BAD_ARG;
+    }
+    RSG_CUDA_TRY(cudaGetLastError());
+    return RSG_OK;
+}
+
+template int spmv_run<double, double>(rsg_context *, int, int, int, const int *, const int *, const double *, double,
+                                      const double *, double, double *);
+template int spmv_run<float, float>(rsg_context *, int, int, int, const int *, const int *, const float *, float,
+                                    const float *, float, float *);
+template int spmv_run<float, double>(rsg_context *, int, int, int, const int *, const int *, const float *, double,
+                                     const double *, double, double *);
+
+int row_partition(rsg_context *h, int m, int base, const int *rowptr, int ngpu, int balanced, int *row_starts_host)
+{
+    if (ngpu < 1 || ngpu > 63 || m < 0 || !rowptr || !row_starts_host) return RSG_BAD_ARG;
+    row_partition_kernel<<<1, 64, 0, h->stream>>>(m, base, rowptr, ngpu, balanced, h->scratch_i);
+    h->launches++;
+    RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i, h->scratch_i, sizeof(int) * (size_t)(ngpu + 1), cudaMemcpyDeviceToHost, h->stream));
+    RSG_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    for (int g = 0; g <= ngpu; ++g) row_starts_host[g] = h->pinned_i[g];
+    return RSG_OK;
+}
+
+} // namespace rsg

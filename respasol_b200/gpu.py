@@ -1,0 +1,205 @@
+"""Handle: libreaspasol_gpu's C ABI called on torch CUDA tensors.
+
+torch is used for device memory and streams only; every kernel that runs is one of this
+repository's (respasol_b200/csrc).  Method names and argument meaning follow the C ABI
+(include/reaspasol_gpu.h), which in turn mirrors the cuSPARSE call groups of the reference
+harness (GPU/spmv.cu:122-186, GPU/ilu0.cu:196-310)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from ._lib import gpu_lib
+from .host import CSR
+
+OPT = dict(SPMV_ALGO=0, SPMV_REDUCE=1, SPMV_LONG_ROW=2, SPMV_VARIANT=3, SPMV_CACHE_HINT=4,
+           TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7)
+ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4)
+INFO = dict(KERNEL_LAUNCHES=0, SPMV_ALGO_USED=1, SPMV_ROW_BLOCKS=2, SPMV_MAX_ROW=3, LEVELS_L=4, LEVELS_U=5,
+            SM_COUNT=6, WORKSPACE_BYTES=7)
+OK, ZERO_PIVOT_STRUCTURAL, ZERO_PIVOT_NUMERIC = 0, 5, 6
+
+_PREC = {"d": (torch.float64, torch.float64), "s": (torch.float32, torch.float32), "m": (torch.float32, torch.float64)}
+
+
+class RsgError(RuntimeError):
+    def __init__(self, status, where):
+        self.status = status
+        msg = gpu_lib().rsg_status_string(status).decode()
+        super().__init__(f"{where}: {msg} (status {status})")
+
+
+def _check(status, where, allow=()):
+    if status != OK and status not in allow:
+        raise RsgError(status, where)
+    return status
+
+
+class DeviceCSR:
+    """CSR arrays resident in HBM: int32 rowptr/colidx, values in the storage precision."""
+
+    def __init__(self, a: CSR, precision="d", device="cuda:0"):
+        self.m, self.n, self.base, self.precision = a.m, a.n, a.base, precision
+        self.stored = a.stored
+        off = int(a.rowptr[0] - a.base)
+        if off:  # entries are addressed by rowptr-base: keep a leading gap so indices stay direct
+            raise ValueError("row-slab views must be rebased before upload (CSR.rows does this)")
+        vt, _ = _PREC[precision]
+        self.rowptr = torch.from_numpy(a.rowptr.astype(np.int32)).to(device)
+        self.colidx = torch.from_numpy(a.colidx.astype(np.int32)).to(device)
+        self.values = torch.from_numpy(a.values).to(device).to(vt)
+        self.device = self.rowptr.device
+
+    def bytes(self):
+        v, x = {"d": (8, 8), "s": (4, 4), "m": (4, 8)}[self.precision]
+        return self.stored * (v + 4) + (self.m + 1) * 4 + self.m * x + self.n * x
+
+
+class Handle:
+    def __init__(self, device=0):
+        self.lib = gpu_lib()
+        self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
+        h = C.c_void_p()
+        _check(self.lib.rsg_create(C.byref(h), self.device.index or 0), "rsg_create")
+        self.h = h
+        self.use_current_stream()
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.rsg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing
+    def use_current_stream(self):
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        _check(self.lib.rsg_set_stream(self.h, C.c_void_p(s)), "rsg_set_stream")
+
+    def set_option(self, name, value):
+        _check(self.lib.rsg_set_option(self.h, OPT[name], int(value)), "rsg_set_option")
+
+    def info(self, name):
+        v = C.c_longlong()
+        _check(self.lib.rsg_get_info(self.h, INFO[name], C.byref(v)), "rsg_get_info")
+        return v.value
+
+    def synchronize(self):
+        _check(self.lib.rsg_synchronize(self.h), "rsg_synchronize")
+
+    @staticmethod
+    def _p(t):
+        return C.c_void_p(t.data_ptr()) if t is not None else None
+
+    # ---- SpMV
+    def spmv_analysis(self, A: DeviceCSR):
+        _check(self.lib.rsg_spmv_analysis(self.h, A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx)),
+               "rsg_spmv_analysis")
+
+    def spmv(self, A: DeviceCSR, x, y=None, alpha=1.0, beta=0.0):
+        """y = alpha*A*x + beta*y through spmv_csr_d / spmv_csr_s / spmv_csr_mixed."""
+        _, xt = _PREC[A.precision]
+        assert x.dtype == xt and x.is_cuda and x.numel() >= A.n
+        if y is None:
+            y = torch.empty(A.m, dtype=xt, device=x.device)
+        fn = {"d": self.lib.spmv_csr_d, "s": self.lib.spmv_csr_s, "m": self.lib.spmv_csr_mixed}[A.precision]
+        _check(fn(self.h, A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
+                  alpha, self._p(x), beta, self._p(y)), "spmv_csr_" + A.precision)
+        return y
+
+    # ---- ILU0 / SpTRSV
+    def ilu0_analysis(self, A: DeviceCSR):
+        zp = C.c_int(-1)
+        st = self.lib.rsg_ilu0_analysis(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), C.byref(zp))
+        _check(st, "rsg_ilu0_analysis", allow=(ZERO_PIVOT_STRUCTURAL,))
+        return st, zp.value
+
+    def sptrsv_analysis(self, A: DeviceCSR):
+        _check(self.lib.rsg_sptrsv_analysis(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx)),
+               "rsg_sptrsv_analysis")
+
+    def ilu0_factor(self, A: DeviceCSR, values=None, report_pivot=True):
+        """In-place ILU(0) of `values` (default A.values).  Returns (status, zero_pivot_row)."""
+        v = A.values if values is None else values
+        fn = self.lib.ilu0_factor_d if v.dtype == torch.float64 else self.lib.ilu0_factor_s
+        zp = C.c_int(-1)
+        st = fn(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(v),
+                C.byref(zp) if report_pivot else None)
+        _check(st, "ilu0_factor", allow=(ZERO_PIVOT_STRUCTURAL, ZERO_PIVOT_NUMERIC))
+        return st, zp.value
+
+    def sptrsv_lu(self, A: DeviceCSR, lu, b, z=None, y=None):
+        """L z = b (unit lower) then U y = z (non-unit upper) on the in-place LU values."""
+        z = torch.empty_like(b) if z is None else z
+        y = torch.empty_like(b) if y is None else y
+        fn = self.lib.sptrsv_lu_d if lu.dtype == torch.float64 else self.lib.sptrsv_lu_s
+        _check(fn(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(lu), self._p(b),
+                  self._p(z), self._p(y)), "sptrsv_lu")
+        return z, y
+
+    def levels(self, which, n):
+        """(level_ptr, level_rows) of the last analysed matrix; which 0 = L, 1 = U."""
+        nl = C.c_int(0)
+        _check(self.lib.rsg_get_levels(self.h, which, C.byref(nl), None, None), "rsg_get_levels")
+        lp = np.zeros(nl.value + 1, dtype=np.int32)
+        rows = np.zeros(max(n, 1), dtype=np.int32)
+        _check(self.lib.rsg_get_levels(self.h, which, C.byref(nl), C.c_void_p(lp.ctypes.data), C.c_void_p(rows.ctypes.data)),
+               "rsg_get_levels")
+        return lp, rows[:n]
+
+    def analyse_levels(self, A: DeviceCSR):
+        """ILU0 analysis that tolerates a missing diagonal (levels are still defined)."""
+        return self.ilu0_analysis(A)
+
+    def row_partition(self, A: DeviceCSR, ngpu, balanced=True):
+        out = np.zeros(ngpu + 1, dtype=np.int32)
+        _check(self.lib.rsg_get_row_partition(self.h, A.m, A.base, self._p(A.rowptr), ngpu, int(balanced),
+                                              C.c_void_p(out.ctypes.data)), "rsg_get_row_partition")
+        return out
+
+    # ---- host-pointer entry points (numpy in, numpy out; H2D/D2H inside the call)
+    def spmv_host(self, a: CSR, x, precision="d", alpha=1.0, beta=0.0, y=None):
+        vt = np.float64 if precision == "d" else np.float32
+        xt = np.float32 if precision == "s" else np.float64
+        vals = np.ascontiguousarray(a.values, dtype=vt)
+        x = np.ascontiguousarray(x, dtype=xt)
+        y = np.zeros(a.m, dtype=xt) if y is None else np.ascontiguousarray(y, dtype=xt)
+        fn = {"d": self.lib.spmv_csr_d_host, "s": self.lib.spmv_csr_s_host, "m": self.lib.spmv_csr_mixed_host}[precision]
+        _check(fn(self.h, a.m, a.n, a.stored, a.base, a.rowptr.ctypes.data, a.colidx.ctypes.data, vals.ctypes.data,
+                  alpha, x.ctypes.data, beta, y.ctypes.data), "spmv_csr_host")
+        return y
+
+    def ilu0_factor_host(self, a: CSR, dtype=np.float64):
+        vals = np.array(a.values, dtype=dtype)
+        zp = C.c_int(-1)
+        fn = self.lib.ilu0_factor_d_host if dtype == np.float64 else self.lib.ilu0_factor_s_host
+        st = fn(self.h, a.m, a.stored, a.base, a.rowptr.ctypes.data, a.colidx.ctypes.data, vals.ctypes.data, C.byref(zp))
+        _check(st, "ilu0_factor_host", allow=(ZERO_PIVOT_STRUCTURAL, ZERO_PIVOT_NUMERIC))
+        return st, zp.value, vals
+
+    def sptrsv_lu_host(self, a: CSR, lu, b):
+        lu = np.ascontiguousarray(lu)
+        b = np.ascontiguousarray(b, dtype=lu.dtype)
+        y = np.zeros(a.m, dtype=lu.dtype)
+        fn = self.lib.sptrsv_lu_d_host if lu.dtype == np.float64 else self.lib.sptrsv_lu_s_host
+        _check(fn(self.h, a.m, a.stored, a.base, a.rowptr.ctypes.data, a.colidx.ctypes.data, lu.ctypes.data,
+                  b.ctypes.data, y.ctypes.data), "sptrsv_lu_host")
+        return y
+
+    def matrix_upload(self, a: CSR, precision="d"):
+        mat = C.c_void_p()
+        vals = np.ascontiguousarray(a.values, dtype=np.float64)
+        _check(self.lib.rsg_matrix_upload(self.h, precision.encode(), a.m, a.n, a.stored, a.base, a.rowptr.ctypes.data,
+                                          a.colidx.ctypes.data, vals.ctypes.data, C.byref(mat)), "rsg_matrix_upload")
+        return mat
+
+    def matrix_spmv_host(self, mat, x, y, alpha=1.0, beta=0.0):
+        _check(self.lib.rsg_matrix_spmv_host(self.h, mat, alpha, x.ctypes.data, beta, y.ctypes.data), "rsg_matrix_spmv_host")
+        return y
+
+    def matrix_free(self, mat):
+        _check(self.lib.rsg_matrix_free(self.h, mat), "rsg_matrix_free")
