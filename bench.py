@@ -1,0 +1,403 @@
+#!/usr/bin/env python
+"""bench.py -- the driver's measurement contract for the ReSpaSol hot path on B200.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+Step   = one CSR SpMV (the hot path, BASELINE.json configs[1]: 3-D 27-point stencil 100^3, 1M rows,
+         26.46M entries, fp64) over one of R resident replicas of the matrix (rotated so that the
+         ~338 MB a step streams never comes out of the 126 MB L2: "inputs larger than L2").
+Metric = achieved HBM GB/s on ALGORITHMIC bytes (12*nnz + 4(m+1) + 8m + 8n for fp64).
+N > 1  = weak scaling: every rank owns a 100x100x100-plane slab of a 100x100x(100N) grid; a step is
+         the x-halo all-gather (NCCL over NVLink) followed by the local SpMV.
+The line also carries fp32 / mixed SpMV, the skewed (merge-path) config, ILU0 analysis/factor/solve
+milliseconds (config 3), the end-to-end figure through the host-pointer C ABI, the roofline object,
+the host-CPU baseline and the clocks seen during the timed region.
+--impl reference times the reference's CPU implementation of the path (its MKL sparse mv is absent
+from this image: the oracle's OpenMP row-parallel restatement stands in) on all host threads.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+GRID = 100          # configs[1]: 27-point stencil on 100^3
+REPLICAS = 2
+METRIC = "SpMV achieved HBM GB/s (fp64 CSR, algorithmic bytes / device time)"
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi's clocks / throttle reasons through NVML, polled while the timed region runs."""
+
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.stop_flag, self.ok = [], False, False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.dev = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(self.dev, nv.NVML_CLOCK_SM)
+                rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev)
+                pw = nv.nvmlDeviceGetPowerUsage(self.dev) / 1000.0
+                self.samples.append((time.time(), sm, rs, pw))
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def summary(self, t0, t1):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "err", "?")]}
+        sel = [s for s in self.samples if t0 <= s[0] <= t1] or self.samples[-3:]
+        names = {0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x10: "sync_boost",
+                 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown",
+                 0x100: "display_clock_setting"}
+        bits = 0
+        for s in sel:
+            bits |= s[2]
+        reasons = [n for b, n in names.items() if bits & b]
+        return {"sm_mhz": float(np.median([s[1] for s in sel])) if sel else None, "sm_max_mhz": float(self.max_sm),
+                "reasons": reasons, "samples": len(sel), "power_w_max": max([s[3] for s in sel]) if sel else None}
+
+
+def spmv_bytes(stored, m, n, precision):
+    v, x = {"d": (8, 8), "s": (4, 4), "m": (4, 8)}[precision]
+    return stored * (v + 4) + (m + 1) * 4 + m * x + n * x
+
+
+# ------------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """The reference's CPU SpMV path (test_spmv.c:168-180, mkl_sparse_d_mv under OpenMP) on this box's
+    host cores.  MKL is not in the image and cannot be installed: the oracle's OpenMP restatement of
+    that call is timed instead (kind "port").  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import orc
+    from respasol_b200 import host
+    threads = orc.max_threads()
+    a = host.gen_stencil27(GRID, seed=2)
+    x = orc.dlarnv(a.n) - 0.5
+    bytes_per = spmv_bytes(a.stored, a.m, a.n, "d")
+    for _ in range(max(args.warmup, 1)):
+        orc.spmv(a, x, "d", threads=threads)
+    steps = max(1, min(args.steps, 200))  # bounded sample: each product is tens of ms on the host
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        y = orc.spmv(a, x, "d", threads=threads)
+    dt = time.perf_counter() - t0
+    val = bytes_per * steps / dt * 1e-9
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "GB/s", "n_gpus": args.gpus, "steps": steps,
+            "warmup": max(args.warmup, 1), "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "CSR SpMV fp64, 3-D 27-point stencil 100^3 (1M rows, 26463592 entries), host CPU"},
+            "cpu_baseline": {"value": val, "unit": "GB/s", "cores": threads, "kind": "port",
+                             "sample": "%d products of the full config-2 matrix, OpenMP static rows, all %d host threads; "
+                                       "stands in for mkl_sparse_d_mv (MKL absent)" % (steps, threads)},
+            "e2e": {"value": val, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gflops": 2.0 * a.stored * steps / dt * 1e-9, "checksum": float(np.abs(y).sum())}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------ our arm
+def timed_loop(torch, fn, steps, barrier):
+    """K calls bracketed by barrier + synchronize, timed with CUDA events on the launching stream."""
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    w0 = time.time()
+    start.record()
+    for i in range(steps):
+        fn(i)
+    stop.record()
+    torch.cuda.synchronize()
+    w1 = time.time()
+    barrier()
+    return start.elapsed_time(stop), w0, w1  # ms
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import orc
+    from respasol_b200 import host
+    from respasol_b200.dist import RowBlockSpmv
+    from respasol_b200.gpu import ALGO, DeviceCSR, Handle
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (no CPU fallback)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus or world == 1 and args.gpus == 1, "launch with torchrun --nproc-per-node N for --gpus N"
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def allmax(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    h = Handle(local_rank)
+    K, W = args.steps, max(args.warmup, 3)
+    peak, peak_src = peaks()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    extra = {}
+
+    # ---- the timed workload: this rank's slab of the 100 x 100 x (100*world) stencil
+    nz = GRID * world
+    a = host.gen_stencil27(GRID, GRID, nz, rank * GRID, (rank + 1) * GRID, seed=2)
+    bytes_per = spmv_bytes(a.stored, a.m, a.m, "d")  # per rank: its rows, its slice of x
+    xs = orc.dlarnv(GRID * GRID * nz)[rank * a.m:(rank + 1) * a.m] - 0.5
+    launches0 = h.info("KERNEL_LAUNCHES")
+    if world == 1:
+        mats = [DeviceCSR(a, "d", dev) for _ in range(REPLICAS)]
+        xd = [torch.from_numpy(xs).to(dev) for _ in range(REPLICAS)]
+        yd = [torch.empty(a.m, dtype=torch.float64, device=dev) for _ in range(REPLICAS)]
+
+        def step(i):
+            r = i % REPLICAS
+            h.spmv(mats[r], xd[r], yd[r])
+        for r in range(REPLICAS):
+            h.spmv_analysis(mats[r])
+        launches_per_step = 1
+    else:
+        row_starts = np.arange(world + 1, dtype=np.int64) * a.m
+        ops = []
+        for r in range(REPLICAS):
+            op = RowBlockSpmv(a, row_starts, "halo", lambda c: DeviceCSR(c, "d", dev),
+                              lambda A, x, y: h.spmv(A, x, y), dev, torch.float64)
+            op.set_x(torch.from_numpy(xs).to(dev))
+            h.spmv_analysis(op.A)
+            ops.append(op)
+        yd = [op.y for op in ops]
+
+        def step(i):
+            ops[i % REPLICAS].step()
+        launches_per_step = 1
+        extra["exchange"] = {"mode": "halo all-gather (NCCL)", "bytes_received_per_rank_per_step": ops[0].exchange_bytes}
+
+    for i in range(W):
+        step(i)
+    launches_before = h.info("KERNEL_LAUNCHES")
+    ms, w0, w1 = timed_loop(torch, step, K, barrier)
+    gpu_launches = h.info("KERNEL_LAUNCHES") - launches_before
+    ms = allmax(ms)
+    total_bytes = allsum(float(bytes_per))
+    value = total_bytes * K / (ms * 1e-3) * 1e-9
+    # keep the load up a little longer so the 20 ms clock poll sees the kernel even for a short K
+    t_end = time.time() + max(0.0, 0.4 - (w1 - w0))
+    while time.time() < t_end:
+        for i in range(200):
+            step(i)
+        torch.cuda.synchronize()
+    w1b = time.time()
+    clocks = sampler.summary(w0, max(w1, w1b))
+
+    # parity spot check of what was just timed (first rows of this rank against the oracle)
+    if world == 1:
+        ref = orc.spmv(a.rows(0, 2000), xs, "d")
+        got = yd[0][:2000].cpu().numpy()
+        assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max(), "bench result differs from the oracle"
+
+    # ---- roofline of the dominant kernel (single GPU: the step IS one launch of it)
+    per_launch_ms = ms / K
+    achieved = bytes_per / (per_launch_ms * 1e-3) * 1e-9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        with open(tp) as f:
+            traffic = json.load(f).get("spmv_rowblock_fp64_c2_bytes_per_launch")
+    roofline = {"bound": "hbm", "kernel": "spmv_rowblock_kernel<double,double>", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": bytes_per, "frac_of_8TBs_nominal": achieved / 8000.0,
+                "us_per_launch": per_launch_ms * 1e3}
+
+    e2e = None
+    cpu_baseline = None
+    full = a if world == 1 else host.gen_stencil27(GRID, seed=2)
+    xfull = orc.dlarnv(full.n) - 0.5
+    if world == 1:
+        # ---- other precisions / configs (single-GPU kernels; reported, not the headline)
+        def rate(A, x, y, reps):
+            for _ in range(3):
+                h.spmv(A, x, y)
+            t, _, _ = timed_loop(torch, lambda i: h.spmv(A, x, y), reps, lambda: None)
+            return t / reps
+
+        reps = max(20, min(K, 500))
+        for p in ("s", "m"):
+            As = [DeviceCSR(full, p, dev) for _ in range(REPLICAS)]
+            xt = torch.float32 if p == "s" else torch.float64
+            xv = torch.from_numpy(xfull).to(dev).to(xt)
+            yv = torch.empty(full.m, dtype=xt, device=dev)
+            for _ in range(3):
+                for A in As:
+                    h.spmv(A, xv, yv)
+            t, _, _ = timed_loop(torch, lambda i: h.spmv(As[i % REPLICAS], xv, yv), reps, lambda: None)
+            b = spmv_bytes(full.stored, full.m, full.n, p)
+            extra["spmv_" + {"s": "fp32", "m": "mixed"}[p]] = {"GBps": b / (t / reps * 1e-3) * 1e-9, "us": t / reps * 1e3,
+                                                                "GFLOPs": 2.0 * full.stored / (t / reps * 1e-3) * 1e-9}
+            del As
+        extra["spmv_fp64"] = {"GBps": achieved, "us": per_launch_ms * 1e3, "GFLOPs": 2.0 * a.stored / (per_launch_ms * 1e-3) * 1e-9}
+        # config 4: skewed rows, merge-path (fits L2: warm figure, labelled)
+        c4 = host.gen_powerlaw(320000, 2.2, 64, 4, 100000, 4)
+        A4 = DeviceCSR(c4, "d", dev)
+        x4 = torch.from_numpy(orc.dlarnv(c4.n)).to(dev)
+        y4 = torch.empty(c4.m, dtype=torch.float64, device=dev)
+        t4 = rate(A4, x4, y4, reps)
+        extra["spmv_c4_powerlaw_fp64"] = {"us": t4 * 1e3, "GBps_L2_warm": spmv_bytes(c4.stored, c4.m, c4.n, "d") / (t4 * 1e-3) * 1e-9,
+                                          "algo": h.info("SPMV_ALGO_USED"), "max_row": h.info("SPMV_MAX_ROW"), "stored": c4.stored}
+        h.set_option("SPMV_ALGO", ALGO["rowblock"])
+        t4r = rate(A4, x4, y4, max(5, reps // 10))
+        h.set_option("SPMV_ALGO", 0)
+        extra["spmv_c4_powerlaw_fp64"]["us_rowblock_cta_per_row"] = t4r * 1e3
+        # config 1 (fits L2: warm figure, labelled)
+        c1 = host.gen_laplace2d(1000)
+        A1 = DeviceCSR(c1, "d", dev)
+        x1 = torch.ones(c1.n, dtype=torch.float64, device=dev)
+        y1 = torch.empty(c1.m, dtype=torch.float64, device=dev)
+        t1 = rate(A1, x1, y1, reps)
+        extra["spmv_c1_lap2d_fp64"] = {"us": t1 * 1e3, "GBps_L2_warm": spmv_bytes(c1.stored, c1.m, c1.n, "d") / (t1 * 1e-3) * 1e-9}
+        # config 3: ILU0 analysis / factor / L+U solve, median of 10
+        c3 = host.gen_femlike(47, 0.58, 3)
+        for dt_, p in ((torch.float64, "d"), (torch.float32, "s")):
+            A3 = DeviceCSR(c3, p, dev)
+            pristine = A3.values.clone()
+            b3 = torch.ones(c3.m, dtype=dt_, device=dev)
+            z3, y3 = torch.empty_like(b3), torch.empty_like(b3)
+            ta, tf, ts = [], [], []
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            for it in range(11):
+                A3.values.copy_(pristine)
+                torch.cuda.synchronize()
+                ev[0].record(); h.ilu0_analysis(A3); h.sptrsv_analysis(A3); ev[1].record(); torch.cuda.synchronize()
+                ta.append(ev[0].elapsed_time(ev[1]))
+                ev[0].record(); h.ilu0_factor(A3, report_pivot=False); ev[1].record(); torch.cuda.synchronize()
+                tf.append(ev[0].elapsed_time(ev[1]))
+                ev[0].record(); h.sptrsv_lu(A3, A3.values, b3, z3, y3); ev[1].record(); torch.cuda.synchronize()
+                ts.append(ev[0].elapsed_time(ev[1]))
+            extra["ilu0_c3_" + {"d": "fp64", "s": "fp32"}[p]] = {
+                "analysis_ms": float(np.median(ta[1:])), "factor_ms": float(np.median(tf[1:])),
+                "solve_LU_ms": float(np.median(ts[1:])), "levels_L": h.info("LEVELS_L"), "levels_U": h.info("LEVELS_U"),
+                "n": c3.m, "stored": c3.stored}
+        pass
+    # ---- end to end through the host-pointer C ABI (matrix resident like the harness, spmv.cu:111-118;
+    # every step: x from pinned host memory -> device, SpMV, y device -> host).  Every rank runs its own
+    # config-2 product; the aggregate is all ranks' bytes over the slowest rank's time.
+    full64 = full
+    mat = h.matrix_upload(full64, "d")
+    xh = np.ascontiguousarray(xfull)
+    yh = np.zeros(full64.m)
+    for _ in range(3):
+        h.matrix_spmv_host(mat, xh, yh)
+    e_steps = max(5, min(K, 50))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        h.matrix_spmv_host(mat, xh, yh)
+    edt = allmax((time.perf_counter() - t0) / e_steps)
+    h.matrix_free(mat)
+    refy = orc.spmv(full64.rows(0, 1000), xfull, "d")
+    assert np.abs(yh[:1000] - refy).max() <= 1e-12 * np.abs(refy).max()
+    e2e = {"value": world * spmv_bytes(full64.stored, full64.m, full64.n, "d") / edt * 1e-9, "unit": "GB/s",
+           "h2d_bytes_per_step": 8 * full64.n * world, "d2h_bytes_per_step": 8 * full64.m * world, "ms_per_step": edt * 1e3,
+           "note": "rsg_matrix_spmv_host on every rank: matrix resident in HBM (uploaded once, as GPU/spmv.cu:111-118 does), "
+                   "x H2D + SpMV + y D2H inside every timed step"}
+    if world == 1:
+        # ---- CPU baseline on this box's host cores (bounded sample)
+        if not args.no_cpu:
+            threads = orc.max_threads()
+            orc.spmv(full64, xfull, "d", threads=threads)
+            n_cpu, t0 = 0, time.perf_counter()
+            while time.perf_counter() - t0 < 8.0 and n_cpu < 200:
+                orc.spmv(full64, xfull, "d", threads=threads)
+                n_cpu += 1
+            cdt = (time.perf_counter() - t0) / n_cpu
+            cpu_baseline = {"value": spmv_bytes(full64.stored, full64.m, full64.n, "d") / cdt * 1e-9, "unit": "GB/s",
+                            "cores": threads, "kind": "port", "ms_per_product": cdt * 1e3,
+                            "sample": "%d fp64 products of the full config-2 matrix (~8 s), OpenMP static rows on all host "
+                                      "threads; stands in for mkl_sparse_d_mv (test_spmv.c:168-170), MKL absent" % n_cpu}
+            t0 = time.perf_counter()
+            orc.ilu0(c3)
+            extra["cpu_ilu0_c3_fp64_ms"] = (time.perf_counter() - t0) * 1e3
+    sampler.stop_flag = True
+    barrier()
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic",
+                "config": {"workload": "CSR SpMV fp64, 3-D 27-point stencil 100x100x%d, %d rows / %d entries per GPU "
+                                       "(BASELINE configs[1] per GPU)" % (nz, a.m, a.stored),
+                           "l2_policy": "inputs larger than L2: %d resident replicas of the matrix and vectors rotated "
+                                        "(%.0f MB per step, %.0f MB working set vs 126 MB L2)"
+                                        % (REPLICAS, bytes_per / 1e6, REPLICAS * bytes_per / 1e6),
+                           "parallelism": "row-block x%d, x-halo all-gather" % world if world > 1 else "single GPU"},
+                "gflops": 2.0 * a.stored * world * K / (ms * 1e-3) * 1e-9,
+                "frac_of_8TBs_nominal": value / (8000.0 * world),
+                "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "launches_per_step": launches_per_step,
+                "roofline": roofline, "cpu_baseline": cpu_baseline, "extra": extra}
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the host-CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

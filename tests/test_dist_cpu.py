@@ -1,0 +1,102 @@
+"""World-size-2 (and 3) gloo runs of the row-block partitioned SpMV's host logic on CPU: partition,
+halo discovery, column relabelling and the exchange step.  The local product is done by the oracle
+here (the CUDA kernel is exercised by the -m gpu tests); the distributed result must equal the
+single-process oracle product bit for bit, because relabelling keeps each row's summation order."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, mode, kind, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import orc
+    from respasol_b200 import host
+    from respasol_b200.dist import RowBlockSpmv
+    if kind == "stencil":
+        full = host.gen_stencil27(7, 6, 12, seed=2)
+    else:
+        full = host.gen_powerlaw(3000, 2.2, 24, 2, 700, 4)
+    starts = orc.row_partition(full, world, True)
+    local = full.rows(int(starts[rank]), int(starts[rank + 1]))
+    x = orc.dlarnv(full.n) - 0.5
+
+    def spmv(A, xe, y):
+        y.copy_(torch.from_numpy(orc.spmv(A, xe.numpy(), "d")))
+
+    op = RowBlockSpmv(local, starts, mode, lambda c: c, spmv, torch.device("cpu"), torch.float64)
+    op.set_x(torch.from_numpy(x[starts[rank]:starts[rank + 1]].copy()))
+    y = op.step().numpy()
+    ref = orc.spmv(full, x, "d")[starts[rank]:starts[rank + 1]]
+    ok = np.array_equal(y, ref)
+    # second product with a changed x slice: the exchange must carry the new values
+    x2 = x * 1.5 + 0.25
+    op.set_x(torch.from_numpy(x2[starts[rank]:starts[rank + 1]].copy()))
+    y2 = op.step().numpy()
+    ok = ok and np.array_equal(y2, orc.spmv(full, x2, "d")[starts[rank]:starts[rank + 1]])
+    if mode == "halo" and kind == "stencil":  # only the neighbouring planes (cuts need not be plane-aligned)
+        ok = ok and op.plan.width <= 2 * (7 * 6 + 7 + 1)
+    res = torch.tensor([1 if ok else 0])
+    dist.all_reduce(res, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        out.put(int(res.item()))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("mode", ["halo", "allgather"])
+@pytest.mark.parametrize("kind", ["stencil", "powerlaw"])
+def test_rowblock_spmv_gloo(world, mode, kind):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, mode, kind, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert out.get(timeout=5) == 1
+
+
+def test_halo_plan_single_process():
+    from respasol_b200 import host
+    from respasol_b200.dist import HaloPlan
+    full = host.gen_stencil27(5, 5, 9, seed=0)
+    starts = np.array([0, 75, 150, 225])
+    plans = [HaloPlan(full.rows(starts[r], starts[r + 1]), starts, r) for r in range(3)]
+    needs = [p.need for p in plans]
+    for p in plans:
+        p.finish(needs)
+    # middle rank needs one plane from each neighbour; end ranks need one plane
+    assert [len(n) for n in needs] == [25, 50, 25]
+    assert plans[1].width == 50 and plans[0].remapped.n == 75 + 3 * 50
+    # relabelled columns decode back to the original global columns
+    for r, p in enumerate(plans):
+        loc = full.rows(starts[r], starts[r + 1])
+        dec = np.empty(loc.stored, dtype=np.int64)
+        c = p.remapped.colidx.astype(np.int64)
+        own = c < p.n_local
+        dec[own] = c[own] + starts[r]
+        o = (c[~own] - p.n_local) // p.width
+        pos = (c[~own] - p.n_local) % p.width
+        dec[~own] = np.array([p.send_idx[oo][pp] + starts[oo] for oo, pp in zip(o, pos)])
+        assert np.array_equal(dec, loc.colidx)

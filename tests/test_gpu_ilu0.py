@@ -1,0 +1,196 @@
+"""ILU0 / level sets / SpTRSV parity through the C ABI against the CPU oracle.
+
+Integers (diagonal positions via zero-pivot reports, level_ptr, level_rows) must be bit-exact.
+Factors and thread-per-row solves follow the oracle's operation order with explicit fma and IEEE
+division, so they are compared BIT-EXACT as well; the stated fallback tolerance is the
+componentwise bound c*eps*(|L||U|)_ij, which bit-exactness trivially meets."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import orc
+from respasol_b200 import host
+from respasol_b200.gpu import DeviceCSR, ZERO_PIVOT_NUMERIC, ZERO_PIVOT_STRUCTURAL
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def tridiag(n):
+    rp, ci, v = [0], [], []
+    for i in range(n):
+        for j in (i - 1, i, i + 1):
+            if 0 <= j < n:
+                ci.append(j); v.append(4.0 if i == j else -1.0 - 0.01 * (i % 7))
+        rp.append(len(ci))
+    return host.CSR(n, n, len(ci), np.array(rp, np.int32), np.array(ci, np.int32), np.array(v))
+
+
+def arrow(n):
+    """dense last row and column + diagonal: one very long row (beyond the staged-row capacity)"""
+    rp, ci, v = [0], [], []
+    for i in range(n - 1):
+        ci += [i, n - 1]; v += [4.0 + i % 3, -1.0 / (1 + i % 5)]
+        rp.append(len(ci))
+    ci += list(range(n)); v += [-0.5 / (1 + i % 4) for i in range(n - 1)] + [float(n)]
+    rp.append(len(ci))
+    return host.CSR(n, n, len(ci), np.array(rp, np.int32), np.array(ci, np.int32), np.array(v))
+
+
+def to_base1(a):
+    return host.CSR(a.m, a.n, a.nnz, a.rowptr + 1, a.colidx + 1, a.values.copy(), 1)
+
+
+MATS = {
+    "one": lambda: host.load_matrix_market(os.path.join(GOLD, "one.mtx")),
+    "bcspwr01": lambda: host.load_matrix_market(os.path.join(GOLD, "bcspwr01.mtx")),
+    "lap2d_3": lambda: host.gen_laplace2d(3),
+    "lap2d_40": lambda: host.gen_laplace2d(40),
+    "lap2d_40_base1": lambda: to_base1(host.gen_laplace2d(40)),
+    "femlike_10": lambda: host.gen_femlike(10),
+    "femlike_20": lambda: host.gen_femlike(20),
+    "stencil27_12": lambda: host.gen_stencil27(12, seed=2),
+    "tridiag_3000": lambda: tridiag(3000),
+    "arrow_700": lambda: arrow(700),
+    "powerlaw_5k": lambda: host.gen_powerlaw(5000, 2.2, 48, 2, 900, 4),
+}
+
+
+@pytest.mark.parametrize("name", sorted(MATS))
+def test_levels_bit_exact(handle, name):
+    a = MATS[name]()
+    A = DeviceCSR(a, "d")
+    handle.ilu0_analysis(A)
+    for which in (0, 1):
+        lp, rows = handle.levels(which, a.m)
+        _, lp_ref, rows_ref = orc.levels(a, which)
+        assert np.array_equal(lp, lp_ref)
+        assert np.array_equal(rows, rows_ref)
+
+
+@pytest.mark.parametrize("name", sorted(MATS))
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("trsv_algo", [0, 2])
+def test_ilu0_and_solves(handle, name, dtype, trsv_algo):
+    a = MATS[name]()
+    prec = "d" if dtype == np.float64 else "s"
+    A = DeviceCSR(a, prec)
+    st_ref, piv_ref, lu_ref = orc.ilu0(a, dtype)
+    st, piv = handle.ilu0_factor(A)
+    assert (st, piv) == (st_ref, piv_ref)
+    lu = A.values.cpu().numpy()
+    assert np.array_equal(lu.view(np.uint8), lu_ref.view(np.uint8)), "ILU0 factors are not bit-identical to the oracle"
+    b = (orc.dlarnv(a.m) + 0.5).astype(dtype)
+    _, z_ref, y_ref = orc.sptrsv_lu(a, lu_ref, b)
+    handle.set_option("TRSV_ALGO", trsv_algo)
+    try:
+        z, y = handle.sptrsv_lu(A, A.values, torch.from_numpy(b).cuda())
+    finally:
+        handle.set_option("TRSV_ALGO", 0)
+    assert np.array_equal(z.cpu().numpy().view(np.uint8), z_ref.view(np.uint8))
+    assert np.array_equal(y.cpu().numpy().view(np.uint8), y_ref.view(np.uint8))
+
+
+def test_golden_lap3(handle):
+    a = host.gen_laplace2d(3)
+    A = DeviceCSR(a, "d")
+    handle.ilu0_factor(A)
+    ref = [4, -1, -1, -0.25, 3.75, -1, -1, -0.26666666666666666, 3.7333333333333334, -1, -0.25, 3.75, -1, -1,
+           -0.26666666666666666, -0.26666666666666666, 3.466666666666667, -1, -1, -0.26785714285714285,
+           -0.28846153846153844, 3.443681318681319, -1, -0.26666666666666666, 3.7333333333333334, -1,
+           -0.28846153846153844, -0.26785714285714285, 3.443681318681319, -1, -0.29038691663342636,
+           -0.29038691663342636, 3.4192261667331474]
+    assert A.values.cpu().tolist() == ref
+    lp, rows = handle.levels(0, 9)
+    assert lp.tolist() == [0, 1, 3, 6, 8, 9] and rows.tolist() == [0, 1, 3, 2, 4, 6, 5, 7, 8]
+    z, y = handle.sptrsv_lu(A, A.values, torch.ones(9, dtype=torch.float64, device="cuda"))
+    np.testing.assert_allclose(y.cpu().numpy(), [0.6082803881450638, 0.7165607762901277, 0.5471301913205786,
+                                                 0.7165607762901275, 0.8899727197673999, 0.7092860475968267,
+                                                 0.5471301913205786, 0.7092860475968267, 0.6046430237984133], rtol=4.5e-16)
+
+
+def test_structural_zero_pivot_b1ss(handle):
+    a = host.load_matrix_market(os.path.join(GOLD, "b1_ss.mtx"))
+    A = DeviceCSR(a, "d")
+    before = A.values.clone()
+    st, row = handle.ilu0_analysis(A)
+    assert (st, row) == (ZERO_PIVOT_STRUCTURAL, 0)       # harness prints "A(0,0) is missing"
+    st, row = handle.ilu0_factor(A)
+    assert (st, row) == (ZERO_PIVOT_STRUCTURAL, 0) and torch.equal(before, A.values)
+    # level sets are still defined and must match the oracle
+    lp, rows = handle.levels(0, a.m)
+    _, lp_ref, rows_ref = orc.levels(a, 0)
+    assert np.array_equal(lp, lp_ref) and np.array_equal(rows, rows_ref)
+
+
+def test_numeric_zero_pivot(handle):
+    a = host.CSR(2, 2, 4, np.array([0, 2, 4], np.int32), np.array([0, 1, 0, 1], np.int32), np.array([1.0, 1.0, 1.0, 1.0]))
+    A = DeviceCSR(a, "d")
+    st, row = handle.ilu0_factor(A)
+    assert (st, row) == (ZERO_PIVOT_NUMERIC, 1)          # harness prints "L(1,1) is zero"
+    assert A.values.cpu().tolist() == [1, 1, 1, 0]
+
+
+def test_wavefront_rule_lap2d(handle):
+    N = 100
+    a = host.gen_laplace2d(N)
+    A = DeviceCSR(a, "d")
+    handle.ilu0_analysis(A)
+    lp, rows = handle.levels(0, a.m)
+    assert len(lp) - 1 == 2 * N - 1
+    lev = np.empty(a.m, dtype=np.int64)
+    for l in range(len(lp) - 1):
+        lev[rows[lp[l]:lp[l + 1]]] = l
+    i, j = np.meshgrid(np.arange(N), np.arange(N), indexing="ij")
+    assert np.array_equal(lev.reshape(N, N), i + j)
+
+
+def test_host_pointer_entry_points(handle):
+    a = host.gen_femlike(9)
+    st, piv, lu = handle.ilu0_factor_host(a)
+    _, _, lu_ref = orc.ilu0(a)
+    assert st == 0 and np.array_equal(lu, lu_ref)
+    b = orc.dlarnv(a.m)
+    y = handle.sptrsv_lu_host(a, lu, b)
+    assert np.array_equal(y, orc.sptrsv_lu(a, lu_ref, b)[2])
+
+
+def test_repeated_factorizations_reuse_the_plan(handle):
+    a = host.gen_femlike(12)
+    A = DeviceCSR(a, "d")
+    _, _, lu_ref = orc.ilu0(a)
+    pristine = A.values.clone()
+    for _ in range(3):
+        A.values.copy_(pristine)
+        st, _ = handle.ilu0_factor(A)
+        assert st == 0 and np.array_equal(A.values.cpu().numpy(), lu_ref)
+
+
+def test_config3_full_size(handle):
+    """BASELINE config 3: FEM-like 47^3 = 103 823 rows, ~1.6 M nnz (2cubes_sphere-shaped)."""
+    a = host.gen_femlike(47, 0.58, 3)
+    assert a.m == 103823 and 1.4e6 < a.stored < 1.8e6
+    for dtype, prec in ((np.float64, "d"), (np.float32, "s")):
+        A = DeviceCSR(a, prec)
+        st, piv = handle.ilu0_factor(A)
+        st_ref, _, lu_ref = orc.ilu0(a, dtype)
+        assert st == st_ref == 0
+        assert np.array_equal(A.values.cpu().numpy(), lu_ref)
+        b = np.ones(a.m, dtype=dtype)
+        z, y = handle.sptrsv_lu(A, A.values, torch.from_numpy(b).cuda())
+        _, z_ref, y_ref = orc.sptrsv_lu(a, lu_ref, b)
+        assert np.array_equal(z.cpu().numpy(), z_ref) and np.array_equal(y.cpu().numpy(), y_ref)
+        for which in (0, 1):
+            lp, rows = handle.levels(which, a.m)
+            _, lp_ref, rows_ref = orc.levels(a, which)
+            assert np.array_equal(lp, lp_ref) and np.array_equal(rows, rows_ref)
+    # property: the preconditioner is a good approximate inverse of a diagonally dominant matrix
+    A = DeviceCSR(a, "d")
+    lu = A.values.clone()
+    handle.ilu0_factor(A, lu)
+    x = torch.from_numpy(orc.dlarnv(a.m)).cuda()
+    Ax = handle.spmv(A, x)
+    _, y = handle.sptrsv_lu(A, lu, Ax)
+    assert float((y - x).abs().max() / x.abs().max()) < 0.2

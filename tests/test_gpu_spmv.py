@@ -1,0 +1,257 @@
+"""SpMV parity: the CUDA path through the C ABI against the CPU oracle on the same seeded inputs.
+
+Tolerances (stated by BASELINE.json north_star / SURVEY.md 8c):
+  fp64:   ||y - y_ref||inf <= 1e-12 * ||y_ref||inf
+  fp32 / mixed: per row |dy_i| <= (len_i + 2) * eps * sum_k |a_ik x_k|, eps = 2^-24 (fp32) or
+                2^-53 (mixed accumulates in fp64) -- the ulp-scaled bound for any summation order.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import orc
+from respasol_b200 import host
+from respasol_b200.gpu import ALGO, DeviceCSR
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def row_abs_sums(a, x, precision):
+    vt = np.float64 if precision == "d" else np.float32
+    xt = np.float32 if precision == "s" else np.float64
+    absa = host.CSR(a.m, a.n, a.nnz, a.rowptr, a.colidx, np.abs(a.values.astype(vt)).astype(np.float64), a.base)
+    return orc.spmv(absa, np.abs(x.astype(xt)).astype(np.float64), "d")
+
+
+def check(handle, a, x, precision, alpha=1.0, beta=0.0, y0=None):
+    A = DeviceCSR(a, precision)
+    xt = torch.float32 if precision == "s" else torch.float64
+    xd = torch.from_numpy(x).to("cuda").to(xt)
+    yd = None if y0 is None else torch.from_numpy(y0).to("cuda").to(xt)
+    y = handle.spmv(A, xd, yd, alpha, beta).cpu().numpy()
+    ref = orc.spmv(a, x, precision, alpha, beta, y0)
+    if precision == "d":
+        scale = max(np.abs(ref).max(), 1e-300) if a.m else 1.0
+        assert np.abs(y - ref).max(initial=0.0) <= 1e-12 * scale
+    else:
+        eps = 2.0 ** -24 if precision == "s" else 2.0 ** -53
+        lens = np.diff(a.rowptr).astype(np.float64)
+        bound = (lens + 2) * eps * (abs(alpha) * row_abs_sums(a, x, precision) + abs(beta) * (0 if y0 is None else np.abs(y0)))
+        if precision == "m":  # output rounding of the fp64 result is below the bound already
+            bound = bound + 1e-300
+        assert np.all(np.abs(y.astype(np.float64) - ref.astype(np.float64)) <= bound + 1e-300)
+    return y
+
+
+SMALL = {
+    "one": lambda: host.load_matrix_market(os.path.join(GOLD, "one.mtx")),
+    "b1_ss": lambda: host.load_matrix_market(os.path.join(GOLD, "b1_ss.mtx")),
+    "b1_ss_base1": lambda: host.load_matrix_market(os.path.join(GOLD, "b1_ss.mtx"), 1),
+    "bcspwr01": lambda: host.load_matrix_market(os.path.join(GOLD, "bcspwr01.mtx")),
+    "rect": lambda: host.load_matrix_market(os.path.join(GOLD, "rect.mtx")),
+    "empty_rows": lambda: host.load_matrix_market(os.path.join(GOLD, "empty_rows.mtx")),
+    "dup_unsorted": lambda: host.load_matrix_market(os.path.join(GOLD, "dup_unsorted.mtx")),
+    "lap2d_64": lambda: host.gen_laplace2d(64),
+    "stencil27_20": lambda: host.gen_stencil27(20, 20, 20, seed=2),
+    "stencil27_slab": lambda: host.gen_stencil27(12, 12, 30, 10, 20, seed=2),
+    "femlike_12": lambda: host.gen_femlike(12),
+    "powerlaw_20k": lambda: host.gen_powerlaw(20000, 2.2, 64, 2, 9000, 4),
+}
+
+
+@pytest.mark.parametrize("name", sorted(SMALL))
+@pytest.mark.parametrize("precision", ["d", "s", "m"])
+@pytest.mark.parametrize("algo", ["auto", "rowblock", "merge", "vector", "scalar"])
+def test_spmv_small(handle, name, precision, algo):
+    a = SMALL[name]()
+    handle.set_option("SPMV_ALGO", ALGO[algo])
+    try:
+        x = orc.dlarnv(a.n) - 0.5
+        check(handle, a, x, precision)
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+
+
+def test_golden_b1ss_values(handle):
+    a = SMALL["b1_ss"]()
+    y = check(handle, a, np.ones(7), "d")
+    np.testing.assert_allclose(y, [3, -0.55, -0.9, -0.55, 0.96400058, 0.9823629, 0.992278221], rtol=1e-15)
+    y = check(handle, a, orc.dlarnv(7), "d")
+    np.testing.assert_allclose(y, [1.1964668762652444, -0.50611051611001145, 0.019299642814089787, -0.041548033327566514,
+                                   0.30173623575092434, 0.81428611598229961, 0.99624904350899124], rtol=4e-16)
+
+
+@pytest.mark.parametrize("precision", ["d", "s", "m"])
+@pytest.mark.parametrize("algo", ["rowblock", "merge", "vector"])
+def test_alpha_beta(handle, precision, algo):
+    a = host.gen_stencil27(9, 10, 11, seed=5)
+    handle.set_option("SPMV_ALGO", ALGO[algo])
+    try:
+        x = orc.dlarnv(a.n) - 0.5
+        y0 = (orc.dlarnv(a.m + 3)[3:] - 0.5)
+        check(handle, a, x, precision, alpha=-1.75, beta=0.5, y0=y0)
+        check(handle, a, x, precision, alpha=0.0, beta=2.0, y0=y0)
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+
+
+def test_beta_zero_ignores_nan_y(handle):
+    a = host.gen_laplace2d(30)
+    A = DeviceCSR(a, "d")
+    x = torch.ones(a.n, dtype=torch.float64, device="cuda")
+    y = torch.full((a.m,), float("nan"), dtype=torch.float64, device="cuda")
+    handle.spmv(A, x, y)
+    assert torch.isfinite(y).all()
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("reduce", [0, 1, 2, 4, 8, 16, 32])
+def test_rowblock_variants(handle, variant, reduce):
+    a = host.gen_femlike(14, 0.7, 9)
+    handle.set_option("SPMV_ALGO", ALGO["rowblock"])
+    handle.set_option("SPMV_VARIANT", variant)
+    handle.set_option("SPMV_REDUCE", reduce)
+    try:
+        check(handle, a, orc.dlarnv(a.n) - 0.5, "d")
+        check(handle, a, orc.dlarnv(a.n) - 0.5, "s")
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+        handle.set_option("SPMV_VARIANT", 0)
+        handle.set_option("SPMV_REDUCE", 0)
+
+
+@pytest.mark.parametrize("hint", [0, 1, 2])
+@pytest.mark.parametrize("persist", [0, 1])
+def test_cache_hints(handle, hint, persist):
+    a = host.gen_stencil27(16, 16, 16, seed=2)
+    handle.set_option("SPMV_CACHE_HINT", hint)
+    handle.set_option("SPMV_X_PERSIST", persist)
+    try:
+        for algo in ("rowblock", "merge"):
+            handle.set_option("SPMV_ALGO", ALGO[algo])
+            check(handle, a, orc.dlarnv(a.n), "d")
+            check(handle, a, orc.dlarnv(a.n), "m")
+    finally:
+        handle.set_option("SPMV_CACHE_HINT", 1)
+        handle.set_option("SPMV_X_PERSIST", 0)
+        handle.set_option("SPMV_ALGO", 0)
+
+
+def test_long_rows_cta_per_row_and_merge(handle):
+    # rows far longer than a tile: the row-block kernel falls to CTA-per-row, AUTO picks merge-path
+    a = host.gen_powerlaw(60000, 2.2, 32, 3, 50000, 7)
+    x = orc.dlarnv(a.n) - 0.5
+    for algo in ("rowblock", "merge", "auto"):
+        handle.set_option("SPMV_ALGO", ALGO[algo])
+        for p in ("d", "s", "m"):
+            check(handle, a, x, p)
+    handle.set_option("SPMV_ALGO", 0)
+    check(handle, a, x, "d")
+    assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
+    assert handle.info("SPMV_MAX_ROW") == int(np.diff(a.rowptr).max())
+
+
+def test_unaligned_views_take_scalar_path(handle):
+    a = host.gen_stencil27(10, 10, 10, seed=3)
+    A = DeviceCSR(a, "d")
+    # shift colidx/values by one element so the pointers are not 16-byte aligned
+    ci = torch.empty(A.colidx.numel() + 1, dtype=torch.int32, device="cuda")
+    va = torch.empty(A.values.numel() + 1, dtype=torch.float64, device="cuda")
+    ci[1:] = A.colidx; va[1:] = A.values
+    A.colidx, A.values = ci[1:], va[1:]
+    x = orc.dlarnv(a.n)
+    ref = orc.spmv(a, x)
+    for algo in ("rowblock", "merge"):
+        handle.set_option("SPMV_ALGO", ALGO[algo])
+        y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
+        assert np.abs(y - ref).max() <= 1e-12 * np.abs(ref).max()
+    handle.set_option("SPMV_ALGO", 0)
+
+
+def test_empty_and_degenerate(handle):
+    z = host.CSR(0, 0, 0, np.zeros(1, np.int32), np.zeros(0, np.int32), np.zeros(0))
+    Z = DeviceCSR(z, "d")
+    Z.colidx = torch.zeros(1, dtype=torch.int32, device="cuda"); Z.values = torch.zeros(1, dtype=torch.float64, device="cuda")
+    handle.spmv(Z, torch.zeros(1, dtype=torch.float64, device="cuda"), torch.zeros(1, dtype=torch.float64, device="cuda"))
+    # all rows empty
+    e = host.CSR(5, 5, 0, np.zeros(6, np.int32), np.zeros(0, np.int32), np.zeros(0))
+    E = DeviceCSR(e, "d")
+    E.colidx = torch.zeros(1, dtype=torch.int32, device="cuda"); E.values = torch.zeros(1, dtype=torch.float64, device="cuda")
+    for algo in ("rowblock", "merge", "vector", "scalar"):
+        handle.set_option("SPMV_ALGO", ALGO[algo])
+        y = handle.spmv(E, torch.ones(5, dtype=torch.float64, device="cuda"),
+                        torch.full((5,), 7.0, dtype=torch.float64, device="cuda"))
+        assert y.cpu().tolist() == [0.0] * 5
+    handle.set_option("SPMV_ALGO", 0)
+
+
+def test_host_pointer_entry_points(handle):
+    a = host.gen_femlike(10)
+    x = orc.dlarnv(a.n) - 0.5
+    for p in ("d", "s", "m"):
+        y = handle.spmv_host(a, x, p)
+        ref = orc.spmv(a, x, p)
+        np.testing.assert_allclose(y, ref, rtol=1e-12 if p != "s" else 2e-5, atol=1e-12 if p != "s" else 1e-5)
+    for p in ("d", "s", "m"):
+        mat = handle.matrix_upload(a, p)
+        xt = np.float32 if p == "s" else np.float64
+        y = np.zeros(a.m, dtype=xt)
+        handle.matrix_spmv_host(mat, x.astype(xt), y)
+        ref = orc.spmv(a, x, p)
+        np.testing.assert_allclose(y, ref, rtol=1e-12 if p != "s" else 2e-5, atol=1e-12 if p != "s" else 1e-5)
+        handle.matrix_free(mat)
+
+
+def test_row_partition_bit_exact(handle):
+    for a in (host.gen_laplace2d(50), host.gen_powerlaw(30000, 2.2, 64, 2, 9000, 4), SMALL["b1_ss_base1"]()):
+        A = DeviceCSR(a, "d")
+        for P in (1, 2, 3, 4, 8):
+            for bal in (True, False):
+                assert np.array_equal(handle.row_partition(A, P, bal), orc.row_partition(a, P, bal))
+
+
+# ---- BASELINE.json configs at full size: oracle comparison (the oracle takes well under a second
+# per product) plus size-independent properties (linearity, A*1 = row sums).
+def _config_matrix(name):
+    if name == "C1":  # through a Matrix Market file, like the reference's test_spmv
+        import tempfile
+        a = host.gen_laplace2d(1000)
+        with tempfile.TemporaryDirectory() as d:
+            p = os.path.join(d, "lap1000.mtx")
+            host.write_matrix_market(p, a)
+            b = host.load_matrix_market(p, 0, 0)
+        assert b.stored == 4996000 and np.array_equal(a.colidx, b.colidx)
+        return b
+    if name == "C2":
+        a = host.gen_stencil27(100, seed=2)
+        assert a.stored == 26463592
+        return a
+    if name == "C4":
+        return host.gen_powerlaw(320000, 2.2, 64, 4, 100000, 4)
+    raise KeyError(name)
+
+
+@pytest.mark.parametrize("name", ["C1", "C2", "C4"])
+def test_full_size_configs(handle, name):
+    a = _config_matrix(name)
+    x = orc.dlarnv(a.n) - 0.5
+    yd = None
+    for p in ("d", "s", "m"):
+        y = check(handle, a, x, p)
+        if p == "d":
+            yd = y
+    if name == "C4":
+        assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
+    else:
+        assert handle.info("SPMV_ALGO_USED") == ALGO["rowblock"]
+    # linearity: A(2x + 1) = 2 A x + A 1
+    A = DeviceCSR(a, "d")
+    xd = torch.from_numpy(x).cuda()
+    y1 = handle.spmv(A, torch.ones_like(xd))
+    y2 = handle.spmv(A, 2 * xd + 1)
+    lin = 2 * torch.from_numpy(yd).cuda() + y1
+    rs = torch.from_numpy(row_abs_sums(a, np.abs(x) * 2 + 1, "d")).cuda()
+    assert bool(((y2 - lin).abs() <= 1e-13 * rs + 1e-300).all())
