@@ -69,15 +69,20 @@ typedef enum {
     RSG_OPT_TRSV_ALGO = 5,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_ILU0_ALGO = 6,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_SPMV_X_PERSIST = 7, /* 1: pin x in L2 with an access-policy window on the stream */
+    RSG_OPT_SPMV_X_HINT = 8,    /* stream/pipe kernels: 1 = gather x with an L2 evict_last hint */
+    RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* pipe kernel: tile size in rows per thread (0 = 1) */
+    RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* pipe kernel: cap on resident CTAs per SM (0 = occupancy limit) */
     RSG_OPT_COUNT_
 } rsg_option;
 
 typedef enum {
     RSG_SPMV_AUTO = 0,
-    RSG_SPMV_ROWBLOCK = 1, /* row-length-binned row blocks: thread-, warp- and CTA-per-row paths */
+    RSG_SPMV_ROWBLOCK = 1, /* product-staged row blocks (register-path loads): thread-, warp-, CTA-per-row */
     RSG_SPMV_MERGE = 2,    /* merge-path, for skewed row lengths */
     RSG_SPMV_VECTOR = 3,   /* plain sub-warp-per-row, scalar loads (any alignment) */
-    RSG_SPMV_SCALAR = 4    /* plain thread-per-row, scalar loads */
+    RSG_SPMV_SCALAR = 4,   /* plain thread-per-row, scalar loads */
+    RSG_SPMV_STREAM = 5,   /* TMA bulk-staged tiles, one tile per CTA; thread-, sub-warp-, warp-, CTA-per-row */
+    RSG_SPMV_PIPE = 6      /* persistent CTAs, multi-stage TMA ring (mbarrier pipeline); same reductions */
 } rsg_spmv_algo;
 
 typedef enum {
@@ -91,6 +96,10 @@ typedef enum {
     RSG_INFO_WORKSPACE_BYTES = 7
 } rsg_info;
 
+/* Plans (SpMV tiling, level schedules) are cached per handle, keyed on the device addresses of
+ * rowptr/colidx plus m, n, nnz and base.  When a matrix is freed and another one may be allocated
+ * at the same addresses, call rsg_forget_matrix (or re-run the analysis, which always rebuilds). */
+int rsg_forget_matrix(rsg_handle_t handle, const int *rowptr);
 int rsg_set_option(rsg_handle_t handle, int option, int value);
 int rsg_get_info(rsg_handle_t handle, int info, long long *value);
 

@@ -42,6 +42,7 @@ GPU_SYMBOLS = {
     "rsg_synchronize": (_I, [_P]),
     "rsg_status_string": (C.c_char_p, [_I]),
     "rsg_version": (_I, []),
+    "rsg_forget_matrix": (_I, [_P, _P]),
     "rsg_set_option": (_I, [_P, _I, _I]),
     "rsg_get_info": (_I, [_P, _I, _LLP]),
     "rsg_spmv_analysis": (_I, _CSR_ARGS),

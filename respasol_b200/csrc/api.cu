@@ -147,51 +147,58 @@ int rsg_get_info(rsg_handle_t h, int info, long long *value)
     return RSG_OK;
 }
 
+int rsg_forget_matrix(rsg_handle_t h, const int *rowptr)
+{
+    if (!h) return RSG_BAD_ARG;
+    DeviceGuard g(h->device);
+    cudaStreamSynchronize(h->stream);
+    for (size_t i = h->spmv_plans.size(); i-- > 0;)
+        if (h->spmv_plans[i].rowptr == rowptr) { spmv_free_plan(h->spmv_plans[i]); h->spmv_plans.erase(h->spmv_plans.begin() + (long)i); }
+    for (size_t i = h->tri_plans.size(); i-- > 0;)
+        if (h->tri_plans[i].rowptr == rowptr) { tri_free_plan(h->tri_plans[i]); h->tri_plans.erase(h->tri_plans.begin() + (long)i); h->last_tri = -1; }
+    return RSG_OK;
+}
+
 // ---- SpMV ---------------------------------------------------------------------------------
 int rsg_spmv_analysis(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx)
 {
-    (void)nnz;
     if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
     SpmvPlan *p = nullptr;
-    return spmv_get_plan(h, m, n, base, rowptr, colidx, true, &p);
+    return spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p);
 }
 
 int spmv_csr_d(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
                const double *values, double alpha, const double *x, double beta, double *y)
 {
-    (void)nnz;
     if (!h) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    return spmv_run<double, double>(h, m, n, base, rowptr, colidx, values, alpha, x, beta, y);
+    return spmv_run<double, double>(h, m, n, nnz, base, rowptr, colidx, values, alpha, x, beta, y);
 }
 
 int spmv_csr_s(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
                const float *values, float alpha, const float *x, float beta, float *y)
 {
-    (void)nnz;
     if (!h) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    return spmv_run<float, float>(h, m, n, base, rowptr, colidx, values, alpha, x, beta, y);
+    return spmv_run<float, float>(h, m, n, nnz, base, rowptr, colidx, values, alpha, x, beta, y);
 }
 
 int spmv_csr_mixed(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
                    const float *values, double alpha, const double *x, double beta, double *y)
 {
-    (void)nnz;
     if (!h) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    return spmv_run<float, double>(h, m, n, base, rowptr, colidx, values, alpha, x, beta, y);
+    return spmv_run<float, double>(h, m, n, nnz, base, rowptr, colidx, values, alpha, x, beta, y);
 }
 
 // ---- ILU0 / SpTRSV ------------------------------------------------------------------------
 int rsg_ilu0_analysis(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, int *zero_pivot_row)
 {
-    (void)nnz;
     if (!h || n < 0 || (base != 0 && base != 1) || !rowptr) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
-    RSG_TRY(tri_get_plan(h, n, base, rowptr, colidx, true, &p));
+    RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, true, &p));
     if (zero_pivot_row) *zero_pivot_row = p->missing_diag_row;
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
     return tri_build_levels(h, p, 0);
@@ -199,58 +206,53 @@ int rsg_ilu0_analysis(rsg_handle_t h, int n, int nnz, int base, const int *rowpt
 
 int rsg_sptrsv_analysis(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx)
 {
-    (void)nnz;
     if (!h || n < 0 || (base != 0 && base != 1) || !rowptr) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
-    RSG_TRY(tri_get_plan(h, n, base, rowptr, colidx, false, &p));
+    RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
     RSG_TRY(tri_build_levels(h, p, 0));
     return tri_build_levels(h, p, 1);
 }
 
 extern "C++" template <typename T>
-int ilu0_factor_impl(rsg_handle_t h, int n, int base, const int *rowptr, const int *colidx, T *values, int *zp)
+int ilu0_factor_impl(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, T *values, int *zp)
 {
     if (!h || n < 0 || (base != 0 && base != 1) || !rowptr || (n > 0 && !values)) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
-    RSG_TRY(tri_get_plan(h, n, base, rowptr, colidx, false, &p));
+    RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
     return ilu0_run<T>(h, p, values, zp);
 }
 
 int ilu0_factor_d(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, double *values, int *zp)
 {
-    (void)nnz;
-    return ilu0_factor_impl<double>(h, n, base, rowptr, colidx, values, zp);
+    return ilu0_factor_impl<double>(h, n, nnz, base, rowptr, colidx, values, zp);
 }
 int ilu0_factor_s(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, float *values, int *zp)
 {
-    (void)nnz;
-    return ilu0_factor_impl<float>(h, n, base, rowptr, colidx, values, zp);
+    return ilu0_factor_impl<float>(h, n, nnz, base, rowptr, colidx, values, zp);
 }
 
 extern "C++" template <typename T>
-int sptrsv_impl(rsg_handle_t h, int n, int base, const int *rowptr, const int *colidx, const T *lu, const T *b, T *z, T *y)
+int sptrsv_impl(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const T *lu, const T *b, T *z, T *y)
 {
     if (!h || n < 0 || (base != 0 && base != 1) || !rowptr) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
-    RSG_TRY(tri_get_plan(h, n, base, rowptr, colidx, false, &p));
+    RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
     return trsv_run<T>(h, p, lu, b, z, y);
 }
 
 int sptrsv_lu_d(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *lu,
                 const double *b, double *z, double *y)
 {
-    (void)nnz;
-    return sptrsv_impl<double>(h, n, base, rowptr, colidx, lu, b, z, y);
+    return sptrsv_impl<double>(h, n, nnz, base, rowptr, colidx, lu, b, z, y);
 }
 int sptrsv_lu_s(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const float *lu,
                 const float *b, float *z, float *y)
 {
-    (void)nnz;
-    return sptrsv_impl<float>(h, n, base, rowptr, colidx, lu, b, z, y);
+    return sptrsv_impl<float>(h, n, nnz, base, rowptr, colidx, lu, b, z, y);
 }
 
 // ---- introspection ------------------------------------------------------------------------
@@ -301,7 +303,7 @@ int spmv_host_impl(rsg_handle_t h, int m, int n, int base, const int *rowptr, co
     RSG_TRY(d_x.upload(x, (size_t)n, st));
     RSG_TRY(d_y.alloc((size_t)m));
     if (beta != (TX)0 && m) RSG_CUDA_TRY(cudaMemcpyAsync(d_y.p, y, sizeof(TX) * (size_t)m, cudaMemcpyHostToDevice, st));
-    int rc = spmv_run<TV, TX>(h, m, n, base, d_rp.p, d_ci.p, d_v.p, alpha, d_x.p, beta, d_y.p);
+    int rc = spmv_run<TV, TX>(h, m, n, (int)nnz, base, d_rp.p, d_ci.p, d_v.p, alpha, d_x.p, beta, d_y.p);
     if (rc == RSG_OK && m) {
         if (cudaMemcpyAsync(y, d_y.p, sizeof(TX) * (size_t)m, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = RSG_CUDA_ERROR;
     }
@@ -356,7 +358,7 @@ int ilu0_host_impl(rsg_handle_t h, int n, int base, const int *rowptr, const int
     RSG_TRY(d_ci.upload(colidx, nnz, st));
     RSG_TRY(d_v.upload(values, nnz, st));
     int dummy = -1;
-    int rc = ilu0_factor_impl<T>(h, n, base, d_rp.p, d_ci.p, d_v.p, zp ? zp : &dummy);
+    int rc = ilu0_factor_impl<T>(h, n, (int)nnz, base, d_rp.p, d_ci.p, d_v.p, zp ? zp : &dummy);
     if ((rc == RSG_OK || rc == RSG_ZERO_PIVOT_NUMERIC) && nnz) {
         if (cudaMemcpyAsync(values, d_v.p, sizeof(T) * nnz, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = RSG_CUDA_ERROR;
     }
@@ -391,7 +393,7 @@ int sptrsv_host_impl(rsg_handle_t h, int n, int base, const int *rowptr, const i
     RSG_TRY(d_b.upload(b, (size_t)n, st));
     RSG_TRY(d_z.alloc((size_t)n));
     RSG_TRY(d_y.alloc((size_t)n));
-    int rc = sptrsv_impl<T>(h, n, base, d_rp.p, d_ci.p, d_v.p, d_b.p, d_z.p, d_y.p);
+    int rc = sptrsv_impl<T>(h, n, (int)nnz, base, d_rp.p, d_ci.p, d_v.p, d_b.p, d_z.p, d_y.p);
     if (rc == RSG_OK && n) {
         if (cudaMemcpyAsync(y, d_y.p, sizeof(T) * (size_t)n, cudaMemcpyDeviceToHost, st) != cudaSuccess) rc = RSG_CUDA_ERROR;
     }
@@ -476,13 +478,13 @@ int rsg_matrix_spmv_host(rsg_handle_t h, rsg_matrix_t a, double alpha, const voi
     }
     int rc;
     if (a->precision == 'd')
-        rc = spmv_run<double, double>(h, a->m, a->n, a->base, a->rowptr, a->colidx, static_cast<const double *>(a->values),
+        rc = spmv_run<double, double>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const double *>(a->values),
                                       alpha, static_cast<const double *>(a->x), beta, static_cast<double *>(a->y));
     else if (a->precision == 's')
-        rc = spmv_run<float, float>(h, a->m, a->n, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
+        rc = spmv_run<float, float>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
                                     (float)alpha, static_cast<const float *>(a->x), (float)beta, static_cast<float *>(a->y));
     else
-        rc = spmv_run<float, double>(h, a->m, a->n, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
+        rc = spmv_run<float, double>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
                                      alpha, static_cast<const double *>(a->x), beta, static_cast<double *>(a->y));
     RSG_TRY(rc);
     RSG_CUDA_TRY(cudaMemcpyAsync(a->pin_y, a->y, xs * (size_t)a->m, cudaMemcpyDeviceToHost, st));

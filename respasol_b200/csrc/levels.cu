@@ -131,11 +131,12 @@ void tri_free_plan(TriPlan &p)
     p = TriPlan();
 }
 
-int tri_get_plan(rsg_context *h, int n, int base, const int *rowptr, const int *colidx, bool force_rebuild, TriPlan **out)
+int tri_get_plan(rsg_context *h, int n, int nnz_hint, int base, const int *rowptr, const int *colidx, bool force_rebuild,
+                 TriPlan **out)
 {
     for (size_t i = 0; i < h->tri_plans.size(); ++i) {
         TriPlan &p = h->tri_plans[i];
-        if (p.rowptr == rowptr && p.colidx == colidx && p.n == n && p.base == base) {
+        if (p.rowptr == rowptr && p.colidx == colidx && p.n == n && p.nnz_hint == nnz_hint && p.base == base) {
             if (!force_rebuild) { *out = &p; h->last_tri = (int)i; return RSG_OK; }
             tri_free_plan(p);
             h->tri_plans.erase(h->tri_plans.begin() + (long)i);
@@ -147,7 +148,7 @@ int tri_get_plan(rsg_context *h, int n, int base, const int *rowptr, const int *
         h->tri_plans.erase(h->tri_plans.begin());
     }
     TriPlan p;
-    p.rowptr = rowptr; p.colidx = colidx; p.n = n; p.base = base;
+    p.rowptr = rowptr; p.colidx = colidx; p.n = n; p.nnz_hint = nnz_hint; p.base = base;
     cudaStream_t st = h->stream;
     const size_t nn = (size_t)(n > 0 ? n : 1);
     RSG_CUDA_TRY(cudaMalloc(&p.diag_pos, sizeof(int) * nn));

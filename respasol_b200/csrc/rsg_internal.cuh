@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "../../include/reaspasol_gpu.h"
@@ -30,6 +31,7 @@ struct SpmvPlan {
     const int *rowptr = nullptr;
     const int *colidx = nullptr;
     int m = 0, n = 0, base = 0;
+    int nnz_hint = 0;      // the caller's nnz argument (part of the key: pointers get recycled)
     int opt_sig = 0;       // hash of the options that shape the plan
     // statistics
     int nnz = 0;           // stored entries, rowptr[m]-rowptr[0]
@@ -41,6 +43,10 @@ struct SpmvPlan {
     int tile = 0;          // merged items (rows + entries) per CTA
     int nblk = 0;
     int *blk_row = nullptr;    // nblk+1 row indices
+    int2 *sblk = nullptr;      // stream kernel: nblk+1 (first row, zero-based entry offset)
+    int4 *pdesc = nullptr;     // pipe kernel: nblk+1 (first row, zero-based entry offset, longest row, 0)
+    int *rp0 = nullptr;        // pipe kernel: zero-based padded copy of rowptr
+    int rp0_len = 0;
     // merge-path kernel
     int merge_items = 0;   // rows+entries per CTA
     int ntiles = 0;
@@ -55,6 +61,7 @@ struct TriPlan {
     const int *rowptr = nullptr;
     const int *colidx = nullptr;
     int n = 0, base = 0, nnz = 0;
+    int nnz_hint = 0;              // the caller's nnz argument (part of the key)
     int *diag_pos = nullptr;       // zero-based position of a_ii in colidx/values, -1 if missing
     int missing_diag_row = -1;     // first row without a diagonal entry
     int max_row = 0;
@@ -111,17 +118,23 @@ namespace rsg {
 int ensure_cub_tmp(rsg_context *h, size_t bytes);
 
 // spmv.cu
-int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
+int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
                   bool force_rebuild, SpmvPlan **out);
 void spmv_free_plan(SpmvPlan &p);
 template <typename TV, typename TX>
-int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
+int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
              const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 int row_partition(rsg_context *h, int m, int base, const int *rowptr, int ngpu, int balanced,
                   int *row_starts_host);
 
+// spmv_pipe.cu
+int pipe_num_variants();
+int pipe_build_plan(rsg_context *h, SpmvPlan &p);
+template <typename TV, typename TX>
+int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
+
 // levels.cu
-int tri_get_plan(rsg_context *h, int n, int base, const int *rowptr, const int *colidx,
+int tri_get_plan(rsg_context *h, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
                  bool force_rebuild, TriPlan **out);
 int tri_build_levels(rsg_context *h, TriPlan *p, int which);
 void tri_free_plan(TriPlan &p);

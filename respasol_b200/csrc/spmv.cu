@@ -16,216 +16,11 @@
 //   scalar    plain thread-per-row (fallback / cross-check)
 // TX is the vector / accumulation type, TV the stored-value type: (double,double) fp64,
 // (float,float) fp32, (float,double) the mixed variant.
-#include "rsg_internal.cuh"
+#include "spmv_device.cuh"
 
 #include <cub/block/block_scan.cuh>
 
 namespace rsg {
-
-// ------------------------------------------------------------------ streaming loads
-// HINT 0: ld.global.nc   1: + L1::no_allocate   2: + L2 evict_first policy
-template <int HINT> __device__ __forceinline__ int4 ld_stream(const int4 *p, uint64_t pol)
-{
-    int4 r;
-    if (HINT == 0) {
-        asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    } else if (HINT == 1) {
-        asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
-    } else {
-        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.s32 {%0,%1,%2,%3}, [%4], %5;"
-                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
-    }
-    return r;
-}
-template <int HINT> __device__ __forceinline__ float4 ld_stream(const float4 *p, uint64_t pol)
-{
-    int4 r = ld_stream<HINT>(reinterpret_cast<const int4 *>(p), pol);
-    return make_float4(__int_as_float(r.x), __int_as_float(r.y), __int_as_float(r.z), __int_as_float(r.w));
-}
-template <int HINT> __device__ __forceinline__ double2 ld_stream(const double2 *p, uint64_t pol)
-{
-    double2 r;
-    if (HINT == 0) {
-        asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
-    } else if (HINT == 1) {
-        asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
-    } else {
-        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;"
-                     : "=d"(r.x), "=d"(r.y) : "l"(p), "l"(pol));
-    }
-    return r;
-}
-__device__ __forceinline__ uint64_t make_evict_first_policy()
-{
-    uint64_t pol;
-    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
-    return pol;
-}
-
-// four consecutive stored values starting at an index that is a multiple of 4
-template <int HINT> __device__ __forceinline__ void ld_values4(const double *p, uint64_t pol, double (&v)[4])
-{
-    double2 a = ld_stream<HINT>(reinterpret_cast<const double2 *>(p), pol);
-    double2 b = ld_stream<HINT>(reinterpret_cast<const double2 *>(p) + 1, pol);
-    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
-}
-template <int HINT> __device__ __forceinline__ void ld_values4(const float *p, uint64_t pol, float (&v)[4])
-{
-    float4 a = ld_stream<HINT>(reinterpret_cast<const float4 *>(p), pol);
-    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
-}
-__device__ __forceinline__ void st_shared4(double *p, const double (&v)[4])
-{
-    reinterpret_cast<double2 *>(p)[0] = make_double2(v[0], v[1]);
-    reinterpret_cast<double2 *>(p)[1] = make_double2(v[2], v[3]);
-}
-__device__ __forceinline__ void st_shared4(float *p, const float (&v)[4])
-{
-    *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
-}
-
-// ------------------------------------------------------------------ entry staging
-// Products a_k * x[col_k] for the entries [k0,k1) go to s_prod[k - (k0 & ~3)].  VEC: whole
-// aligned quads use one 128-bit colidx load + 128/256 bits of values per thread, two quads in
-// flight per thread; the ragged head and tail quads are done with guarded scalar loads.
-template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
-__device__ __forceinline__ void stage_products(int k0, int k1, const int *__restrict__ colidx,
-                                               const TV *__restrict__ values, const TX *__restrict__ x,
-                                               int base, TX *s_prod, uint64_t pol)
-{
-    const int tid = threadIdx.x;
-    if (VEC) {
-        const int sb = k0 & ~3;
-        const int qf0 = (k0 + 3) >> 2, qf1 = k1 >> 2; // whole quads [qf0,qf1)
-        if (qf0 <= qf1) {
-            const int he = qf0 << 2, tb = qf1 << 2;
-            if (tid < 4) { // head
-                const int k = k0 + tid;
-                if (k < he) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
-            } else if (tid >= 32 && tid < 36) { // tail
-                const int k = tb + (tid - 32);
-                if (k < k1) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
-            }
-            for (int q = qf0 + tid; q < qf1; q += 2 * THREADS) {
-                const int qb = q + THREADS;
-                const bool hb = qb < qf1;
-                int4 ca, cb = make_int4(base, base, base, base);
-                TV va[4], vb[4] = {0, 0, 0, 0};
-                ca = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
-                ld_values4<HINT>(values + (q << 2), pol, va);
-                if (hb) {
-                    cb = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (qb << 2)), pol);
-                    ld_values4<HINT>(values + (qb << 2), pol, vb);
-                }
-                TX pa[4], pb[4];
-                pa[0] = __ldg(x + (ca.x - base)); pa[1] = __ldg(x + (ca.y - base));
-                pa[2] = __ldg(x + (ca.z - base)); pa[3] = __ldg(x + (ca.w - base));
-                if (hb) {
-                    pb[0] = __ldg(x + (cb.x - base)); pb[1] = __ldg(x + (cb.y - base));
-                    pb[2] = __ldg(x + (cb.z - base)); pb[3] = __ldg(x + (cb.w - base));
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) pa[j] *= (TX)va[j];
-                st_shared4(s_prod + ((q << 2) - sb), pa);
-                if (hb) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) pb[j] *= (TX)vb[j];
-                    st_shared4(s_prod + ((qb << 2) - sb), pb);
-                }
-            }
-        } else { // [k0,k1) lies inside one quad
-            const int k = k0 + tid;
-            if (k < k1) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
-        }
-    } else {
-        const int sb = k0 & ~3;
-        for (int k = k0 + tid; k < k1; k += THREADS)
-            s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
-    }
-}
-
-// CTA-wide sum of a_k*x[col_k] over [k0,k1), result valid in thread 0 (CTA-per-row path).
-template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
-__device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict__ colidx,
-                                          const TV *__restrict__ values, const TX *__restrict__ x,
-                                          int base, TX *s_red, uint64_t pol)
-{
-    const int tid = threadIdx.x;
-    TX acc = 0;
-    int ks = k0, ke = k1;
-    if (VEC) {
-        const int qf0 = (k0 + 3) >> 2, qf1 = k1 >> 2;
-        if (qf0 < qf1) {
-            ks = qf0 << 2; ke = qf1 << 2;
-            TX acc2 = 0;
-            for (int q = qf0 + tid; q < qf1; q += THREADS) {
-                int4 c = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
-                TV v[4];
-                ld_values4<HINT>(values + (q << 2), pol, v);
-                acc += (TX)v[0] * __ldg(x + (c.x - base));
-                acc2 += (TX)v[1] * __ldg(x + (c.y - base));
-                acc += (TX)v[2] * __ldg(x + (c.z - base));
-                acc2 += (TX)v[3] * __ldg(x + (c.w - base));
-            }
-            acc += acc2;
-            // ragged ends
-            for (int k = k0 + tid; k < ks; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
-            for (int k = ke + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
-        } else {
-            for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
-        }
-    } else {
-        for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    __syncthreads();
-    if ((tid & 31) == 0) s_red[tid >> 5] = acc;
-    __syncthreads();
-    TX tot = 0;
-    if (tid == 0)
-        for (int w = 0; w < THREADS / 32; ++w) tot += s_red[w];
-    __syncthreads();
-    return tot;
-}
-
-template <typename TX> __device__ __forceinline__ void store_y(TX *y, int r, TX sum, TX alpha, TX beta)
-{
-    y[r] = (beta == (TX)0) ? alpha * sum : alpha * sum + beta * y[r];
-}
-
-// rows [row_lo,row_lo+nrows) of the tile, entries already staged; G lanes per row
-template <typename TX, int THREADS, int G>
-__device__ __forceinline__ void reduce_rows(const TX *s_prod, const int *s_rp, int sb, int nrows, int row_glob,
-                                            TX *__restrict__ y, TX alpha, TX beta)
-{
-    const int tid = threadIdx.x;
-    if (G == 1) {
-        for (int i = tid; i < nrows; i += THREADS) {
-            const int a = s_rp[i] - sb, b = s_rp[i + 1] - sb;
-            TX s = 0;
-            for (int k = a; k < b; ++k) s += s_prod[k];
-            store_y(y, row_glob + i, s, alpha, beta);
-        }
-    } else {
-        constexpr int GROUPS = THREADS / G;
-        const int gid = tid / G, lane = tid % G;
-        const int iters = (nrows + GROUPS - 1) / GROUPS;
-        for (int it = 0; it < iters; ++it) {
-            const int i = it * GROUPS + gid;
-            TX s = 0;
-            if (i < nrows) {
-                const int a = s_rp[i] - sb, b = s_rp[i + 1] - sb;
-                for (int k = a + lane; k < b; k += G) s += s_prod[k];
-            }
-#pragma unroll
-            for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
-        }
-    }
-}
 
 // ------------------------------------------------------------------ row-block kernel
 template <int TILE> struct RowBlockShape {
@@ -292,6 +87,164 @@ spmv_rowblock_kernel(int base, const int *__restrict__ rowptr, const int *__rest
         cur = pe;
         if (cur < nr) __syncthreads();
     }
+}
+
+
+// ------------------------------------------------------------------ stream kernel (TMA-staged)
+// The dominant kernel.  The entries of a CTA tile are brought into shared memory RAW (colidx and
+// values, not products) by two 1-D bulk async copies (cp.async.bulk -> UBLKCP, completion on an
+// mbarrier): one elected thread issues the whole tile, so the bytes in flight per SM do not
+// depend on what the other threads are doing, and several CTAs per SM keep one tile loading
+// while another one reduces.  x is gathered in the REDUCTION phase: with one thread per row
+// (short rows) lane l of a warp reads x[col(r0+l, k)], which for banded/stencil patterns is a
+// contiguous run -- 2-3 cache lines per warp load instead of ~11 when gathering in entry order
+// (the L1 wavefront rate, ~1 line per cycle per SM, is what bounds an entry-order gather of a
+// 27-point stencil at ~3 TB/s).  A thread-per-row sum runs left to right like the oracle's.
+// Longer rows take 2..32 lanes each (shuffle reduction); a row beyond the staging capacity is
+// reduced CTA-per-row straight from global memory.
+// W: weight of a row in the tile partition (items = entries + W*rows <= TILE => rows <= TILE/W)
+template <int TILE, int W> struct StreamShape {
+    static constexpr int CAP = TILE + TILE / 8; // staged entries per pass
+    static constexpr int ROWS = TILE / W;       // rows per tile
+    template <typename TV> static constexpr size_t smem()
+    {
+        return (sizeof(TV) + sizeof(int)) * (size_t)(CAP + 8) + sizeof(int) * (size_t)(ROWS + 4) + 16;
+    }
+};
+
+template <typename TV, typename TX, int THREADS, int TILE, int W, int XH>
+__global__ void __launch_bounds__(THREADS, (TILE <= 2048 ? 6 : TILE <= 4096 ? 4 : 2) * (THREADS <= 256 ? 1 : 1))
+spmv_stream_kernel(int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
+                   const int2 *__restrict__ blk, int reduce_opt)
+{
+    typedef StreamShape<TILE, W> Shape;
+    constexpr int CAP = Shape::CAP;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    TV *s_val = reinterpret_cast<TV *>(smem_raw);                                   // CAP + 8
+    int *s_col = reinterpret_cast<int *>(s_val + CAP + 8);                          // CAP + 8
+    int *s_rp = s_col + CAP + 8;                                                    // ROWS + 1 (+ pad)
+    uint64_t *bar = reinterpret_cast<uint64_t *>(s_rp + ((Shape::ROWS + 4) & ~1)); // 8-byte aligned
+    __shared__ int s_maxlen;
+    const int tid = threadIdx.x;
+    const int2 c0 = blk[blockIdx.x], c1 = blk[blockIdx.x + 1];
+    const int r0 = c0.x, nr = c1.x - c0.x;
+    if (nr <= 0) return;
+    const uint64_t spol = make_evict_first_policy();
+    uint64_t xpol = 0;
+    if (XH) xpol = make_evict_last_policy();
+    // the first pass can be issued before the row pointers arrive when the whole tile fits
+    const int kb = c0.y, ke = c1.y; // zero-based entry range of the tile
+    const bool single = (ke - (kb & ~3)) <= CAP;
+    if (tid == 0) {
+        s_maxlen = 0;
+        mbar_init(bar, 1);
+    }
+    __syncthreads();
+    uint32_t parity = 0;
+    bool issued = false;
+    if (single) {
+        const int sb = kb & ~3, qe = ke & ~3;
+        if (tid == 0 && qe > sb) {
+            const uint32_t nq = (uint32_t)(qe - sb);
+            mbar_expect_tx(bar, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+            bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), bar, spol);
+            bulk_g2s(s_col, colidx + sb, nq * (uint32_t)sizeof(int), bar, spol);
+        }
+        issued = true;
+    }
+    {
+        int ml = 0;
+        for (int i = tid; i <= nr; i += THREADS) {
+            const int a = rowptr[r0 + i] - base;
+            s_rp[i] = a;
+            if (i < nr) ml = max(ml, rowptr[r0 + i + 1] - base - a);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) ml = max(ml, __shfl_xor_sync(0xffffffffu, ml, o));
+        if ((tid & 31) == 0 && ml > 0) atomicMax(&s_maxlen, ml);
+    }
+    __syncthreads();
+    const int maxlen = s_maxlen;
+    int cur = 0;
+    while (cur < nr) {
+        const int k0 = s_rp[cur];
+        const int sb = k0 & ~3;
+        int pe;
+        if (s_rp[nr] - sb <= CAP) {
+            pe = nr;
+        } else { // largest pe in [cur,nr] with s_rp[pe]-sb <= CAP
+            int lo = cur, hi = nr;
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (s_rp[mid] - sb <= CAP) lo = mid; else hi = mid - 1;
+            }
+            pe = lo;
+        }
+        if (pe == cur) { // this row alone exceeds the staging capacity: CTA-per-row
+            const TX tot = cta_row_sum<TV, TX, THREADS, 1, true>(k0, s_rp[cur + 1], colidx, values, x, base,
+                                                                 reinterpret_cast<TX *>(smem_raw), spol);
+            if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
+            cur += 1;
+            continue;
+        }
+        const int k1 = s_rp[pe];
+        const int qe = k1 & ~3;
+        if (!issued) {
+            if (tid == 0 && qe > sb) {
+                const uint32_t nq = (uint32_t)(qe - sb);
+                mbar_expect_tx(bar, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+                bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), bar, spol);
+                bulk_g2s(s_col, colidx + sb, nq * (uint32_t)sizeof(int), bar, spol);
+            }
+        }
+        issued = false;
+        { // ragged tail (< 4 entries) by plain loads
+            const int k = max(qe, sb) + tid;
+            if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
+        }
+        __syncthreads();
+        if (qe > sb) { mbar_wait(bar, parity); parity ^= 1; }
+        const int nrows = pe - cur;
+        int g = reduce_opt;
+        if (g == 0) { // row-length bin of this tile: lanes per row
+            const int avg = (k1 - k0) / nrows;
+            const int len = max(avg, maxlen >> 3);
+            g = len <= 40 ? 1 : len <= 80 ? 4 : len <= 160 ? 8 : len <= 320 ? 16 : 32;
+            while (g < 32 && nrows * g * 2 <= THREADS) g <<= 1; // few rows: spread them over the CTA
+            if (g == 2) g = (avg <= 40 && maxlen <= 64) ? 1 : 4;
+        }
+        const int *rp = s_rp + cur;
+        switch (g) {
+        case 1: reduce_rows_gather<TV, TX, THREADS, 1, XH, 16>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 2: reduce_rows_gather<TV, TX, THREADS, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 4: reduce_rows_gather<TV, TX, THREADS, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 8: reduce_rows_gather<TV, TX, THREADS, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 16: reduce_rows_gather<TV, TX, THREADS, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        default: reduce_rows_gather<TV, TX, THREADS, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        }
+        cur = pe;
+        if (cur < nr) __syncthreads();
+    }
+}
+
+// blk[b] = (first row of tile b, its zero-based entry offset); item coordinate = entries + w*rows
+__global__ void stream_partition_kernel(int m, int base, const int *__restrict__ rowptr, int tile, int w, int nblk, int2 *blk)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > nblk) return;
+    int r = m;
+    if (b < nblk) {
+        const int rp0 = rowptr[0];
+        const long long target = (long long)b * tile;
+        int lo = 0, hi = m;
+        while (lo < hi) {
+            const int mid = lo + ((hi - lo) >> 1);
+            if ((long long)(rowptr[mid] - rp0) + (long long)w * mid < target) lo = mid + 1; else hi = mid;
+        }
+        r = lo;
+    }
+    blk[b] = make_int2(r, rowptr[r] - base);
 }
 
 // first row r in [0,m] with (rowptr[r]-rowptr[0]) + r >= target  (merged-item coordinate)
@@ -481,25 +434,31 @@ struct Variant { int threads, tile; };
 static const Variant kVariants[] = {{256, 4096}, {128, 2048}, {256, 2048}, {512, 8192}, {128, 1024}};
 static const int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 static const int kMergeThreads = 256, kMergeIpt = 8;
+// stream kernel shapes (threads, entries+W*rows per CTA); W = kStreamW
+static const Variant kStreamVariants[] = {{256, 4096}, {128, 4096}, {128, 2048}, {256, 8192}, {512, 8192}, {256, 2048}};
+static const int kNumStreamVariants = (int)(sizeof(kStreamVariants) / sizeof(kStreamVariants[0]));
+static constexpr int kStreamW = 2;
 
 void spmv_free_plan(SpmvPlan &p)
 {
-    cudaFree(p.blk_row); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
+    cudaFree(p.blk_row); cudaFree(p.sblk); cudaFree(p.pdesc); cudaFree(p.rp0); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
     p = SpmvPlan();
 }
 
 static int plan_signature(const rsg_context *h)
 {
-    return h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW];
+    return h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW] +
+           h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD] * 7919 + h->opts[RSG_OPT_SPMV_REDUCE] * 104729;
 }
 
-int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx,
+int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
                   bool force_rebuild, SpmvPlan **out)
 {
     const int sig = plan_signature(h);
     for (size_t i = 0; i < h->spmv_plans.size(); ++i) {
         SpmvPlan &p = h->spmv_plans[i];
-        if (p.rowptr == rowptr && p.colidx == colidx && p.m == m && p.n == n && p.base == base && p.opt_sig == sig) {
+        if (p.rowptr == rowptr && p.colidx == colidx && p.m == m && p.n == n && p.nnz_hint == nnz_hint && p.base == base &&
+            p.opt_sig == sig) {
             if (!force_rebuild) { *out = &p; return RSG_OK; }
             spmv_free_plan(p);
             h->spmv_plans.erase(h->spmv_plans.begin() + (long)i);
@@ -511,7 +470,7 @@ int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, con
         h->spmv_plans.erase(h->spmv_plans.begin());
     }
     SpmvPlan p;
-    p.rowptr = rowptr; p.colidx = colidx; p.m = m; p.n = n; p.base = base; p.opt_sig = sig;
+    p.rowptr = rowptr; p.colidx = colidx; p.m = m; p.n = n; p.nnz_hint = nnz_hint; p.base = base; p.opt_sig = sig;
     cudaStream_t st = h->stream;
     RSG_CUDA_TRY(cudaMemsetAsync(h->scratch_i, 0, 4 * sizeof(int), st));
     if (m > 0) {
@@ -531,16 +490,19 @@ int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, con
 
     int algo = h->opts[RSG_OPT_SPMV_ALGO];
     int variant = h->opts[RSG_OPT_SPMV_VARIANT];
-    if (variant < 0 || variant >= kNumVariants) variant = 0;
-    p.variant = variant;
-    p.tile = kVariants[variant].tile;
+    const bool aligned = (((uintptr_t)colidx) & 15) == 0;
     if (algo == RSG_SPMV_AUTO) {
         // A row reduced by one CTA streams at one SM's share of the bandwidth (~1/148); past
         // roughly nnz/64 entries that single row outlasts the rest of the product: merge-path.
         const int cap = RowBlockShape<4096>::CAP;
         const long long skew = std::max<long long>(cap, (long long)p.nnz / 64);
-        algo = (p.max_row > skew) ? RSG_SPMV_MERGE : RSG_SPMV_ROWBLOCK;
+        algo = (p.max_row > skew) ? RSG_SPMV_MERGE : (aligned ? RSG_SPMV_PIPE : RSG_SPMV_ROWBLOCK);
     }
+    if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE) && !aligned) algo = RSG_SPMV_ROWBLOCK; // bulk copies need 16-byte aligned arrays
+    const int nvar = algo == RSG_SPMV_STREAM ? kNumStreamVariants : algo == RSG_SPMV_PIPE ? pipe_num_variants() : kNumVariants;
+    if (variant < 0 || variant >= nvar) variant = 0;
+    p.variant = variant;
+    p.tile = algo == RSG_SPMV_STREAM ? kStreamVariants[variant].tile : kVariants[variant].tile;
     p.algo = algo;
     const long long items = (long long)m + p.nnz;
     if (algo == RSG_SPMV_ROWBLOCK && m > 0) {
@@ -548,6 +510,15 @@ int spmv_get_plan(rsg_context *h, int m, int n, int base, const int *rowptr, con
         RSG_CUDA_TRY(cudaMalloc(&p.blk_row, sizeof(int) * ((size_t)p.nblk + 1)));
         p.bytes += sizeof(int) * ((size_t)p.nblk + 1);
         rowblock_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, rowptr, p.tile, p.nblk, p.blk_row);
+        h->launches++;
+    } else if (algo == RSG_SPMV_PIPE && m > 0) {
+        RSG_TRY(pipe_build_plan(h, p));
+    } else if (algo == RSG_SPMV_STREAM && m > 0) {
+        const long long witems = (long long)kStreamW * m + p.nnz;
+        p.nblk = (int)((witems + p.tile - 1) / p.tile);
+        RSG_CUDA_TRY(cudaMalloc(&p.sblk, sizeof(int2) * ((size_t)p.nblk + 1)));
+        p.bytes += sizeof(int2) * ((size_t)p.nblk + 1);
+        stream_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, base, rowptr, p.tile, kStreamW, p.nblk, p.sblk);
         h->launches++;
     } else if (algo == RSG_SPMV_MERGE && m > 0) {
         p.merge_items = kMergeThreads * kMergeIpt;
@@ -605,6 +576,42 @@ static int launch_rowblock(rsg_context *h, const SpmvPlan *p, bool vec, const TV
     }
 }
 
+template <typename TV, typename TX, int THREADS, int TILE>
+static int launch_stream_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    const size_t smem = StreamShape<TILE, kStreamW>::template smem<TV>();
+    const int xh = h->opts[RSG_OPT_SPMV_X_HINT];
+    static bool configured = false; // per instantiation
+    if (!configured) {
+        RSG_CUDA_TRY(cudaFuncSetAttribute(spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 0>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RSG_CUDA_TRY(cudaFuncSetAttribute(spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 1>,
+                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    if (xh)
+        spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 1><<<p->nblk, THREADS, smem, h->stream>>>(
+            p->base, p->rowptr, p->colidx, values, x, y, alpha, beta, p->sblk, h->opts[RSG_OPT_SPMV_REDUCE]);
+    else
+        spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 0><<<p->nblk, THREADS, smem, h->stream>>>(
+            p->base, p->rowptr, p->colidx, values, x, y, alpha, beta, p->sblk, h->opts[RSG_OPT_SPMV_REDUCE]);
+    h->launches++;
+    return RSG_OK;
+}
+
+template <typename TV, typename TX>
+static int launch_stream(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    switch (p->variant) {
+    case 1: return launch_stream_one<TV, TX, 128, 4096>(h, p, values, alpha, x, beta, y);
+    case 2: return launch_stream_one<TV, TX, 128, 2048>(h, p, values, alpha, x, beta, y);
+    case 3: return launch_stream_one<TV, TX, 256, 8192>(h, p, values, alpha, x, beta, y);
+    case 4: return launch_stream_one<TV, TX, 512, 8192>(h, p, values, alpha, x, beta, y);
+    case 5: return launch_stream_one<TV, TX, 256, 2048>(h, p, values, alpha, x, beta, y);
+    default: return launch_stream_one<TV, TX, 256, 4096>(h, p, values, alpha, x, beta, y);
+    }
+}
+
 template <typename TV, typename TX>
 static int launch_merge(rsg_context *h, const SpmvPlan *p, bool vec, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
 {
@@ -653,13 +660,13 @@ static int set_x_persistence(rsg_context *h, const void *x, size_t bytes)
 }
 
 template <typename TV, typename TX>
-int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx, const TV *values,
-             TX alpha, const TX *x, TX beta, TX *y)
+int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
+             const TV *values, TX alpha, const TX *x, TX beta, TX *y)
 {
     if (m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || (m > 0 && !y)) return RSG_BAD_ARG;
     if (m == 0) return RSG_OK;
     SpmvPlan *p = nullptr;
-    RSG_TRY(spmv_get_plan(h, m, n, base, rowptr, colidx, false, &p));
+    RSG_TRY(spmv_get_plan(h, m, n, nnz_hint, base, rowptr, colidx, false, &p));
     if (p->nnz > 0 && (!colidx || !values || !x)) return RSG_BAD_ARG;
     h->last_spmv_algo = p->algo;
     h->last_spmv_maxrow = p->max_row;
@@ -669,6 +676,15 @@ int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const in
     case RSG_SPMV_ROWBLOCK:
         h->last_spmv_blocks = p->nblk;
         RSG_TRY((launch_rowblock<TV, TX>(h, p, vec, values, alpha, x, beta, y)));
+        break;
+    case RSG_SPMV_PIPE:
+        if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays
+        RSG_TRY((pipe_launch<TV, TX>(h, p, values, alpha, x, beta, y)));
+        break;
+    case RSG_SPMV_STREAM:
+        if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays
+        h->last_spmv_blocks = p->nblk;
+        RSG_TRY((launch_stream<TV, TX>(h, p, values, alpha, x, beta, y)));
         break;
     case RSG_SPMV_MERGE:
         h->last_spmv_blocks = p->ntiles;
@@ -698,11 +714,11 @@ int spmv_run(rsg_context *h, int m, int n, int base, const int *rowptr, const in
     return RSG_OK;
 }
 
-template int spmv_run<double, double>(rsg_context *, int, int, int, const int *, const int *, const double *, double,
+template int spmv_run<double, double>(rsg_context *, int, int, int, int, const int *, const int *, const double *, double,
                                       const double *, double, double *);
-template int spmv_run<float, float>(rsg_context *, int, int, int, const int *, const int *, const float *, float,
+template int spmv_run<float, float>(rsg_context *, int, int, int, int, const int *, const int *, const float *, float,
                                     const float *, float, float *);
-template int spmv_run<float, double>(rsg_context *, int, int, int, const int *, const int *, const float *, double,
+template int spmv_run<float, double>(rsg_context *, int, int, int, int, const int *, const int *, const float *, double,
                                      const double *, double, double *);
 
 int row_partition(rsg_context *h, int m, int base, const int *rowptr, int ngpu, int balanced, int *row_starts_host)

@@ -1,0 +1,376 @@
+// spmv_device.cuh -- device helpers shared by the SpMV kernels (spmv.cu, spmv_pipe.cu):
+// streaming / gather loads with cache hints, mbarrier + 1-D bulk-copy (TMA) wrappers, the
+// staging and row-reduction building blocks.
+#pragma once
+
+#include "rsg_internal.cuh"
+
+namespace rsg {
+
+// ------------------------------------------------------------------ streaming loads
+// HINT 0: ld.global.nc   1: + L1::no_allocate   2: + L2 evict_first policy
+template <int HINT> __device__ __forceinline__ int4 ld_stream(const int4 *p, uint64_t pol)
+{
+    int4 r;
+    if (HINT == 0) {
+        asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    } else if (HINT == 1) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.s32 {%0,%1,%2,%3}, [%4], %5;"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+    }
+    return r;
+}
+template <int HINT> __device__ __forceinline__ float4 ld_stream(const float4 *p, uint64_t pol)
+{
+    int4 r = ld_stream<HINT>(reinterpret_cast<const int4 *>(p), pol);
+    return make_float4(__int_as_float(r.x), __int_as_float(r.y), __int_as_float(r.z), __int_as_float(r.w));
+}
+template <int HINT> __device__ __forceinline__ double2 ld_stream(const double2 *p, uint64_t pol)
+{
+    double2 r;
+    if (HINT == 0) {
+        asm volatile("ld.global.nc.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    } else if (HINT == 1) {
+        asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    } else {
+        asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.f64 {%0,%1}, [%2], %3;"
+                     : "=d"(r.x), "=d"(r.y) : "l"(p), "l"(pol));
+    }
+    return r;
+}
+__device__ __forceinline__ uint64_t make_evict_first_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+
+// four consecutive stored values starting at an index that is a multiple of 4
+template <int HINT> __device__ __forceinline__ void ld_values4(const double *p, uint64_t pol, double (&v)[4])
+{
+    double2 a = ld_stream<HINT>(reinterpret_cast<const double2 *>(p), pol);
+    double2 b = ld_stream<HINT>(reinterpret_cast<const double2 *>(p) + 1, pol);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+template <int HINT> __device__ __forceinline__ void ld_values4(const float *p, uint64_t pol, float (&v)[4])
+{
+    float4 a = ld_stream<HINT>(reinterpret_cast<const float4 *>(p), pol);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+}
+__device__ __forceinline__ void st_shared4(double *p, const double (&v)[4])
+{
+    reinterpret_cast<double2 *>(p)[0] = make_double2(v[0], v[1]);
+    reinterpret_cast<double2 *>(p)[1] = make_double2(v[2], v[3]);
+}
+__device__ __forceinline__ void st_shared4(float *p, const float (&v)[4])
+{
+    *reinterpret_cast<float4 *>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+// ------------------------------------------------------------------ entry staging
+// Products a_k * x[col_k] for the entries [k0,k1) go to s_prod[k - (k0 & ~3)].  VEC: whole
+// aligned quads use one 128-bit colidx load + 128/256 bits of values per thread, two quads in
+// flight per thread; the ragged head and tail quads are done with guarded scalar loads.
+template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
+__device__ __forceinline__ void stage_products(int k0, int k1, const int *__restrict__ colidx,
+                                               const TV *__restrict__ values, const TX *__restrict__ x,
+                                               int base, TX *s_prod, uint64_t pol)
+{
+    const int tid = threadIdx.x;
+    if (VEC) {
+        const int sb = k0 & ~3;
+        const int qf0 = (k0 + 3) >> 2, qf1 = k1 >> 2; // whole quads [qf0,qf1)
+        if (qf0 <= qf1) {
+            const int he = qf0 << 2, tb = qf1 << 2;
+            if (tid < 4) { // head
+                const int k = k0 + tid;
+                if (k < he) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+            } else if (tid >= 32 && tid < 36) { // tail
+                const int k = tb + (tid - 32);
+                if (k < k1) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+            }
+            for (int q = qf0 + tid; q < qf1; q += 2 * THREADS) {
+                const int qb = q + THREADS;
+                const bool hb = qb < qf1;
+                int4 ca, cb = make_int4(base, base, base, base);
+                TV va[4], vb[4] = {0, 0, 0, 0};
+                ca = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
+                ld_values4<HINT>(values + (q << 2), pol, va);
+                if (hb) {
+                    cb = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (qb << 2)), pol);
+                    ld_values4<HINT>(values + (qb << 2), pol, vb);
+                }
+                TX pa[4], pb[4];
+                pa[0] = __ldg(x + (ca.x - base)); pa[1] = __ldg(x + (ca.y - base));
+                pa[2] = __ldg(x + (ca.z - base)); pa[3] = __ldg(x + (ca.w - base));
+                if (hb) {
+                    pb[0] = __ldg(x + (cb.x - base)); pb[1] = __ldg(x + (cb.y - base));
+                    pb[2] = __ldg(x + (cb.z - base)); pb[3] = __ldg(x + (cb.w - base));
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) pa[j] *= (TX)va[j];
+                st_shared4(s_prod + ((q << 2) - sb), pa);
+                if (hb) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) pb[j] *= (TX)vb[j];
+                    st_shared4(s_prod + ((qb << 2) - sb), pb);
+                }
+            }
+        } else { // [k0,k1) lies inside one quad
+            const int k = k0 + tid;
+            if (k < k1) s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+        }
+    } else {
+        const int sb = k0 & ~3;
+        for (int k = k0 + tid; k < k1; k += THREADS)
+            s_prod[k - sb] = (TX)values[k] * __ldg(x + (colidx[k] - base));
+    }
+}
+
+// CTA-wide sum of a_k*x[col_k] over [k0,k1), result valid in thread 0 (CTA-per-row path).
+template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
+__device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict__ colidx,
+                                          const TV *__restrict__ values, const TX *__restrict__ x,
+                                          int base, TX *s_red, uint64_t pol)
+{
+    const int tid = threadIdx.x;
+    TX acc = 0;
+    int ks = k0, ke = k1;
+    if (VEC) {
+        const int qf0 = (k0 + 3) >> 2, qf1 = k1 >> 2;
+        if (qf0 < qf1) {
+            ks = qf0 << 2; ke = qf1 << 2;
+            TX acc2 = 0;
+            for (int q = qf0 + tid; q < qf1; q += THREADS) {
+                int4 c = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
+                TV v[4];
+                ld_values4<HINT>(values + (q << 2), pol, v);
+                acc += (TX)v[0] * __ldg(x + (c.x - base));
+                acc2 += (TX)v[1] * __ldg(x + (c.y - base));
+                acc += (TX)v[2] * __ldg(x + (c.z - base));
+                acc2 += (TX)v[3] * __ldg(x + (c.w - base));
+            }
+            acc += acc2;
+            // ragged ends
+            for (int k = k0 + tid; k < ks; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+            for (int k = ke + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+        } else {
+            for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+        }
+    } else {
+        for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __syncthreads();
+    if ((tid & 31) == 0) s_red[tid >> 5] = acc;
+    __syncthreads();
+    TX tot = 0;
+    if (tid == 0)
+        for (int w = 0; w < THREADS / 32; ++w) tot += s_red[w];
+    __syncthreads();
+    return tot;
+}
+
+template <typename TX> __device__ __forceinline__ void store_y(TX *y, int r, TX sum, TX alpha, TX beta)
+{
+    y[r] = (beta == (TX)0) ? alpha * sum : alpha * sum + beta * y[r];
+}
+
+// rows [row_lo,row_lo+nrows) of the tile, entries already staged; G lanes per row
+template <typename TX, int THREADS, int G>
+__device__ __forceinline__ void reduce_rows(const TX *s_prod, const int *s_rp, int sb, int nrows, int row_glob,
+                                            TX *__restrict__ y, TX alpha, TX beta)
+{
+    const int tid = threadIdx.x;
+    if (G == 1) {
+        for (int i = tid; i < nrows; i += THREADS) {
+            const int a = s_rp[i] - sb, b = s_rp[i + 1] - sb;
+            TX s = 0;
+            for (int k = a; k < b; ++k) s += s_prod[k];
+            store_y(y, row_glob + i, s, alpha, beta);
+        }
+    } else {
+        constexpr int GROUPS = THREADS / G;
+        const int gid = tid / G, lane = tid % G;
+        const int iters = (nrows + GROUPS - 1) / GROUPS;
+        for (int it = 0; it < iters; ++it) {
+            const int i = it * GROUPS + gid;
+            TX s = 0;
+            if (i < nrows) {
+                const int a = s_rp[i] - sb, b = s_rp[i + 1] - sb;
+                for (int k = a + lane; k < b; k += G) s += s_prod[k];
+            }
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ mbarrier / bulk copy / x gather
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+// 1-D bulk copy global -> shared; bytes % 16 == 0, both addresses 16-byte aligned
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar, uint64_t pol)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(smem_u32(dst)), "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+__device__ __forceinline__ uint64_t make_evict_last_policy()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+// x gather: read-only path (L1-allocating); XH = 1 adds an L2 evict_last hint so the streamed
+// matrix does not push x out of L2
+// (asm volatile on purpose: __ldg is an invariant load the compiler may sink past the barrier
+// that separates "issue all gathers" from "use them")
+template <int XH> __device__ __forceinline__ double ld_x(const double *p, uint64_t pol)
+{
+    double r;
+    if (XH == 0) asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(r) : "l"(p));
+    else asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
+    return r;
+}
+template <int XH> __device__ __forceinline__ float ld_x(const float *p, uint64_t pol)
+{
+    float r;
+    if (XH == 0) asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    else asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
+    return r;
+}
+
+// NOTE on code shape (measured with cuobjdump): ptxas only keeps many gathers in flight when
+// (a) the kernel states its residency (__launch_bounds__(T, minBlocks)) -- otherwise it aims at 32
+// registers and sinks every load next to its use -- and (b) the loads are NOT predicated (there
+// are 7 predicate registers): out-of-range slots therefore re-read the row's last entry (same
+// cache line as the previous load) and their product is dropped by a select.
+
+// sum over the staged entries k, k+G, k+2G, ... < e of s_val[.] * x[s_col[.]], in that order.
+// Software-pipelined: the x gathers of batch i+1 (B per lane) are issued before batch i is
+// consumed, so up to 2B independent loads are in flight per lane.
+template <typename TV, typename TX, int G, int B, int XH>
+__device__ __forceinline__ TX row_dot(const TV *s_val, const int *s_col, int k, int e, const TX *xb, uint64_t xpol)
+{
+    TX s = 0;
+    if (k >= e) return s;
+    const int last = k + ((e - 1 - k) / G) * G; // this lane's last entry
+    TX xa[B];
+#pragma unroll
+    for (int u = 0; u < B; ++u) xa[u] = ld_x<XH>(xb + s_col[min(k + u * G, last)], xpol);
+    while (k <= last) {
+        const int kn = k + B * G;
+        TX xn[B];
+        if (kn <= last) {
+#pragma unroll
+            for (int u = 0; u < B; ++u) xn[u] = ld_x<XH>(xb + s_col[min(kn + u * G, last)], xpol);
+        }
+#pragma unroll
+        for (int u = 0; u < B; ++u) {
+            const TX p = (TX)s_val[min(k + u * G, last)] * xa[u];
+            s += (k + u * G <= last) ? p : (TX)0;
+        }
+#pragma unroll
+        for (int u = 0; u < B; ++u) xa[u] = xn[u];
+        k = kn;
+    }
+    return s;
+}
+
+// one thread, one row, every gather of the row in flight at once: the first B1 entries are
+// issued back to back before any of them is used; a longer row continues with the pipelined
+// loop.  Left-to-right summation like the oracle (adding +0 for the unused slots changes nothing).
+template <typename TV, typename TX, int B1, int XH>
+__device__ __forceinline__ TX row_dot_oneshot(const TV *s_val, const int *s_col, int k, int e, const TX *xb, uint64_t xpol)
+{
+    TX s = 0;
+    if (k >= e) return s;
+    const int last = e - 1;
+    TX xa[B1];
+#pragma unroll
+    for (int u = 0; u < B1; ++u) xa[u] = ld_x<XH>(xb + s_col[min(k + u, last)], xpol);
+#pragma unroll
+    for (int u = 0; u < B1; ++u) {
+        const TX p = (TX)s_val[min(k + u, last)] * xa[u];
+        s += (k + u <= last) ? p : (TX)0;
+    }
+    k += B1;
+    if (k <= last) { // rest of a long row: pipelined batches of 8, same order
+        TX xr[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) xr[u] = ld_x<XH>(xb + s_col[min(k + u, last)], xpol);
+        while (k <= last) {
+            const int kn = k + 8;
+            TX xn[8];
+            if (kn <= last) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) xn[u] = ld_x<XH>(xb + s_col[min(kn + u, last)], xpol);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const TX p = (TX)s_val[min(k + u, last)] * xr[u];
+                s += (k + u <= last) ? p : (TX)0;
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) xr[u] = xn[u];
+            k = kn;
+        }
+    }
+    return s;
+}
+
+// rows of one pass out of the staged raw entries; G lanes per row.  G == 1 keeps the oracle's
+// summation order (left to right, multiply then add).  B1 > 0: whole-row-in-flight gathers.
+template <typename TV, typename TX, int THREADS, int G, int XH, int B1 = 0>
+__device__ __forceinline__ void reduce_rows_gather(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
+                                                   int row_glob, const TX *__restrict__ x, int base, uint64_t xpol,
+                                                   TX *__restrict__ y, TX alpha, TX beta)
+{
+    const int tid = threadIdx.x;
+    const TX *xb = x - base;
+    asm volatile("" : "+l"(xb)); // opaque: keeps the gather address a single IMAD.WIDE (col, 8, xb)
+    if (G == 1) {
+        for (int i = tid; i < nrows; i += THREADS) {
+            TX s;
+            if (B1 > 0) s = row_dot_oneshot<TV, TX, (B1 > 0 ? B1 : 8), XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
+            else s = row_dot<TV, TX, 1, 8, XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
+            store_y(y, row_glob + i, s, alpha, beta);
+        }
+    } else {
+        constexpr int GROUPS = THREADS / G;
+        const int gid = tid / G, lane = tid % G;
+        const int iters = (nrows + GROUPS - 1) / GROUPS;
+        for (int it = 0; it < iters; ++it) {
+            const int i = it * GROUPS + gid;
+            TX s = 0;
+            if (i < nrows) s = row_dot<TV, TX, G, (G <= 4 ? 8 : 4), XH>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb, xpol);
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
+        }
+    }
+}
+
+} // namespace rsg

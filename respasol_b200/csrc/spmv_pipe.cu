@@ -1,0 +1,313 @@
+// spmv_pipe.cu -- the pipelined SpMV kernel (RSG_SPMV_PIPE): persistent CTAs, each walking its
+// tiles through a ring of STAGES shared-memory buffers.  Replaces the cusparseSpMV call of the
+// reference harness (/root/reference/GPU/spmv.cu:174-186) for row lengths without extreme skew.
+//
+// One elected thread is the producer: for the tile S-1 ahead of the one being reduced it issues
+// three 1-D bulk async copies (cp.async.bulk -> UBLKCP): the row-pointer slice, colidx and
+// values, all completing on that stage's mbarrier.  The bytes in flight per SM are therefore
+// (STAGES-1) tiles per CTA at all times, independent of what the consumer threads do; consumers
+// wait on the mbarrier, reduce the tile (thread-, sub-warp- or warp-per-row, x gathered in
+// row order so that neighbouring rows of banded matrices read neighbouring x), store y, meet at
+// one block barrier and hand the buffer back to the producer.  Nothing on the critical path of
+// a tile depends on a global load issued by a consumer except the x gathers themselves.
+//
+// Plan (built on device by pipe_build_plan): a zero-based, padded copy of the row pointers (so
+// that any slice can be bulk-copied from a 16-byte aligned address) and one descriptor per tile
+// (first row, first entry, longest row).  Tiles that do not fit a stage (a row longer than the
+// tile slack) take a synchronous multi-pass path; a row longer than a whole stage is reduced
+// CTA-per-row straight from global memory.
+#include "spmv_device.cuh"
+
+namespace rsg {
+
+template <typename TV, int CAPE, int ROWS> struct PipeStage {
+    static constexpr size_t val_off = 0;
+    static constexpr size_t col_off = sizeof(TV) * (size_t)(CAPE + 8);
+    static constexpr size_t rp_off = col_off + sizeof(int) * (size_t)(CAPE + 8);
+    static constexpr size_t bytes = (rp_off + sizeof(int) * (size_t)(ROWS + 8) + 127) & ~(size_t)127;
+};
+
+struct PipeMeta { // written by the producer, read by everybody after the mbarrier wait
+    int r0, nr, k0, k1; // rows [r0,r0+nr), zero-based entries [k0,k1)
+    int maxlen, staged_end; // entries [k0&~3, staged_end) arrived by bulk copy (0: nothing staged)
+    int rp_shift, pad;      // s_rp[rp_shift + i] = zero-based start of row r0+i
+};
+
+template <typename TV, typename TX, int THREADS, int CAPE, int ROWS, int STAGES, int XH, int B1, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+spmv_pipe_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
+                 const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
+                 int ntiles, int nnz_end, int reduce_opt)
+{
+    typedef PipeStage<TV, CAPE, ROWS> Stage;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t s_full[STAGES];
+    __shared__ __align__(8) uint64_t s_aux;
+    __shared__ PipeMeta s_meta[STAGES];
+    const int tid = threadIdx.x;
+    const uint64_t spol = make_evict_first_policy();
+    uint64_t xpol = 0;
+    if (XH) xpol = make_evict_last_policy();
+
+    auto issue = [&](int t, int s) { // producer: tile t -> stage s
+        const int4 d0 = desc[t], d1 = desc[t + 1];
+        unsigned char *sp = smem_raw + (size_t)s * Stage::bytes;
+        PipeMeta mt;
+        mt.r0 = d0.x; mt.nr = d1.x - d0.x; mt.k0 = d0.y; mt.k1 = d1.y; mt.maxlen = d0.z; mt.pad = 0;
+        const int ra = mt.r0 & ~3;
+        mt.rp_shift = mt.r0 - ra;
+        const uint32_t nrp = (uint32_t)((mt.rp_shift + mt.nr + 1 + 3) & ~3);
+        const int sb = mt.k0 & ~3;
+        // whole quads only; the last quad may reach into the next tile's entries (valid memory)
+        // but never past the end of the arrays
+        int qe = min((mt.k1 + 3) & ~3, nnz_end & ~3);
+        const bool fits = (mt.k1 - sb) <= CAPE && qe > sb;
+        if (!fits) qe = sb;
+        mt.staged_end = fits ? qe : 0;
+        s_meta[s] = mt;
+        const uint32_t nq = (uint32_t)(qe - sb);
+        mbar_expect_tx(&s_full[s], nrp * 4u + nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+        bulk_g2s(sp + Stage::rp_off, rp0 + ra, nrp * 4u, &s_full[s], spol);
+        if (nq) {
+            bulk_g2s(sp + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full[s], spol);
+            bulk_g2s(sp + Stage::col_off, colidx + sb, nq * 4u, &s_full[s], spol);
+        }
+    };
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
+        mbar_init(&s_aux, 1);
+    }
+    __syncthreads();
+    // a contiguous run of tiles per CTA: consecutive tiles of a banded matrix share x lines (L1)
+    const int t_begin = (int)(((long long)ntiles * blockIdx.x) / gridDim.x);
+    const int t_end = (int)(((long long)ntiles * (blockIdx.x + 1)) / gridDim.x);
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES - 1; ++s) {
+            const int t = t_begin + s;
+            if (t < t_end) issue(t, s);
+        }
+    }
+    uint32_t aux_parity = 0;
+    int it = 0;
+    for (int t = t_begin; t < t_end; ++t, ++it) {
+        const int s = it % STAGES;
+        if (tid == 0) { // keep STAGES-1 tiles in flight: the buffer freed by the previous iteration
+            const int tn = t + (STAGES - 1);
+            if (tn < t_end) issue(tn, (it + STAGES - 1) % STAGES);
+        }
+        mbar_wait(&s_full[s], (uint32_t)((it / STAGES) & 1));
+        unsigned char *sp = smem_raw + (size_t)s * Stage::bytes;
+        TV *s_val = reinterpret_cast<TV *>(sp + Stage::val_off);
+        int *s_col = reinterpret_cast<int *>(sp + Stage::col_off);
+        const PipeMeta mt = s_meta[s];
+        const int *s_rp = reinterpret_cast<const int *>(sp + Stage::rp_off) + mt.rp_shift;
+        const int nr = mt.nr, r0 = mt.r0;
+        int cur = 0;
+        bool staged = mt.staged_end > 0;
+        while (cur < nr) {
+            const int k0 = s_rp[cur];
+            const int sb = k0 & ~3;
+            int pe, k1;
+            if (staged) {
+                pe = nr; k1 = mt.k1;
+                if (mt.staged_end < k1) { // only the last tile of a matrix whose entry count is not a multiple of 4
+                    const int k = mt.staged_end + tid;
+                    if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
+                    __syncthreads();
+                }
+            } else { // synchronous multi-pass path for a tile that does not fit one stage
+                if (s_rp[nr] - sb <= CAPE) {
+                    pe = nr;
+                } else { // largest pe in [cur,nr] with s_rp[pe]-sb <= CAPE
+                    int lo = cur, hi = nr;
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) >> 1;
+                        if (s_rp[mid] - sb <= CAPE) lo = mid; else hi = mid - 1;
+                    }
+                    pe = lo;
+                }
+                if (pe == cur) { // this row alone exceeds a stage: CTA-per-row from global memory
+                    const TX tot = cta_row_sum<TV, TX, THREADS, 1, true>(k0, s_rp[cur + 1], colidx, values, x, base,
+                                                                         reinterpret_cast<TX *>(s_val), spol);
+                    if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
+                    cur += 1;
+                    continue;
+                }
+                k1 = s_rp[pe];
+                const int qe = k1 & ~3;
+                if (tid == 0 && qe > sb) {
+                    const uint32_t nq = (uint32_t)(qe - sb);
+                    mbar_expect_tx(&s_aux, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+                    bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), &s_aux, spol);
+                    bulk_g2s(s_col, colidx + sb, nq * 4u, &s_aux, spol);
+                }
+                {
+                    const int k = max(qe, sb) + tid;
+                    if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
+                }
+                __syncthreads();
+                if (qe > sb) { mbar_wait(&s_aux, aux_parity); aux_parity ^= 1; }
+            }
+            const int nrows = pe - cur;
+            int g = reduce_opt;
+            if (g == 0) { // lanes per row from the tile's row-length statistics
+                const int avg = (k1 - k0) / nrows;
+                const int len = max(avg, mt.maxlen >> 3);
+                g = len <= 40 ? 1 : len <= 80 ? 4 : len <= 160 ? 8 : len <= 320 ? 16 : 32;
+                while (g < 32 && nrows * g * 2 <= THREADS) g <<= 1; // few rows: spread them over the CTA
+                if (g == 2) g = (avg <= 40 && mt.maxlen <= 64) ? 1 : 4;
+            }
+            const int *rp = s_rp + cur;
+            switch (g) {
+            case 1: reduce_rows_gather<TV, TX, THREADS, 1, XH, B1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 2: reduce_rows_gather<TV, TX, THREADS, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 4: reduce_rows_gather<TV, TX, THREADS, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 8: reduce_rows_gather<TV, TX, THREADS, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 16: reduce_rows_gather<TV, TX, THREADS, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            default: reduce_rows_gather<TV, TX, THREADS, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            }
+            cur = pe;
+            staged = false;
+            if (cur < nr) __syncthreads();
+        }
+        __syncthreads(); // every thread is done with stage s: the producer may refill it
+    }
+}
+
+// desc[b] = (first row, its zero-based entry offset, longest row of the tile, 0); item coordinate
+// = entries + w*rows, so a tile holds at most tile/w rows and tile + (its last row) entries.
+__global__ void pipe_partition_kernel(int m, int base, const int *__restrict__ rowptr, int tile, int w, int ntiles, int4 *desc)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > ntiles) return;
+    int r = m;
+    if (b < ntiles) {
+        const int rp0 = rowptr[0];
+        const long long target = (long long)b * tile;
+        int lo = 0, hi = m;
+        while (lo < hi) {
+            const int mid = lo + ((hi - lo) >> 1);
+            if ((long long)(rowptr[mid] - rp0) + (long long)w * mid < target) lo = mid + 1; else hi = mid;
+        }
+        r = lo;
+    }
+    desc[b] = make_int4(r, rowptr[r] - base, 0, 0);
+}
+
+// one warp per tile: longest row -> desc[b].z
+__global__ void pipe_maxlen_kernel(int ntiles, int base, const int *__restrict__ rowptr, int4 *desc)
+{
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (b >= ntiles) return;
+    const int r0 = desc[b].x, r1 = desc[b + 1].x;
+    int ml = 0;
+    for (int r = r0 + lane; r < r1; r += 32) ml = max(ml, rowptr[r + 1] - rowptr[r]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ml = max(ml, __shfl_xor_sync(0xffffffffu, ml, o));
+    if (lane == 0) desc[b].z = ml;
+}
+
+// zero-based copy of the row pointers, padded to a multiple of 4 (+4) with the end offset
+__global__ void pipe_rowptr_copy_kernel(int m, int padded, int base, const int *__restrict__ rowptr, int *__restrict__ rp0)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= padded) return;
+    rp0[i] = rowptr[min(i, m)] - base;
+}
+
+// ------------------------------------------------------------------ host side
+struct PipeVariant { int threads, cape, rows, stages; };
+static const PipeVariant kPipeVariants[] = {
+    {128, 4352, 512, 2}, {512, 4352, 512, 2}, {64, 2304, 512, 2}, {256, 4352, 512, 2},
+    {256, 8704, 1024, 2}, {96, 3456, 768, 2}, {512, 8704, 1024, 2}, {1024, 8704, 1024, 2},
+};
+static const int kNumPipeVariants = (int)(sizeof(kPipeVariants) / sizeof(kPipeVariants[0]));
+
+int pipe_num_variants() { return kNumPipeVariants; }
+
+int pipe_build_plan(rsg_context *h, SpmvPlan &p)
+{
+    cudaStream_t st = h->stream;
+    const PipeVariant &v = kPipeVariants[p.variant];
+    const int m = p.m;
+    // tile: about one row per thread (rows_per_thread option scales it), within the stage capacity
+    const int tmax = v.cape * 8 / 9;
+    const int w = (tmax + v.rows - 1) / v.rows;
+    const double avg = m > 0 ? (double)p.nnz / m : 0.0;
+    int rpt = h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD];
+    if (rpt <= 0) rpt = 1;
+    int lanes = h->opts[RSG_OPT_SPMV_REDUCE]; // forced lanes per row: size the tile for threads/lanes rows
+    if (lanes < 1 || lanes > 32) lanes = 1;
+    long long want = (long long)((avg + w) * (v.threads / lanes) * rpt + 0.5);
+    int tile = (int)std::min<long long>(tmax, std::max<long long>(want, 512));
+    if (h->opts[RSG_OPT_SPMV_LONG_ROW] > 0) tile = std::min(tmax, std::max(64, h->opts[RSG_OPT_SPMV_LONG_ROW]));
+    p.tile = tile;
+    const long long items = (long long)w * m + p.nnz;
+    p.nblk = (int)std::max<long long>(1, (items + tile - 1) / tile);
+    p.rp0_len = ((m + 1 + 3) & ~3) + 4;
+    RSG_CUDA_TRY(cudaMalloc(&p.pdesc, sizeof(int4) * ((size_t)p.nblk + 1)));
+    RSG_CUDA_TRY(cudaMalloc(&p.rp0, sizeof(int) * (size_t)p.rp0_len));
+    p.bytes += sizeof(int4) * ((size_t)p.nblk + 1) + sizeof(int) * (size_t)p.rp0_len;
+    pipe_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, p.base, p.rowptr, tile, w, p.nblk, p.pdesc);
+    pipe_maxlen_kernel<<<(p.nblk * 32 + 255) / 256, 256, 0, st>>>(p.nblk, p.base, p.rowptr, p.pdesc);
+    pipe_rowptr_copy_kernel<<<(p.rp0_len + 255) / 256, 256, 0, st>>>(m, p.rp0_len, p.base, p.rowptr, p.rp0);
+    h->launches += 3;
+    RSG_CUDA_TRY(cudaGetLastError());
+    return RSG_OK;
+}
+
+template <typename TV, typename TX, int THREADS, int CAPE, int ROWS, int STAGES>
+static int pipe_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    const size_t smem = PipeStage<TV, CAPE, ROWS>::bytes * STAGES;
+    // resident CTAs per SM the shared memory allows (fp64 figure; ptxas sizes its register budget on it)
+    constexpr int MINB = (int)std::min<size_t>(8, std::max<size_t>(1, (size_t)(227 * 1024) / (PipeStage<double, CAPE, ROWS>::bytes * STAGES + 1024)));
+    constexpr int B1 = (THREADS * MINB <= 256) ? 32 : (THREADS * MINB <= 512) ? 16 : 8; // whole-row gathers when registers allow
+    auto k0 = spmv_pipe_kernel<TV, TX, THREADS, CAPE, ROWS, STAGES, 0, B1, MINB>;
+    auto k1 = spmv_pipe_kernel<TV, TX, THREADS, CAPE, ROWS, STAGES, 1, B1, MINB>;
+    static int per_sm = 0; // per instantiation
+    if (per_sm == 0) {
+        RSG_CUDA_TRY(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RSG_CUDA_TRY(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int n = 0;
+        RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k0, THREADS, smem));
+        per_sm = std::max(n, 1);
+    }
+    int ctas = per_sm;
+    if (h->opts[RSG_OPT_SPMV_CTAS_PER_SM] > 0) ctas = std::min(ctas, h->opts[RSG_OPT_SPMV_CTAS_PER_SM]);
+    const int grid = std::max(1, std::min(p->nblk, h->sm_count * ctas));
+    const int nnz_end = p->first + p->nnz;
+    if (h->opts[RSG_OPT_SPMV_X_HINT])
+        k1<<<grid, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc, p->nblk, nnz_end,
+                                               h->opts[RSG_OPT_SPMV_REDUCE]);
+    else
+        k0<<<grid, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc, p->nblk, nnz_end,
+                                               h->opts[RSG_OPT_SPMV_REDUCE]);
+    h->launches++;
+    h->last_spmv_blocks = grid;
+    return RSG_OK;
+}
+
+template <typename TV, typename TX>
+int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    switch (p->variant) {
+    case 1: return pipe_launch_one<TV, TX, 512, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
+    case 2: return pipe_launch_one<TV, TX, 64, 2304, 512, 2>(h, p, values, alpha, x, beta, y);
+    case 3: return pipe_launch_one<TV, TX, 256, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
+    case 4: return pipe_launch_one<TV, TX, 256, 8704, 1024, 2>(h, p, values, alpha, x, beta, y);
+    case 5: return pipe_launch_one<TV, TX, 96, 3456, 768, 2>(h, p, values, alpha, x, beta, y);
+    case 6: return pipe_launch_one<TV, TX, 512, 8704, 1024, 2>(h, p, values, alpha, x, beta, y);
+    case 7: return pipe_launch_one<TV, TX, 1024, 8704, 1024, 2>(h, p, values, alpha, x, beta, y);
+    default: return pipe_launch_one<TV, TX, 128, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
+    }
+}
+
+template int pipe_launch<double, double>(rsg_context *, const SpmvPlan *, const double *, double, const double *, double, double *);
+template int pipe_launch<float, float>(rsg_context *, const SpmvPlan *, const float *, float, const float *, float, float *);
+template int pipe_launch<float, double>(rsg_context *, const SpmvPlan *, const float *, double, const double *, double, double *);
+
+} // namespace rsg

@@ -13,8 +13,9 @@ from ._lib import gpu_lib
 from .host import CSR
 
 OPT = dict(SPMV_ALGO=0, SPMV_REDUCE=1, SPMV_LONG_ROW=2, SPMV_VARIANT=3, SPMV_CACHE_HINT=4,
-           TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7)
-ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4)
+           TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7, SPMV_X_HINT=8,
+           SPMV_ROWS_PER_THREAD=9, SPMV_CTAS_PER_SM=10)
+ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4, stream=5, pipe=6)
 INFO = dict(KERNEL_LAUNCHES=0, SPMV_ALGO_USED=1, SPMV_ROW_BLOCKS=2, SPMV_MAX_ROW=3, LEVELS_L=4, LEVELS_U=5,
             SM_COUNT=6, WORKSPACE_BYTES=7)
 OK, ZERO_PIVOT_STRUCTURAL, ZERO_PIVOT_NUMERIC = 0, 5, 6
@@ -37,8 +38,11 @@ def _check(status, where, allow=()):
 
 class DeviceCSR:
     """CSR arrays resident in HBM: int32 rowptr/colidx, values in the storage precision."""
+    _next_uid = 0
 
     def __init__(self, a: CSR, precision="d", device="cuda:0"):
+        DeviceCSR._next_uid += 1
+        self.uid = DeviceCSR._next_uid
         self.m, self.n, self.base, self.precision = a.m, a.n, a.base, precision
         self.stored = a.stored
         off = int(a.rowptr[0] - a.base)
@@ -62,6 +66,7 @@ class Handle:
         h = C.c_void_p()
         _check(self.lib.rsg_create(C.byref(h), self.device.index or 0), "rsg_create")
         self.h = h
+        self._owner = {}  # rowptr device address -> uid of the DeviceCSR last seen there
         self.use_current_stream()
 
     def close(self):
@@ -95,13 +100,24 @@ class Handle:
     def _p(t):
         return C.c_void_p(t.data_ptr()) if t is not None else None
 
+    def _claim(self, A):
+        """The library caches plans per device address; torch's allocator recycles addresses, so a
+        new DeviceCSR appearing at a known rowptr address drops the plans cached for the old one."""
+        key = A.rowptr.data_ptr()
+        if self._owner.get(key) != A.uid:
+            if key in self._owner:
+                _check(self.lib.rsg_forget_matrix(self.h, C.c_void_p(key)), "rsg_forget_matrix")
+            self._owner[key] = A.uid
+
     # ---- SpMV
     def spmv_analysis(self, A: DeviceCSR):
+        self._claim(A)
         _check(self.lib.rsg_spmv_analysis(self.h, A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx)),
                "rsg_spmv_analysis")
 
     def spmv(self, A: DeviceCSR, x, y=None, alpha=1.0, beta=0.0):
         """y = alpha*A*x + beta*y through spmv_csr_d / spmv_csr_s / spmv_csr_mixed."""
+        self._claim(A)
         _, xt = _PREC[A.precision]
         assert x.dtype == xt and x.is_cuda and x.numel() >= A.n
         if y is None:
@@ -113,17 +129,20 @@ class Handle:
 
     # ---- ILU0 / SpTRSV
     def ilu0_analysis(self, A: DeviceCSR):
+        self._claim(A)
         zp = C.c_int(-1)
         st = self.lib.rsg_ilu0_analysis(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), C.byref(zp))
         _check(st, "rsg_ilu0_analysis", allow=(ZERO_PIVOT_STRUCTURAL,))
         return st, zp.value
 
     def sptrsv_analysis(self, A: DeviceCSR):
+        self._claim(A)
         _check(self.lib.rsg_sptrsv_analysis(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx)),
                "rsg_sptrsv_analysis")
 
     def ilu0_factor(self, A: DeviceCSR, values=None, report_pivot=True):
         """In-place ILU(0) of `values` (default A.values).  Returns (status, zero_pivot_row)."""
+        self._claim(A)
         v = A.values if values is None else values
         fn = self.lib.ilu0_factor_d if v.dtype == torch.float64 else self.lib.ilu0_factor_s
         zp = C.c_int(-1)
@@ -134,6 +153,7 @@ class Handle:
 
     def sptrsv_lu(self, A: DeviceCSR, lu, b, z=None, y=None):
         """L z = b (unit lower) then U y = z (non-unit upper) on the in-place LU values."""
+        self._claim(A)
         z = torch.empty_like(b) if z is None else z
         y = torch.empty_like(b) if y is None else y
         fn = self.lib.sptrsv_lu_d if lu.dtype == torch.float64 else self.lib.sptrsv_lu_s
@@ -156,6 +176,7 @@ class Handle:
         return self.ilu0_analysis(A)
 
     def row_partition(self, A: DeviceCSR, ngpu, balanced=True):
+        self._claim(A)
         out = np.zeros(ngpu + 1, dtype=np.int32)
         _check(self.lib.rsg_get_row_partition(self.h, A.m, A.base, self._p(A.rowptr), ngpu, int(balanced),
                                               C.c_void_p(out.ctypes.data)), "rsg_get_row_partition")

@@ -186,11 +186,28 @@ def test_config3_full_size(handle):
             lp, rows = handle.levels(which, a.m)
             _, lp_ref, rows_ref = orc.levels(a, which)
             assert np.array_equal(lp, lp_ref) and np.array_equal(rows, rows_ref)
-    # property: the preconditioner is a good approximate inverse of a diagonally dominant matrix
+    # size-independent properties.  (1) the defining one of ILU(0): (L*U)_ij = a_ij on the pattern of A.
+    import scipy.sparse as sp
     A = DeviceCSR(a, "d")
     lu = A.values.clone()
     handle.ilu0_factor(A, lu)
+    luv = lu.cpu().numpy()
+    rp, ci = a.rowptr.astype(np.int64), a.colidx.astype(np.int64)
+    rows = np.repeat(np.arange(a.m), np.diff(rp))
+    low = ci < rows
+    L = sp.csr_matrix((np.where(low, luv, 0.0), ci, rp), shape=(a.m, a.m)) + sp.identity(a.m, format="csr")
+    U = sp.csr_matrix((np.where(low, 0.0, luv), ci, rp), shape=(a.m, a.m))
+    P = (L @ U).tocsr()
+    on_pattern = np.asarray(P[rows, ci]).ravel()
+    absP = (abs(L) @ abs(U)).tocsr()
+    bound = 40 * 2.0 ** -53 * np.asarray(absP[rows, ci]).ravel()
+    assert np.all(np.abs(on_pattern - a.values) <= bound)
+    # (2) L U y = b is solved to rounding: r = b - L(U y) against |L||U||y|
     x = torch.from_numpy(orc.dlarnv(a.m)).cuda()
     Ax = handle.spmv(A, x)
     _, y = handle.sptrsv_lu(A, lu, Ax)
-    assert float((y - x).abs().max() / x.abs().max()) < 0.2
+    yh = y.cpu().numpy()
+    r = Ax.cpu().numpy() - L @ (U @ yh)
+    assert np.all(np.abs(r) <= 200 * 2.0 ** -53 * (abs(L) @ (abs(U) @ np.abs(yh))) + 1e-300)
+    # (3) M^-1 A is a contraction towards the identity for this diagonally dominant matrix
+    assert float((y - x).abs().max() / x.abs().max()) < 1.0

@@ -64,7 +64,7 @@ SMALL = {
 
 @pytest.mark.parametrize("name", sorted(SMALL))
 @pytest.mark.parametrize("precision", ["d", "s", "m"])
-@pytest.mark.parametrize("algo", ["auto", "rowblock", "merge", "vector", "scalar"])
+@pytest.mark.parametrize("algo", ["auto", "pipe", "stream", "rowblock", "merge", "vector", "scalar"])
 def test_spmv_small(handle, name, precision, algo):
     a = SMALL[name]()
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -85,7 +85,7 @@ def test_golden_b1ss_values(handle):
 
 
 @pytest.mark.parametrize("precision", ["d", "s", "m"])
-@pytest.mark.parametrize("algo", ["rowblock", "merge", "vector"])
+@pytest.mark.parametrize("algo", ["pipe", "stream", "rowblock", "merge", "vector"])
 def test_alpha_beta(handle, precision, algo):
     a = host.gen_stencil27(9, 10, 11, seed=5)
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -123,6 +123,76 @@ def test_rowblock_variants(handle, variant, reduce):
         handle.set_option("SPMV_REDUCE", 0)
 
 
+@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+@pytest.mark.parametrize("reduce", [0, 1, 2, 4, 8, 16, 32])
+def test_stream_variants(handle, variant, reduce):
+    """every compiled tile shape x every lanes-per-row reduction of the TMA-staged kernel"""
+    handle.set_option("SPMV_ALGO", ALGO["stream"])
+    handle.set_option("SPMV_VARIANT", variant)
+    handle.set_option("SPMV_REDUCE", reduce)
+    try:
+        for a in (host.gen_femlike(14, 0.7, 9), host.gen_powerlaw(6000, 2.2, 48, 2, 700 + 611 * variant, 4)):
+            x = orc.dlarnv(a.n) - 0.5
+            for p in ("d", "s", "m"):
+                check(handle, a, x, p)
+        if reduce == 1:  # thread-per-row sums left to right like the oracle: bit-exact
+            a = host.gen_stencil27(11, 12, 13, seed=4)
+            x = orc.dlarnv(a.n) - 0.5
+            A = DeviceCSR(a, "d")
+            y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
+            assert np.array_equal(y, orc.spmv(a, x, "d"))
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+        handle.set_option("SPMV_VARIANT", 0)
+        handle.set_option("SPMV_REDUCE", 0)
+
+
+@pytest.mark.parametrize("variant", list(range(8)))
+@pytest.mark.parametrize("reduce", [0, 1, 4, 32])
+@pytest.mark.parametrize("rpt", [0, 3])
+def test_pipe_variants(handle, variant, reduce, rpt):
+    """every compiled (threads, stage capacity, stages) shape of the pipelined kernel: fitting tiles,
+    multi-pass tiles (rows longer than the tile slack), CTA-per-row rows, a ragged last quad"""
+    handle.set_option("SPMV_ALGO", ALGO["pipe"])
+    handle.set_option("SPMV_VARIANT", variant)
+    handle.set_option("SPMV_REDUCE", reduce)
+    handle.set_option("SPMV_ROWS_PER_THREAD", rpt)
+    try:
+        mats = [host.gen_femlike(14, 0.7, 9), host.gen_powerlaw(16000, 2.2, 48, 3, 700 + 1733 * variant, 4),
+                host.gen_laplace2d(37)]
+        for a in mats:
+            x = orc.dlarnv(a.n) - 0.5
+            for p in ("d", "s", "m"):
+                check(handle, a, x, p)
+        if reduce == 1:  # thread-per-row sums left to right like the oracle: bit-exact
+            a = host.gen_stencil27(11, 12, 13, seed=4)
+            x = orc.dlarnv(a.n) - 0.5
+            A = DeviceCSR(a, "d")
+            y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
+            assert np.array_equal(y, orc.spmv(a, x, "d"))
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+        handle.set_option("SPMV_VARIANT", 0)
+        handle.set_option("SPMV_REDUCE", 0)
+        handle.set_option("SPMV_ROWS_PER_THREAD", 0)
+
+
+def test_pipe_tiny_tiles_and_slabs(handle):
+    """tile size forced down to 64 items: many tiles per CTA, empty tiles inside long rows, slab views
+    whose first entry is not entry 0"""
+    handle.set_option("SPMV_ALGO", ALGO["pipe"])
+    handle.set_option("SPMV_LONG_ROW", 64)
+    try:
+        for a in (host.gen_stencil27(12, 12, 30, 10, 20, seed=2), host.gen_powerlaw(3000, 2.2, 48, 2, 2500, 4),
+                  SMALL["empty_rows"](), SMALL["rect"](), SMALL["b1_ss_base1"]()):
+            x = orc.dlarnv(a.n) - 0.5
+            for p in ("d", "s", "m"):
+                check(handle, a, x, p, alpha=0.75, beta=-0.5, y0=orc.dlarnv(a.m) - 0.25)
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+        handle.set_option("SPMV_LONG_ROW", 0)
+
+
 @pytest.mark.parametrize("hint", [0, 1, 2])
 @pytest.mark.parametrize("persist", [0, 1])
 def test_cache_hints(handle, hint, persist):
@@ -130,13 +200,15 @@ def test_cache_hints(handle, hint, persist):
     handle.set_option("SPMV_CACHE_HINT", hint)
     handle.set_option("SPMV_X_PERSIST", persist)
     try:
-        for algo in ("rowblock", "merge"):
+        for algo in ("pipe", "stream", "rowblock", "merge"):
             handle.set_option("SPMV_ALGO", ALGO[algo])
+            handle.set_option("SPMV_X_HINT", persist)
             check(handle, a, orc.dlarnv(a.n), "d")
             check(handle, a, orc.dlarnv(a.n), "m")
     finally:
         handle.set_option("SPMV_CACHE_HINT", 1)
         handle.set_option("SPMV_X_PERSIST", 0)
+        handle.set_option("SPMV_X_HINT", 0)
         handle.set_option("SPMV_ALGO", 0)
 
 
@@ -144,7 +216,7 @@ def test_long_rows_cta_per_row_and_merge(handle):
     # rows far longer than a tile: the row-block kernel falls to CTA-per-row, AUTO picks merge-path
     a = host.gen_powerlaw(60000, 2.2, 32, 3, 50000, 7)
     x = orc.dlarnv(a.n) - 0.5
-    for algo in ("rowblock", "merge", "auto"):
+    for algo in ("pipe", "stream", "rowblock", "merge", "auto"):
         handle.set_option("SPMV_ALGO", ALGO[algo])
         for p in ("d", "s", "m"):
             check(handle, a, x, p)
@@ -164,7 +236,7 @@ def test_unaligned_views_take_scalar_path(handle):
     A.colidx, A.values = ci[1:], va[1:]
     x = orc.dlarnv(a.n)
     ref = orc.spmv(a, x)
-    for algo in ("rowblock", "merge"):
+    for algo in ("auto", "pipe", "stream", "rowblock", "merge"):  # pipe/stream fall back to rowblock's scalar staging
         handle.set_option("SPMV_ALGO", ALGO[algo])
         y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
         assert np.abs(y - ref).max() <= 1e-12 * np.abs(ref).max()
@@ -180,7 +252,7 @@ def test_empty_and_degenerate(handle):
     e = host.CSR(5, 5, 0, np.zeros(6, np.int32), np.zeros(0, np.int32), np.zeros(0))
     E = DeviceCSR(e, "d")
     E.colidx = torch.zeros(1, dtype=torch.int32, device="cuda"); E.values = torch.zeros(1, dtype=torch.float64, device="cuda")
-    for algo in ("rowblock", "merge", "vector", "scalar"):
+    for algo in ("pipe", "stream", "rowblock", "merge", "vector", "scalar"):
         handle.set_option("SPMV_ALGO", ALGO[algo])
         y = handle.spmv(E, torch.ones(5, dtype=torch.float64, device="cuda"),
                         torch.full((5,), 7.0, dtype=torch.float64, device="cuda"))
@@ -246,7 +318,7 @@ def test_full_size_configs(handle, name):
     if name == "C4":
         assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
     else:
-        assert handle.info("SPMV_ALGO_USED") == ALGO["rowblock"]
+        assert handle.info("SPMV_ALGO_USED") == ALGO["pipe"]
     # linearity: A(2x + 1) = 2 A x + A 1
     A = DeviceCSR(a, "d")
     xd = torch.from_numpy(x).cuda()
