@@ -113,7 +113,7 @@ template <int TILE, int W> struct StreamShape {
 };
 
 template <typename TV, typename TX, int THREADS, int TILE, int W, int XH>
-__global__ void __launch_bounds__(THREADS, (TILE <= 2048 ? 6 : TILE <= 4096 ? 4 : 2) * (THREADS <= 256 ? 1 : 1))
+__global__ void __launch_bounds__(THREADS)
 spmv_stream_kernel(int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
                    const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
                    const int2 *__restrict__ blk, int reduce_opt)
@@ -216,12 +216,12 @@ spmv_stream_kernel(int base, const int *__restrict__ rowptr, const int *__restri
         }
         const int *rp = s_rp + cur;
         switch (g) {
-        case 1: reduce_rows_gather<TV, TX, THREADS, 1, XH, 16>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 2: reduce_rows_gather<TV, TX, THREADS, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 4: reduce_rows_gather<TV, TX, THREADS, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 8: reduce_rows_gather<TV, TX, THREADS, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 16: reduce_rows_gather<TV, TX, THREADS, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        default: reduce_rows_gather<TV, TX, THREADS, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 1: reduce_rows_lean<TV, TX, THREADS, 1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+        case 2: reduce_rows_lean<TV, TX, THREADS, 2>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+        case 4: reduce_rows_lean<TV, TX, THREADS, 4>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+        case 8: reduce_rows_lean<TV, TX, THREADS, 8>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+        case 16: reduce_rows_lean<TV, TX, THREADS, 16>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+        default: reduce_rows_lean<TV, TX, THREADS, 32>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
         }
         cur = pe;
         if (cur < nr) __syncthreads();

@@ -131,8 +131,16 @@ __device__ __forceinline__ void stage_products(int k0, int k1, const int *__rest
     }
 }
 
+// barrier over the first THREADS threads of the CTA: id 0 = __syncthreads (whole CTA), otherwise a
+// named barrier (kernels with a producer warp that does not take part)
+template <int BARID, int THREADS> __device__ __forceinline__ void group_sync()
+{
+    if (BARID == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"n"(BARID), "n"(THREADS) : "memory");
+}
+
 // CTA-wide sum of a_k*x[col_k] over [k0,k1), result valid in thread 0 (CTA-per-row path).
-template <typename TV, typename TX, int THREADS, int HINT, bool VEC>
+template <typename TV, typename TX, int THREADS, int HINT, bool VEC, int BARID = 0>
 __device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict__ colidx,
                                           const TV *__restrict__ values, const TX *__restrict__ x,
                                           int base, TX *s_red, uint64_t pol)
@@ -166,13 +174,13 @@ __device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict_
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    __syncthreads();
+    group_sync<BARID, THREADS>();
     if ((tid & 31) == 0) s_red[tid >> 5] = acc;
-    __syncthreads();
+    group_sync<BARID, THREADS>();
     TX tot = 0;
     if (tid == 0)
         for (int w = 0; w < THREADS / 32; ++w) tot += s_red[w];
-    __syncthreads();
+    group_sync<BARID, THREADS>();
     return tot;
 }
 
@@ -223,6 +231,10 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
 {
     uint32_t ok;
@@ -270,28 +282,45 @@ template <int XH> __device__ __forceinline__ float ld_x(const float *p, uint64_t
 
 // sum over the staged entries k, k+G, k+2G, ... < e of s_val[.] * x[s_col[.]], in that order.
 // Software-pipelined: the x gathers of batch i+1 (B per lane) are issued before batch i is
-// consumed, so up to 2B independent loads are in flight per lane.
+// consumed, so up to 2B independent loads are in flight per lane.  FULL batches run without any
+// clamp, predicate or select (6 instructions per entry: LDS col, IMAD.WIDE, LDG, LDS val, MUL,
+// ADD); only the last partial batch of a row pays for the clamped indices and the selects.
 template <typename TV, typename TX, int G, int B, int XH>
 __device__ __forceinline__ TX row_dot(const TV *s_val, const int *s_col, int k, int e, const TX *xb, uint64_t xpol)
 {
     TX s = 0;
     if (k >= e) return s;
     const int last = k + ((e - 1 - k) / G) * G; // this lane's last entry
+    constexpr int SPAN = (B - 1) * G;
     TX xa[B];
+    if (k + SPAN <= last) {
 #pragma unroll
-    for (int u = 0; u < B; ++u) xa[u] = ld_x<XH>(xb + s_col[min(k + u * G, last)], xpol);
-    while (k <= last) {
+        for (int u = 0; u < B; ++u) xa[u] = ld_x<XH>(xb + s_col[k + u * G], xpol);
+    } else {
+#pragma unroll
+        for (int u = 0; u < B; ++u) xa[u] = ld_x<XH>(xb + s_col[min(k + u * G, last)], xpol);
+    }
+    for (;;) {
         const int kn = k + B * G;
         TX xn[B];
-        if (kn <= last) {
+        if (kn + SPAN <= last) {
+#pragma unroll
+            for (int u = 0; u < B; ++u) xn[u] = ld_x<XH>(xb + s_col[kn + u * G], xpol);
+        } else if (kn <= last) {
 #pragma unroll
             for (int u = 0; u < B; ++u) xn[u] = ld_x<XH>(xb + s_col[min(kn + u * G, last)], xpol);
         }
+        if (k + SPAN <= last) {
 #pragma unroll
-        for (int u = 0; u < B; ++u) {
-            const TX p = (TX)s_val[min(k + u * G, last)] * xa[u];
-            s += (k + u * G <= last) ? p : (TX)0;
+            for (int u = 0; u < B; ++u) s += (TX)s_val[k + u * G] * xa[u];
+        } else {
+#pragma unroll
+            for (int u = 0; u < B; ++u) {
+                const TX p = (TX)s_val[min(k + u * G, last)] * xa[u];
+                s += (k + u * G <= last) ? p : (TX)0;
+            }
         }
+        if (kn > last) break;
 #pragma unroll
         for (int u = 0; u < B; ++u) xa[u] = xn[u];
         k = kn;
@@ -341,6 +370,95 @@ __device__ __forceinline__ TX row_dot_oneshot(const TV *s_val, const int *s_col,
     return s;
 }
 
+// ---- one thread, one row of at most 32 entries, split in two phases so that the gathers of the
+// NEXT tile's row can be in flight while the current row is consumed (cross-tile pipelining):
+//   row_issue32    : every x gather of the row is issued (groups of 4, no use of the results)
+//   row_consume32  : s = sum_k val_k * x_k, left to right like the oracle
+// Entries k..last (inclusive) index the stage's s_col / s_val; last < k means "no row".
+template <typename TX, int XH>
+__device__ __forceinline__ void row_issue32(const int *s_col, int k, int last, const TX *xb, uint64_t xpol, TX (&xv)[32])
+{
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        if (k + 4 * b <= last) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) xv[4 * b + v] = ld_x<XH>(xb + s_col[min(k + 4 * b + v, last)], xpol);
+        }
+    }
+}
+template <typename TV, typename TX>
+__device__ __forceinline__ TX row_consume32(const TV *s_val, int k, int last, const TX (&xv)[32])
+{
+    TX s = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        if (k + 4 * b + 3 <= last) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) s += (TX)s_val[k + 4 * b + v] * xv[4 * b + v];
+        } else if (k + 4 * b <= last) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+                const TX p = (TX)s_val[min(k + 4 * b + v, last)] * xv[4 * b + v];
+                s += (k + 4 * b + v <= last) ? p : (TX)0;
+            }
+        }
+    }
+    return s;
+}
+
+// "lean" variant of row_dot for kernels that run MANY warps per SM (stream kernel: no residency
+// hint in __launch_bounds__, so ptxas keeps it at 32-40 registers and 7 CTAs fit an SM): predicated
+// __ldg gathers, a few in flight per lane; the latency is hidden by occupancy instead.  Measured
+// faster than the register-hungry batched form whenever the latter costs resident warps.
+template <typename TV, typename TX, int G, int B>
+__device__ __forceinline__ TX row_dot_lean(const TV *s_val, const int *s_col, int k, int e, const TX *xb)
+{
+    TX s = 0;
+    TX xa[B];
+#pragma unroll
+    for (int u = 0; u < B; ++u) xa[u] = (k + u * G < e) ? __ldg(xb + s_col[k + u * G]) : (TX)0;
+    while (k < e) {
+        const int kn = k + B * G;
+        TX xn[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u) xn[u] = (kn + u * G < e) ? __ldg(xb + s_col[kn + u * G]) : (TX)0;
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (k + u * G < e) s += (TX)s_val[k + u * G] * xa[u];
+#pragma unroll
+        for (int u = 0; u < B; ++u) xa[u] = xn[u];
+        k = kn;
+    }
+    return s;
+}
+
+template <typename TV, typename TX, int THREADS, int G>
+__device__ __forceinline__ void reduce_rows_lean(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
+                                                 int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
+                                                 TX alpha, TX beta)
+{
+    const int tid = threadIdx.x;
+    const TX *xb = x - base;
+    if (G == 1) {
+        for (int i = tid; i < nrows; i += THREADS) {
+            const TX s = row_dot_lean<TV, TX, 1, 8>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
+            store_y(y, row_glob + i, s, alpha, beta);
+        }
+    } else {
+        constexpr int GROUPS = THREADS / G;
+        const int gid = tid / G, lane = tid % G;
+        const int iters = (nrows + GROUPS - 1) / GROUPS;
+        for (int it = 0; it < iters; ++it) {
+            const int i = it * GROUPS + gid;
+            TX s = 0;
+            if (i < nrows) s = row_dot_lean<TV, TX, G, 4>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
+        }
+    }
+}
+
 // rows of one pass out of the staged raw entries; G lanes per row.  G == 1 keeps the oracle's
 // summation order (left to right, multiply then add).  B1 > 0: whole-row-in-flight gathers.
 template <typename TV, typename TX, int THREADS, int G, int XH, int B1 = 0>
@@ -354,7 +472,7 @@ __device__ __forceinline__ void reduce_rows_gather(const TV *s_val, const int *s
     if (G == 1) {
         for (int i = tid; i < nrows; i += THREADS) {
             TX s;
-            if (B1 > 0) s = row_dot_oneshot<TV, TX, (B1 > 0 ? B1 : 8), XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
+            if (B1 >= 32) s = row_dot_oneshot<TV, TX, (B1 > 0 ? B1 : 8), XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
             else s = row_dot<TV, TX, 1, 8, XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
             store_y(y, row_glob + i, s, alpha, beta);
         }

@@ -33,147 +33,165 @@ struct PipeMeta { // written by the producer, read by everybody after the mbarri
     int rp_shift, pad;      // s_rp[rp_shift + i] = zero-based start of row r0+i
 };
 
-template <typename TV, typename TX, int THREADS, int CAPE, int ROWS, int STAGES, int XH, int B1, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB)
+// A tile that is not "simple" (see the kernel): any row lengths, multi-pass when it does not fit one
+// stage, CTA-per-row for a row longer than a stage.  Runs on the NC consumer threads (barrier 1).
+template <typename TV, typename TX, int NC, int CAPE, int XH, typename Stage>
+__device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeMeta &mt, int base, const int *__restrict__ colidx,
+                                                  const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
+                                                  TX alpha, TX beta, int reduce_opt, uint64_t spol, uint64_t xpol,
+                                                  uint64_t *s_aux, uint32_t &aux_parity)
+{
+    const int tid = threadIdx.x;
+    TV *s_val = reinterpret_cast<TV *>(sp + Stage::val_off);
+    int *s_col = reinterpret_cast<int *>(sp + Stage::col_off);
+    const int *s_rp = reinterpret_cast<const int *>(sp + Stage::rp_off) + mt.rp_shift;
+    const int nr = mt.nr, r0 = mt.r0;
+    int cur = 0;
+    bool staged = mt.staged_end > 0;
+    while (cur < nr) {
+        const int k0 = s_rp[cur];
+        const int sb = k0 & ~3;
+        int pe, k1;
+        if (staged) {
+            pe = nr; k1 = mt.k1;
+            if (mt.staged_end < k1) { // only the last tile of a matrix whose entry count is not a multiple of 4
+                const int k = mt.staged_end + tid;
+                if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
+                group_sync<1, NC>();
+            }
+        } else { // synchronous multi-pass path for a tile that does not fit one stage
+            if (s_rp[nr] - sb <= CAPE) {
+                pe = nr;
+            } else { // largest pe in [cur,nr] with s_rp[pe]-sb <= CAPE
+                int lo = cur, hi = nr;
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (s_rp[mid] - sb <= CAPE) lo = mid; else hi = mid - 1;
+                }
+                pe = lo;
+            }
+            if (pe == cur) { // this row alone exceeds a stage: CTA-per-row from global memory
+                const TX tot = cta_row_sum<TV, TX, NC, 1, true, 1>(k0, s_rp[cur + 1], colidx, values, x, base,
+                                                                   reinterpret_cast<TX *>(s_val), spol);
+                if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
+                cur += 1;
+                continue;
+            }
+            k1 = s_rp[pe];
+            const int qe = k1 & ~3;
+            if (tid == 0 && qe > sb) {
+                const uint32_t nq = (uint32_t)(qe - sb);
+                mbar_expect_tx(s_aux, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+                bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), s_aux, spol);
+                bulk_g2s(s_col, colidx + sb, nq * 4u, s_aux, spol);
+            }
+            {
+                const int k = max(qe, sb) + tid;
+                if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
+            }
+            group_sync<1, NC>();
+            if (qe > sb) { mbar_wait(s_aux, aux_parity); aux_parity ^= 1; }
+        }
+        const int nrows = pe - cur;
+        int g = reduce_opt;
+        if (g == 0) { // lanes per row from the tile's row-length statistics
+            const int avg = (k1 - k0) / nrows;
+            const int len = max(avg, mt.maxlen >> 3);
+            g = len <= 40 ? 1 : len <= 80 ? 4 : len <= 160 ? 8 : len <= 320 ? 16 : 32;
+            while (g < 32 && nrows * g * 2 <= NC) g <<= 1; // few rows: spread them over the CTA
+            if (g == 2) g = (avg <= 40 && mt.maxlen <= 64) ? 1 : 4;
+        }
+        const int *rp = s_rp + cur;
+        switch (g) {
+        case 1: reduce_rows_gather<TV, TX, NC, 1, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 2: reduce_rows_gather<TV, TX, NC, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 4: reduce_rows_gather<TV, TX, NC, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 8: reduce_rows_gather<TV, TX, NC, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        case 16: reduce_rows_gather<TV, TX, NC, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        default: reduce_rows_gather<TV, TX, NC, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+        }
+        cur = pe;
+        if (!staged || cur < nr) group_sync<1, NC>(); // the synchronous path reuses the buffers
+        staged = false;
+    }
+}
+
+// NCW consumer warps + 1 producer warp.  Barrier id 1 = the consumer threads only.
+template <typename TV, typename TX, int NCW, int CAPE, int ROWS, int STAGES, int XH, int MINB>
+__global__ void __launch_bounds__((NCW + 1) * 32, MINB)
 spmv_pipe_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
                  const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
                  int ntiles, int nnz_end, int reduce_opt)
 {
     typedef PipeStage<TV, CAPE, ROWS> Stage;
+    constexpr int NC = NCW * 32; // consumer threads
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t s_full[STAGES];
+    __shared__ __align__(8) uint64_t s_empty[STAGES];
     __shared__ __align__(8) uint64_t s_aux;
     __shared__ PipeMeta s_meta[STAGES];
     const int tid = threadIdx.x;
-    const uint64_t spol = make_evict_first_policy();
-    uint64_t xpol = 0;
-    if (XH) xpol = make_evict_last_policy();
-
-    auto issue = [&](int t, int s) { // producer: tile t -> stage s
-        const int4 d0 = desc[t], d1 = desc[t + 1];
-        unsigned char *sp = smem_raw + (size_t)s * Stage::bytes;
-        PipeMeta mt;
-        mt.r0 = d0.x; mt.nr = d1.x - d0.x; mt.k0 = d0.y; mt.k1 = d1.y; mt.maxlen = d0.z; mt.pad = 0;
-        const int ra = mt.r0 & ~3;
-        mt.rp_shift = mt.r0 - ra;
-        const uint32_t nrp = (uint32_t)((mt.rp_shift + mt.nr + 1 + 3) & ~3);
-        const int sb = mt.k0 & ~3;
-        // whole quads only; the last quad may reach into the next tile's entries (valid memory)
-        // but never past the end of the arrays
-        int qe = min((mt.k1 + 3) & ~3, nnz_end & ~3);
-        const bool fits = (mt.k1 - sb) <= CAPE && qe > sb;
-        if (!fits) qe = sb;
-        mt.staged_end = fits ? qe : 0;
-        s_meta[s] = mt;
-        const uint32_t nq = (uint32_t)(qe - sb);
-        mbar_expect_tx(&s_full[s], nrp * 4u + nq * (uint32_t)(sizeof(TV) + sizeof(int)));
-        bulk_g2s(sp + Stage::rp_off, rp0 + ra, nrp * 4u, &s_full[s], spol);
-        if (nq) {
-            bulk_g2s(sp + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full[s], spol);
-            bulk_g2s(sp + Stage::col_off, colidx + sb, nq * 4u, &s_full[s], spol);
-        }
-    };
-
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < STAGES; ++s) mbar_init(&s_full[s], 1);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&s_full[s], 1); mbar_init(&s_empty[s], NCW); }
         mbar_init(&s_aux, 1);
     }
     __syncthreads();
     // a contiguous run of tiles per CTA: consecutive tiles of a banded matrix share x lines (L1)
     const int t_begin = (int)(((long long)ntiles * blockIdx.x) / gridDim.x);
     const int t_end = (int)(((long long)ntiles * (blockIdx.x + 1)) / gridDim.x);
-    if (tid == 0) {
-#pragma unroll
-        for (int s = 0; s < STAGES - 1; ++s) {
-            const int t = t_begin + s;
-            if (t < t_end) issue(t, s);
+    const uint64_t spol = make_evict_first_policy();
+
+    if (tid >= NC) { // ---------------------------------------------------------------- producer warp
+        if (tid != NC || t_begin >= t_end) return;
+        int4 d0 = desc[t_begin], d1 = desc[t_begin + 1];
+        int it = 0;
+        for (int t = t_begin; t < t_end; ++t, ++it) {
+            const int s = it % STAGES;
+            // the descriptor of the tile after this one is fetched now and used one iteration later
+            const int4 d2 = desc[min(t + 2, ntiles)];
+            if (it >= STAGES) mbar_wait(&s_empty[s], (uint32_t)(((it / STAGES) - 1) & 1));
+            unsigned char *sp = smem_raw + (size_t)s * Stage::bytes;
+            PipeMeta mt;
+            mt.r0 = d0.x; mt.nr = d1.x - d0.x; mt.k0 = d0.y; mt.k1 = d1.y; mt.maxlen = d0.z; mt.pad = 0;
+            const int ra = mt.r0 & ~3;
+            mt.rp_shift = mt.r0 - ra;
+            const uint32_t nrp = (uint32_t)((mt.rp_shift + mt.nr + 1 + 3) & ~3);
+            const int sb = mt.k0 & ~3;
+            // whole quads only; the last quad may reach into the next tile's entries (valid memory)
+            // but never past the end of the arrays
+            int qe = min((mt.k1 + 3) & ~3, nnz_end & ~3);
+            const bool fits = (mt.k1 - sb) <= CAPE && qe > sb;
+            if (!fits) qe = sb;
+            mt.staged_end = fits ? qe : 0;
+            s_meta[s] = mt;
+            const uint32_t nq = (uint32_t)(qe - sb);
+            mbar_expect_tx(&s_full[s], nrp * 4u + nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+            bulk_g2s(sp + Stage::rp_off, rp0 + ra, nrp * 4u, &s_full[s], spol);
+            if (nq) {
+                bulk_g2s(sp + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full[s], spol);
+                bulk_g2s(sp + Stage::col_off, colidx + sb, nq * 4u, &s_full[s], spol);
+            }
+            d0 = d1; d1 = d2;
         }
+        return;
     }
+
+    // ------------------------------------------------------------------------------ consumer warps
+    uint64_t xpol = 0;
+    if (XH) xpol = make_evict_last_policy();
     uint32_t aux_parity = 0;
     int it = 0;
     for (int t = t_begin; t < t_end; ++t, ++it) {
         const int s = it % STAGES;
-        if (tid == 0) { // keep STAGES-1 tiles in flight: the buffer freed by the previous iteration
-            const int tn = t + (STAGES - 1);
-            if (tn < t_end) issue(tn, (it + STAGES - 1) % STAGES);
-        }
         mbar_wait(&s_full[s], (uint32_t)((it / STAGES) & 1));
         unsigned char *sp = smem_raw + (size_t)s * Stage::bytes;
-        TV *s_val = reinterpret_cast<TV *>(sp + Stage::val_off);
-        int *s_col = reinterpret_cast<int *>(sp + Stage::col_off);
-        const PipeMeta mt = s_meta[s];
-        const int *s_rp = reinterpret_cast<const int *>(sp + Stage::rp_off) + mt.rp_shift;
-        const int nr = mt.nr, r0 = mt.r0;
-        int cur = 0;
-        bool staged = mt.staged_end > 0;
-        while (cur < nr) {
-            const int k0 = s_rp[cur];
-            const int sb = k0 & ~3;
-            int pe, k1;
-            if (staged) {
-                pe = nr; k1 = mt.k1;
-                if (mt.staged_end < k1) { // only the last tile of a matrix whose entry count is not a multiple of 4
-                    const int k = mt.staged_end + tid;
-                    if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
-                    __syncthreads();
-                }
-            } else { // synchronous multi-pass path for a tile that does not fit one stage
-                if (s_rp[nr] - sb <= CAPE) {
-                    pe = nr;
-                } else { // largest pe in [cur,nr] with s_rp[pe]-sb <= CAPE
-                    int lo = cur, hi = nr;
-                    while (lo < hi) {
-                        const int mid = (lo + hi + 1) >> 1;
-                        if (s_rp[mid] - sb <= CAPE) lo = mid; else hi = mid - 1;
-                    }
-                    pe = lo;
-                }
-                if (pe == cur) { // this row alone exceeds a stage: CTA-per-row from global memory
-                    const TX tot = cta_row_sum<TV, TX, THREADS, 1, true>(k0, s_rp[cur + 1], colidx, values, x, base,
-                                                                         reinterpret_cast<TX *>(s_val), spol);
-                    if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
-                    cur += 1;
-                    continue;
-                }
-                k1 = s_rp[pe];
-                const int qe = k1 & ~3;
-                if (tid == 0 && qe > sb) {
-                    const uint32_t nq = (uint32_t)(qe - sb);
-                    mbar_expect_tx(&s_aux, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
-                    bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), &s_aux, spol);
-                    bulk_g2s(s_col, colidx + sb, nq * 4u, &s_aux, spol);
-                }
-                {
-                    const int k = max(qe, sb) + tid;
-                    if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
-                }
-                __syncthreads();
-                if (qe > sb) { mbar_wait(&s_aux, aux_parity); aux_parity ^= 1; }
-            }
-            const int nrows = pe - cur;
-            int g = reduce_opt;
-            if (g == 0) { // lanes per row from the tile's row-length statistics
-                const int avg = (k1 - k0) / nrows;
-                const int len = max(avg, mt.maxlen >> 3);
-                g = len <= 40 ? 1 : len <= 80 ? 4 : len <= 160 ? 8 : len <= 320 ? 16 : 32;
-                while (g < 32 && nrows * g * 2 <= THREADS) g <<= 1; // few rows: spread them over the CTA
-                if (g == 2) g = (avg <= 40 && mt.maxlen <= 64) ? 1 : 4;
-            }
-            const int *rp = s_rp + cur;
-            switch (g) {
-            case 1: reduce_rows_gather<TV, TX, THREADS, 1, XH, B1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-            case 2: reduce_rows_gather<TV, TX, THREADS, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-            case 4: reduce_rows_gather<TV, TX, THREADS, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-            case 8: reduce_rows_gather<TV, TX, THREADS, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-            case 16: reduce_rows_gather<TV, TX, THREADS, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-            default: reduce_rows_gather<TV, TX, THREADS, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-            }
-            cur = pe;
-            staged = false;
-            if (cur < nr) __syncthreads();
-        }
-        __syncthreads(); // every thread is done with stage s: the producer may refill it
+        const PipeMeta mc = s_meta[s];
+        pipe_general_tile<TV, TX, NC, CAPE, XH, Stage>(sp, mc, base, colidx, values, x, y, alpha, beta, reduce_opt, spol, xpol,
+                                                      &s_aux, aux_parity);
+        // this warp is done with stage s: one arrival per consumer warp hands it back to the producer
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(&s_empty[s]);
     }
 }
 
@@ -220,9 +238,9 @@ __global__ void pipe_rowptr_copy_kernel(int m, int padded, int base, const int *
 
 // ------------------------------------------------------------------ host side
 struct PipeVariant { int threads, cape, rows, stages; };
-static const PipeVariant kPipeVariants[] = {
-    {128, 4352, 512, 2}, {512, 4352, 512, 2}, {64, 2304, 512, 2}, {256, 4352, 512, 2},
-    {256, 8704, 1024, 2}, {96, 3456, 768, 2}, {512, 8704, 1024, 2}, {1024, 8704, 1024, 2},
+static const PipeVariant kPipeVariants[] = { // consumer threads, entries per stage, rows per stage, stages
+    {128, 4352, 512, 3}, {64, 2304, 256, 3}, {32, 1152, 128, 3}, {128, 4352, 512, 2},
+    {256, 8704, 1024, 2}, {32, 1152, 128, 4}, {64, 2304, 256, 2}, {96, 3456, 384, 3},
 };
 static const int kNumPipeVariants = (int)(sizeof(kPipeVariants) / sizeof(kPipeVariants[0]));
 
@@ -259,15 +277,15 @@ int pipe_build_plan(rsg_context *h, SpmvPlan &p)
     return RSG_OK;
 }
 
-template <typename TV, typename TX, int THREADS, int CAPE, int ROWS, int STAGES>
+template <typename TV, typename TX, int NC, int CAPE, int ROWS, int STAGES>
 static int pipe_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
 {
     const size_t smem = PipeStage<TV, CAPE, ROWS>::bytes * STAGES;
+    constexpr int THREADS = NC + 32; // + the producer warp
     // resident CTAs per SM the shared memory allows (fp64 figure; ptxas sizes its register budget on it)
     constexpr int MINB = (int)std::min<size_t>(8, std::max<size_t>(1, (size_t)(227 * 1024) / (PipeStage<double, CAPE, ROWS>::bytes * STAGES + 1024)));
-    constexpr int B1 = (THREADS * MINB <= 256) ? 32 : (THREADS * MINB <= 512) ? 16 : 8; // whole-row gathers when registers allow
-    auto k0 = spmv_pipe_kernel<TV, TX, THREADS, CAPE, ROWS, STAGES, 0, B1, MINB>;
-    auto k1 = spmv_pipe_kernel<TV, TX, THREADS, CAPE, ROWS, STAGES, 1, B1, MINB>;
+    auto k0 = spmv_pipe_kernel<TV, TX, NC / 32, CAPE, ROWS, STAGES, 0, MINB>;
+    auto k1 = spmv_pipe_kernel<TV, TX, NC / 32, CAPE, ROWS, STAGES, 1, MINB>;
     static int per_sm = 0; // per instantiation
     if (per_sm == 0) {
         RSG_CUDA_TRY(cudaFuncSetAttribute(k0, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -295,14 +313,14 @@ template <typename TV, typename TX>
 int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
 {
     switch (p->variant) {
-    case 1: return pipe_launch_one<TV, TX, 512, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
-    case 2: return pipe_launch_one<TV, TX, 64, 2304, 512, 2>(h, p, values, alpha, x, beta, y);
-    case 3: return pipe_launch_one<TV, TX, 256, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
+    case 1: return pipe_launch_one<TV, TX, 64, 2304, 256, 3>(h, p, values, alpha, x, beta, y);
+    case 2: return pipe_launch_one<TV, TX, 32, 1152, 128, 3>(h, p, values, alpha, x, beta, y);
+    case 3: return pipe_launch_one<TV, TX, 128, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
     case 4: return pipe_launch_one<TV, TX, 256, 8704, 1024, 2>(h, p, values, alpha, x, beta, y);
-    case 5: return pipe_launch_one<TV, TX, 96, 3456, 768, 2>(h, p, values, alpha, x, beta, y);
-    case 6: return pipe_launch_one<TV, TX, 512, 8704, 1024, 2>(h, p, values, alpha, x, beta, y);
-    case 7: return pipe_launch_one<TV, TX, 1024, 8704, 1024, 2>(h, p, values, alpha, x, beta, y);
-    default: return pipe_launch_one<TV, TX, 128, 4352, 512, 2>(h, p, values, alpha, x, beta, y);
+    case 5: return pipe_launch_one<TV, TX, 32, 1152, 128, 4>(h, p, values, alpha, x, beta, y);
+    case 6: return pipe_launch_one<TV, TX, 64, 2304, 256, 2>(h, p, values, alpha, x, beta, y);
+    case 7: return pipe_launch_one<TV, TX, 96, 3456, 384, 3>(h, p, values, alpha, x, beta, y);
+    default: return pipe_launch_one<TV, TX, 128, 4352, 512, 3>(h, p, values, alpha, x, beta, y);
     }
 }
 

@@ -52,7 +52,7 @@ def main():
     out = open(args.out, "a")
     combos = []
     for v in range(8):
-        for lanes in (1, 2, 4, 8):  # pipe: the "xhint" slot carries the forced lanes per row
+        for lanes in (0,):  # pipe: the "xhint" slot carries the forced lanes per row
             combos.append(("pipe", v, lanes, 1))
     for v in range(6):
         for xh in (0, 1):
