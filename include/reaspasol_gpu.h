@@ -82,7 +82,8 @@ typedef enum {
     RSG_SPMV_VECTOR = 3,   /* plain sub-warp-per-row, scalar loads (any alignment) */
     RSG_SPMV_SCALAR = 4,   /* plain thread-per-row, scalar loads */
     RSG_SPMV_STREAM = 5,   /* TMA bulk-staged tiles, one tile per CTA; thread-, sub-warp-, warp-, CTA-per-row */
-    RSG_SPMV_PIPE = 6      /* persistent CTAs, multi-stage TMA ring (mbarrier pipeline); same reductions */
+    RSG_SPMV_PIPE = 6,     /* persistent CTAs, multi-stage TMA ring (mbarrier pipeline); same reductions */
+    RSG_SPMV_TILE = 7      /* one TMA-staged tile per CTA (row pointers staged too), many small CTAs per SM */
 } rsg_spmv_algo;
 
 typedef enum {

@@ -81,7 +81,7 @@ int rsg_create(rsg_handle_t *handle, int device)
         delete h;
         return RSG_ALLOC_FAILED;
     }
-    h->spmv_plans.reserve(17);
+    h->spmv_plans.reserve(65);
     h->tri_plans.reserve(9);
     *handle = h;
     return RSG_OK;
@@ -164,8 +164,9 @@ int rsg_spmv_analysis(rsg_handle_t h, int m, int n, int nnz, int base, const int
 {
     if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    SpmvPlan *p = nullptr;
-    return spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p);
+    SpmvPlan *p = nullptr; // one plan per stored-value size (fp64 / fp32+mixed): the tile shape differs
+    RSG_TRY(spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p, 8));
+    return spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p, 4);
 }
 
 int spmv_csr_d(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
@@ -469,12 +470,19 @@ int rsg_matrix_spmv_host(rsg_handle_t h, rsg_matrix_t a, double alpha, const voi
     DeviceGuard g(h->device);
     cudaStream_t st = h->stream;
     const size_t xs = a->precision == 's' ? 4 : 8;
-    // pageable -> pinned staging -> device, like the harness's cudaMemcpy but asynchronous
-    std::memcpy(a->pin_x, x_host, xs * (size_t)a->n);
-    RSG_CUDA_TRY(cudaMemcpyAsync(a->x, a->pin_x, xs * (size_t)a->n, cudaMemcpyHostToDevice, st));
+    // pageable -> pinned staging -> device, like the harness's cudaMemcpy but asynchronous; a caller
+    // buffer that is already page-locked (cudaMallocHost / cudaHostRegister) is copied from directly
+    auto pinned = [](const void *p) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+        return at.type == cudaMemoryTypeHost;
+    };
+    const bool x_pinned = a->n > 0 && pinned(x_host), y_pinned = pinned(y_host);
+    if (!x_pinned) std::memcpy(a->pin_x, x_host, xs * (size_t)a->n);
+    RSG_CUDA_TRY(cudaMemcpyAsync(a->x, x_pinned ? x_host : a->pin_x, xs * (size_t)a->n, cudaMemcpyHostToDevice, st));
     if (beta != 0.0) {
-        std::memcpy(a->pin_y, y_host, xs * (size_t)a->m);
-        RSG_CUDA_TRY(cudaMemcpyAsync(a->y, a->pin_y, xs * (size_t)a->m, cudaMemcpyHostToDevice, st));
+        if (!y_pinned) std::memcpy(a->pin_y, y_host, xs * (size_t)a->m);
+        RSG_CUDA_TRY(cudaMemcpyAsync(a->y, y_pinned ? y_host : a->pin_y, xs * (size_t)a->m, cudaMemcpyHostToDevice, st));
     }
     int rc;
     if (a->precision == 'd')
@@ -487,9 +495,9 @@ int rsg_matrix_spmv_host(rsg_handle_t h, rsg_matrix_t a, double alpha, const voi
         rc = spmv_run<float, double>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
                                      alpha, static_cast<const double *>(a->x), beta, static_cast<double *>(a->y));
     RSG_TRY(rc);
-    RSG_CUDA_TRY(cudaMemcpyAsync(a->pin_y, a->y, xs * (size_t)a->m, cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaMemcpyAsync(y_pinned ? y_host : a->pin_y, a->y, xs * (size_t)a->m, cudaMemcpyDeviceToHost, st));
     RSG_CUDA_TRY(cudaStreamSynchronize(st));
-    std::memcpy(y_host, a->pin_y, xs * (size_t)a->m);
+    if (!y_pinned) std::memcpy(y_host, a->pin_y, xs * (size_t)a->m);
     return RSG_OK;
 }
 

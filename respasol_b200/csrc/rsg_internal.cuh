@@ -119,7 +119,7 @@ int ensure_cub_tmp(rsg_context *h, size_t bytes);
 
 // spmv.cu
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
-                  bool force_rebuild, SpmvPlan **out);
+                  bool force_rebuild, SpmvPlan **out, int vbytes = 8);
 void spmv_free_plan(SpmvPlan &p);
 template <typename TV, typename TX>
 int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
@@ -129,6 +129,9 @@ int row_partition(rsg_context *h, int m, int base, const int *rowptr, int ngpu, 
 
 // spmv_pipe.cu
 int pipe_num_variants();
+int tile_num_variants();
+template <typename TV, typename TX>
+int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 int pipe_build_plan(rsg_context *h, SpmvPlan &p);
 template <typename TV, typename TX>
 int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);

@@ -452,9 +452,9 @@ static int plan_signature(const rsg_context *h)
 }
 
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
-                  bool force_rebuild, SpmvPlan **out)
+                  bool force_rebuild, SpmvPlan **out, int vbytes)
 {
-    const int sig = plan_signature(h);
+    const int sig = plan_signature(h) + vbytes * 15485863; // the tile shape depends on the stored-value size
     for (size_t i = 0; i < h->spmv_plans.size(); ++i) {
         SpmvPlan &p = h->spmv_plans[i];
         if (p.rowptr == rowptr && p.colidx == colidx && p.m == m && p.n == n && p.nnz_hint == nnz_hint && p.base == base &&
@@ -465,7 +465,7 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
             break;
         }
     }
-    if (h->spmv_plans.size() >= 16) { // bounded cache: drop the oldest
+    if (h->spmv_plans.size() >= 64) { // bounded cache: drop the oldest
         spmv_free_plan(h->spmv_plans.front());
         h->spmv_plans.erase(h->spmv_plans.begin());
     }
@@ -491,15 +491,26 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
     int algo = h->opts[RSG_OPT_SPMV_ALGO];
     int variant = h->opts[RSG_OPT_SPMV_VARIANT];
     const bool aligned = (((uintptr_t)colidx) & 15) == 0;
+    const bool auto_algo = algo == RSG_SPMV_AUTO;
     if (algo == RSG_SPMV_AUTO) {
         // A row reduced by one CTA streams at one SM's share of the bandwidth (~1/148); past
         // roughly nnz/64 entries that single row outlasts the rest of the product: merge-path.
         const int cap = RowBlockShape<4096>::CAP;
         const long long skew = std::max<long long>(cap, (long long)p.nnz / 64);
-        algo = (p.max_row > skew) ? RSG_SPMV_MERGE : (aligned ? RSG_SPMV_PIPE : RSG_SPMV_ROWBLOCK);
+        algo = (p.max_row > skew) ? RSG_SPMV_MERGE : (aligned ? RSG_SPMV_TILE : RSG_SPMV_ROWBLOCK);
+        // measured on config 2 (tools/spmv_sweep.py): ~24-28 KB of entries per CTA is the sweet spot:
+        // 8-byte values -> 128 threads x 2304 entries, 4-byte values -> 128 threads x 4352 entries
+        // short rows (5-point stencils): more rows than threads per tile otherwise -> 256 threads
+        if (algo == RSG_SPMV_TILE) {
+            const double avg = (double)p.nnz / std::max(m, 1);
+            variant = vbytes >= 8 ? (avg < 12.0 ? 4 : 0) : (avg < 12.0 ? 0 : 1);
+        }
     }
-    if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE) && !aligned) algo = RSG_SPMV_ROWBLOCK; // bulk copies need 16-byte aligned arrays
-    const int nvar = algo == RSG_SPMV_STREAM ? kNumStreamVariants : algo == RSG_SPMV_PIPE ? pipe_num_variants() : kNumVariants;
+    (void)auto_algo;
+    if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)
+        algo = RSG_SPMV_ROWBLOCK; // bulk copies need 16-byte aligned arrays
+    const int nvar = algo == RSG_SPMV_STREAM ? kNumStreamVariants : algo == RSG_SPMV_PIPE ? pipe_num_variants()
+                   : algo == RSG_SPMV_TILE ? tile_num_variants() : kNumVariants;
     if (variant < 0 || variant >= nvar) variant = 0;
     p.variant = variant;
     p.tile = algo == RSG_SPMV_STREAM ? kStreamVariants[variant].tile : kVariants[variant].tile;
@@ -511,7 +522,7 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         p.bytes += sizeof(int) * ((size_t)p.nblk + 1);
         rowblock_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, rowptr, p.tile, p.nblk, p.blk_row);
         h->launches++;
-    } else if (algo == RSG_SPMV_PIPE && m > 0) {
+    } else if ((algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && m > 0) {
         RSG_TRY(pipe_build_plan(h, p));
     } else if (algo == RSG_SPMV_STREAM && m > 0) {
         const long long witems = (long long)kStreamW * m + p.nnz;
@@ -666,7 +677,7 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     if (m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || (m > 0 && !y)) return RSG_BAD_ARG;
     if (m == 0) return RSG_OK;
     SpmvPlan *p = nullptr;
-    RSG_TRY(spmv_get_plan(h, m, n, nnz_hint, base, rowptr, colidx, false, &p));
+    RSG_TRY(spmv_get_plan(h, m, n, nnz_hint, base, rowptr, colidx, false, &p, (int)sizeof(TV)));
     if (p->nnz > 0 && (!colidx || !values || !x)) return RSG_BAD_ARG;
     h->last_spmv_algo = p->algo;
     h->last_spmv_maxrow = p->max_row;
@@ -676,6 +687,10 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     case RSG_SPMV_ROWBLOCK:
         h->last_spmv_blocks = p->nblk;
         RSG_TRY((launch_rowblock<TV, TX>(h, p, vec, values, alpha, x, beta, y)));
+        break;
+    case RSG_SPMV_TILE:
+        if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays
+        RSG_TRY((tile_launch<TV, TX>(h, p, values, alpha, x, beta, y)));
         break;
     case RSG_SPMV_PIPE:
         if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays

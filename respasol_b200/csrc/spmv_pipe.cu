@@ -35,7 +35,7 @@ struct PipeMeta { // written by the producer, read by everybody after the mbarri
 
 // A tile that is not "simple" (see the kernel): any row lengths, multi-pass when it does not fit one
 // stage, CTA-per-row for a row longer than a stage.  Runs on the NC consumer threads (barrier 1).
-template <typename TV, typename TX, int NC, int CAPE, int XH, typename Stage>
+template <typename TV, typename TX, int NC, int CAPE, int XH, typename Stage, int BARID = 1, bool LEAN = false>
 __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeMeta &mt, int base, const int *__restrict__ colidx,
                                                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
                                                   TX alpha, TX beta, int reduce_opt, uint64_t spol, uint64_t xpol,
@@ -57,7 +57,7 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
             if (mt.staged_end < k1) { // only the last tile of a matrix whose entry count is not a multiple of 4
                 const int k = mt.staged_end + tid;
                 if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
-                group_sync<1, NC>();
+                group_sync<BARID, NC>();
             }
         } else { // synchronous multi-pass path for a tile that does not fit one stage
             if (s_rp[nr] - sb <= CAPE) {
@@ -71,7 +71,7 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
                 pe = lo;
             }
             if (pe == cur) { // this row alone exceeds a stage: CTA-per-row from global memory
-                const TX tot = cta_row_sum<TV, TX, NC, 1, true, 1>(k0, s_rp[cur + 1], colidx, values, x, base,
+                const TX tot = cta_row_sum<TV, TX, NC, 1, true, BARID>(k0, s_rp[cur + 1], colidx, values, x, base,
                                                                    reinterpret_cast<TX *>(s_val), spol);
                 if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
                 cur += 1;
@@ -89,7 +89,7 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
                 const int k = max(qe, sb) + tid;
                 if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
             }
-            group_sync<1, NC>();
+            group_sync<BARID, NC>();
             if (qe > sb) { mbar_wait(s_aux, aux_parity); aux_parity ^= 1; }
         }
         const int nrows = pe - cur;
@@ -102,16 +102,27 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
             if (g == 2) g = (avg <= 40 && mt.maxlen <= 64) ? 1 : 4;
         }
         const int *rp = s_rp + cur;
+        if (LEAN) {
+            switch (g) {
+            case 1: reduce_rows_lean<TV, TX, NC, 1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            case 2: reduce_rows_lean<TV, TX, NC, 2>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            case 4: reduce_rows_lean<TV, TX, NC, 4>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            case 8: reduce_rows_lean<TV, TX, NC, 8>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            case 16: reduce_rows_lean<TV, TX, NC, 16>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            default: reduce_rows_lean<TV, TX, NC, 32>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            }
+        } else {
         switch (g) {
-        case 1: reduce_rows_gather<TV, TX, NC, 1, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 2: reduce_rows_gather<TV, TX, NC, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 4: reduce_rows_gather<TV, TX, NC, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 8: reduce_rows_gather<TV, TX, NC, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        case 16: reduce_rows_gather<TV, TX, NC, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
-        default: reduce_rows_gather<TV, TX, NC, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 1: reduce_rows_gather<TV, TX, NC, 1, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 2: reduce_rows_gather<TV, TX, NC, 2, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 4: reduce_rows_gather<TV, TX, NC, 4, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 8: reduce_rows_gather<TV, TX, NC, 8, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            case 16: reduce_rows_gather<TV, TX, NC, 16, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            default: reduce_rows_gather<TV, TX, NC, 32, XH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, xpol, y, alpha, beta); break;
+            }
         }
         cur = pe;
-        if (!staged || cur < nr) group_sync<1, NC>(); // the synchronous path reuses the buffers
+        if (!staged || cur < nr) group_sync<BARID, NC>(); // the synchronous path reuses the buffers
         staged = false;
     }
 }
@@ -195,6 +206,52 @@ spmv_pipe_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
     }
 }
 
+// One tile per CTA (RSG_SPMV_TILE): the same plan and staging as the pipelined kernel, but the
+// latency is hidden by many small co-resident CTAs instead of a stage ring -- no residency hint in
+// __launch_bounds__, ptxas keeps the kernel at ~40 registers, 6-7 CTAs of 128 threads fit an SM.
+// Critical path of a CTA: descriptor load -> three bulk copies (row pointers, colidx, values) ->
+// mbarrier wait -> reduction.  No consumer-issued global load before the x gathers.
+template <typename TV, typename TX, int THREADS, int CAPE, int ROWS>
+__global__ void __launch_bounds__(THREADS)
+spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
+                 const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
+                 int nnz_end, int reduce_opt)
+{
+    typedef PipeStage<TV, CAPE, ROWS> Stage;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) uint64_t s_full;
+    __shared__ __align__(8) uint64_t s_aux;
+    const int tid = threadIdx.x;
+    const int4 d0 = desc[blockIdx.x], d1 = desc[blockIdx.x + 1];
+    if (tid == 0) { mbar_init(&s_full, 1); mbar_init(&s_aux, 1); }
+    __syncthreads();
+    const uint64_t spol = make_evict_first_policy();
+    PipeMeta mt;
+    mt.r0 = d0.x; mt.nr = d1.x - d0.x; mt.k0 = d0.y; mt.k1 = d1.y; mt.maxlen = d0.z; mt.pad = 0;
+    if (mt.nr <= 0) return;
+    const int ra = mt.r0 & ~3;
+    mt.rp_shift = mt.r0 - ra;
+    const uint32_t nrp = (uint32_t)((mt.rp_shift + mt.nr + 1 + 3) & ~3);
+    const int sb = mt.k0 & ~3;
+    int qe = min((mt.k1 + 3) & ~3, nnz_end & ~3);
+    const bool fits = (mt.k1 - sb) <= CAPE && qe > sb;
+    if (!fits) qe = sb;
+    mt.staged_end = fits ? qe : 0;
+    if (tid == 0) {
+        const uint32_t nq = (uint32_t)(qe - sb);
+        mbar_expect_tx(&s_full, nrp * 4u + nq * (uint32_t)(sizeof(TV) + sizeof(int)));
+        bulk_g2s(smem_raw + Stage::rp_off, rp0 + ra, nrp * 4u, &s_full, spol);
+        if (nq) {
+            bulk_g2s(smem_raw + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full, spol);
+            bulk_g2s(smem_raw + Stage::col_off, colidx + sb, nq * 4u, &s_full, spol);
+        }
+    }
+    mbar_wait(&s_full, 0);
+    uint32_t aux_parity = 0;
+    pipe_general_tile<TV, TX, THREADS, CAPE, 0, Stage, 0, true>(smem_raw, mt, base, colidx, values, x, y, alpha, beta, reduce_opt,
+                                                                spol, 0, &s_aux, aux_parity);
+}
+
 // desc[b] = (first row, its zero-based entry offset, longest row of the tile, 0); item coordinate
 // = entries + w*rows, so a tile holds at most tile/w rows and tile + (its last row) entries.
 __global__ void pipe_partition_kernel(int m, int base, const int *__restrict__ rowptr, int tile, int w, int ntiles, int4 *desc)
@@ -246,10 +303,17 @@ static const int kNumPipeVariants = (int)(sizeof(kPipeVariants) / sizeof(kPipeVa
 
 int pipe_num_variants() { return kNumPipeVariants; }
 
+static const PipeVariant kTileVariants[] = { // threads, entries per CTA, rows per CTA (stages unused)
+    {128, 2304, 512, 1}, {128, 4352, 512, 1}, {64, 1152, 256, 1}, {64, 2304, 512, 1},
+    {256, 4352, 512, 1}, {96, 3456, 384, 1}, {192, 6528, 768, 1}, {256, 8704, 1024, 1},
+};
+static const int kNumTileVariants = (int)(sizeof(kTileVariants) / sizeof(kTileVariants[0]));
+int tile_num_variants() { return kNumTileVariants; }
+
 int pipe_build_plan(rsg_context *h, SpmvPlan &p)
 {
     cudaStream_t st = h->stream;
-    const PipeVariant &v = kPipeVariants[p.variant];
+    const PipeVariant &v = p.algo == RSG_SPMV_TILE ? kTileVariants[p.variant] : kPipeVariants[p.variant];
     const int m = p.m;
     // tile: about one row per thread (rows_per_thread option scales it), within the stage capacity
     const int tmax = v.cape * 8 / 9;
@@ -323,6 +387,42 @@ int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, c
     default: return pipe_launch_one<TV, TX, 128, 4352, 512, 3>(h, p, values, alpha, x, beta, y);
     }
 }
+
+template <typename TV, typename TX, int THREADS, int CAPE, int ROWS>
+static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    const size_t smem = PipeStage<TV, CAPE, ROWS>::bytes;
+    auto kern = spmv_tile_kernel<TV, TX, THREADS, CAPE, ROWS>;
+    static bool configured = false; // per instantiation
+    if (!configured) {
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    kern<<<p->nblk, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc, p->first + p->nnz,
+                                                h->opts[RSG_OPT_SPMV_REDUCE]);
+    h->launches++;
+    h->last_spmv_blocks = p->nblk;
+    return RSG_OK;
+}
+
+template <typename TV, typename TX>
+int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
+{
+    switch (p->variant) {
+    case 1: return tile_launch_one<TV, TX, 128, 4352, 512>(h, p, values, alpha, x, beta, y);
+    case 2: return tile_launch_one<TV, TX, 64, 1152, 256>(h, p, values, alpha, x, beta, y);
+    case 3: return tile_launch_one<TV, TX, 64, 2304, 512>(h, p, values, alpha, x, beta, y);
+    case 4: return tile_launch_one<TV, TX, 256, 4352, 512>(h, p, values, alpha, x, beta, y);
+    case 5: return tile_launch_one<TV, TX, 96, 3456, 384>(h, p, values, alpha, x, beta, y);
+    case 6: return tile_launch_one<TV, TX, 192, 6528, 768>(h, p, values, alpha, x, beta, y);
+    case 7: return tile_launch_one<TV, TX, 256, 8704, 1024>(h, p, values, alpha, x, beta, y);
+    default: return tile_launch_one<TV, TX, 128, 2304, 512>(h, p, values, alpha, x, beta, y);
+    }
+}
+
+template int tile_launch<double, double>(rsg_context *, const SpmvPlan *, const double *, double, const double *, double, double *);
+template int tile_launch<float, float>(rsg_context *, const SpmvPlan *, const float *, float, const float *, float, float *);
+template int tile_launch<float, double>(rsg_context *, const SpmvPlan *, const float *, double, const double *, double, double *);
 
 template int pipe_launch<double, double>(rsg_context *, const SpmvPlan *, const double *, double, const double *, double, double *);
 template int pipe_launch<float, float>(rsg_context *, const SpmvPlan *, const float *, float, const float *, float, float *);

@@ -64,7 +64,7 @@ SMALL = {
 
 @pytest.mark.parametrize("name", sorted(SMALL))
 @pytest.mark.parametrize("precision", ["d", "s", "m"])
-@pytest.mark.parametrize("algo", ["auto", "pipe", "stream", "rowblock", "merge", "vector", "scalar"])
+@pytest.mark.parametrize("algo", ["auto", "tile", "pipe", "stream", "rowblock", "merge", "vector", "scalar"])
 def test_spmv_small(handle, name, precision, algo):
     a = SMALL[name]()
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -85,7 +85,7 @@ def test_golden_b1ss_values(handle):
 
 
 @pytest.mark.parametrize("precision", ["d", "s", "m"])
-@pytest.mark.parametrize("algo", ["pipe", "stream", "rowblock", "merge", "vector"])
+@pytest.mark.parametrize("algo", ["tile", "pipe", "stream", "rowblock", "merge", "vector"])
 def test_alpha_beta(handle, precision, algo):
     a = host.gen_stencil27(9, 10, 11, seed=5)
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -150,10 +150,11 @@ def test_stream_variants(handle, variant, reduce):
 @pytest.mark.parametrize("variant", list(range(8)))
 @pytest.mark.parametrize("reduce", [0, 1, 4, 32])
 @pytest.mark.parametrize("rpt", [0, 3])
-def test_pipe_variants(handle, variant, reduce, rpt):
-    """every compiled (threads, stage capacity, stages) shape of the pipelined kernel: fitting tiles,
-    multi-pass tiles (rows longer than the tile slack), CTA-per-row rows, a ragged last quad"""
-    handle.set_option("SPMV_ALGO", ALGO["pipe"])
+@pytest.mark.parametrize("algo", ["pipe", "tile"])
+def test_pipe_variants(handle, variant, reduce, rpt, algo):
+    """every compiled shape of the pipelined (persistent, stage ring) and tile (one tile per CTA) kernels:
+    fitting tiles, multi-pass tiles (rows longer than the tile slack), CTA-per-row rows, a ragged last quad"""
+    handle.set_option("SPMV_ALGO", ALGO[algo])
     handle.set_option("SPMV_VARIANT", variant)
     handle.set_option("SPMV_REDUCE", reduce)
     handle.set_option("SPMV_ROWS_PER_THREAD", rpt)
@@ -180,7 +181,12 @@ def test_pipe_variants(handle, variant, reduce, rpt):
 def test_pipe_tiny_tiles_and_slabs(handle):
     """tile size forced down to 64 items: many tiles per CTA, empty tiles inside long rows, slab views
     whose first entry is not entry 0"""
-    handle.set_option("SPMV_ALGO", ALGO["pipe"])
+    for algo in ("pipe", "tile"):
+        _tiny_tiles(handle, algo)
+
+
+def _tiny_tiles(handle, algo):
+    handle.set_option("SPMV_ALGO", ALGO[algo])
     handle.set_option("SPMV_LONG_ROW", 64)
     try:
         for a in (host.gen_stencil27(12, 12, 30, 10, 20, seed=2), host.gen_powerlaw(3000, 2.2, 48, 2, 2500, 4),
@@ -318,7 +324,7 @@ def test_full_size_configs(handle, name):
     if name == "C4":
         assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
     else:
-        assert handle.info("SPMV_ALGO_USED") == ALGO["pipe"]
+        assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
     # linearity: A(2x + 1) = 2 A x + A 1
     A = DeviceCSR(a, "d")
     xd = torch.from_numpy(x).cuda()

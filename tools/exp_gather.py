@@ -21,6 +21,24 @@ R = 3
 rows = np.repeat(np.arange(a.m, dtype=np.int32), np.diff(a.rowptr))
 rng = np.random.default_rng(1)
 cols = {"real": a.colidx, "own_row": rows, "random": np.sort(rng.integers(0, a.n, size=(a.m, 1), dtype=np.int32).repeat(1, 1), axis=1).ravel()[rows] if False else rng.integers(0, a.n, size=a.stored, dtype=np.int32)}
+# ceiling: plain streaming reads of the same number of bytes (torch.sum = CUB reduce) and a copy
+for nbytes in (340e6, 680e6):
+    n = int(nbytes // 8)
+    bufs = [torch.ones(n, dtype=torch.float64, device="cuda") for _ in range(3)]
+    for name, fn, moved in (("sum(read)", lambda b: b.sum(), 1), ("copy(r+w)", lambda b: bufs[0].copy_(b) if b is not bufs[0] else bufs[1].copy_(b), 2)):
+        for b in bufs:
+            fn(b)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(60):
+            fn(bufs[i % 3])
+        e1.record()
+        torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) / 60 * 1e3
+        print("ceiling %s %.0f MB: %.2f us  %.0f GB/s" % (name, nbytes / 1e6, us, moved * n * 8 / us * 1e-3), flush=True)
+    del bufs
+    torch.cuda.empty_cache()
 for prec in ("d", "s"):
     xt = torch.float32 if prec == "s" else torch.float64
     x = torch.ones(a.n, dtype=xt, device="cuda")
@@ -31,7 +49,7 @@ for prec in ("d", "s"):
             A.colidx = torch.from_numpy(np.ascontiguousarray(c)).cuda()
             mats.append(A)
         y = torch.empty(a.m, dtype=xt, device="cuda")
-        for algo, var in (("pipe", 0), ("pipe", 3), ("pipe", 6), ("stream", 2), ("stream", 0), ("rowblock", 2)):
+        for algo, var in (("tile", 0), ("tile", 1), ("tile", 2), ("stream", 2), ("stream", 0), ("pipe", 3)):
             h.set_option("SPMV_ALGO", ALGO[algo])
             h.set_option("SPMV_VARIANT", var)
             for A in mats:

@@ -54,6 +54,9 @@ def main():
     for v in range(8):
         for lanes in (0,):  # pipe: the "xhint" slot carries the forced lanes per row
             combos.append(("pipe", v, lanes, 1))
+    for v in range(8):
+        for ts in (0,):  # tile: the "xhint" slot carries the tile size (0 = heuristic)
+            combos.append(("tile", v, ts, 1))
     for v in range(6):
         for xh in (0, 1):
             combos.append(("stream", v, xh, 1))
@@ -81,7 +84,8 @@ def main():
             for algo, var, xh, hint in combos:
                 h.set_option("SPMV_ALGO", ALGO[algo])
                 h.set_option("SPMV_VARIANT", var)
-                h.set_option("SPMV_X_HINT", xh if algo != "pipe" else 0)
+                h.set_option("SPMV_X_HINT", xh if algo not in ("pipe", "tile") else 0)
+                h.set_option("SPMV_LONG_ROW", xh if algo == "tile" else 0)
                 h.set_option("SPMV_REDUCE", xh if algo == "pipe" else 0)
                 h.set_option("SPMV_CACHE_HINT", hint if algo != "pipe" else 1)
                 h.set_option("SPMV_ROWS_PER_THREAD", hint if algo == "pipe" else 0)
@@ -112,6 +116,7 @@ def main():
     h.set_option("SPMV_ALGO", 0)
     h.set_option("SPMV_ROWS_PER_THREAD", 0)
     h.set_option("SPMV_REDUCE", 0)
+    h.set_option("SPMV_LONG_ROW", 0)
     h.close()
 
 
