@@ -72,6 +72,10 @@ typedef enum {
     RSG_OPT_SPMV_X_HINT = 8,    /* stream/pipe kernels: 1 = gather x with an L2 evict_last hint */
     RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* pipe kernel: tile size in rows per thread (0 = 1) */
     RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* pipe kernel: cap on resident CTAs per SM (0 = occupancy limit) */
+    RSG_OPT_TRSV_BATCH = 11,    /* sync-free solves: solution entries polled per round trip (1,2,4,8; 0 = default) */
+    RSG_OPT_TRSV_GATE = 12,     /* sync-free solves: 1 = a row first polls only its deepest dependency, 2 = off, 0 = default */
+    RSG_OPT_TRI_CTAS_PER_SM = 13, /* sync-free ILU0 / solves: cap on resident CTAs per SM (0 = default) */
+    RSG_OPT_TRSV_BLOCK = 14,    /* sync-free solves: threads per CTA (multiple of 32, <= 256; 0 = default) */
     RSG_OPT_COUNT_
 } rsg_option;
 

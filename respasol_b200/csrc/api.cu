@@ -202,7 +202,9 @@ int rsg_ilu0_analysis(rsg_handle_t h, int n, int nnz, int base, const int *rowpt
     RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, true, &p));
     if (zero_pivot_row) *zero_pivot_row = p->missing_diag_row;
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
-    return tri_build_levels(h, p, 0);
+    // both patterns in one launch: the L and U dependency chains overlap, and the harness asks for
+    // the U levels right afterwards anyway (ilu0.cu:229-252)
+    return tri_build_levels(h, p, -1);
 }
 
 int rsg_sptrsv_analysis(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx)
@@ -212,8 +214,7 @@ int rsg_sptrsv_analysis(rsg_handle_t h, int n, int nnz, int base, const int *row
     TriPlan *p = nullptr;
     RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
-    RSG_TRY(tri_build_levels(h, p, 0));
-    return tri_build_levels(h, p, 1);
+    return tri_build_levels(h, p, -1);
 }
 
 extern "C++" template <typename T>

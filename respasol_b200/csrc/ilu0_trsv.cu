@@ -20,6 +20,11 @@
 namespace rsg {
 
 #define RSG_SPIN_LIMIT (1 << 22) // sweeps before a waiting row gives up (malformed schedule)
+// measured on config 3 (tools/tri_sweep.py, profiles/r1_tri_sweep.log): 8 entries per poll, no gate,
+// and only ~32 levels' worth of rows in flight -- every extra waiting row is polling traffic in L2
+// that slows the rows on the dependency chain down (2.8 ms with every row resident, 1.4 ms so).
+#define RSG_TRSV_DEFAULT_BATCH 8
+#define RSG_TRSV_DEFAULT_GATE 0
 
 // ------------------------------------------------------------------ flags / sentinels
 __device__ __forceinline__ int ld_acquire(const int *p)
@@ -76,14 +81,90 @@ template <> __device__ __forceinline__ float div_t(float a, float b) { return __
 
 // ------------------------------------------------------------------ ILU(0), warp per row
 // ctl[0] ticket, ctl[1] timeout flag, ctl[2] smallest row with a zero pivot
-template <typename T, int WARPS, int WCAP>
+//
+// Row i needs, for every lower entry k (ascending):  l_ik = a_ik / u_kk,  then  a_ij -= l_ik u_kj
+// for the j > k stored in both rows.  Which entry of row k lands on which position of row i is a
+// property of the PATTERN, so the warp works that out (the "candidate list": source position in
+// `values`, destination slot in the staged row) while the rows it depends on are still being
+// factorized -- warps draw tickets several levels ahead of the wavefront.  What is left on the
+// dependency chain of a level is: see the flag, fetch the values of the list in ONE round trip,
+// run the short fma chain out of shared memory, write the row, release the flag.  Lower entries
+// are consumed in ready-prefix runs, so only the entries of the LAST level are processed after
+// the final flag arrives.
+
+// Generic path (row or candidate list too long for the staging buffers): everything in global
+// memory, one lower entry at a time.
+template <typename T>
+__device__ __noinline__ void ilu0_row_generic(int lane, int i, int rs, int len, int nl, int base, const int *__restrict__ rowptr,
+                                              const int *__restrict__ colidx, T *values, const int *__restrict__ diag_pos,
+                                              const int *done, int epoch, int *ctl)
+{
+    const int *rc = colidx + rs;
+    volatile T *rv = values + rs;
+    for (int c0 = 0; c0 < nl; c0 += 32) {
+        // lane <-> lower entry c0+lane: wait for its row, fetch that row's pivot and extent
+        const int lk = c0 + lane;
+        const bool mine = lk < nl;
+        int k = 0, dpk = 0, rek = 0;
+        T ukk = 1;
+        if (mine) k = rc[lk] - base;
+        bool ready = !mine;
+        int spins = 0;
+        while (!__all_sync(0xffffffffu, ready)) {
+            if (!ready) ready = (ld_acquire(done + k) == epoch);
+            if (++spins > RSG_SPIN_LIMIT) { if (lane == 0) atomicExch(ctl + 1, 1); break; }
+        }
+        __syncwarp();
+        if (mine) {
+            dpk = diag_pos[k];
+            rek = rowptr[k + 1] - base;
+            ukk = __ldcg(values + dpk);
+        }
+        const int cnt = min(32, nl - c0);
+        for (int u = 0; u < cnt; ++u) {
+            const int dk = __shfl_sync(0xffffffffu, dpk, u);
+            const int ek = __shfl_sync(0xffffffffu, rek, u);
+            const T pk = __shfl_sync(0xffffffffu, ukk, u);
+            T lik = 0;
+            if (lane == 0) {
+                lik = div_t<T>(rv[c0 + u], pk);
+                rv[c0 + u] = lik;
+            }
+            lik = __shfl_sync(0xffffffffu, lik, 0);
+            for (int jj = dk + 1 + lane; jj < ek; jj += 32) {
+                const int jraw = colidx[jj];
+                const T ukj = __ldcg(values + jj);
+                int lo = c0 + u + 1, hi = len;
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (rc[mid] < jraw) lo = mid + 1; else hi = mid;
+                }
+                if (lo < len && rc[lo] == jraw) rv[lo] = fma_t<T>(-lik, ukj, rv[lo]);
+            }
+            __syncwarp();
+        }
+    }
+    if (lane == 0 && rv[nl] == (T)0) atomicMin(ctl + 2, i);
+}
+
+template <typename T, int WARPS, int WCAP, int LCAP>
 __global__ void __launch_bounds__(WARPS * 32)
 ilu0_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx, T *values,
             const int *__restrict__ diag_pos, const int *__restrict__ order, int *done, int epoch, int *ctl)
 {
-    __shared__ int s_col[WARPS][WCAP];
-    __shared__ T s_val[WARPS][WCAP];
+    constexpr unsigned short NONE = 0xffff;
+    __shared__ int s_col[WARPS][WCAP];            // row i: raw column indices
+    __shared__ T s_val[WARPS][WCAP];              // row i: values, updated in place
+    __shared__ int s_koff[WARPS][WCAP + 1];       // lower entry u owns candidates [koff[u], koff[u+1])
+    __shared__ int s_kb[WARPS][WCAP];             // first upper position of row k_u (diag_pos[k_u] + 1)
+    __shared__ int s_src[WARPS][LCAP];            // candidate: position in `values` of u_kj
+    __shared__ unsigned short s_dst[WARPS][LCAP]; // candidate: slot of a_ij in the staged row, NONE = no fill
+    __shared__ T s_uv[WARPS][LCAP];               // candidate: fetched u_kj
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int *col = s_col[w], *koff = s_koff[w], *kbeg = s_kb[w], *src = s_src[w];
+    unsigned short *dst = s_dst[w];
+    volatile T *val = s_val[w];
+    T *uv = s_uv[w];
     for (;;) {
         int t = 0;
         if (lane == 0) t = (*(volatile int *)(ctl + 1)) ? n : atomicAdd(ctl, 1); // stop drawing rows after a timeout
@@ -92,71 +173,114 @@ ilu0_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restri
         const int i = order[t];
         const int rs = rowptr[i] - base, len = rowptr[i + 1] - base - rs;
         const int nl = diag_pos[i] - rs; // lower entries are [0,nl) of the row (columns sorted)
-        const bool staged = len <= WCAP;
-        const int *rc;
-        volatile T *rv;
-        if (staged) {
-            for (int l = lane; l < len; l += 32) { s_col[w][l] = colidx[rs + l]; s_val[w][l] = values[rs + l]; }
-            rc = s_col[w];
-            rv = s_val[w];
-        } else {
-            rc = colidx + rs;
-            rv = values + rs;
-        }
-        __syncwarp();
-        for (int c0 = 0; c0 < nl; c0 += 32) {
-            // lane <-> lower entry c0+lane: wait for its row, fetch that row's pivot and extent
-            const int lk = c0 + lane;
-            const bool mine = lk < nl;
-            int k = 0, dpk = 0, rek = 0;
-            T ukk = 1;
-            if (mine) k = rc[lk] - base;
-            bool ready = !mine;
-            int spins = 0;
-            while (!__all_sync(0xffffffffu, ready)) {
-                if (!ready) ready = (ld_acquire(done + k) == epoch);
-                if (++spins > RSG_SPIN_LIMIT) { if (lane == 0) atomicExch(ctl + 1, 1); break; }
-            }
-            __threadfence();
+        bool fast = len <= WCAP;
+        int tot = 0;
+        if (fast) {
+            // ---- structure only: stage the row, size the candidate list
+            for (int l = lane; l < len; l += 32) { col[l] = colidx[rs + l]; val[l] = values[rs + l]; }
             __syncwarp();
-            if (mine) {
-                dpk = diag_pos[k];
-                rek = rowptr[k + 1] - base;
-                ukk = __ldcg(values + dpk);
-            }
-            const int cnt = min(32, nl - c0);
-            for (int u = 0; u < cnt; ++u) {
-                const int dk = __shfl_sync(0xffffffffu, dpk, u);
-                const int ek = __shfl_sync(0xffffffffu, rek, u);
-                const T pk = __shfl_sync(0xffffffffu, ukk, u);
-                T lik = 0;
-                if (lane == 0) {
-                    lik = div_t<T>(rv[c0 + u], pk);
-                    rv[c0 + u] = lik;
+            for (int c0 = 0; c0 < nl; c0 += 32) {
+                const int lk = c0 + lane;
+                int cnt = 0, kb = 0;
+                if (lk < nl) {
+                    const int k = col[lk] - base;
+                    kb = diag_pos[k] + 1;
+                    cnt = rowptr[k + 1] - base - kb;
                 }
-                lik = __shfl_sync(0xffffffffu, lik, 0);
-                for (int jj = dk + 1 + lane; jj < ek; jj += 32) {
-                    const int jraw = colidx[jj];
-                    const T ukj = __ldcg(values + jj);
-                    int lo = c0 + u + 1, hi = len;
-                    while (lo < hi) {
-                        const int mid = (lo + hi) >> 1;
-                        if (rc[mid] < jraw) lo = mid + 1; else hi = mid;
+                int incl = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += v;
+                }
+                if (lk < nl) { kbeg[lk] = kb; koff[lk] = tot + incl - cnt; }
+                tot += __shfl_sync(0xffffffffu, incl, 31);
+            }
+            if (lane == 0) koff[nl] = tot;
+            __syncwarp();
+            fast = tot <= LCAP;
+        }
+        if (!fast) {
+            ilu0_row_generic<T>(lane, i, rs, len, nl, base, rowptr, colidx, values, diag_pos, done, epoch, ctl);
+        } else {
+            // ---- structure only: match every upper entry of every row k against row i
+            for (int c = lane; c < tot; c += 32) {
+                int lo = 0, hi = nl; // u = the lower entry with koff[u] <= c < koff[u+1]
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (koff[mid] <= c) lo = mid; else hi = mid;
+                }
+                const int sp = kbeg[lo] + (c - koff[lo]);
+                const int jraw = colidx[sp];
+                int a = lo + 1, b = len;
+                while (a < b) {
+                    const int mid = (a + b) >> 1;
+                    if (col[mid] < jraw) a = mid + 1; else b = mid;
+                }
+                src[c] = sp;
+                dst[c] = (a < len && col[a] == jraw) ? (unsigned short)a : NONE;
+            }
+            __syncwarp();
+            // ---- the dependent part
+            bool timed_out = false;
+            for (int c0 = 0; c0 < nl && !timed_out; c0 += 32) {
+                const int lk = c0 + lane;
+                const bool mine = lk < nl;
+                const int cnt = min(32, nl - c0);
+                const int k = mine ? col[lk] - base : 0;
+                bool ready = !mine;
+                int processed = 0, spins = 0;
+                while (processed < cnt) {
+                    if (!ready) ready = (ld_acquire(done + k) == epoch);
+                    const unsigned mask = __ballot_sync(0xffffffffu, ready);
+                    const unsigned pend = ~(mask >> processed); // bit 0 <-> entry `processed` of the chunk
+                    int run = pend ? __ffs((int)pend) - 1 : 32;
+                    run = min(run, cnt - processed);
+                    if (run == 0) {
+                        if (++spins > RSG_SPIN_LIMIT) { if (lane == 0) atomicExch(ctl + 1, 1); timed_out = true; break; }
+                        continue;
                     }
-                    if (lo < len && rc[lo] == jraw) rv[lo] = fma_t<T>(-lik, ukj, rv[lo]);
+                    __syncwarp(); // the acquiring lanes' observations now order every lane's loads below
+                    const int ua = c0 + processed, ub = ua + run;
+                    const int cb = koff[ua], ce = koff[ub];
+                    for (int c = cb + lane; c < ce; c += 128) {
+                        T v[4];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const int cc = c + 32 * q;
+                            v[q] = (cc < ce && dst[cc] != NONE) ? __ldcg(values + src[cc]) : (T)0;
+                        }
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            const int cc = c + 32 * q;
+                            if (cc < ce) uv[cc] = v[q];
+                        }
+                    }
+                    T piv = 1;
+                    if (lane >= processed && lane < processed + run) piv = __ldcg(values + kbeg[lk] - 1);
+                    __syncwarp();
+                    for (int u = ua; u < ub; ++u) {
+                        const T pk = __shfl_sync(0xffffffffu, piv, u - c0);
+                        const T aik = val[u];
+                        __syncwarp();
+                        const T lik = div_t<T>(aik, pk);
+                        for (int c = koff[u] + lane; c < koff[u + 1]; c += 32) {
+                            const unsigned short d = dst[c];
+                            if (d != NONE) val[d] = fma_t<T>(-lik, uv[c], val[d]);
+                        }
+                        if (lane == 0) val[u] = lik;
+                        __syncwarp();
+                    }
+                    processed += run;
                 }
-                __syncwarp();
             }
+            for (int l = lane; l < len; l += 32) values[rs + l] = val[l];
+            if (lane == 0 && val[nl] == (T)0) atomicMin(ctl + 2, i);
         }
-        if (staged)
-            for (int l = lane; l < len; l += 32) values[rs + l] = s_val[w][l];
-        if (lane == 0 && rv[nl] == (T)0) atomicMin(ctl + 2, i);
-        __threadfence();
+        // the row is written: publish it (lane 0's release is cumulative over the warp's stores
+        // that the warp barrier ordered before it)
         __syncwarp();
-        if (lane == 0) {
-            __threadfence();
-            st_release(done + i, epoch);
-        }
+        if (lane == 0) st_release(done + i, epoch);
         __syncwarp();
     }
 }
@@ -174,14 +298,20 @@ template <typename T> __global__ void fill_pending_kernel(int n, T *a, T *b)
 // UPPER = false:  z_i = b_i - sum_{j<i} l_ij z_j            (unit diagonal)
 // UPPER = true :  y_i = (z_i - sum_{j>i} u_ij y_j) / u_ii
 // `sol` is pre-filled with the pending sentinel; rhs is b (lower) or z (upper).
-template <typename T, bool UPPER>
+// A thread keeps a batch of B entries of its row (column, coefficient) in registers and polls the
+// B solution entries in one round trip; the ready prefix is consumed in stored order (the fma
+// chain is the oracle's), the rest is polled again on the next sweep without re-reading the row.
+// The diagonal of U is fetched before the first wait, off the dependency chain.
+// GATE: until the dependency with the deepest level (crit[i], recorded by the level kernel) is
+// written, a row polls that ONE entry only -- rows far ahead of the wavefront then cost one L2
+// request per sweep instead of B.
+template <typename T, bool UPPER, int B, bool GATE>
 __global__ void __launch_bounds__(256)
 trsv_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
             const T *__restrict__ lu, const int *__restrict__ diag_pos, const int *__restrict__ order,
-            const T *__restrict__ rhs, T *sol, int *ctl)
+            const int *__restrict__ crit, const T *__restrict__ rhs, T *sol, int *ctl)
 {
     typedef Pending<T> P;
-    constexpr int B = 4; // dependencies fetched per round trip
     const int lane = threadIdx.x & 31;
     for (;;) {
         int t0 = 0;
@@ -190,42 +320,49 @@ trsv_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restri
         if (t0 >= n) break;
         const int t = t0 + lane;
         const bool have = t < n;
-        int i = 0, k = 0, ke = 0, kd = 0;
-        T s = 0;
+        int i = 0, k = 0, ke = 0, gate = -1;
+        T s = 0, dg = 1;
         if (have) {
             i = order[t];
-            kd = diag_pos[i];
-            if (UPPER) { k = kd + 1; ke = rowptr[i + 1] - base; }
+            if (GATE) gate = crit[i];
+            const int kd = diag_pos[i];
+            if (UPPER) { k = kd + 1; ke = rowptr[i + 1] - base; dg = lu[kd]; }
             else { k = rowptr[i] - base; ke = kd; }
             s = rhs[i];
         }
+        int col[B];
+        T a[B];
+        int nb = 0, head = 0; // cached entries k .. k+nb, of which [0,head) are consumed
         bool done = !have;
         int spins = 0;
         while (!__all_sync(0xffffffffu, done)) {
-            if (!done) {
-                while (k < ke) {
-                    const int nb = min(B, ke - k);
+            if (GATE && !done && gate >= 0 && P::load(sol + gate) != P::kBits) gate = -1;
+            if (!done && gate < 0) {
+                for (;;) {
+                    if (head == nb) {
+                        k += nb;
+                        head = 0;
+                        nb = min(B, ke - k);
+                        if (nb <= 0) {
+                            P::store(sol + i, UPPER ? div_t<T>(s, dg) : s);
+                            done = true;
+                            break;
+                        }
+#pragma unroll
+                        for (int u = 0; u < B; ++u)
+                            if (u < nb) { col[u] = colidx[k + u] - base; a[u] = lu[k + u]; }
+                    }
                     typename P::bits_t v[B];
-                    T a[B];
 #pragma unroll
                     for (int u = 0; u < B; ++u)
-                        if (u < nb) {
-                            v[u] = P::load(sol + (colidx[k + u] - base));
-                            a[u] = lu[k + u];
-                        }
-                    int adv = 0;
+                        if (u >= head && u < nb) v[u] = P::load(sol + col[u]);
 #pragma unroll
                     for (int u = 0; u < B; ++u)
-                        if (u < nb && adv == u && v[u] != P::kBits) {
+                        if (u == head && u < nb && v[u] != P::kBits) {
                             s = fma_t<T>(-a[u], P::value(v[u]), s);
-                            adv = u + 1;
+                            head = u + 1;
                         }
-                    k += adv;
-                    if (adv < nb) break; // a dependency is still pending: next sweep
-                }
-                if (k >= ke) {
-                    P::store(sol + i, UPPER ? div_t<T>(s, lu[kd]) : s);
-                    done = true;
+                    if (head < nb) break; // a dependency is still pending: next sweep
                 }
             }
             if (++spins > RSG_SPIN_LIMIT) { atomicExch(ctl + 1, 1); break; }
@@ -298,11 +435,13 @@ int ilu0_run(rsg_context *h, TriPlan *p, T *values, int *zero_pivot_row)
     }
     h->pinned_i[8] = 0; h->pinned_i[9] = 0; h->pinned_i[10] = 0x7fffffff; h->pinned_i[11] = 0;
     RSG_CUDA_TRY(cudaMemcpyAsync(p->ctl, h->pinned_i + 8, 4 * sizeof(int), cudaMemcpyHostToDevice, st));
-    constexpr int WARPS = 8, WCAP = 128;
-    auto kern = ilu0_kernel<T, WARPS, WCAP>;
+    constexpr int WARPS = 4, WCAP = 128, LCAP = 512;
+    auto kern = ilu0_kernel<T, WARPS, WCAP, LCAP>;
     int per_sm = 0;
     RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WARPS * 32, 0));
-    const int grid = std::max(1, std::min(h->sm_count * std::max(per_sm, 1), (p->n + WARPS - 1) / WARPS));
+    per_sm = std::max(per_sm, 1);
+    if (h->opts[RSG_OPT_TRI_CTAS_PER_SM] > 0) per_sm = std::min(per_sm, h->opts[RSG_OPT_TRI_CTAS_PER_SM]);
+    const int grid = std::max(1, std::min(h->sm_count * per_sm, (p->n + WARPS - 1) / WARPS));
     kern<<<grid, WARPS * 32, 0, st>>>(p->n, p->base, p->rowptr, p->colidx, values, p->diag_pos, p->order[0], p->done,
                                       p->epoch, p->ctl);
     h->launches++;
@@ -351,8 +490,7 @@ int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
     if (p->n == 0) return RSG_OK;
     if (!lu || !b || !z || !y || b == z || z == y || b == y) return RSG_BAD_ARG;
-    RSG_TRY(tri_build_levels(h, p, 0));
-    RSG_TRY(tri_build_levels(h, p, 1));
+    RSG_TRY(tri_build_levels(h, p, -1));
     cudaStream_t st = h->stream;
     const int n = p->n;
     if (h->opts[RSG_OPT_TRSV_ALGO] == 2) {
@@ -364,10 +502,31 @@ int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
     RSG_CUDA_TRY(cudaMemsetAsync(p->ctl, 0, 8 * sizeof(int), st));
     fill_pending_kernel<T><<<(n + 255) / 256, 256, 0, st>>>(n, z, y);
     int per_sm = 0;
-    RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trsv_kernel<T, false>, 256, 0));
-    const int grid = std::max(1, std::min(h->sm_count * std::max(per_sm, 1), (n + 255) / 256));
-    trsv_kernel<T, false><<<grid, 256, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[0], b, z, p->ctl);
-    trsv_kernel<T, true><<<grid, 256, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[1], z, y, p->ctl + 4);
+    int batch = h->opts[RSG_OPT_TRSV_BATCH];
+    if (batch != 1 && batch != 2 && batch != 4 && batch != 8) batch = RSG_TRSV_DEFAULT_BATCH;
+    const bool gate = h->opts[RSG_OPT_TRSV_GATE] ? h->opts[RSG_OPT_TRSV_GATE] == 1 : (RSG_TRSV_DEFAULT_GATE != 0);
+    int block = h->opts[RSG_OPT_TRSV_BLOCK];
+    if (block < 32 || block > 256 || (block & 31)) block = 64;
+    typedef void (*kern_t)(int, int, const int *, const int *, const T *, const int *, const int *, const int *, const T *, T *, int *);
+    kern_t kl = nullptr, ku = nullptr;
+#define RSG_PICK(BB, GG) { kl = trsv_kernel<T, false, BB, GG>; ku = trsv_kernel<T, true, BB, GG>; }
+    if (gate) { if (batch == 1) RSG_PICK(1, true) else if (batch == 2) RSG_PICK(2, true) else if (batch == 4) RSG_PICK(4, true) else RSG_PICK(8, true) }
+    else { if (batch == 1) RSG_PICK(1, false) else if (batch == 2) RSG_PICK(2, false) else if (batch == 4) RSG_PICK(4, false) else RSG_PICK(8, false) }
+#undef RSG_PICK
+    RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ku, block, 0));
+    per_sm = std::max(per_sm, 1);
+    int grid;
+    if (h->opts[RSG_OPT_TRI_CTAS_PER_SM] > 0) {
+        grid = h->sm_count * std::min(per_sm, h->opts[RSG_OPT_TRI_CTAS_PER_SM]);
+    } else {
+        // rows in flight ~ 32 x the average level width, at least one CTA per SM
+        const long long width = std::max(1, n / std::max(1, std::min(p->nlevels[0], p->nlevels[1])));
+        const long long want = (32 * width + block - 1) / block;
+        grid = (int)std::min<long long>((long long)h->sm_count * per_sm, std::max<long long>(h->sm_count, want));
+    }
+    grid = std::max(1, std::min(grid, (n + block - 1) / block));
+    kl<<<grid, block, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[0], p->crit[0], b, z, p->ctl);
+    ku<<<grid, block, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[1], p->crit[1], z, y, p->ctl + 4);
     h->launches += 3;
     RSG_CUDA_TRY(cudaGetLastError());
     return RSG_OK;

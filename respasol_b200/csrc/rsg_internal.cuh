@@ -70,10 +70,15 @@ struct TriPlan {
     int *lev[2] = {nullptr, nullptr};       // level of every row
     int *order[2] = {nullptr, nullptr};     // rows sorted by (level, row): "level_rows"
     int *level_ptr[2] = {nullptr, nullptr}; // nlevels+1 offsets into order (device)
+    int *crit[2] = {nullptr, nullptr};      // per row: the dependency (zero-based column) with the deepest level, -1 if none
     std::vector<int> level_ptr_host[2];
     int *done = nullptr;           // per-row dependency flags (epoch-stamped)
     int epoch = 0;
-    int *ctl = nullptr;            // [0] ticket counter, [1] error flag, [2] min zero-pivot row, [3] 2nd ticket
+    int *ctl = nullptr;            // 16 ints: [0] ticket, [1] error flag, [2] min zero-pivot row; [4..7] second kernel
+    int *sort_keys = nullptr;      // radix-sort scratch (n ints each)
+    int *sort_vals = nullptr;
+    int *slab = nullptr;           // ONE allocation holding every array above (re-used when the analysis is re-run)
+    int slab_n = 0;
     size_t bytes = 0;
 };
 
@@ -139,7 +144,7 @@ int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, c
 // levels.cu
 int tri_get_plan(rsg_context *h, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
                  bool force_rebuild, TriPlan **out);
-int tri_build_levels(rsg_context *h, TriPlan *p, int which);
+int tri_build_levels(rsg_context *h, TriPlan *p, int which); // which = -1: both, one launch
 void tri_free_plan(TriPlan &p);
 
 // ilu0_trsv.cu
