@@ -206,24 +206,59 @@ def run_ours(args):
     else:
         row_starts = np.arange(world + 1, dtype=np.int64) * a.m
         ops = []
+        hp = Handle(local_rank)  # the push kernels run on a stream of their own, beside the product
+        side = torch.cuda.Stream(device=dev)
+        with torch.cuda.stream(side):
+            hp.use_current_stream()
+        if args.exchange == "p2p-barrier":
+            hp.use_current_stream()
+        push = hp.halo_push
         for r in range(REPLICAS):
-            op = RowBlockSpmv(a, row_starts, "halo", lambda c: DeviceCSR(c, "d", dev),
-                              lambda A, x, y: h.spmv(A, x, y), dev, torch.float64)
+            op = RowBlockSpmv(a, row_starts, "p2p" if args.exchange.startswith("p2p") else "halo", lambda c: DeviceCSR(c, "d", dev),
+                              lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
+                              view=(lambda A, r0, r1: A.view_rows(r0, r1)) if args.overlap else None,
+                              push=(push, None if args.exchange == "p2p-barrier" else h.spmv_halo_wait), side=side)
             op.set_x(torch.from_numpy(xs).to(dev))
-            h.spmv_analysis(op.A)
+            if op.p2p is not None and op.p2p[1] is not None:
+                h.set_option("SPMV_HALO_START", op.plan.halo_base)  # marks the tiles that must wait for the peers
+            for A in ([piece for piece, _, _ in op.split] if op.split else [op.A]):
+                h.spmv_analysis(A)
             ops.append(op)
         yd = [op.y for op in ops]
+        if args.graph:
+            for op in ops:
+                for _ in range(3):  # eager steps first: plans, NCCL channels, allocator all settled
+                    op.step()
+                op.capture(h.use_current_stream)
+            extra["cuda_graph"] = "one graph per step (pack + NCCL all-gather + SpMV launches), replayed"
 
         def step(i):
             ops[i % REPLICAS].step()
-        launches_per_step = 1
-        extra["exchange"] = {"mode": "halo all-gather (NCCL)", "bytes_received_per_rank_per_step": ops[0].exchange_bytes}
+        launches_per_step = len(ops[0].split) if ops[0].split else 1
+        launches_per_step += 1 if ops[0].p2p is not None else 0
+        extra["exchange"] = {"mode": (("halo push over NVLink peer memory (rsg_halo_push) + " +
+                                       ("arrival flags awaited inside the SpMV's boundary tiles" if ops[0].p2p[1] else "symmetric-memory barrier"))
+                                      if ops[0].p2p is not None else "halo all-gather (NCCL)") + (" on a side stream, overlapped with the %d interior rows; "
+                                                                   "boundary rows follow" % ops[0].interior_rows if ops[0].split else ""),
+                             "bytes_received_per_rank_per_step": ops[0].exchange_bytes}
 
     for i in range(W):
         step(i)
     launches_before = h.info("KERNEL_LAUNCHES")
+    push_launches_before = hp.info("KERNEL_LAUNCHES") if world > 1 else 0
     ms, w0, w1 = timed_loop(torch, step, K, barrier)
     gpu_launches = h.info("KERNEL_LAUNCHES") - launches_before
+    if world > 1:
+        gpu_launches += hp.info("KERNEL_LAUNCHES") - push_launches_before
+    if "cuda_graph" in extra:  # replayed launches do not pass through the library's counter
+        gpu_launches = K * launches_per_step
+    if world > 1:  # how long the host needs to issue a step (a step cannot be faster than this)
+        torch.cuda.synchronize()
+        c0 = time.perf_counter()
+        for i in range(200):
+            step(i)
+        extra["host_issue_us_per_step"] = (time.perf_counter() - c0) / 200 * 1e6
+        torch.cuda.synchronize()
     ms = allmax(ms)
     total_bytes = allsum(float(bytes_per))
     value = total_bytes * K / (ms * 1e-3) * 1e-9
@@ -236,11 +271,21 @@ def run_ours(args):
     w1b = time.time()
     clocks = sampler.summary(w0, max(w1, w1b))
 
+    h.set_option("SPMV_HALO_START", 0)
     # parity spot check of what was just timed (first rows of this rank against the oracle)
     if world == 1:
         ref = orc.spmv(a.rows(0, 2000), xs, "d")
         got = yd[0][:2000].cpu().numpy()
         assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max(), "bench result differs from the oracle"
+    else:
+        # both ends of this rank's block read the neighbours' entries: they check the exchange as well
+        xg = orc.dlarnv(GRID * GRID * nz) - 0.5
+        for r0, r1 in ((0, 3000), (a.m - 3000, a.m)):
+            ref = orc.spmv(a.rows(r0, r1), xg, "d")
+            for yv in yd:
+                got = yv[r0:r1].cpu().numpy()
+                assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max(), "rank %d: distributed result differs from the oracle" % rank
+        extra["parity"] = "rows at both ends of every rank's block (they read the neighbours' halo) match the oracle to 1e-12"
 
     # ---- roofline of the dominant kernel (single GPU: the step IS one launch of it)
     per_launch_ms = ms / K
@@ -382,9 +427,14 @@ def run_ours(args):
                 "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "launches_per_step": launches_per_step,
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "extra": extra}
         print(json.dumps(line))
-    h.close()
     if world > 1:
-        dist.destroy_process_group()
+        # symmetric-memory handles / NCCL communicators are torn down by process exit: an orderly
+        # destroy_process_group after P2P mappings (or captured graphs) can block on a peer that is already gone
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        os._exit(0)
+    h.close()
 
 
 def main():
@@ -394,6 +444,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the host-CPU baseline leg")
+    ap.add_argument("--graph", action="store_true", help="N>1: replay each step from a CUDA graph (NCCL exchange only)")
+    ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -76,6 +76,9 @@ typedef enum {
     RSG_OPT_TRSV_GATE = 12,     /* sync-free solves: 1 = a row first polls only its deepest dependency, 2 = off, 0 = default */
     RSG_OPT_TRI_CTAS_PER_SM = 13, /* sync-free ILU0 / solves: cap on resident CTAs per SM (0 = default) */
     RSG_OPT_TRSV_BLOCK = 14,    /* sync-free solves: threads per CTA (multiple of 32, <= 256; 0 = default) */
+    RSG_OPT_SPMV_HALO_START = 15, /* multi-GPU: zero-based column from which x is filled by peers (0 = none); read when
+                                     the SpMV plan is built: tiles that touch such columns are marked and can wait on
+                                     arrival flags (rsg_spmv_halo_wait) */
     RSG_OPT_COUNT_
 } rsg_option;
 
@@ -152,6 +155,24 @@ int rsg_get_levels(rsg_handle_t handle, int which, int *nlevels, int *level_ptr,
  * start[g] = first row r with rowptr[r]-rowptr[0] >= floor(g*nnz/ngpu); 0: ceil(g*m/ngpu). */
 int rsg_get_row_partition(rsg_handle_t handle, int m, int base, const int *rowptr,
                           int ngpu, int balanced, int *row_starts);
+
+/* ---- multi-GPU x-halo push (north_star: row-block SpMV across the box; no reference equivalent) -- */
+/* x_local[send_idx[j]] (j < nsend) is stored to peer_slots[q][j] for every q < npeers with a non-NULL
+ * slot.  peer_slots is a HOST array of DEVICE pointers into the peers' halo buffers (P2P-mapped, e.g.
+ * CUDA IPC / symmetric memory), each already offset to this rank's slot.  Asynchronous on the handle's
+ * stream; the caller orders it against the peers' reads with its own cross-GPU barrier. */
+#define RSG_MAX_PEERS 16
+/* peer_flags (may be NULL): HOST array of npeers DEVICE pointers to one int each, in the peers' memory; after
+ * every store of this launch is visible system-wide, `epoch` is stored (release, system scope) to each
+ * non-NULL flag -- "this rank's entries for step `epoch` have landed". */
+int rsg_halo_push(rsg_handle_t handle, int elem_bytes, int nsend, const int *send_idx, const void *x_local,
+                  int npeers, void *const *peer_slots, int *const *peer_flags, int epoch);
+/* One-shot: the NEXT spmv_csr_* call on this handle makes every tile that reads columns >=
+ * RSG_OPT_SPMV_HALO_START wait (acquire, system scope) until flags[i] >= epoch for all i < nflags
+ * (flags: DEVICE pointer, nflags <= RSG_MAX_PEERS), while all other tiles run at once: the exchange
+ * overlaps the product without splitting it.  Needs the TILE kernel (AUTO picks it for regular rows);
+ * other kernels return RSG_UNSUPPORTED.  A wait gives up after ~1 s (result then undefined). */
+int rsg_spmv_halo_wait(rsg_handle_t handle, const int *flags, int nflags, int epoch);
 
 /* ---- host-pointer convenience wrappers (allocate, H2D, run, D2H, free; synchronous) ------- */
 int spmv_csr_d_host(rsg_handle_t handle, int m, int n, int nnz, int base,

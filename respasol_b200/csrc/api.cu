@@ -74,7 +74,7 @@ int rsg_create(rsg_handle_t *handle, int device)
     cudaDeviceGetAttribute(&h->l2_bytes, cudaDevAttrL2CacheSize, device);
     cudaDeviceGetAttribute(&h->max_smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
     h->opts[RSG_OPT_SPMV_CACHE_HINT] = 1;
-    if (cudaMalloc(&h->scratch_i, 64 * sizeof(int)) != cudaSuccess ||
+    if (cudaMalloc(&h->scratch_i, 64 * sizeof(int)) != cudaSuccess || cudaMemset(h->scratch_i, 0, 64 * sizeof(int)) != cudaSuccess ||
         cudaMallocHost(&h->pinned_i, 64 * sizeof(int)) != cudaSuccess) {
         (void)cudaGetLastError();
         if (h->scratch_i) cudaFree(h->scratch_i);

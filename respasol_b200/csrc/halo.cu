@@ -1,0 +1,84 @@
+// halo.cu -- x-halo exchange of the row-block partitioned SpMV over NVLink peer memory.
+// The reference is single-GPU (new capability); the exchange step the north star names
+// is an all-gather of the entries other ranks reference.  Here every rank PUSHES them: one kernel
+// reads each boundary entry of the local x once and stores it straight into every peer's halo
+// buffer (P2P-mapped symmetric memory, plain st.global over NVLink/NVSwitch), so the step costs one
+// small launch plus one cross-GPU barrier instead of an NCCL collective's ~15 us of setup.
+#include "rsg_internal.cuh"
+
+namespace rsg {
+
+struct HaloPeers {
+    void *dst[RSG_MAX_PEERS]; // peer q's halo slot for THIS rank (already offset), NULL = skip
+    int *flag[RSG_MAX_PEERS]; // peer q's arrival flag for THIS rank, NULL = no signal
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+halo_push_kernel(int nsend, const int *__restrict__ send_idx, const T *__restrict__ x_local, int npeers, HaloPeers peers,
+                 int epoch, int *cta_counter)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < nsend) {
+        const T v = x_local[send_idx[j]];
+#pragma unroll 1
+        for (int q = 0; q < npeers; ++q) {
+            T *d = static_cast<T *>(peers.dst[q]);
+            if (d) d[j] = v;
+        }
+    }
+    if (epoch == 0) return;
+    // signal: the last CTA to finish publishes the epoch to every peer once all stores are visible
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int done = atomicAdd(cta_counter, 1);
+        if (done == (int)gridDim.x - 1) {
+            *cta_counter = 0; // next launch on this stream starts from zero
+            __threadfence_system();
+            for (int q = 0; q < npeers; ++q)
+                if (peers.flag[q]) asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(peers.flag[q]), "r"(epoch) : "memory");
+        }
+    }
+}
+
+} // namespace rsg
+
+extern "C" int rsg_halo_push(rsg_handle_t h, int elem_bytes, int nsend, const int *send_idx, const void *x_local,
+                             int npeers, void *const *peer_slots, int *const *peer_flags, int epoch)
+{
+    using namespace rsg;
+    if (!h || nsend < 0 || npeers < 0 || npeers > RSG_MAX_PEERS || (elem_bytes != 4 && elem_bytes != 8)) return RSG_BAD_ARG;
+    if (!peer_flags) epoch = 0;
+    if (npeers == 0 || (nsend == 0 && epoch == 0)) return RSG_OK;
+    if (nsend > 0 && (!send_idx || !x_local || !peer_slots)) return RSG_BAD_ARG;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    if (prev != h->device) cudaSetDevice(h->device);
+    HaloPeers peers;
+    for (int q = 0; q < RSG_MAX_PEERS; ++q) {
+        peers.dst[q] = (q < npeers && peer_slots) ? peer_slots[q] : nullptr;
+        peers.flag[q] = (q < npeers && peer_flags) ? peer_flags[q] : nullptr;
+    }
+    const int grid = std::max(1, (nsend + 255) / 256);
+    int *counter = h->scratch_i + 62; // zero since rsg_create; every signalling launch leaves it at zero
+    if (elem_bytes == 8)
+        halo_push_kernel<double><<<grid, 256, 0, h->stream>>>(nsend, send_idx, static_cast<const double *>(x_local), npeers, peers,
+                                                              epoch, counter);
+    else
+        halo_push_kernel<float><<<grid, 256, 0, h->stream>>>(nsend, send_idx, static_cast<const float *>(x_local), npeers, peers,
+                                                             epoch, counter);
+    h->launches++;
+    const cudaError_t e = cudaGetLastError();
+    if (prev != h->device && prev >= 0) cudaSetDevice(prev);
+    return e == cudaSuccess ? RSG_OK : RSG_CUDA_ERROR;
+}
+
+extern "C" int rsg_spmv_halo_wait(rsg_handle_t h, const int *flags, int nflags, int epoch)
+{
+    if (!h || nflags < 0 || nflags > RSG_MAX_PEERS || (nflags > 0 && !flags)) return RSG_BAD_ARG;
+    h->wait_flags = nflags > 0 ? flags : nullptr;
+    h->wait_n = nflags;
+    h->wait_epoch = epoch;
+    return RSG_OK;
+}

@@ -102,6 +102,8 @@ struct rsg_context {
     size_t cub_tmp_bytes = 0;
     int *scratch_i = nullptr; // small device scratch (stats), 64 ints
     int *pinned_i = nullptr;  // small pinned host mirror, 64 ints
+    const int *wait_flags = nullptr;   // one-shot halo wait for the next SpMV (rsg_spmv_halo_wait)
+    int wait_n = 0, wait_epoch = 0;
     const void *persist_ptr = nullptr; // x currently covered by the L2 access-policy window
     size_t persist_bytes = 0;
 };

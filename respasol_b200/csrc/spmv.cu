@@ -448,7 +448,8 @@ void spmv_free_plan(SpmvPlan &p)
 static int plan_signature(const rsg_context *h)
 {
     return h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW] +
-           h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD] * 7919 + h->opts[RSG_OPT_SPMV_REDUCE] * 104729;
+           h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD] * 7919 + h->opts[RSG_OPT_SPMV_REDUCE] * 104729 +
+           h->opts[RSG_OPT_SPMV_HALO_START] * 31;
 }
 
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
@@ -683,6 +684,7 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     h->last_spmv_maxrow = p->max_row;
     RSG_TRY(set_x_persistence(h, x, sizeof(TX) * (size_t)n));
     const bool vec = (((uintptr_t)colidx | (uintptr_t)values) & 15) == 0;
+    if (h->wait_flags && p->algo != RSG_SPMV_TILE) { h->wait_flags = nullptr; return RSG_UNSUPPORTED; }
     switch (p->algo) {
     case RSG_SPMV_ROWBLOCK:
         h->last_spmv_blocks = p->nblk;

@@ -215,7 +215,7 @@ template <typename TV, typename TX, int THREADS, int CAPE, int ROWS>
 __global__ void __launch_bounds__(THREADS)
 spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
                  const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
-                 int nnz_end, int reduce_opt)
+                 int nnz_end, int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch)
 {
     typedef PipeStage<TV, CAPE, ROWS> Stage;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -245,6 +245,17 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
             bulk_g2s(smem_raw + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full, spol);
             bulk_g2s(smem_raw + Stage::col_off, colidx + sb, nq * 4u, &s_full, spol);
         }
+    }
+    if (d0.w != 0 && wait_n > 0) {
+        // this tile gathers x entries that peers write over NVLink: wait for their arrival flags
+        // (while the bulk copies of the tile are in flight); every other tile never looks at them
+        if (tid < wait_n) {
+            int spins = 0, v;
+            do {
+                asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(wait_flags + tid) : "memory");
+            } while (v < wait_epoch && ++spins < (1 << 21));
+        }
+        __syncthreads();
     }
     mbar_wait(&s_full, 0);
     uint32_t aux_parity = 0;
@@ -283,6 +294,18 @@ __global__ void pipe_maxlen_kernel(int ntiles, int base, const int *__restrict__
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ml = max(ml, __shfl_xor_sync(0xffffffffu, ml, o));
     if (lane == 0) desc[b].z = ml;
+}
+
+// one warp per tile: does the tile read a column >= halo_start (an x entry filled by a peer)?  -> desc[b].w
+__global__ void pipe_halo_mark_kernel(int ntiles, int base, int halo_start, const int *__restrict__ colidx, int4 *desc)
+{
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (b >= ntiles) return;
+    const int k0 = desc[b].y, k1 = desc[b + 1].y;
+    int hit = 0;
+    for (int k = k0 + lane; k < k1; k += 32) hit |= (colidx[k] - base >= halo_start);
+    hit = __any_sync(0xffffffffu, hit);
+    if (lane == 0) desc[b].w = hit ? 1 : 0;
 }
 
 // zero-based copy of the row pointers, padded to a multiple of 4 (+4) with the end offset
@@ -337,6 +360,10 @@ int pipe_build_plan(rsg_context *h, SpmvPlan &p)
     pipe_maxlen_kernel<<<(p.nblk * 32 + 255) / 256, 256, 0, st>>>(p.nblk, p.base, p.rowptr, p.pdesc);
     pipe_rowptr_copy_kernel<<<(p.rp0_len + 255) / 256, 256, 0, st>>>(m, p.rp0_len, p.base, p.rowptr, p.rp0);
     h->launches += 3;
+    if (h->opts[RSG_OPT_SPMV_HALO_START] > 0) {
+        pipe_halo_mark_kernel<<<(p.nblk * 32 + 255) / 256, 256, 0, st>>>(p.nblk, p.base, h->opts[RSG_OPT_SPMV_HALO_START], p.colidx, p.pdesc);
+        h->launches++;
+    }
     RSG_CUDA_TRY(cudaGetLastError());
     return RSG_OK;
 }
@@ -399,7 +426,8 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
         configured = true;
     }
     kern<<<p->nblk, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc, p->first + p->nnz,
-                                                h->opts[RSG_OPT_SPMV_REDUCE]);
+                                                h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags, h->wait_flags ? h->wait_n : 0, h->wait_epoch);
+    h->wait_flags = nullptr; // one-shot
     h->launches++;
     h->last_spmv_blocks = p->nblk;
     return RSG_OK;

@@ -9,6 +9,15 @@ matching slice of x.  One product = one exchange step + one local SpMV:
                     off-block column indices are remapped ONCE at setup into the packed halo
                     buffer appended behind the local slice.  Relabelling keeps the order of the
                     entries inside each row, so every row is summed in the same order as on one GPU.
+  mode "p2p":       same relabelling as "halo", but every rank PUSHES its boundary entries straight into the
+                    peers' halo buffers (torch symmetric memory = P2P-mapped allocations over NVLink; the
+                    library's rsg_halo_push kernel does the stores), followed by one cross-GPU barrier.
+                    x lives in two such buffers used in turn, so a rank one step ahead never overwrites
+                    a halo a slower peer is still reading.
+Overlap (`view` given): the rows are cut into [0,r0) | [r0,r1) | [r1,m) where [r0,r1) is the longest run
+of rows that reference no other rank's entries (for a slab of a stencil: everything but the two outer
+planes).  The exchange runs on a side stream while the interior rows are multiplied; the two boundary
+pieces follow once the halo has landed.  Row order, and the order inside each row, are unchanged.
 ILU0 / SpTRSV do not shard (dependency chains cross any row cut): replicas only.
 """
 import numpy as np
@@ -16,6 +25,22 @@ import torch
 import torch.distributed as dist
 
 from .host import CSR
+
+
+HALO_ALIGN = 32  # elements: the halo region starts on its own 128/256-byte line, so a cache line never
+#                  mixes entries this GPU owns with entries a peer writes while the product is running
+
+
+def halo_base(n_local):
+    return (int(n_local) + HALO_ALIGN - 1) // HALO_ALIGN * HALO_ALIGN
+
+
+def p2p_slot_offsets(row_starts, width, rank, stride):
+    """Element offset, inside peer q's symmetric buffer (two x_ext images of `stride` elements), of the
+    halo slot that belongs to `rank`: image p of peer q holds [its n_local entries, padded | P slots of `width`]."""
+    rs = np.asarray(row_starts, dtype=np.int64)
+    n_local = np.diff(rs)
+    return [[int(p * stride + halo_base(n_local[q]) + rank * width) for q in range(len(n_local))] for p in range(2)]
 
 
 def owner_of(cols, row_starts):
@@ -31,6 +56,7 @@ class HaloPlan:
         self.row_starts = np.asarray(row_starts, dtype=np.int64)
         self.lo, self.hi = int(row_starts[rank]), int(row_starts[rank + 1])
         self.n_local = self.hi - self.lo
+        self.halo_base = halo_base(self.n_local)
         cols = local.colidx.astype(np.int64) - local.base
         off = (cols < self.lo) | (cols >= self.hi)
         self.need = np.unique(cols[off])  # global indices this rank reads from other ranks
@@ -56,21 +82,45 @@ class HaloPlan:
             for o in np.unique(own):
                 sel = own == o
                 pos[sel] = np.searchsorted(send[o], oc[sel] - rs[o])
-            new[off] = self.n_local + own * self.width + pos
-        self.n_ext = self.n_local + P * self.width
+            new[off] = self.halo_base + own * self.width + pos
+        self.n_ext = self.halo_base + P * self.width
         a = self.local
         self.remapped = CSR(a.m, self.n_ext, a.stored, (a.rowptr - a.base).astype(np.int32), new.astype(np.int32),
                             a.values, 0)
         self.my_send = send[self.rank]
+        lo, hi = rs[self.rank], rs[self.rank + 1]  # peers that read at least one of this rank's entries
+        self.readers = [q for q, nb in enumerate(needs_by_rank) if q != self.rank and np.any((nb >= lo) & (nb < hi))]
+        self.interior = self._interior_run(a, off)
         return self
+
+    @staticmethod
+    def _interior_run(a, off):
+        """[r0, r1): the longest run of consecutive rows without an off-block column."""
+        rp = (a.rowptr - a.base).astype(np.int64)
+        per_row = np.add.reduceat(off.astype(np.int64), np.minimum(rp[:-1], max(len(off) - 1, 0))) if len(off) else np.zeros(a.m, np.int64)
+        per_row = np.where(rp[1:] > rp[:-1], per_row, 0)  # reduceat on an empty row picks up a neighbour's entry
+        dirty = np.flatnonzero(per_row > 0)
+        if len(dirty) == 0:
+            return 0, a.m
+        edges = np.concatenate(([-1], dirty, [a.m]))
+        gaps = np.diff(edges) - 1
+        g = int(np.argmax(gaps))
+        return int(edges[g] + 1), int(edges[g + 1])
 
 
 class RowBlockSpmv:
     """y_local = A_local * x, x distributed by rows.  `upload(csr)` and `spmv(A, x_ext, y)` are injected so
     the same exchange logic runs on the GPU (libreaspasol_gpu through Handle) and in the gloo CPU tests."""
 
-    def __init__(self, local: CSR, row_starts, mode, upload, spmv, device, dtype, group=None):
+    def __init__(self, local: CSR, row_starts, mode, upload, spmv, device, dtype, group=None, view=None, push=None, side=None):
         self.group = group
+        self.split = None
+        self.p2p = None
+        self.side = side  # p2p: the stream the push kernels run on (the caller binds its push handle to it)
+        if mode == "p2p":
+            mode, self.p2p = "halo", push  # (rsg_halo_push, rsg_spmv_halo_wait or None) of the library's handle
+            if push[1] is not None:
+                view = None  # the boundary tiles wait inside the kernel: nothing to split
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.P = len(row_starts) - 1
         self.mode = mode
@@ -88,10 +138,23 @@ class RowBlockSpmv:
             plan.finish(needs)
             self.plan = plan
             self.A = upload(plan.remapped)
-            self.x_ext = torch.zeros(plan.n_ext, dtype=dtype, device=device)
+            r0, r1 = plan.interior
+            if view is not None and self.P > 1 and r1 - r0 >= local.m // 2:
+                # (piece, first row, end row): interior first, then the pieces that wait for the halo
+                self.split = [(view(self.A, a, b), a, b) for a, b in ((r0, r1), (0, r0), (r1, local.m)) if b > a]
+                self.interior_rows = r1 - r0
+                if torch.device(device).type == "cuda":
+                    if self.side is None:
+                        self.side = torch.cuda.Stream(device=device)
+                    self.landed = torch.cuda.Event()
+            if self.p2p is not None and self.P > 1:
+                self._setup_p2p(plan, dtype, device)
+            else:
+                self.p2p = None
+                self.x_ext = torch.zeros(plan.n_ext, dtype=dtype, device=device)
             self.send_idx = torch.from_numpy(plan.my_send).to(device)
             self.pack = torch.zeros(plan.width, dtype=dtype, device=device)
-            self.halo = self.x_ext[plan.n_local:]
+            self.halo = self.x_ext[plan.halo_base:]
             self.exchange_bytes = plan.width * self.P * self.x_ext.element_size()
         elif mode == "allgather":
             self.width = int(np.diff(self.row_starts).max())
@@ -109,15 +172,71 @@ class RowBlockSpmv:
             raise ValueError(mode)
         self.y = torch.zeros(local.m, dtype=dtype, device=device)
 
+    def _setup_p2p(self, plan, dtype, device):
+        import torch.distributed._symmetric_memory as symm_mem
+        group = self.group if self.group is not None else dist.group.WORLD
+        n_ext_all = [None] * self.P
+        dist.all_gather_object(n_ext_all, int(plan.n_ext), group=self.group)
+        stride = (max(n_ext_all) + 31) // 32 * 32
+        buf = symm_mem.empty(2 * stride, dtype=dtype, device=device)
+        buf.zero_()
+        self.symm = symm_mem.rendezvous(buf, group)
+        self.symm_buf = buf
+        self.images = [buf[p * stride:p * stride + plan.n_ext] for p in range(2)]
+        self.x_ext = self.images[0]
+        esz = buf.element_size()
+        offs = p2p_slot_offsets(self.row_starts, plan.width, self.rank, stride)
+        ptrs = list(self.symm.buffer_ptrs)
+        self.slots = [[(ptrs[q] + offs[p][q] * esz) if q in plan.readers else 0 for q in range(self.P)] for p in range(2)]
+        # arrival flags: image p, one int per sending rank; every rank signals every peer (and itself), so a
+        # rank can never run more than one step ahead of any other -- the two images are enough
+        fl = symm_mem.empty(2 * 32, dtype=torch.int32, device=device)
+        fl.zero_()
+        self.symm_flags = symm_mem.rendezvous(fl, group)
+        self.flags = fl
+        fptrs = list(self.symm_flags.buffer_ptrs)
+        self.flag_slots = [[fptrs[q] + 4 * (32 * p + self.rank) for q in range(self.P)] for p in range(2)]
+        self.epoch = 0
+        self.parity = 0
+        if self.side is None:
+            self.side = torch.cuda.Stream(device=device)
+        to_c = getattr(self.p2p[0], "__self__", None)
+        if to_c is not None and hasattr(to_c, "ptr_array"):  # pre-built argument arrays: nothing is rebuilt per step
+            self.slots = [to_c.ptr_array(v) for v in self.slots]
+            self.flag_slots = [to_c.ptr_array(v) for v in self.flag_slots]
+        self.flag_views = [self.flags[32 * p:] for p in range(2)]
+        self.send_idx32 = torch.from_numpy(plan.my_send.astype(np.int32)).to(device)
+        torch.cuda.synchronize(device)
+        self.symm.barrier(channel=0)
+
     def set_x(self, x_local):
         """x_local: this rank's slice of x (device tensor)."""
-        if self.mode == "halo":
+        if self.p2p is not None:
+            for im in self.images:
+                im[:self.n_local].copy_(x_local)
+        elif self.mode == "halo":
             self.x_ext[:self.n_local].copy_(x_local)
         else:
             self.pack[:self.n_local].copy_(x_local)
 
     def exchange(self):
-        if self.mode == "halo":
+        if self.p2p is not None:
+            # push + signal; the product that follows waits for the peers' flags inside its boundary tiles
+            self.epoch += 1
+            self.x_ext = self.images[self.parity]
+            push, arm = self.p2p
+            if arm is not None:
+                # the push runs beside the product (its own stream): only the boundary tiles wait for a peer
+                # (`push` launches on self.side: the caller's push handle is bound to that stream)
+                self.side.wait_stream(torch.cuda.current_stream(self.x_ext.device))
+                push(self.send_idx32, self.x_ext, self.slots[self.parity], self.flag_slots[self.parity], self.epoch)
+                arm(self.flag_views[self.parity], self.P, self.epoch)
+                self.join_side = True
+            else:
+                push(self.send_idx32, self.x_ext, self.slots[self.parity], self.flag_slots[self.parity], self.epoch)
+                self.symm.barrier(channel=0)  # no in-kernel wait: every peer's push into this image has landed
+            self.parity ^= 1
+        elif self.mode == "halo":
             if self.P == 1:
                 return
             n = self.send_idx.numel()
@@ -130,8 +249,44 @@ class RowBlockSpmv:
             else:
                 dist.all_gather_into_tensor(self.x_ext, self.pack, group=self.group)
 
+    def capture(self, rebind_stream):
+        """Record one step (pack, all-gather, the SpMV launches, the stream fork/join) into a CUDA graph:
+        a step is 5-7 launches of 5-60 us each, and issuing them from Python costs more than they run.
+        `rebind_stream()` points the SpMV library's handle at torch's current stream."""
+        self.graph = None
+        torch.cuda.synchronize(self.x_ext.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            rebind_stream()
+            self.step()
+        rebind_stream()
+        self.graph = g
+        return g
+
     def step(self):
         """one distributed product: exchange step, then the local SpMV into self.y"""
-        self.exchange()
-        self.spmv_fn(self.A, self.x_ext, self.y)
+        if getattr(self, "graph", None) is not None:
+            self.graph.replay()
+            return self.y
+        if self.split is None:
+            self.exchange()
+            self.spmv_fn(self.A, self.x_ext, self.y)
+            if getattr(self, "join_side", False):  # x may be rewritten once the step returns
+                torch.cuda.current_stream(self.x_ext.device).wait_stream(self.side)
+            return self.y
+        cuda = self.x_ext.is_cuda
+        if cuda:
+            main = torch.cuda.current_stream(self.x_ext.device)
+            self.side.wait_stream(main)  # this rank's slice of x is final
+            with torch.cuda.stream(self.side):
+                self.exchange()
+                self.landed.record(self.side)
+        else:
+            self.exchange()
+        for j, (piece, a, b) in enumerate(self.split):
+            if j == 1 and cuda:
+                main.wait_event(self.landed)
+            self.spmv_fn(piece, self.x_ext, self.y[a:b])
+        if cuda and len(self.split) == 1:
+            main.wait_event(self.landed)
         return self.y

@@ -15,7 +15,7 @@ from .host import CSR
 OPT = dict(SPMV_ALGO=0, SPMV_REDUCE=1, SPMV_LONG_ROW=2, SPMV_VARIANT=3, SPMV_CACHE_HINT=4,
            TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7, SPMV_X_HINT=8,
            SPMV_ROWS_PER_THREAD=9, SPMV_CTAS_PER_SM=10, TRSV_BATCH=11, TRSV_GATE=12,
-           TRI_CTAS_PER_SM=13, TRSV_BLOCK=14)
+           TRI_CTAS_PER_SM=13, TRSV_BLOCK=14, SPMV_HALO_START=15)
 ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4, stream=5, pipe=6, tile=7)
 INFO = dict(KERNEL_LAUNCHES=0, SPMV_ALGO_USED=1, SPMV_ROW_BLOCKS=2, SPMV_MAX_ROW=3, LEVELS_L=4, LEVELS_U=5,
             SM_COUNT=6, WORKSPACE_BYTES=7)
@@ -54,6 +54,18 @@ class DeviceCSR:
         self.colidx = torch.from_numpy(a.colidx.astype(np.int32)).to(device)
         self.values = torch.from_numpy(a.values).to(device).to(vt)
         self.device = self.rowptr.device
+
+    def view_rows(self, r0, r1):
+        """Rows [r0, r1) as a slab view: the row pointers are a slice of the parent's (they keep indexing
+        the parent's colidx / values directly, which is what the C ABI's `first = rowptr[0]-base` handles)."""
+        v = object.__new__(DeviceCSR)
+        DeviceCSR._next_uid += 1
+        v.uid = DeviceCSR._next_uid
+        v.m, v.n, v.base, v.precision = r1 - r0, self.n, self.base, self.precision
+        v.rowptr = self.rowptr[r0:r1 + 1]
+        v.colidx, v.values, v.device = self.colidx, self.values, self.device
+        v.stored = self.stored  # advisory (the library reads rowptr[m]-rowptr[0])
+        return v
 
     def bytes(self):
         v, x = {"d": (8, 8), "s": (4, 4), "m": (4, 8)}[self.precision]
@@ -127,6 +139,28 @@ class Handle:
         _check(fn(self.h, A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
                   alpha, self._p(x), beta, self._p(y)), "spmv_csr_" + A.precision)
         return y
+
+    @staticmethod
+    def ptr_array(addresses):
+        """HOST array of device addresses (0 = NULL) in the form the C ABI takes; build once, pass many times."""
+        return (C.c_void_p * len(addresses))(*[C.c_void_p(int(p) if p else None) for p in addresses])
+
+    def halo_push(self, send_idx, x_local, peer_slots, peer_flags=None, epoch=0):
+        """x_local[send_idx[j]] -> peer_slots[q][j] for every non-zero device address in peer_slots (the peers'
+        P2P-mapped halo buffers, already offset to this rank's slot); then, if peer_flags is given, `epoch`
+        is released to every non-zero flag address.  One launch on the handle's stream."""
+        n = len(peer_slots)
+        slots = peer_slots if isinstance(peer_slots, C.Array) else self.ptr_array(peer_slots)
+        flags = None
+        if peer_flags is not None:
+            assert len(peer_flags) == n and epoch > 0
+            flags = peer_flags if isinstance(peer_flags, C.Array) else self.ptr_array(peer_flags)
+        _check(self.lib.rsg_halo_push(self.h, x_local.element_size(), int(send_idx.numel()), self._p(send_idx),
+                                      self._p(x_local), n, slots, flags, int(epoch)), "rsg_halo_push")
+
+    def spmv_halo_wait(self, flags, nflags, epoch):
+        """One-shot: tiles of the next spmv that read columns >= SPMV_HALO_START wait for flags[i] >= epoch."""
+        _check(self.lib.rsg_spmv_halo_wait(self.h, self._p(flags), int(nflags), int(epoch)), "rsg_spmv_halo_wait")
 
     # ---- ILU0 / SpTRSV
     def ilu0_analysis(self, A: DeviceCSR):

@@ -42,7 +42,11 @@ def _worker(rank, world, port, mode, kind, out):
     def spmv(A, xe, y):
         y.copy_(torch.from_numpy(orc.spmv(A, xe.numpy(), "d")))
 
-    op = RowBlockSpmv(local, starts, mode, lambda c: c, spmv, torch.device("cpu"), torch.float64)
+    # the stencil runs use the overlap split (interior rows first, boundary pieces after the exchange)
+    view = (lambda A, a, b: A.rows(a, b)) if kind == "stencil" else None
+    op = RowBlockSpmv(local, starts, mode, lambda c: c, spmv, torch.device("cpu"), torch.float64, view=view)
+    if kind == "stencil" and mode == "halo" and world == 2:
+        assert op.split is not None and sum(b - a for _, a, b in op.split) == local.m
     op.set_x(torch.from_numpy(x[starts[rank]:starts[rank + 1]].copy()))
     y = op.step().numpy()
     ref = orc.spmv(full, x, "d")[starts[rank]:starts[rank + 1]]
@@ -88,15 +92,40 @@ def test_halo_plan_single_process():
         p.finish(needs)
     # middle rank needs one plane from each neighbour; end ranks need one plane
     assert [len(n) for n in needs] == [25, 50, 25]
-    assert plans[1].width == 50 and plans[0].remapped.n == 75 + 3 * 50
+    assert plans[1].width == 50 and plans[0].remapped.n == 96 + 3 * 50 and plans[0].halo_base == 96
     # relabelled columns decode back to the original global columns
     for r, p in enumerate(plans):
         loc = full.rows(starts[r], starts[r + 1])
         dec = np.empty(loc.stored, dtype=np.int64)
         c = p.remapped.colidx.astype(np.int64)
         own = c < p.n_local
+        assert not np.any((c >= p.n_local) & (c < p.halo_base))  # the alignment gap is never referenced
         dec[own] = c[own] + starts[r]
-        o = (c[~own] - p.n_local) // p.width
-        pos = (c[~own] - p.n_local) % p.width
+        o = (c[~own] - p.halo_base) // p.width
+        pos = (c[~own] - p.halo_base) % p.width
         dec[~own] = np.array([p.send_idx[oo][pp] + starts[oo] for oo, pp in zip(o, pos)])
         assert np.array_equal(dec, loc.colidx)
+
+
+def test_p2p_slot_offsets_and_readers():
+    """Host logic of the peer-memory exchange: where this rank's halo slot sits inside every peer's
+    symmetric buffer, and which peers read from this rank at all."""
+    from respasol_b200 import host
+    from respasol_b200.dist import HaloPlan, p2p_slot_offsets
+    full = host.gen_stencil27(5, 5, 9, seed=0)
+    starts = np.array([0, 75, 175, 225])
+    plans = [HaloPlan(full.rows(starts[r], starts[r + 1]), starts, r) for r in range(3)]
+    needs = [p.need for p in plans]
+    for p in plans:
+        p.finish(needs)
+    assert [p.readers for p in plans] == [[1], [0, 2], [1]]
+    w = plans[0].width
+    stride = 512
+    offs = p2p_slot_offsets(starts, w, 1, stride)
+    # image 0: behind peer q's own entries, slot number = the sender's rank; image 1 one stride further
+    assert offs[0] == [96 + w, 128 + w, 64 + w] and offs[1] == [o + stride for o in offs[0]]
+    # the slot is exactly where the relabelled columns of the reader point
+    p0 = plans[0]
+    c = p0.remapped.colidx.astype(np.int64)
+    halo_cols = np.unique(c[c >= p0.halo_base])
+    assert halo_cols.min() >= offs[0][0] and halo_cols.max() < offs[0][0] + w

@@ -13,7 +13,7 @@ import torch
 
 import orc
 from respasol_b200 import host
-from respasol_b200.gpu import ALGO, DeviceCSR
+from respasol_b200.gpu import ALGO, DeviceCSR, Handle
 
 pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
@@ -333,3 +333,95 @@ def test_full_size_configs(handle, name):
     lin = 2 * torch.from_numpy(yd).cuda() + y1
     rs = torch.from_numpy(row_abs_sums(a, np.abs(x) * 2 + 1, "d")).cuda()
     assert bool(((y2 - lin).abs() <= 1e-13 * rs + 1e-300).all())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["d", "s", "m"])
+def test_row_range_views_of_a_resident_matrix(handle, precision):
+    """DeviceCSR.view_rows: the interior / boundary pieces the multi-GPU overlap multiplies separately
+    (row pointers are a slice of the parent's and keep indexing the parent's entries).  The pieces
+    written into slices of one y must reproduce the oracle's product of the whole matrix."""
+    a = host.gen_stencil27(20, 20, 24, seed=2)
+    x = orc.dlarnv(a.n) - 0.5
+    A = DeviceCSR(a, precision)
+    xt = torch.float32 if precision == "s" else torch.float64
+    xd = torch.from_numpy(x).cuda().to(xt)
+    y = torch.full((a.m,), float("nan"), dtype=xt, device="cuda")
+    cuts = [0, 401, 402, 3 * 400 + 7, a.m - 400, a.m]
+    for r0, r1 in zip(cuts[:-1], cuts[1:]):
+        handle.spmv(A.view_rows(r0, r1), xd, y[r0:r1])
+    ref = orc.spmv(a, x, precision).astype(np.float64)
+    got = y.cpu().numpy().astype(np.float64)
+    tol = 1e-12 if precision == "d" else 5e-5
+    assert np.abs(got - ref).max() <= tol * np.abs(ref).max()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_halo_push_kernel(handle, dtype):
+    """rsg_halo_push on one device: two 'peer' buffers stand in for P2P-mapped halo slots; a NULL slot is skipped."""
+    n, ns = 5000, 1237
+    x = torch.from_numpy(orc.dlarnv(n)).cuda().to(dtype)
+    idx = torch.from_numpy(np.random.default_rng(5).permutation(n)[:ns].astype(np.int32)).cuda()
+    peers = [torch.full((ns + 8,), -7.0, dtype=dtype, device="cuda") for _ in range(3)]
+    slots = [peers[0][3:].data_ptr(), 0, peers[2].data_ptr()]
+    handle.halo_push(idx, x, slots)
+    torch.cuda.synchronize()
+    want = x[idx.long()]
+    assert torch.equal(peers[0][3:3 + ns], want) and torch.equal(peers[2][:ns], want)
+    assert bool((peers[1] == -7.0).all()) and bool((peers[0][:3] == -7.0).all()) and bool((peers[0][3 + ns:] == -7.0).all())
+
+
+@pytest.mark.gpu
+def test_halo_push_signal_and_in_kernel_wait(handle):
+    """Two ranks emulated on one device: rank 0's block (columns relabelled by HaloPlan) is multiplied while
+    'rank 1' pushes its boundary entries LATE, from another stream.  The tiles that read halo columns must
+    wait for the arrival flag (rsg_spmv_halo_wait); the result must equal the oracle's rows of the full product."""
+    from respasol_b200.dist import HaloPlan
+    full = host.gen_stencil27(24, 24, 40, seed=2)
+    starts = np.array([0, full.m // 2, full.m])
+    plans = [HaloPlan(full.rows(int(starts[r]), int(starts[r + 1])), starts, r) for r in range(2)]
+    needs = [p.need for p in plans]
+    for p in plans:
+        p.finish(needs)
+    p0, p1 = plans
+    x = orc.dlarnv(full.n) - 0.5
+    ref = orc.spmv(full, x, "d")[:p0.n_local]
+    handle.set_option("SPMV_HALO_START", p0.halo_base)
+    try:
+        A = DeviceCSR(p0.remapped, "d")
+        handle.spmv_analysis(A)
+        x_ext = torch.zeros(p0.n_ext, dtype=torch.float64, device="cuda")
+        x_ext[:p0.n_local] = torch.from_numpy(x[:p0.n_local]).cuda()
+        x1 = torch.from_numpy(x[p0.n_local:]).cuda()                      # rank 1's slice
+        send1 = torch.from_numpy(p1.my_send.astype(np.int32)).cuda()      # what rank 1 publishes
+        flags = torch.zeros(32, dtype=torch.int32, device="cuda")
+        slot = x_ext[p0.halo_base + 1 * p0.width:].data_ptr()             # rank 1's slot in rank 0's halo
+        other = Handle(0)
+        side = torch.cuda.Stream()
+        y = torch.empty(p0.n_local, dtype=torch.float64, device="cuda")
+        # first launches load their modules, which may wait for running kernels: do that before anything spins
+        with torch.cuda.stream(side):
+            other.use_current_stream()
+            torch.cuda._sleep(1000)
+            other.halo_push(send1, x1, [slot], [flags[8:].data_ptr()], 1)
+        torch.cuda.synchronize()
+        for epoch in (1, 2):
+            x_ext[p0.halo_base:].fill_(float("nan"))
+            torch.cuda.synchronize()
+            # flags[0] (this rank's own signal) is set up front, flags[1] arrives while the product runs
+            flags[0] = epoch
+            torch.cuda.synchronize()
+            handle.spmv_halo_wait(flags, 2, epoch)
+            handle.spmv(A, x_ext, y)
+            with torch.cuda.stream(side):
+                other.use_current_stream()
+                torch.cuda._sleep(2_000_000)  # ~1 ms: the product is long spinning by now
+                other.halo_push(send1, x1, [slot], [flags[1:].data_ptr()], epoch)
+            torch.cuda.synchronize()
+            assert int(flags[1].item()) == epoch
+            got = y.cpu().numpy()
+            assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max()
+        other.close()
+    finally:
+        handle.set_option("SPMV_HALO_START", 0)
