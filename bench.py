@@ -213,11 +213,13 @@ def run_ours(args):
         if args.exchange == "p2p-barrier":
             hp.use_current_stream()
         push = hp.halo_push
+        P2P_FNS = {"p2p": (push, h.spmv_halo_wait, h.spmv_halo_fuse), "p2p-side": (push, h.spmv_halo_wait),
+                   "p2p-barrier": (push, None), "nccl": (push, None)}[args.exchange]
         for r in range(REPLICAS):
             op = RowBlockSpmv(a, row_starts, "p2p" if args.exchange.startswith("p2p") else "halo", lambda c: DeviceCSR(c, "d", dev),
                               lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
                               view=(lambda A, r0, r1: A.view_rows(r0, r1)) if args.overlap else None,
-                              push=(push, None if args.exchange == "p2p-barrier" else h.spmv_halo_wait), side=side)
+                              push=P2P_FNS, side=side)
             op.set_x(torch.from_numpy(xs).to(dev))
             if op.p2p is not None and op.p2p[1] is not None:
                 h.set_option("SPMV_HALO_START", op.plan.halo_base)  # marks the tiles that must wait for the peers
@@ -235,9 +237,10 @@ def run_ours(args):
         def step(i):
             ops[i % REPLICAS].step()
         launches_per_step = len(ops[0].split) if ops[0].split else 1
-        launches_per_step += 1 if ops[0].p2p is not None else 0
+        launches_per_step += 1 if (ops[0].p2p is not None and len(ops[0].p2p) < 3) else 0
         extra["exchange"] = {"mode": (("halo push over NVLink peer memory (rsg_halo_push) + " +
-                                       ("arrival flags awaited inside the SpMV's boundary tiles" if ops[0].p2p[1] else "symmetric-memory barrier"))
+                                       ("FUSED into the SpMV launch (first CTAs push + signal, boundary tiles await the neighbours' flags)" if len(ops[0].p2p) > 2
+                                        else "arrival flags awaited inside the SpMV's boundary tiles" if ops[0].p2p[1] else "symmetric-memory barrier"))
                                       if ops[0].p2p is not None else "halo all-gather (NCCL)") + (" on a side stream, overlapped with the %d interior rows; "
                                                                    "boundary rows follow" % ops[0].interior_rows if ops[0].split else ""),
                              "bytes_received_per_rank_per_step": ops[0].exchange_bytes}
@@ -299,6 +302,45 @@ def run_ours(args):
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": bytes_per, "frac_of_8TBs_nominal": achieved / 8000.0,
                 "us_per_launch": per_launch_ms * 1e3}
+
+    # ---- BASELINE configs[4]: the 64M-entry matrix (27-point, 134^3), STRONG scaling: plane-aligned row blocks
+    # over all ranks, same exchange as above; two resident copies rotated (per-rank share > L2 only up to N=4,
+    # so the copies keep a step from being served out of L2)
+    if not args.no_c5:
+        G5 = 134
+        cuts = [(r * G5 + world // 2) // world for r in range(world + 1)]
+        a5 = host.gen_stencil27(G5, G5, G5, cuts[rank], cuts[rank + 1], seed=2)
+        starts5 = np.array(cuts, dtype=np.int64) * G5 * G5
+        x5 = (orc.dlarnv(G5 ** 3) - 0.5)[starts5[rank]:starts5[rank + 1]]
+        ops5 = []
+        for r in range(REPLICAS):
+            if world > 1:
+                op = RowBlockSpmv(a5, starts5, "p2p" if args.exchange.startswith("p2p") else "halo", lambda c: DeviceCSR(c, "d", dev),
+                                  lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
+                                  push=P2P_FNS, side=side)
+                if op.p2p is not None and op.p2p[1] is not None:
+                    h.set_option("SPMV_HALO_START", op.plan.halo_base)
+            else:
+                op = RowBlockSpmv(a5, starts5, "halo", lambda c: DeviceCSR(c, "d", dev), lambda A, x, y: h.spmv(A, x, y), dev,
+                                  torch.float64)
+            op.set_x(torch.from_numpy(x5.copy()).to(dev))
+            h.spmv_analysis(op.A)
+            ops5.append(op)
+        for i in range(6):
+            ops5[i % REPLICAS].step()
+        K5 = max(50, min(K, 400))
+        ms5, _, _ = timed_loop(torch, lambda i: ops5[i % REPLICAS].step(), K5, barrier)
+        ms5 = allmax(ms5)
+        stored5 = allsum(float(a5.stored))
+        b5 = stored5 * 12 + (G5 ** 3 + 1) * 4 + 2 * 8 * G5 ** 3
+        ref5 = orc.spmv(a5.rows(a5.m - 2000, a5.m), orc.dlarnv(G5 ** 3) - 0.5, "d")
+        got5 = ops5[(K5 - 1) % REPLICAS].y[a5.m - 2000:].cpu().numpy()
+        assert np.abs(got5 - ref5).max() <= 1e-12 * np.abs(ref5).max(), "rank %d: config-5 result differs from the oracle" % rank
+        extra["c5_strong_fp64"] = {"workload": "27-point 134^3, %d entries in total, row blocks of whole planes over %d GPU(s)" % (int(stored5), world),
+                                   "us_per_product": ms5 / K5 * 1e3, "GBps_aggregate": b5 / (ms5 / K5 * 1e-3) * 1e-9,
+                                   "GFLOPs": 2.0 * stored5 / (ms5 / K5 * 1e-3) * 1e-9, "scaling": "strong"}
+        h.set_option("SPMV_HALO_START", 0)
+        del ops5, a5
 
     e2e = None
     cpu_baseline = None
@@ -444,9 +486,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the host-CPU baseline leg")
+    ap.add_argument("--no-c5", action="store_true", help="skip the 64M-entry strong-scaling leg (BASELINE configs[4])")
     ap.add_argument("--graph", action="store_true", help="N>1: replay each step from a CUDA graph (NCCL exchange only)")
     ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
-    ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-side", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -173,6 +173,12 @@ int rsg_halo_push(rsg_handle_t handle, int elem_bytes, int nsend, const int *sen
  * overlaps the product without splitting it.  Needs the TILE kernel (AUTO picks it for regular rows);
  * other kernels return RSG_UNSUPPORTED.  A wait gives up after ~1 s (result then undefined). */
 int rsg_spmv_halo_wait(rsg_handle_t handle, const int *flags, int nflags, int epoch);
+/* One-shot: the NEXT spmv_csr_* call also performs the push of rsg_halo_push itself -- its first few CTAs
+ * store x[send_idx[j]] (x = that call's x) into the peers' slots and release `epoch` to their flags, the
+ * tiles follow in the same grid: ONE launch exchanges and multiplies.  Same argument meaning as rsg_halo_push;
+ * TILE kernel only. */
+int rsg_spmv_halo_fuse(rsg_handle_t handle, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
+                       int *const *peer_flags, int epoch);
 
 /* ---- host-pointer convenience wrappers (allocate, H2D, run, D2H, free; synchronous) ------- */
 int spmv_csr_d_host(rsg_handle_t handle, int m, int n, int nnz, int base,

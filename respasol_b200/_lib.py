@@ -69,6 +69,7 @@ GPU_SYMBOLS = {
     "rsg_matrix_free": (_I, [_P, _P]),
     "rsg_halo_push": (_I, [_P, _I, _I, _P, _P, _I, _P, _P, _I]),
     "rsg_spmv_halo_wait": (_I, [_P, _P, _I, _I]),
+    "rsg_spmv_halo_fuse": (_I, [_P, _I, _P, _I, _P, _P, _I]),
 }
 
 HOST_SYMBOLS = {

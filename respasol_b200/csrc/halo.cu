@@ -29,16 +29,19 @@ halo_push_kernel(int nsend, const int *__restrict__ send_idx, const T *__restric
     }
     if (epoch == 0) return;
     // signal: the last CTA to finish publishes the epoch to every peer once all stores are visible
+    // (one thread per peer: the system-scope fences overlap instead of queueing behind each other)
+    __shared__ int s_last;
     __threadfence_system();
     __syncthreads();
     if (threadIdx.x == 0) {
         const int done = atomicAdd(cta_counter, 1);
-        if (done == (int)gridDim.x - 1) {
-            *cta_counter = 0; // next launch on this stream starts from zero
-            __threadfence_system();
-            for (int q = 0; q < npeers; ++q)
-                if (peers.flag[q]) asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(peers.flag[q]), "r"(epoch) : "memory");
-        }
+        s_last = (done == (int)gridDim.x - 1);
+        if (s_last) *cta_counter = 0; // next launch on this stream starts from zero
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < npeers && peers.flag[threadIdx.x]) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(peers.flag[threadIdx.x]), "r"(epoch) : "memory");
     }
 }
 
@@ -80,5 +83,22 @@ extern "C" int rsg_spmv_halo_wait(rsg_handle_t h, const int *flags, int nflags, 
     h->wait_flags = nflags > 0 ? flags : nullptr;
     h->wait_n = nflags;
     h->wait_epoch = epoch;
+    return RSG_OK;
+}
+
+extern "C" int rsg_spmv_halo_fuse(rsg_handle_t h, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
+                                  int *const *peer_flags, int epoch)
+{
+    if (!h || nsend < 0 || npeers < 0 || npeers > RSG_MAX_PEERS || epoch <= 0 || !peer_flags) return RSG_BAD_ARG;
+    if (nsend > 0 && (!send_idx || !peer_slots)) return RSG_BAD_ARG;
+    rsg::HaloFuse &f = h->fuse;
+    for (int q = 0; q < RSG_MAX_PEERS; ++q) {
+        f.dst[q] = (q < npeers && peer_slots) ? peer_slots[q] : nullptr;
+        f.flag[q] = q < npeers ? peer_flags[q] : nullptr;
+    }
+    f.send_idx = send_idx;
+    f.counter = h->scratch_i + 62;
+    f.nsend = nsend; f.npeers = npeers; f.epoch = epoch;
+    f.ctas = 1; // sized at launch from the kernel's CTA width
     return RSG_OK;
 }

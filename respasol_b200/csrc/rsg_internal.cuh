@@ -23,6 +23,16 @@
 
 namespace rsg {
 
+// x-halo push folded into the SpMV launch (rsg_spmv_halo_fuse): the first `ctas` CTAs of the grid store
+// x[send_idx[j]] into the peers' halo slots and release `epoch` to their flags, the rest are the tiles.
+struct HaloFuse {
+    void *dst[RSG_MAX_PEERS];
+    int *flag[RSG_MAX_PEERS];
+    const int *send_idx;
+    int *counter;
+    int nsend, npeers, epoch, ctas;
+};
+
 // ------------------------------------------------------------------ SpMV plan
 // Built once per sparsity pattern by rsg_spmv_analysis (device kernels + one small D2H of
 // the statistics), cached in the handle; the analogue of cusparseSpMV_bufferSize/preprocess.
@@ -104,6 +114,7 @@ struct rsg_context {
     int *pinned_i = nullptr;  // small pinned host mirror, 64 ints
     const int *wait_flags = nullptr;   // one-shot halo wait for the next SpMV (rsg_spmv_halo_wait)
     int wait_n = 0, wait_epoch = 0;
+    rsg::HaloFuse fuse = {};           // one-shot fused push for the next SpMV (rsg_spmv_halo_fuse); ctas == 0: none
     const void *persist_ptr = nullptr; // x currently covered by the L2 access-policy window
     size_t persist_bytes = 0;
 };

@@ -215,14 +215,41 @@ template <typename TV, typename TX, int THREADS, int CAPE, int ROWS>
 __global__ void __launch_bounds__(THREADS)
 spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
                  const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
-                 int nnz_end, int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch)
+                 int nnz_end, int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch, const HaloFuse fuse)
 {
     typedef PipeStage<TV, CAPE, ROWS> Stage;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t s_full;
     __shared__ __align__(8) uint64_t s_aux;
     const int tid = threadIdx.x;
-    const int4 d0 = desc[blockIdx.x], d1 = desc[blockIdx.x + 1];
+    if ((int)blockIdx.x < fuse.ctas) {
+        // ---- fused exchange: these CTAs are dispatched first; they publish this rank's boundary entries of x
+        // to the peers (plain stores into P2P-mapped memory over NVLink) while the tiles behind them multiply
+        __shared__ int s_last;
+        for (int j = blockIdx.x * THREADS + tid; j < fuse.nsend; j += fuse.ctas * THREADS) {
+            const TX v = x[fuse.send_idx[j]];
+#pragma unroll 1
+            for (int q = 0; q < fuse.npeers; ++q) {
+                TX *d = static_cast<TX *>(fuse.dst[q]);
+                if (d) d[j] = v;
+            }
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            const int done = atomicAdd(fuse.counter, 1);
+            s_last = (done == fuse.ctas - 1);
+            if (s_last) *fuse.counter = 0;
+        }
+        __syncthreads();
+        if (s_last && tid < fuse.npeers && fuse.flag[tid]) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(fuse.flag[tid]), "r"(fuse.epoch) : "memory");
+        }
+        return;
+    }
+    const int tile_id = (int)blockIdx.x - fuse.ctas;
+    const int4 d0 = desc[tile_id], d1 = desc[tile_id + 1];
     if (tid == 0) { mbar_init(&s_full, 1); mbar_init(&s_aux, 1); }
     __syncthreads();
     const uint64_t spol = make_evict_first_policy();
@@ -425,9 +452,13 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
         RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = true;
     }
-    kern<<<p->nblk, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc, p->first + p->nnz,
-                                                h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags, h->wait_flags ? h->wait_n : 0, h->wait_epoch);
+    HaloFuse fuse = h->fuse;
+    if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
+    kern<<<p->nblk + fuse.ctas, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc,
+                                                            p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags,
+                                                            h->wait_flags ? h->wait_n : 0, h->wait_epoch, fuse);
     h->wait_flags = nullptr; // one-shot
+    h->fuse.ctas = 0;
     h->launches++;
     h->last_spmv_blocks = p->nblk;
     return RSG_OK;

@@ -90,6 +90,10 @@ class HaloPlan:
         self.my_send = send[self.rank]
         lo, hi = rs[self.rank], rs[self.rank + 1]  # peers that read at least one of this rank's entries
         self.readers = [q for q, nb in enumerate(needs_by_rank) if q != self.rank and np.any((nb >= lo) & (nb < hi))]
+        # neighbours[q] (identical on every rank): the ranks q exchanges entries with, in either direction.
+        # A rank signals and awaits exactly its neighbours -- enough to keep it within one step of each of them.
+        reads = [[o for o in range(P) if o != q and np.any((nb >= rs[o]) & (nb < rs[o + 1]))] for q, nb in enumerate(needs_by_rank)]
+        self.neighbours = [sorted(set(reads[q]) | {o for o in range(P) if q in reads[o]}) for q in range(P)]
         self.interior = self._interior_run(a, off)
         return self
 
@@ -188,14 +192,19 @@ class RowBlockSpmv:
         offs = p2p_slot_offsets(self.row_starts, plan.width, self.rank, stride)
         ptrs = list(self.symm.buffer_ptrs)
         self.slots = [[(ptrs[q] + offs[p][q] * esz) if q in plan.readers else 0 for q in range(self.P)] for p in range(2)]
-        # arrival flags: image p, one int per sending rank; every rank signals every peer (and itself), so a
-        # rank can never run more than one step ahead of any other -- the two images are enough
+        # arrival flags: image p, one int per NEIGHBOUR (slot = the sender's position in the receiver's list).
+        # A rank signals all its neighbours, data or not, and awaits all of them, so it can never run more
+        # than one step ahead of a rank it exchanges entries with -- the two images are enough
         fl = symm_mem.empty(2 * 32, dtype=torch.int32, device=device)
         fl.zero_()
         self.symm_flags = symm_mem.rendezvous(fl, group)
         self.flags = fl
         fptrs = list(self.symm_flags.buffer_ptrs)
-        self.flag_slots = [[fptrs[q] + 4 * (32 * p + self.rank) for q in range(self.P)] for p in range(2)]
+        nb = plan.neighbours
+        self.n_wait = len(nb[self.rank])
+        assert self.n_wait <= 16, "more neighbours than RSG_MAX_PEERS"
+        self.flag_slots = [[(fptrs[q] + 4 * (32 * p + nb[q].index(self.rank))) if q in nb[self.rank] else 0
+                            for q in range(self.P)] for p in range(2)]
         self.epoch = 0
         self.parity = 0
         if self.side is None:
@@ -224,13 +233,19 @@ class RowBlockSpmv:
             # push + signal; the product that follows waits for the peers' flags inside its boundary tiles
             self.epoch += 1
             self.x_ext = self.images[self.parity]
-            push, arm = self.p2p
-            if arm is not None:
+            push, arm = self.p2p[0], self.p2p[1]
+            fuse = self.p2p[2] if len(self.p2p) > 2 else None
+            if fuse is not None:
+                # ONE launch: the product's first CTAs push this rank's boundary entries and signal, its boundary
+                # tiles wait for the neighbours' signals, everything else multiplies meanwhile
+                fuse(self.send_idx32, self.slots[self.parity], self.flag_slots[self.parity], self.epoch)
+                arm(self.flag_views[self.parity], self.n_wait, self.epoch)
+            elif arm is not None:
                 # the push runs beside the product (its own stream): only the boundary tiles wait for a peer
                 # (`push` launches on self.side: the caller's push handle is bound to that stream)
                 self.side.wait_stream(torch.cuda.current_stream(self.x_ext.device))
                 push(self.send_idx32, self.x_ext, self.slots[self.parity], self.flag_slots[self.parity], self.epoch)
-                arm(self.flag_views[self.parity], self.P, self.epoch)
+                arm(self.flag_views[self.parity], self.n_wait, self.epoch)
                 self.join_side = True
             else:
                 push(self.send_idx32, self.x_ext, self.slots[self.parity], self.flag_slots[self.parity], self.epoch)

@@ -158,6 +158,13 @@ class Handle:
         _check(self.lib.rsg_halo_push(self.h, x_local.element_size(), int(send_idx.numel()), self._p(send_idx),
                                       self._p(x_local), n, slots, flags, int(epoch)), "rsg_halo_push")
 
+    def spmv_halo_fuse(self, send_idx, peer_slots, peer_flags, epoch):
+        """One-shot: the next spmv does the push of halo_push itself (its first CTAs), reading the entries from its own x."""
+        slots = peer_slots if isinstance(peer_slots, C.Array) else self.ptr_array(peer_slots)
+        flags = peer_flags if isinstance(peer_flags, C.Array) else self.ptr_array(peer_flags)
+        _check(self.lib.rsg_spmv_halo_fuse(self.h, int(send_idx.numel()), self._p(send_idx), len(slots), slots, flags,
+                                           int(epoch)), "rsg_spmv_halo_fuse")
+
     def spmv_halo_wait(self, flags, nflags, epoch):
         """One-shot: tiles of the next spmv that read columns >= SPMV_HALO_START wait for flags[i] >= epoch."""
         _check(self.lib.rsg_spmv_halo_wait(self.h, self._p(flags), int(nflags), int(epoch)), "rsg_spmv_halo_wait")

@@ -119,6 +119,7 @@ def test_p2p_slot_offsets_and_readers():
     for p in plans:
         p.finish(needs)
     assert [p.readers for p in plans] == [[1], [0, 2], [1]]
+    assert all(p.neighbours == [[1], [0, 2], [1]] for p in plans)
     w = plans[0].width
     stride = 512
     offs = p2p_slot_offsets(starts, w, 1, stride)

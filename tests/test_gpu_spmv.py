@@ -422,6 +422,26 @@ def test_halo_push_signal_and_in_kernel_wait(handle):
             assert int(flags[1].item()) == epoch
             got = y.cpu().numpy()
             assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max()
+        # fused form: rank 0's own product launch pushes ITS boundary entries into 'rank 1's' halo and signals
+        send0 = torch.from_numpy(p0.my_send.astype(np.int32)).cuda()
+        peer_halo = torch.full((p1.n_ext,), float("nan"), dtype=torch.float64, device="cuda")
+        peer_flags = torch.zeros(32, dtype=torch.int32, device="cuda")
+        flags[:2] = 7
+        torch.cuda.synchronize()
+        handle.spmv_halo_fuse(send0, [0, peer_halo[p1.halo_base + 0 * p1.width:].data_ptr()], [0, peer_flags.data_ptr()], 7)
+        handle.spmv_halo_wait(flags, 2, 7)
+        y.fill_(0)
+        handle.spmv(A, x_ext, y)
+        torch.cuda.synchronize()
+        assert int(peer_flags[0].item()) == 7
+        want = torch.from_numpy(x[:p0.n_local][p0.my_send]).cuda()
+        assert torch.equal(peer_halo[p1.halo_base:p1.halo_base + len(p0.my_send)], want)
+        assert np.abs(y.cpu().numpy() - ref).max() <= 1e-12 * np.abs(ref).max()
+        # one-shot: the next plain product neither pushes nor waits
+        peer_flags.zero_()
+        handle.spmv(A, x_ext, y)
+        torch.cuda.synchronize()
+        assert int(peer_flags[0].item()) == 0 and np.abs(y.cpu().numpy() - ref).max() <= 1e-12 * np.abs(ref).max()
         other.close()
     finally:
         handle.set_option("SPMV_HALO_START", 0)

@@ -39,28 +39,31 @@ def timed(fn, K=500):
     e1.record()
     torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1) / K * 1e3], device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    every = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(every, t)
+    return [round(float(v.item()), 1) for v in every]
 
 
-for mode in ("p2p", "halo"):
+hp = Handle(lr)
+side = torch.cuda.Stream(device=dev)
+with torch.cuda.stream(side):
+    hp.use_current_stream()
+for mode in sys.argv[1:] or ("p2p", "p2p-side", "halo"):
     ops = []
     for r in range(2):
-        op = RowBlockSpmv(a, row_starts, mode, lambda c: DeviceCSR(c, "d", dev), lambda A, x, y: h.spmv(A, x, y), dev,
-                          torch.float64, push=h.halo_push)
+        op = RowBlockSpmv(a, row_starts, "p2p" if mode.startswith("p2p") else mode, lambda c: DeviceCSR(c, "d", dev), lambda A, x, y: h.spmv(A, x, y), dev,
+                          torch.float64, push=(hp.halo_push, h.spmv_halo_wait, h.spmv_halo_fuse) if mode == "p2p" else (hp.halo_push, h.spmv_halo_wait), side=side)
         op.set_x(torch.from_numpy(xs).to(dev))
+        if op.p2p is not None:
+            h.set_option("SPMV_HALO_START", op.plan.halo_base)
         h.spmv_analysis(op.A)
         ops.append(op)
     t_spmv = timed(lambda i: h.spmv(ops[i % 2].A, ops[i % 2].x_ext, ops[i % 2].y))
-    t_exch = timed(lambda i: ops[i % 2].exchange())
+    t_exch = timed(lambda i: ops[i % 2].exchange()) if not mode.startswith("p2p") else "(runs beside the product)"
     t_both = timed(lambda i: ops[i % 2].step())
-    extra = ""
-    if mode == "p2p":
-        t_push = timed(lambda i: h.halo_push(ops[0].send_idx32, ops[0].x_ext, ops[0].slots[0]))
-        t_bar = timed(lambda i: ops[0].symm.barrier(channel=0))
-        extra = " push %.1f barrier %.1f" % (t_push, t_bar)
+    h.set_option("SPMV_HALO_START", 0)
     if rank == 0:
-        print("%s: spmv %.1f us  exchange %.1f us  step %.1f us%s" % (mode, t_spmv, t_exch, t_both, extra), flush=True)
+        print("%s, us per call on every rank:\n  spmv alone %s\n  exchange alone %s\n  step %s" % (mode, t_spmv, t_exch, t_both), flush=True)
 dist.barrier()
 torch.cuda.synchronize()
 os._exit(0)
