@@ -369,7 +369,7 @@ def run_ours(args):
                                                                 "GFLOPs": 2.0 * full.stored / (t / reps * 1e-3) * 1e-9}
             del As
         extra["spmv_fp64"] = {"GBps": achieved, "us": per_launch_ms * 1e3, "GFLOPs": 2.0 * a.stored / (per_launch_ms * 1e-3) * 1e-9}
-        # config 4: skewed rows, merge-path (fits L2: warm figure, labelled)
+        # config 4: skewed rows -- tile kernel with its long rows split into segment CTAs (fits L2: warm figure, labelled)
         c4 = host.gen_powerlaw(320000, 2.2, 64, 4, 100000, 4)
         A4 = DeviceCSR(c4, "d", dev)
         x4 = torch.from_numpy(orc.dlarnv(c4.n)).to(dev)
@@ -381,6 +381,10 @@ def run_ours(args):
         t4r = rate(A4, x4, y4, max(5, reps // 10))
         h.set_option("SPMV_ALGO", 0)
         extra["spmv_c4_powerlaw_fp64"]["us_rowblock_cta_per_row"] = t4r * 1e3
+        h.set_option("SPMV_ALGO", ALGO["merge"])
+        t4m = rate(A4, x4, y4, max(5, reps // 10))
+        h.set_option("SPMV_ALGO", 0)
+        extra["spmv_c4_powerlaw_fp64"]["us_merge_path"] = t4m * 1e3
         # config 1 (fits L2: warm figure, labelled)
         c1 = host.gen_laplace2d(1000)
         A1 = DeviceCSR(c1, "d", dev)

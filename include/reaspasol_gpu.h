@@ -79,6 +79,10 @@ typedef enum {
     RSG_OPT_SPMV_HALO_START = 15, /* multi-GPU: zero-based column from which x is filled by peers (0 = none); read when
                                      the SpMV plan is built: tiles that touch such columns are marked and can wait on
                                      arrival flags (rsg_spmv_halo_wait) */
+    RSG_OPT_HOST_CHUNKS = 16,   /* rsg_matrix_upload: row chunks of the pipelined host-vector product
+                                   (x H2D | SpMV | y D2H overlap chunk by chunk); 0 = default (4), 1 = one piece */
+    RSG_OPT_HOST_Y_DIRECT = 17, /* pipelined host-vector product: 1 = the kernels store y straight into the page-locked host
+                                   buffer (mapped memory, no D2H copy stage); 0 = device memory + async D2H copies (default) */
     RSG_OPT_COUNT_
 } rsg_option;
 
@@ -180,6 +184,18 @@ int rsg_spmv_halo_wait(rsg_handle_t handle, const int *flags, int nflags, int ep
 int rsg_spmv_halo_fuse(rsg_handle_t handle, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
                        int *const *peer_flags, int epoch);
 
+/* ---- preconditioned conjugate gradients on the three calls above -------------------------- */
+/* Solves A x = b for a symmetric positive definite CSR matrix (device arrays; x holds the initial guess on entry).
+ * The reference contains no Krylov loop -- it benchmarks the kernels such a loop is made of (mixed-precision sparse
+ * solvers, README.md:5-7): every iteration is one spmv_csr_d, one sptrsv_lu_* and three fused vector kernels whose
+ * scalars stay on the device.  lu_precision: 0 = no preconditioner (lu_values ignored), 'd' = fp64 ILU(0) factors
+ * from ilu0_factor_d, 's' = fp32 factors from ilu0_factor_s applied inside the fp64 iteration (r rounded to fp32,
+ * z widened back).  Stops when |r|_2 <= rtol |b|_2 (recurrence residual) or after max_iters; *iters and *relres
+ * (= |r|_2 / |b|_2) may be NULL.  Synchronous (the host reads |r|^2 once per iteration). */
+int rsg_pcg_d(rsg_handle_t handle, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+              const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+              int *iters, double *relres);
+
 /* ---- host-pointer convenience wrappers (allocate, H2D, run, D2H, free; synchronous) ------- */
 int spmv_csr_d_host(rsg_handle_t handle, int m, int n, int nnz, int base,
                     const int *rowptr, const int *colidx, const double *values,
@@ -207,7 +223,11 @@ int sptrsv_lu_s_host(rsg_handle_t handle, int n, int nnz, int base,
 int rsg_matrix_upload(rsg_handle_t handle, char precision, int m, int n, int nnz, int base,
                       const int *rowptr_host, const int *colidx_host, const double *values_host,
                       rsg_matrix_t *matrix);
-/* x_host / y_host are fp64 for 'd' and 'm', fp32 for 's' (passed as void*). */
+/* x_host / y_host are fp64 for 'd' and 'm', fp32 for 's' (passed as void*).  Synchronous.  With beta == 0 the
+ * call is pipelined over row chunks fixed at upload time: chunk c's product starts as soon as the prefix of x
+ * its rows reference has arrived, and its slice of y goes back to the host while chunk c+1 is multiplied, so on a
+ * banded matrix the two PCIe directions and the kernel overlap (a matrix whose first rows reference all of x
+ * degrades to "x in, then product and y out overlapped").  Page-locked caller buffers are used in place. */
 int rsg_matrix_spmv_host(rsg_handle_t handle, rsg_matrix_t matrix, double alpha,
                          const void *x_host, double beta, void *y_host);
 int rsg_matrix_free(rsg_handle_t handle, rsg_matrix_t matrix);

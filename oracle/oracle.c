@@ -314,3 +314,67 @@ void orc_row_partition(int m, int base, const int *rowptr, int P, int balanced, 
         start[g] = lo;
     }
 }
+
+/* ------------------------------------------------------------------ PCG ---
+ * Textbook preconditioned conjugate gradients (Hestenes-Stiefel; Saad, Iterative Methods, Alg. 9.1)
+ * on the oracle's own SpMV and triangular solves -- the checker of rsg_pcg_d (the
+ * reference has no Krylov loop, README.md:5-7 names the use).  lu_precision 0: none; 'd': fp64
+ * factors; 's': fp32 factors applied to r rounded to fp32, z widened back.  Left-to-right dots.
+ * Returns the iteration count; *relres = |r|_2/|b|_2 of the recurrence residual. */
+static double orc_dot(int n, const double *a, const double *b)
+{
+    double s = 0;
+    for (int i = 0; i < n; ++i) s = fma(a[i], b[i], s);
+    return s;
+}
+
+int orc_pcg_d(int n, int base, const int *rowptr, const int *colidx, const double *values,
+              const void *lu, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+              double *relres)
+{
+    double *r = malloc(sizeof(double) * (size_t)(n + 1)), *z = malloc(sizeof(double) * (size_t)(n + 1));
+    double *p = malloc(sizeof(double) * (size_t)(n + 1)), *q = malloc(sizeof(double) * (size_t)(n + 1));
+    float *r32 = malloc(sizeof(float) * (size_t)(n + 1)), *z32 = malloc(sizeof(float) * (size_t)(n + 1));
+    float *t32 = malloc(sizeof(float) * (size_t)(n + 1));
+    orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, x, 0.0, q);
+    for (int i = 0; i < n; ++i) r[i] = b[i] - q[i];
+    double bb = orc_dot(n, b, b), rr = orc_dot(n, r, r);
+    if (!(bb > 0)) bb = 1.0;
+    const double stop = rtol * rtol * bb;
+    int it = 0;
+    double rz = 0;
+    if (!(rr <= stop)) {
+        for (;;) {
+            if (lu_precision == 0) {
+                for (int i = 0; i < n; ++i) z[i] = r[i];
+            } else if (lu_precision == 's') {
+                for (int i = 0; i < n; ++i) r32[i] = (float)r[i];
+                orc_sptrsv_lu_s(n, base, rowptr, colidx, (const float *)lu, r32, t32, z32);
+                for (int i = 0; i < n; ++i) z[i] = (double)z32[i];
+            } else {
+                orc_sptrsv_lu_d(n, base, rowptr, colidx, (const double *)lu, r, q, z);
+            }
+            const double rz_new = orc_dot(n, r, z);
+            if (it == 0) {
+                for (int i = 0; i < n; ++i) p[i] = z[i];
+            } else {
+                const double beta = rz_new / rz;
+                for (int i = 0; i < n; ++i) p[i] = fma(beta, p[i], z[i]);
+            }
+            rz = rz_new;
+            if (it >= max_iters || !(rr > stop)) break;
+            orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, p, 0.0, q);
+            const double alpha = rz / orc_dot(n, p, q);
+            rr = 0;
+            for (int i = 0; i < n; ++i) {
+                x[i] = fma(alpha, p[i], x[i]);
+                r[i] = fma(-alpha, q[i], r[i]);
+                rr = fma(r[i], r[i], rr);
+            }
+            ++it;
+        }
+    }
+    if (relres) *relres = sqrt(rr / bb);
+    free(r); free(z); free(p); free(q); free(r32); free(z32); free(t32);
+    return it;
+}

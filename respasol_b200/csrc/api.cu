@@ -95,6 +95,8 @@ int rsg_destroy(rsg_handle_t h)
     for (auto &p : h->spmv_plans) spmv_free_plan(p);
     for (auto &p : h->tri_plans) tri_free_plan(p);
     if (h->cub_tmp) cudaFree(h->cub_tmp);
+    if (h->krylov_ws) cudaFree(h->krylov_ws);
+    if (h->krylov_pin) cudaFreeHost(h->krylov_pin);
     cudaFree(h->scratch_i);
     cudaFreeHost(h->pinned_i);
     delete h;
@@ -461,8 +463,64 @@ int rsg_matrix_upload(rsg_handle_t h, char precision, int m, int n, int nnz, int
     }
     if (cudaStreamSynchronize(st) != cudaSuccess && rc == RSG_OK) rc = RSG_CUDA_ERROR;
     if (rc != RSG_OK) { (void)cudaGetLastError(); rsg_matrix_free(h, a); return rc; }
+    // Row chunks of the pipelined host-vector product: entry-balanced cuts; chunk c needs x[0 .. hi_c) where
+    // hi_c = 1 + the largest zero-based column any row of chunks 0..c references (one pass over colidx).
+    int want = h->opts[RSG_OPT_HOST_CHUNKS] > 0 ? h->opts[RSG_OPT_HOST_CHUNKS] : 4; // measured best on config 2 (tools/e2e_breakdown.py)
+    want = std::min(want, (int)rsg_matrix::kMaxChunks);
+    if ((size_t)m * xs < ((size_t)1 << 20) || cnt == 0) want = 1; // small vectors: one piece, latency wins
+    a->nchunk = 1;
+    a->chunk_row[0] = 0; a->chunk_row[1] = m;
+    a->chunk_x[0] = 0; a->chunk_x[1] = n;
+    if (want > 1) {
+        const long long first = rowptr_host[0], total = (long long)rowptr_host[m] - first;
+        int nc = 0;
+        for (int c = 1; c <= want; ++c) {
+            int r = m;
+            if (c < want) // cut on a multiple of 4 rows: every chunk's y slice stays 16/32-byte aligned
+                r = (int)(std::lower_bound(rowptr_host, rowptr_host + m + 1, (int)(first + total * c / want)) - rowptr_host) & ~3;
+            r = std::min(std::max(r, a->chunk_row[nc]), m);
+            if (r > a->chunk_row[nc]) a->chunk_row[++nc] = r;
+        }
+        a->nchunk = nc;
+        int hi = 0;
+        for (int c = 0; c < nc; ++c) {
+            const int *ci = colidx_host + (rowptr_host[a->chunk_row[c]] - base), *ce = colidx_host + (rowptr_host[a->chunk_row[c + 1]] - base);
+            int mx = -1;
+            for (; ci < ce; ++ci) mx = std::max(mx, *ci);
+            hi = std::max(hi, std::min(mx - base + 1, n));
+            a->chunk_x[c + 1] = c + 1 == nc ? n : hi;
+        }
+    }
+    bool ev_ok = cudaStreamCreateWithFlags(&a->s_in, cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaStreamCreateWithFlags(&a->s_out, cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&a->ev_start, cudaEventDisableTiming) == cudaSuccess;
+    for (int c = 0; ev_ok && c < a->nchunk; ++c)
+        ev_ok = cudaEventCreateWithFlags(&a->ev_in[c], cudaEventDisableTiming) == cudaSuccess &&
+                cudaEventCreateWithFlags(&a->ev_mul[c], cudaEventDisableTiming) == cudaSuccess;
+    if (!ev_ok) { (void)cudaGetLastError(); rsg_matrix_free(h, a); return RSG_CUDA_ERROR; }
+    // plans of the whole matrix and of every chunk view now, so that no product pays for an analysis
+    SpmvPlan *pl = nullptr;
+    rc = spmv_get_plan(h, m, n, a->nnz, base, a->rowptr, a->colidx, false, &pl, (int)vs);
+    for (int c = 0; rc == RSG_OK && a->nchunk > 1 && c < a->nchunk; ++c)
+        rc = spmv_get_plan(h, a->chunk_row[c + 1] - a->chunk_row[c], n, a->nnz, base, a->rowptr + a->chunk_row[c], a->colidx,
+                           false, &pl, (int)vs);
+    if (rc != RSG_OK) { rsg_matrix_free(h, a); return rc; }
     *matrix = a;
     return RSG_OK;
+}
+
+extern "C++" template <typename TV, typename TX>
+int matrix_rows_spmv(rsg_handle_t h, rsg_matrix_t a, int r0, int r1, double alpha, double beta, void *y)
+{
+    return spmv_run<TV, TX>(h, r1 - r0, a->n, a->nnz, a->base, a->rowptr + r0, a->colidx, static_cast<const TV *>(a->values),
+                            (TX)alpha, static_cast<const TX *>(a->x), (TX)beta, static_cast<TX *>(y) + r0);
+}
+// y: where row 0 of the product goes (device memory, or page-locked host memory the device can address)
+static int matrix_rows_spmv_any(rsg_handle_t h, rsg_matrix_t a, int r0, int r1, double alpha, double beta, void *y)
+{
+    if (a->precision == 'd') return matrix_rows_spmv<double, double>(h, a, r0, r1, alpha, beta, y);
+    if (a->precision == 's') return matrix_rows_spmv<float, float>(h, a, r0, r1, alpha, beta, y);
+    return matrix_rows_spmv<float, double>(h, a, r0, r1, alpha, beta, y);
 }
 
 int rsg_matrix_spmv_host(rsg_handle_t h, rsg_matrix_t a, double alpha, const void *x_host, double beta, void *y_host)
@@ -480,24 +538,46 @@ int rsg_matrix_spmv_host(rsg_handle_t h, rsg_matrix_t a, double alpha, const voi
     };
     const bool x_pinned = a->n > 0 && pinned(x_host), y_pinned = pinned(y_host);
     if (!x_pinned) std::memcpy(a->pin_x, x_host, xs * (size_t)a->n);
-    RSG_CUDA_TRY(cudaMemcpyAsync(a->x, x_pinned ? x_host : a->pin_x, xs * (size_t)a->n, cudaMemcpyHostToDevice, st));
-    if (beta != 0.0) {
-        if (!y_pinned) std::memcpy(a->pin_y, y_host, xs * (size_t)a->m);
-        RSG_CUDA_TRY(cudaMemcpyAsync(a->y, y_pinned ? y_host : a->pin_y, xs * (size_t)a->m, cudaMemcpyHostToDevice, st));
+    const char *xsrc = static_cast<const char *>(x_pinned ? x_host : a->pin_x);
+    char *ydst = static_cast<char *>(y_pinned ? y_host : a->pin_y);
+    if (beta != 0.0 || a->nchunk <= 1) { // one piece: x in, product, y out on the handle's stream
+        RSG_CUDA_TRY(cudaMemcpyAsync(a->x, xsrc, xs * (size_t)a->n, cudaMemcpyHostToDevice, st));
+        if (beta != 0.0) {
+            if (!y_pinned) std::memcpy(a->pin_y, y_host, xs * (size_t)a->m);
+            RSG_CUDA_TRY(cudaMemcpyAsync(a->y, ydst, xs * (size_t)a->m, cudaMemcpyHostToDevice, st));
+        }
+        RSG_TRY(matrix_rows_spmv_any(h, a, 0, a->m, alpha, beta, a->y));
+        RSG_CUDA_TRY(cudaMemcpyAsync(ydst, a->y, xs * (size_t)a->m, cudaMemcpyDeviceToHost, st));
+        RSG_CUDA_TRY(cudaStreamSynchronize(st));
+    } else {
+        // s_in carries x upward piece by piece; the handle's stream multiplies chunk c once its prefix of x has landed.
+        // y: s_out copies chunk c's slice back while chunk c+1 is multiplied; with HOST_Y_DIRECT = 1 the kernels store
+        // straight into the page-locked host buffer instead (mapped memory; measured slower: tools/e2e_breakdown.py)
+        const bool direct = h->opts[RSG_OPT_HOST_Y_DIRECT] == 1;
+        void *ydev = a->y;
+        if (direct && cudaHostGetDevicePointer(&ydev, ydst, 0) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
+        RSG_CUDA_TRY(cudaEventRecord(a->ev_start, st));
+        RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_in, a->ev_start, 0));
+        if (!direct) RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_out, a->ev_start, 0));
+        int rc = RSG_OK;
+        for (int c = 0; c < a->nchunk && rc == RSG_OK; ++c) {
+            const size_t x0 = (size_t)a->chunk_x[c], x1 = (size_t)a->chunk_x[c + 1];
+            if (x1 > x0) RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(a->x) + xs * x0, xsrc + xs * x0, xs * (x1 - x0), cudaMemcpyHostToDevice, a->s_in));
+            RSG_CUDA_TRY(cudaEventRecord(a->ev_in[c], a->s_in));
+        }
+        for (int c = 0; c < a->nchunk && rc == RSG_OK; ++c) {
+            const int r0 = a->chunk_row[c], r1 = a->chunk_row[c + 1];
+            RSG_CUDA_TRY(cudaStreamWaitEvent(st, a->ev_in[c], 0));
+            if (r1 > r0) rc = matrix_rows_spmv_any(h, a, r0, r1, alpha, 0.0, ydev);
+            if (direct) continue;
+            RSG_CUDA_TRY(cudaEventRecord(a->ev_mul[c], st));
+            RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_out, a->ev_mul[c], 0));
+            if (r1 > r0) RSG_CUDA_TRY(cudaMemcpyAsync(ydst + xs * (size_t)r0, static_cast<char *>(a->y) + xs * (size_t)r0, xs * (size_t)(r1 - r0), cudaMemcpyDeviceToHost, a->s_out));
+        }
+        cudaError_t e1 = direct ? cudaSuccess : cudaStreamSynchronize(a->s_out), e2 = cudaStreamSynchronize(st), e3 = cudaStreamSynchronize(a->s_in);
+        RSG_TRY(rc);
+        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
     }
-    int rc;
-    if (a->precision == 'd')
-        rc = spmv_run<double, double>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const double *>(a->values),
-                                      alpha, static_cast<const double *>(a->x), beta, static_cast<double *>(a->y));
-    else if (a->precision == 's')
-        rc = spmv_run<float, float>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
-                                    (float)alpha, static_cast<const float *>(a->x), (float)beta, static_cast<float *>(a->y));
-    else
-        rc = spmv_run<float, double>(h, a->m, a->n, a->nnz, a->base, a->rowptr, a->colidx, static_cast<const float *>(a->values),
-                                     alpha, static_cast<const double *>(a->x), beta, static_cast<double *>(a->y));
-    RSG_TRY(rc);
-    RSG_CUDA_TRY(cudaMemcpyAsync(y_pinned ? y_host : a->pin_y, a->y, xs * (size_t)a->m, cudaMemcpyDeviceToHost, st));
-    RSG_CUDA_TRY(cudaStreamSynchronize(st));
     if (!y_pinned) std::memcpy(y_host, a->pin_y, xs * (size_t)a->m);
     return RSG_OK;
 }
@@ -506,11 +586,21 @@ int rsg_matrix_free(rsg_handle_t h, rsg_matrix_t a)
 {
     if (!h || !a) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    for (size_t i = 0; i < h->spmv_plans.size(); ++i)
-        if (h->spmv_plans[i].rowptr == a->rowptr) { spmv_free_plan(h->spmv_plans[i]); h->spmv_plans.erase(h->spmv_plans.begin() + (long)i); break; }
+    for (size_t i = h->spmv_plans.size(); i-- > 0;) // the matrix's plan and those of its chunk views
+        if (a->rowptr && h->spmv_plans[i].rowptr >= a->rowptr && h->spmv_plans[i].rowptr <= a->rowptr + a->m) {
+            spmv_free_plan(h->spmv_plans[i]);
+            h->spmv_plans.erase(h->spmv_plans.begin() + (long)i);
+        }
     cudaFree(a->rowptr); cudaFree(a->colidx); cudaFree(a->values); cudaFree(a->x); cudaFree(a->y);
     if (a->pin_x) cudaFreeHost(a->pin_x);
     if (a->pin_y) cudaFreeHost(a->pin_y);
+    if (a->s_in) cudaStreamDestroy(a->s_in);
+    if (a->s_out) cudaStreamDestroy(a->s_out);
+    if (a->ev_start) cudaEventDestroy(a->ev_start);
+    for (int c = 0; c < rsg_matrix::kMaxChunks; ++c) {
+        if (a->ev_in[c]) cudaEventDestroy(a->ev_in[c]);
+        if (a->ev_mul[c]) cudaEventDestroy(a->ev_mul[c]);
+    }
     delete a;
     return RSG_OK;
 }

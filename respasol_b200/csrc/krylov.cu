@@ -1,0 +1,217 @@
+// krylov.cu -- preconditioned conjugate gradients on the three hot-path calls: the loop the
+// reference benchmarks its kernels for (mixed-precision sparse solvers, /root/reference/README.md:5-7) but does
+// not contain.  q = A p is spmv_csr_d; z = M^-1 r is sptrsv_lu_d on fp64 ILU(0) factors, or sptrsv_lu_s on fp32
+// factors with r rounded to fp32 and z widened back (fp32 preconditioner inside an fp64 iteration); the vector
+// updates and dot products are fused into three small kernels whose scalars (alpha, beta, r.z, p.q) never leave
+// the device.  Dot products are deterministic: per-CTA partials, the last CTA to arrive adds them in CTA order.
+//
+// One iteration = 1 SpMV + 2 triangular solves + 3 (4 with fp32 factors) vector kernels; the host reads one
+// double (|r|^2) per iteration to decide convergence.
+#include <cuda_runtime.h>
+
+#include <cmath>
+
+#include "rsg_internal.cuh"
+
+namespace rsg {
+
+static constexpr int kVecThreads = 256;
+static constexpr int kMaxVecBlocks = 1024;
+
+// scalars (device doubles): [0] rz (ping), [1] rz (pong), [2] pq, [3] rr, [4] bb
+enum { S_RZ0 = 0, S_RZ1 = 1, S_PQ = 2, S_RR = 3, S_BB = 4, S_COUNT = 8 };
+
+// CTA partial -> partials[blockIdx]; the last CTA adds all partials in index order and stores *out.
+__device__ __forceinline__ void finish_dot(double local, double *partials, unsigned *ticket, double *out)
+{
+    __shared__ double s_red[kVecThreads / 32];
+    __shared__ bool s_last;
+    const int tid = threadIdx.x;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((tid & 31) == 0) s_red[tid >> 5] = local;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0;
+        for (int w = 0; w < kVecThreads / 32; ++w) t += s_red[w];
+        partials[blockIdx.x] = t;
+        __threadfence();
+        s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    double t = 0;
+    for (int i = tid; i < (int)gridDim.x; i += kVecThreads) t += *reinterpret_cast<volatile double *>(partials + i);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    __syncthreads();
+    if ((tid & 31) == 0) s_red[tid >> 5] = t;
+    __syncthreads();
+    if (tid == 0) {
+        double s = 0;
+        for (int w = 0; w < kVecThreads / 32; ++w) s += s_red[w];
+        *out = s;
+        *ticket = 0;
+    }
+}
+
+// out = a . b
+__global__ void __launch_bounds__(kVecThreads) dot_kernel(int n, const double *__restrict__ a, const double *__restrict__ b,
+                                                          double *partials, unsigned *ticket, double *out)
+{
+    double s = 0;
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) s = fma(a[i], b[i], s);
+    finish_dot(s, partials, ticket, out);
+}
+
+// r = b - q (q = A x0), bb = b.b, rr = r.r in one pass (two dots: bb first into partials, rr second)
+__global__ void __launch_bounds__(kVecThreads) residual_kernel(int n, const double *__restrict__ b, const double *__restrict__ q,
+                                                               double *__restrict__ r)
+{
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) r[i] = b[i] - q[i];
+}
+
+// alpha = rz / pq;  x += alpha p;  r -= alpha q;  rr = r.r;  (r32 = (float) r when the preconditioner is fp32)
+__global__ void __launch_bounds__(kVecThreads) pcg_update_xr_kernel(int n, const double *scal, int rz_slot, const double *__restrict__ p,
+                                                                    const double *__restrict__ q, double *__restrict__ x,
+                                                                    double *__restrict__ r, float *__restrict__ r32, double *partials,
+                                                                    unsigned *ticket, double *out_rr)
+{
+    const double alpha = scal[rz_slot] / scal[S_PQ];
+    double s = 0;
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        x[i] = fma(alpha, p[i], x[i]);
+        const double ri = fma(-alpha, q[i], r[i]);
+        r[i] = ri;
+        if (r32) r32[i] = (float)ri;
+        s = fma(ri, ri, s);
+    }
+    finish_dot(s, partials, ticket, out_rr);
+}
+
+// z = (double) z32 (fp32 preconditioner), rz_new = r.z
+__global__ void __launch_bounds__(kVecThreads) pcg_rz_kernel(int n, const double *__restrict__ r, const float *__restrict__ z32,
+                                                             double *__restrict__ z, double *partials, unsigned *ticket, double *out)
+{
+    double s = 0;
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        double zi;
+        if (z32) { zi = (double)z32[i]; z[i] = zi; } else zi = z[i];
+        s = fma(r[i], zi, s);
+    }
+    finish_dot(s, partials, ticket, out);
+}
+
+// beta = rz_new / rz_old (beta = 0 on the first pass: p = z);  p = z + beta p
+__global__ void __launch_bounds__(kVecThreads) pcg_update_p_kernel(int n, const double *scal, int rz_new_slot, int first,
+                                                                   const double *__restrict__ z, double *__restrict__ p)
+{
+    const double beta = first ? 0.0 : scal[rz_new_slot] / scal[rz_new_slot ^ 1];
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) p[i] = first ? z[i] : fma(beta, p[i], z[i]);
+}
+
+__global__ void __launch_bounds__(kVecThreads) cast_kernel(int n, const double *__restrict__ a, float *__restrict__ b)
+{
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) b[i] = (float)a[i];
+}
+
+} // namespace rsg
+
+using namespace rsg;
+
+namespace {
+struct Guard {
+    int prev = 0;
+    explicit Guard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~Guard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+} // namespace
+
+extern "C" int rsg_pcg_d(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                         const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                         int *iters, double *relres)
+{
+    if (!h || n < 0 || !rowptr || (n > 0 && (!b || !x || !values)) || max_iters < 0 ||
+        (lu_precision != 0 && lu_precision != 'd' && lu_precision != 's') || (lu_precision != 0 && !lu_values))
+        return RSG_BAD_ARG;
+    if (iters) *iters = 0;
+    if (relres) *relres = 0.0;
+    if (n == 0) return RSG_OK;
+    Guard g(h->device);
+    cudaStream_t st = h->stream;
+    const bool pre = lu_precision != 0, pre32 = lu_precision == 's';
+    // workspace: r, z, p, q (fp64), r32, z32, t32 (fp32), partials, scalars, ticket
+    const size_t nd = ((size_t)n + 3) & ~(size_t)3;
+    const size_t bytes = nd * 8 * 4 + nd * 4 * 3 + kMaxVecBlocks * 8 + S_COUNT * 8 + 64;
+    if (h->krylov_bytes < bytes) {
+        if (h->krylov_ws) cudaFree(h->krylov_ws);
+        h->krylov_ws = nullptr;
+        h->krylov_bytes = 0;
+        if (cudaMalloc(&h->krylov_ws, bytes) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+        h->krylov_bytes = bytes;
+    }
+    if (!h->krylov_pin && cudaMallocHost(&h->krylov_pin, S_COUNT * sizeof(double)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+    char *w = static_cast<char *>(h->krylov_ws);
+    double *r = reinterpret_cast<double *>(w); w += nd * 8;
+    double *z = reinterpret_cast<double *>(w); w += nd * 8;
+    double *p = reinterpret_cast<double *>(w); w += nd * 8;
+    double *q = reinterpret_cast<double *>(w); w += nd * 8;
+    float *r32 = reinterpret_cast<float *>(w); w += nd * 4;
+    float *z32 = reinterpret_cast<float *>(w); w += nd * 4;
+    float *t32 = reinterpret_cast<float *>(w); w += nd * 4;
+    double *partials = reinterpret_cast<double *>(w); w += kMaxVecBlocks * 8;
+    double *scal = reinterpret_cast<double *>(w); w += S_COUNT * 8;
+    unsigned *ticket = reinterpret_cast<unsigned *>(w);
+    RSG_CUDA_TRY(cudaMemsetAsync(scal, 0, S_COUNT * 8 + 64, st));
+    const int grid = std::max(1, std::min(kMaxVecBlocks, std::min(h->sm_count * 8, (n + kVecThreads * 4 - 1) / (kVecThreads * 4))));
+    double *pin = h->krylov_pin;
+
+    auto precondition = [&](bool first) -> int { // z = M^-1 r, rz -> scal[slot]
+        (void)first;
+        if (!pre) { RSG_CUDA_TRY(cudaMemcpyAsync(z, r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st)); return RSG_OK; }
+        if (pre32) return sptrsv_lu_s(h, n, nnz, base, rowptr, colidx, static_cast<const float *>(lu_values), r32, t32, z32);
+        return sptrsv_lu_d(h, n, nnz, base, rowptr, colidx, static_cast<const double *>(lu_values), r, q, z); // q is free here
+    };
+
+    // r = b - A x0;  bb = b.b;  rr = r.r
+    RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, x, 0.0, q));
+    residual_kernel<<<grid, kVecThreads, 0, st>>>(n, b, q, r);
+    dot_kernel<<<grid, kVecThreads, 0, st>>>(n, b, b, partials, ticket, scal + S_BB);
+    dot_kernel<<<grid, kVecThreads, 0, st>>>(n, r, r, partials, ticket, scal + S_RR);
+    h->launches += 3;
+    if (pre32) { cast_kernel<<<grid, kVecThreads, 0, st>>>(n, r, r32); h->launches++; }
+    RSG_CUDA_TRY(cudaMemcpyAsync(pin, scal, S_COUNT * sizeof(double), cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaStreamSynchronize(st));
+    const double bb = pin[S_BB] > 0 ? pin[S_BB] : 1.0;
+    double rr = pin[S_RR];
+    int it = 0, slot = S_RZ0;
+    const double stop = rtol * rtol * bb;
+    if (!(rr <= stop)) {
+        RSG_TRY(precondition(true));
+        pcg_rz_kernel<<<grid, kVecThreads, 0, st>>>(n, r, pre32 ? z32 : nullptr, z, partials, ticket, scal + slot);
+        pcg_update_p_kernel<<<grid, kVecThreads, 0, st>>>(n, scal, slot, 1, z, p);
+        h->launches += 2;
+        while (it < max_iters) {
+            RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, p, 0.0, q));
+            dot_kernel<<<grid, kVecThreads, 0, st>>>(n, p, q, partials, ticket, scal + S_PQ);
+            pcg_update_xr_kernel<<<grid, kVecThreads, 0, st>>>(n, scal, slot, p, q, x, r, pre32 ? r32 : nullptr, partials, ticket, scal + S_RR);
+            h->launches += 2;
+            RSG_CUDA_TRY(cudaMemcpyAsync(pin + S_RR, scal + S_RR, sizeof(double), cudaMemcpyDeviceToHost, st));
+            ++it;
+            // the next preconditioner application is issued before the host looks at |r|: the stream stays busy
+            RSG_TRY(precondition(false));
+            slot ^= 1;
+            pcg_rz_kernel<<<grid, kVecThreads, 0, st>>>(n, r, pre32 ? z32 : nullptr, z, partials, ticket, scal + slot);
+            pcg_update_p_kernel<<<grid, kVecThreads, 0, st>>>(n, scal, slot, 0, z, p);
+            h->launches += 2;
+            RSG_CUDA_TRY(cudaStreamSynchronize(st));
+            rr = pin[S_RR];
+            if (!(rr > stop) || !std::isfinite(rr)) break;
+        }
+    }
+    RSG_CUDA_TRY(cudaGetLastError());
+    if (iters) *iters = it;
+    if (relres) *relres = std::sqrt(rr / bb);
+    return std::isfinite(rr) ? RSG_OK : RSG_ZERO_PIVOT_NUMERIC;
+}

@@ -33,6 +33,17 @@ struct HaloFuse {
     int nsend, npeers, epoch, ctas;
 };
 
+// Long rows of a TILE plan (longer than a CTA's staging capacity) are cut into segments, one CTA each, placed in
+// the grid ahead of the tiles: partial sums meet in `part`, the last segment of a row to arrive adds them in
+// segment order (deterministic) and stores y.  The tiles skip those rows.
+struct LongSplit {
+    const int4 *seg;  // per segment: (row, first zero-based entry, end entry, index into lrow)
+    const int2 *lrow; // per long row: (first segment slot, number of segments)
+    double *part;     // one 8-byte slot per segment
+    int *cnt;         // arrivals per long row (reset by the last arrival)
+    int nseg;
+};
+
 // ------------------------------------------------------------------ SpMV plan
 // Built once per sparsity pattern by rsg_spmv_analysis (device kernels + one small D2H of
 // the statistics), cached in the handle; the analogue of cusparseSpMV_bufferSize/preprocess.
@@ -57,6 +68,12 @@ struct SpmvPlan {
     int4 *pdesc = nullptr;     // pipe kernel: nblk+1 (first row, zero-based entry offset, longest row, 0)
     int *rp0 = nullptr;        // pipe kernel: zero-based padded copy of rowptr
     int rp0_len = 0;
+    // tile kernel: split long rows (LongSplit)
+    int4 *seg = nullptr;
+    int2 *lrow = nullptr;
+    double *seg_part = nullptr;
+    int *seg_cnt = nullptr;
+    int nseg = 0, nlong = 0;
     // merge-path kernel
     int merge_items = 0;   // rows+entries per CTA
     int ntiles = 0;
@@ -117,6 +134,9 @@ struct rsg_context {
     rsg::HaloFuse fuse = {};           // one-shot fused push for the next SpMV (rsg_spmv_halo_fuse); ctas == 0: none
     const void *persist_ptr = nullptr; // x currently covered by the L2 access-policy window
     size_t persist_bytes = 0;
+    void *krylov_ws = nullptr;         // grow-only workspace of rsg_pcg_d (vectors, partial sums, scalars)
+    size_t krylov_bytes = 0;
+    double *krylov_pin = nullptr;      // pinned host mirror of the scalars
 };
 
 struct rsg_matrix {
@@ -129,6 +149,13 @@ struct rsg_matrix {
     void *y;
     void *pin_x; // pinned staging
     void *pin_y;
+    // pipelined host-vector product (rsg_matrix_spmv_host): row chunks fixed at upload time
+    static constexpr int kMaxChunks = 32;
+    int nchunk;                   // 1 = not pipelined
+    int chunk_row[kMaxChunks + 1]; // first row of every chunk
+    int chunk_x[kMaxChunks + 1];   // chunk c may start once x[0 .. chunk_x[c+1]) is on the device (monotone)
+    cudaStream_t s_in, s_out;
+    cudaEvent_t ev_start, ev_in[kMaxChunks], ev_mul[kMaxChunks];
 };
 
 namespace rsg {
@@ -150,7 +177,7 @@ int pipe_num_variants();
 int tile_num_variants();
 template <typename TV, typename TX>
 int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
-int pipe_build_plan(rsg_context *h, SpmvPlan &p);
+int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split = false);
 template <typename TV, typename TX>
 int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 

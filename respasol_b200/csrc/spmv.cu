@@ -441,7 +441,7 @@ static constexpr int kStreamW = 2;
 
 void spmv_free_plan(SpmvPlan &p)
 {
-    cudaFree(p.blk_row); cudaFree(p.sblk); cudaFree(p.pdesc); cudaFree(p.rp0); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
+    cudaFree(p.blk_row); cudaFree(p.sblk); cudaFree(p.pdesc); cudaFree(p.rp0); cudaFree(p.seg); cudaFree(p.lrow); cudaFree(p.seg_part); cudaFree(p.seg_cnt); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
     p = SpmvPlan();
 }
 
@@ -498,16 +498,18 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         // roughly nnz/64 entries that single row outlasts the rest of the product: merge-path.
         const int cap = RowBlockShape<4096>::CAP;
         const long long skew = std::max<long long>(cap, (long long)p.nnz / 64);
-        algo = (p.max_row > skew) ? RSG_SPMV_MERGE : (aligned ? RSG_SPMV_TILE : RSG_SPMV_ROWBLOCK);
-        // measured on config 2 (tools/spmv_sweep.py): ~24-28 KB of entries per CTA is the sweet spot:
-        // 8-byte values -> 128 threads x 2304 entries, 4-byte values -> 128 threads x 4352 entries
-        // short rows (5-point stencils): more rows than threads per tile otherwise -> 256 threads
+        // aligned arrays: the TILE kernel, which cuts rows longer than a CTA's stage into one-CTA segments (up to
+        // a few thousand such rows; beyond that pipe_build_plan declines and merge-path takes over)
+        algo = aligned ? RSG_SPMV_TILE : (p.max_row > skew ? RSG_SPMV_MERGE : RSG_SPMV_ROWBLOCK);
+        // measured (tools/spmv_sweep.py).  Config 2: ~24-28 KB of entries per CTA is the sweet spot: 8-byte values ->
+        // 128 threads x 2304 entries, 4-byte values -> 128 threads x 4352 entries.  Short rows (5-point stencils,
+        // power-law rows; configs 1 and 4) are bound by the latency of the x gathers, not by the stream: a small
+        // stage (128 threads x 1152 entries, 15 KB) keeps ~60 warps resident per SM
         if (algo == RSG_SPMV_TILE) {
             const double avg = (double)p.nnz / std::max(m, 1);
-            variant = vbytes >= 8 ? (avg < 12.0 ? 4 : 0) : (avg < 12.0 ? 0 : 1);
+            variant = avg < 12.0 ? 9 : (vbytes >= 8 ? 0 : 1);
         }
     }
-    (void)auto_algo;
     if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)
         algo = RSG_SPMV_ROWBLOCK; // bulk copies need 16-byte aligned arrays
     const int nvar = algo == RSG_SPMV_STREAM ? kNumStreamVariants : algo == RSG_SPMV_PIPE ? pipe_num_variants()
@@ -517,14 +519,25 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
     p.tile = algo == RSG_SPMV_STREAM ? kStreamVariants[variant].tile : kVariants[variant].tile;
     p.algo = algo;
     const long long items = (long long)m + p.nnz;
+    if ((algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && m > 0) {
+        const SpmvPlan bare = p; // nothing allocated yet
+        const int rc = pipe_build_plan(h, p, auto_algo);
+        if (rc == RSG_UNSUPPORTED && auto_algo) { // too many long rows to split: merge-path
+            spmv_free_plan(p);
+            p = bare;
+            algo = p.algo = RSG_SPMV_MERGE;
+            p.variant = 0;
+            p.tile = kVariants[0].tile;
+        } else {
+            RSG_TRY(rc);
+        }
+    }
     if (algo == RSG_SPMV_ROWBLOCK && m > 0) {
         p.nblk = (int)((items + p.tile - 1) / p.tile);
         RSG_CUDA_TRY(cudaMalloc(&p.blk_row, sizeof(int) * ((size_t)p.nblk + 1)));
         p.bytes += sizeof(int) * ((size_t)p.nblk + 1);
         rowblock_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, rowptr, p.tile, p.nblk, p.blk_row);
         h->launches++;
-    } else if ((algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && m > 0) {
-        RSG_TRY(pipe_build_plan(h, p));
     } else if (algo == RSG_SPMV_STREAM && m > 0) {
         const long long witems = (long long)kStreamW * m + p.nnz;
         p.nblk = (int)((witems + p.tile - 1) / p.tile);

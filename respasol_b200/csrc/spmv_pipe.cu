@@ -39,7 +39,7 @@ template <typename TV, typename TX, int NC, int CAPE, int XH, typename Stage, in
 __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeMeta &mt, int base, const int *__restrict__ colidx,
                                                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
                                                   TX alpha, TX beta, int reduce_opt, uint64_t spol, uint64_t xpol,
-                                                  uint64_t *s_aux, uint32_t &aux_parity)
+                                                  uint64_t *s_aux, uint32_t &aux_parity, bool skip_long = false)
 {
     const int tid = threadIdx.x;
     TV *s_val = reinterpret_cast<TV *>(sp + Stage::val_off);
@@ -71,6 +71,7 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
                 pe = lo;
             }
             if (pe == cur) { // this row alone exceeds a stage: CTA-per-row from global memory
+                if (skip_long && s_rp[cur + 1] - k0 > CAPE) { cur += 1; continue; } // reduced by the segment CTAs (LongSplit)
                 const TX tot = cta_row_sum<TV, TX, NC, 1, true, BARID>(k0, s_rp[cur + 1], colidx, values, x, base,
                                                                    reinterpret_cast<TX *>(s_val), spol);
                 if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
@@ -215,7 +216,8 @@ template <typename TV, typename TX, int THREADS, int CAPE, int ROWS>
 __global__ void __launch_bounds__(THREADS)
 spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
                  const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
-                 int nnz_end, int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch, const HaloFuse fuse)
+                 int nnz_end, int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch, const HaloFuse fuse,
+                 const LongSplit ls)
 {
     typedef PipeStage<TV, CAPE, ROWS> Stage;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -248,7 +250,30 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
         }
         return;
     }
-    const int tile_id = (int)blockIdx.x - fuse.ctas;
+    const int seg_id = (int)blockIdx.x - fuse.ctas;
+    if (seg_id < ls.nseg) {
+        // ---- one segment of a long row, straight from global memory with 128-bit loads; the last segment of the
+        // row to arrive adds the partial sums in segment order and stores y
+        const int4 sg = ls.seg[seg_id];
+        const TX tot = cta_row_sum<TV, TX, THREADS, 1, true, 0>(sg.y, sg.z, colidx, values, x, base, reinterpret_cast<TX *>(smem_raw),
+                                                               make_evict_first_policy());
+        if (tid == 0) {
+            const int2 lr = ls.lrow[sg.w];
+            volatile TX *part = reinterpret_cast<volatile TX *>(ls.part + lr.x);
+            *reinterpret_cast<volatile TX *>(ls.part + seg_id) = tot;
+            __threadfence();
+            if (atomicAdd(ls.cnt + sg.w, 1) == lr.y - 1) {
+                __threadfence();
+                TX sum = 0;
+                for (int i = 0; i < lr.y; ++i) sum += *reinterpret_cast<volatile TX *>(ls.part + lr.x + i);
+                store_y(y, sg.x, sum, alpha, beta);
+                ls.cnt[sg.w] = 0;
+            }
+            (void)part;
+        }
+        return;
+    }
+    const int tile_id = seg_id - ls.nseg;
     const int4 d0 = desc[tile_id], d1 = desc[tile_id + 1];
     if (tid == 0) { mbar_init(&s_full, 1); mbar_init(&s_aux, 1); }
     __syncthreads();
@@ -287,7 +312,19 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
     mbar_wait(&s_full, 0);
     uint32_t aux_parity = 0;
     pipe_general_tile<TV, TX, THREADS, CAPE, 0, Stage, 0, true>(smem_raw, mt, base, colidx, values, x, y, alpha, beta, reduce_opt,
-                                                                spol, 0, &s_aux, aux_parity);
+                                                                spol, 0, &s_aux, aux_parity, ls.nseg > 0);
+}
+
+// rows longer than `cape` -> list[] = (row, zero-based start, zero-based end, 0), count in *counter (may exceed cap)
+__global__ void long_rows_kernel(int m, int base, int cape, const int *__restrict__ rowptr, int4 *list, int cap, int *counter)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= m) return;
+    const int a = rowptr[r], b = rowptr[r + 1];
+    if (b - a > cape) {
+        const int slot = atomicAdd(counter, 1);
+        if (slot < cap) list[slot] = make_int4(r, a - base, b - base, 0);
+    }
 }
 
 // desc[b] = (first row, its zero-based entry offset, longest row of the tile, 0); item coordinate
@@ -310,14 +347,17 @@ __global__ void pipe_partition_kernel(int m, int base, const int *__restrict__ r
     desc[b] = make_int4(r, rowptr[r] - base, 0, 0);
 }
 
-// one warp per tile: longest row -> desc[b].z
-__global__ void pipe_maxlen_kernel(int ntiles, int base, const int *__restrict__ rowptr, int4 *desc)
+// one warp per tile: longest row -> desc[b].z (rows longer than `skip` > 0 are reduced elsewhere and do not count)
+__global__ void pipe_maxlen_kernel(int ntiles, int base, int skip, const int *__restrict__ rowptr, int4 *desc)
 {
     const int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (b >= ntiles) return;
     const int r0 = desc[b].x, r1 = desc[b + 1].x;
     int ml = 0;
-    for (int r = r0 + lane; r < r1; r += 32) ml = max(ml, rowptr[r + 1] - rowptr[r]);
+    for (int r = r0 + lane; r < r1; r += 32) {
+        const int len = rowptr[r + 1] - rowptr[r];
+        if (skip <= 0 || len <= skip) ml = max(ml, len);
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ml = max(ml, __shfl_xor_sync(0xffffffffu, ml, o));
     if (lane == 0) desc[b].z = ml;
@@ -356,11 +396,69 @@ int pipe_num_variants() { return kNumPipeVariants; }
 static const PipeVariant kTileVariants[] = { // threads, entries per CTA, rows per CTA (stages unused)
     {128, 2304, 512, 1}, {128, 4352, 512, 1}, {64, 1152, 256, 1}, {64, 2304, 512, 1},
     {256, 4352, 512, 1}, {96, 3456, 384, 1}, {192, 6528, 768, 1}, {256, 8704, 1024, 1},
+    // short rows (gather-latency bound): small stages so that 56-60 warps stay resident per SM
+    {256, 2304, 512, 1}, {128, 1152, 256, 1},
 };
 static const int kNumTileVariants = (int)(sizeof(kTileVariants) / sizeof(kTileVariants[0]));
 int tile_num_variants() { return kNumTileVariants; }
 
-int pipe_build_plan(rsg_context *h, SpmvPlan &p)
+static constexpr int kMaxLongRows = 4096;  // rows split into segments per plan
+static constexpr int kSegEntries = 2048;   // entries per segment CTA
+static constexpr int kMaxSegments = 1 << 20;
+
+// LongSplit of a TILE plan.  strict: RSG_UNSUPPORTED when there are too many long rows (the AUTO caller then
+// takes merge-path); otherwise such a plan simply keeps its long rows CTA-per-row inside the tiles.
+static int tile_build_split(rsg_context *h, SpmvPlan &p, int cape, bool strict)
+{
+    cudaStream_t st = h->stream;
+    int4 *list = nullptr;
+    RSG_CUDA_TRY(cudaMalloc(&list, sizeof(int4) * kMaxLongRows));
+    int *counter = h->scratch_i + 8;
+    RSG_CUDA_TRY(cudaMemsetAsync(counter, 0, sizeof(int), st));
+    long_rows_kernel<<<(p.m + 255) / 256, 256, 0, st>>>(p.m, p.base, cape, p.rowptr, list, kMaxLongRows, counter);
+    h->launches++;
+    int nlong = 0;
+    cudaError_t e = cudaMemcpyAsync(&nlong, counter, sizeof(int), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    std::vector<int4> rows;
+    if (e == cudaSuccess && nlong > 0 && nlong <= kMaxLongRows) {
+        rows.resize((size_t)nlong);
+        e = cudaMemcpy(rows.data(), list, sizeof(int4) * (size_t)nlong, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(list);
+    if (e != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
+    if (nlong > kMaxLongRows) return strict ? RSG_UNSUPPORTED : RSG_OK;
+    if (nlong == 0) return RSG_OK;
+    std::sort(rows.begin(), rows.end(), [](const int4 &a, const int4 &b) { return a.x < b.x; });
+    std::vector<int4> seg;
+    std::vector<int2> lrow((size_t)nlong);
+    for (int i = 0; i < nlong; ++i) {
+        const int k0 = rows[i].y, k1 = rows[i].z;
+        lrow[i].x = (int)seg.size();
+        int a = k0;
+        while (a < k1) { // cuts on multiples of 4 entries, so that the 128-bit loads of every segment are aligned
+            int b = (a + kSegEntries) & ~3;
+            if (b >= k1 - 64) b = k1; // no crumbs
+            seg.push_back(make_int4(rows[i].x, a, b, i));
+            a = b;
+        }
+        lrow[i].y = (int)seg.size() - lrow[i].x;
+        if (seg.size() > (size_t)kMaxSegments) return strict ? RSG_UNSUPPORTED : RSG_OK;
+    }
+    p.nseg = (int)seg.size();
+    p.nlong = nlong;
+    RSG_CUDA_TRY(cudaMalloc(&p.seg, sizeof(int4) * seg.size()));
+    RSG_CUDA_TRY(cudaMalloc(&p.lrow, sizeof(int2) * lrow.size()));
+    RSG_CUDA_TRY(cudaMalloc(&p.seg_part, sizeof(double) * seg.size()));
+    RSG_CUDA_TRY(cudaMalloc(&p.seg_cnt, sizeof(int) * lrow.size()));
+    RSG_CUDA_TRY(cudaMemcpy(p.seg, seg.data(), sizeof(int4) * seg.size(), cudaMemcpyHostToDevice));
+    RSG_CUDA_TRY(cudaMemcpy(p.lrow, lrow.data(), sizeof(int2) * lrow.size(), cudaMemcpyHostToDevice));
+    RSG_CUDA_TRY(cudaMemset(p.seg_cnt, 0, sizeof(int) * lrow.size()));
+    p.bytes += (sizeof(int4) + sizeof(double)) * seg.size() + (sizeof(int2) + sizeof(int)) * lrow.size();
+    return RSG_OK;
+}
+
+int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split)
 {
     cudaStream_t st = h->stream;
     const PipeVariant &v = p.algo == RSG_SPMV_TILE ? kTileVariants[p.variant] : kPipeVariants[p.variant];
@@ -384,7 +482,9 @@ int pipe_build_plan(rsg_context *h, SpmvPlan &p)
     RSG_CUDA_TRY(cudaMalloc(&p.rp0, sizeof(int) * (size_t)p.rp0_len));
     p.bytes += sizeof(int4) * ((size_t)p.nblk + 1) + sizeof(int) * (size_t)p.rp0_len;
     pipe_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, p.base, p.rowptr, tile, w, p.nblk, p.pdesc);
-    pipe_maxlen_kernel<<<(p.nblk * 32 + 255) / 256, 256, 0, st>>>(p.nblk, p.base, p.rowptr, p.pdesc);
+    // long rows first: the lanes-per-row choice of a tile must not see a row its CTA will skip
+    if (p.algo == RSG_SPMV_TILE && p.max_row > v.cape) RSG_TRY(tile_build_split(h, p, v.cape, strict_split));
+    pipe_maxlen_kernel<<<(p.nblk * 32 + 255) / 256, 256, 0, st>>>(p.nblk, p.base, p.nseg > 0 ? v.cape : 0, p.rowptr, p.pdesc);
     pipe_rowptr_copy_kernel<<<(p.rp0_len + 255) / 256, 256, 0, st>>>(m, p.rp0_len, p.base, p.rowptr, p.rp0);
     h->launches += 3;
     if (h->opts[RSG_OPT_SPMV_HALO_START] > 0) {
@@ -454,9 +554,10 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
     }
     HaloFuse fuse = h->fuse;
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
-    kern<<<p->nblk + fuse.ctas, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc,
-                                                            p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags,
-                                                            h->wait_flags ? h->wait_n : 0, h->wait_epoch, fuse);
+    LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg};
+    kern<<<p->nblk + fuse.ctas + ls.nseg, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc,
+                                                                      p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags,
+                                                                      h->wait_flags ? h->wait_n : 0, h->wait_epoch, fuse, ls);
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;
     h->launches++;
@@ -475,6 +576,8 @@ int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, c
     case 5: return tile_launch_one<TV, TX, 96, 3456, 384>(h, p, values, alpha, x, beta, y);
     case 6: return tile_launch_one<TV, TX, 192, 6528, 768>(h, p, values, alpha, x, beta, y);
     case 7: return tile_launch_one<TV, TX, 256, 8704, 1024>(h, p, values, alpha, x, beta, y);
+    case 8: return tile_launch_one<TV, TX, 256, 2304, 512>(h, p, values, alpha, x, beta, y);
+    case 9: return tile_launch_one<TV, TX, 128, 1152, 256>(h, p, values, alpha, x, beta, y);
     default: return tile_launch_one<TV, TX, 128, 2304, 512>(h, p, values, alpha, x, beta, y);
     }
 }

@@ -15,7 +15,7 @@ from .host import CSR
 OPT = dict(SPMV_ALGO=0, SPMV_REDUCE=1, SPMV_LONG_ROW=2, SPMV_VARIANT=3, SPMV_CACHE_HINT=4,
            TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7, SPMV_X_HINT=8,
            SPMV_ROWS_PER_THREAD=9, SPMV_CTAS_PER_SM=10, TRSV_BATCH=11, TRSV_GATE=12,
-           TRI_CTAS_PER_SM=13, TRSV_BLOCK=14, SPMV_HALO_START=15)
+           TRI_CTAS_PER_SM=13, TRSV_BLOCK=14, SPMV_HALO_START=15, HOST_CHUNKS=16, HOST_Y_DIRECT=17)
 ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4, stream=5, pipe=6, tile=7)
 INFO = dict(KERNEL_LAUNCHES=0, SPMV_ALGO_USED=1, SPMV_ROW_BLOCKS=2, SPMV_MAX_ROW=3, LEVELS_L=4, LEVELS_U=5,
             SM_COUNT=6, WORKSPACE_BYTES=7)
@@ -202,6 +202,19 @@ class Handle:
         _check(fn(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(lu), self._p(b),
                   self._p(z), self._p(y)), "sptrsv_lu")
         return z, y
+
+    def pcg(self, A: DeviceCSR, b, x=None, lu=None, max_iters=1000, rtol=1e-8):
+        """rsg_pcg_d: A (fp64 DeviceCSR) x = b, preconditioned by ILU(0) factors `lu` (fp64 or fp32 tensor, or None).
+        Returns (x, iterations, relative residual)."""
+        self._claim(A)
+        assert A.precision == "d" and b.dtype == torch.float64
+        x = torch.zeros_like(b) if x is None else x
+        it, rel = C.c_int(0), C.c_double(0.0)
+        prec = 0 if lu is None else (ord("d") if lu.dtype == torch.float64 else ord("s"))
+        _check(self.lib.rsg_pcg_d(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
+                                  self._p(lu), prec, self._p(b), self._p(x), int(max_iters), float(rtol), C.byref(it),
+                                  C.byref(rel)), "rsg_pcg_d")
+        return x, it.value, rel.value
 
     def levels(self, which, n):
         """(level_ptr, level_rows) of the last analysed matrix; which 0 = L, 1 = U."""

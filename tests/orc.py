@@ -136,3 +136,76 @@ def ref_load(path, base=0, transpose=0):
            "values": values}
     _ref.ref_free_csr(C.byref(c))
     return out
+
+
+# ---- the reference's arithmetic library on the GPU box: cuSPARSE (oracle/libcusparse_ref.so) ----
+CUSPARSE_LIB = os.path.join(ORACLE_DIR, "libcusparse_ref.so")
+_cus = None
+
+
+def cusparse():
+    """The reference harness's cuSPARSE call groups (oracle/cusparse_ref.cu); needs a GPU to call."""
+    global _cus
+    if _cus is None:
+        if not os.path.exists(CUSPARSE_LIB):
+            build()
+        _cus = C.CDLL(CUSPARSE_LIB)
+        _cus.cref_spmv.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + \
+            [C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        _cus.cref_ilu0.argtypes = [C.c_int] * 4 + [C.c_void_p] * 5
+        _cus.cref_spsv_lu.argtypes = [C.c_int] * 3 + [C.c_void_p] * 6 + [C.c_int, C.c_void_p]
+    return _cus
+
+
+def _cus_prec(t):
+    import torch
+    return {torch.float64: 0, torch.float32: 1}[t.dtype]
+
+
+def cusparse_spmv(A, x, y=None, alg=0, warm=0, reps=0, flush=None):
+    """cusparseSpMV on a DeviceCSR ('d' or 's', base 0) -> (y, [mean, median, min] us or None)."""
+    import torch
+    assert A.base == 0 and A.values.dtype == x.dtype
+    y = torch.empty(A.m, dtype=x.dtype, device=x.device) if y is None else y
+    us = (C.c_float * 3)()
+    st = cusparse().cref_spmv(_cus_prec(x), alg, A.m, A.n, A.stored, A.rowptr.data_ptr(), A.colidx.data_ptr(),
+                              A.values.data_ptr(), x.data_ptr(), y.data_ptr(), warm, reps,
+                              flush.data_ptr() if flush is not None else None,
+                              flush.numel() * flush.element_size() if flush is not None else 0, us)
+    assert st == 0, "cref_spmv status %d" % st
+    return y, (list(us) if reps else None)
+
+
+def cusparse_ilu0(A, values, level=0):
+    """csrilu02 in place on `values` -> (structural pivot, numeric pivot, analysis ms, numeric ms)."""
+    piv = (C.c_int * 2)()
+    ms = (C.c_float * 2)()
+    st = cusparse().cref_ilu0(_cus_prec(values), level, A.m, A.stored, A.rowptr.data_ptr(), A.colidx.data_ptr(),
+                              values.data_ptr(), piv, ms)
+    assert st == 0, "cref_ilu0 status %d" % st
+    return piv[0], piv[1], ms[0], ms[1]
+
+
+def cusparse_spsv_lu(A, lu, b, reps=1):
+    """cusparseSpSV L (unit lower) then U (non-unit upper) -> (z, y, analysis ms, solve ms)."""
+    import torch
+    z, y = torch.empty_like(b), torch.empty_like(b)
+    ms = (C.c_float * 2)()
+    st = cusparse().cref_spsv_lu(_cus_prec(lu), A.m, A.stored, A.rowptr.data_ptr(), A.colidx.data_ptr(), lu.data_ptr(),
+                                 b.data_ptr(), z.data_ptr(), y.data_ptr(), reps, ms)
+    assert st == 0, "cref_spsv_lu status %d" % st
+    return z, y, ms[0], ms[1]
+
+
+def pcg(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8):
+    """oracle PCG (oracle.c: orc_pcg_d) -> (x, iterations, relres); lu: None | fp64 | fp32 ILU(0) factor values"""
+    x = np.zeros(a.m) if x0 is None else np.array(x0, dtype=np.float64)
+    rel = C.c_double(0.0)
+    prec = 0 if lu is None else (ord("d") if lu.dtype == np.float64 else ord("s"))
+    fn = lib().orc_pcg_d
+    fn.restype = C.c_int
+    vals = np.ascontiguousarray(a.values, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    it = fn(C.c_int(a.m), C.c_int(a.base), _i(a.rowptr), _i(a.colidx), _v(vals), _v(lu) if lu is not None else None,
+            C.c_int(prec), _v(b), _v(x), C.c_int(max_iters), C.c_double(rtol), C.byref(rel))
+    return x, it, rel.value

@@ -1,0 +1,92 @@
+"""rsg_pcg_d (the Krylov loop around the hot path) against the oracle's PCG on the same inputs.
+
+Dot products are summed in a different order on the GPU, so the iterates agree to rounding only: the iteration
+count must match the oracle's within one, the solutions to 1e-6 relative (rtol is 1e-9), and the TRUE residual
+|b - A x| / |b| must meet 10 rtol.  The preconditioned runs must take fewer iterations than the plain one, and the
+fp32-factor run (mixed precision, the reference README's theme) about as many as the fp64-factor run."""
+import numpy as np
+import pytest
+import torch
+
+import orc
+from respasol_b200 import host
+from respasol_b200.gpu import DeviceCSR
+
+pytestmark = pytest.mark.gpu
+
+def sym_femlike(N, p=0.58, seed=3):
+    """gen_femlike is structurally symmetric with unsymmetric values: its symmetric part is SPD (diagonally dominant)"""
+    import scipy.sparse as sp
+    g = host.gen_femlike(N, p, seed)
+    G = sp.csr_matrix((g.values, g.colidx, g.rowptr), shape=(g.m, g.n))
+    M = ((G + G.T) * 0.5).tocsr()
+    M.sort_indices()
+    return host.CSR(g.m, g.n, M.nnz, M.indptr.astype(np.int32), M.indices.astype(np.int32), M.data.copy(), 0)
+
+
+MATS = {
+    "lap2d_80": lambda: host.gen_laplace2d(80),
+    "sym_femlike_22": lambda: sym_femlike(22),
+    "stencil27_24": lambda: host.gen_stencil27(24, seed=0),
+}
+
+
+@pytest.mark.parametrize("name", sorted(MATS))
+def test_pcg_matches_oracle(handle, name):
+    a = MATS[name]()
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n) - 0.5
+    b = orc.spmv(a, xs, "d")
+    bd = torch.from_numpy(b).cuda()
+    rtol = 1e-9
+    iters = {}
+    for pre in (None, "d", "s"):
+        lu = lu_ref = None
+        if pre:
+            F = DeviceCSR(a, pre)
+            st, _ = handle.ilu0_factor(F)
+            assert st == 0
+            lu = F.values
+            lu_ref = orc.ilu0(a, np.float64 if pre == "d" else np.float32)[2]
+        x, it, rel = handle.pcg(A, bd, lu=lu, max_iters=2000, rtol=rtol)
+        x_ref, it_ref, rel_ref = orc.pcg(a, b, lu_ref, max_iters=2000, rtol=rtol)
+        assert abs(it - it_ref) <= 1 and it < 2000, (pre, it, it_ref)
+        assert rel <= rtol
+        xh = x.cpu().numpy()
+        assert np.abs(xh - x_ref).max() <= 1e-6 * np.abs(x_ref).max()
+        true_res = np.linalg.norm(b - orc.spmv(a, xh, "d")) / np.linalg.norm(b)
+        assert true_res <= 10 * rtol
+        assert np.abs(xh - xs).max() <= 1e-5 * np.abs(xs).max()
+        iters[pre] = it
+    assert iters["d"] < iters[None] and iters["s"] <= iters["d"] + 2
+
+
+def test_pcg_initial_guess_and_limits(handle):
+    a = host.gen_laplace2d(40)
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n)
+    b = torch.from_numpy(orc.spmv(a, xs, "d")).cuda()
+    # exact initial guess: zero iterations
+    x, it, rel = handle.pcg(A, b, x=torch.from_numpy(xs).cuda(), rtol=1e-10)
+    assert it == 0 and rel <= 1e-10
+    # iteration cap is honoured and reported
+    x, it, rel = handle.pcg(A, b, max_iters=3, rtol=1e-14)
+    _, it_ref, rel_ref = orc.pcg(a, b.cpu().numpy(), None, max_iters=3, rtol=1e-14)
+    assert it == it_ref == 3 and abs(rel - rel_ref) <= 1e-9 * rel_ref
+
+
+def test_pcg_config3_full_size(handle):
+    """symmetric part of config 3 (FEM-like, 103 823 rows): fp32 ILU(0) inside fp64 CG reaches 1e-10 like the fp64 factors do."""
+    a = sym_femlike(47, 0.58, 3)
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n) - 0.5
+    b = torch.from_numpy(orc.spmv(a, xs, "d")).cuda()
+    its = {}
+    for pre in ("d", "s"):
+        F = DeviceCSR(a, pre)
+        handle.ilu0_factor(F)
+        x, it, rel = handle.pcg(A, b, lu=F.values, max_iters=500, rtol=1e-10)
+        assert rel <= 1e-10 and it < 500
+        assert float((x - torch.from_numpy(xs).cuda()).abs().max()) <= 1e-7
+        its[pre] = it
+    assert abs(its["d"] - its["s"]) <= 2

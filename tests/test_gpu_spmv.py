@@ -147,11 +147,13 @@ def test_stream_variants(handle, variant, reduce):
         handle.set_option("SPMV_REDUCE", 0)
 
 
-@pytest.mark.parametrize("variant", list(range(8)))
+@pytest.mark.parametrize("variant", list(range(10)))
 @pytest.mark.parametrize("reduce", [0, 1, 4, 32])
 @pytest.mark.parametrize("rpt", [0, 3])
 @pytest.mark.parametrize("algo", ["pipe", "tile"])
 def test_pipe_variants(handle, variant, reduce, rpt, algo):
+    if algo == "pipe" and variant >= 8:
+        pytest.skip("the pipe kernel has 8 shapes")
     """every compiled shape of the pipelined (persistent, stage ring) and tile (one tile per CTA) kernels:
     fitting tiles, multi-pass tiles (rows longer than the tile slack), CTA-per-row rows, a ragged last quad"""
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -159,7 +161,7 @@ def test_pipe_variants(handle, variant, reduce, rpt, algo):
     handle.set_option("SPMV_REDUCE", reduce)
     handle.set_option("SPMV_ROWS_PER_THREAD", rpt)
     try:
-        mats = [host.gen_femlike(14, 0.7, 9), host.gen_powerlaw(16000, 2.2, 48, 3, 700 + 1733 * variant, 4),
+        mats = [host.gen_femlike(14, 0.7, 9), host.gen_powerlaw(16000, 2.2, 48, 3, min(700 + 1733 * variant, 15000), 4),
                 host.gen_laplace2d(37)]
         for a in mats:
             x = orc.dlarnv(a.n) - 0.5
@@ -219,16 +221,16 @@ def test_cache_hints(handle, hint, persist):
 
 
 def test_long_rows_cta_per_row_and_merge(handle):
-    # rows far longer than a tile: the row-block kernel falls to CTA-per-row, AUTO picks merge-path
+    # rows far longer than a tile: the row-block kernel falls to CTA-per-row, AUTO picks the tile kernel with split rows
     a = host.gen_powerlaw(60000, 2.2, 32, 3, 50000, 7)
     x = orc.dlarnv(a.n) - 0.5
-    for algo in ("pipe", "stream", "rowblock", "merge", "auto"):
+    for algo in ("pipe", "stream", "rowblock", "merge", "tile", "auto"):
         handle.set_option("SPMV_ALGO", ALGO[algo])
         for p in ("d", "s", "m"):
             check(handle, a, x, p)
     handle.set_option("SPMV_ALGO", 0)
     check(handle, a, x, "d")
-    assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
+    assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
     assert handle.info("SPMV_MAX_ROW") == int(np.diff(a.rowptr).max())
 
 
@@ -283,6 +285,114 @@ def test_host_pointer_entry_points(handle):
         handle.matrix_free(mat)
 
 
+def long_rows_matrix(n, lens, rows_at, base=0, seed=11):
+    """diagonal + a few long rows of the given lengths (contiguous column runs starting at varying offsets)"""
+    rng = np.random.default_rng(seed)
+    cols = [[i] for i in range(n)]
+    for r, ln in zip(rows_at, lens):
+        start = int(rng.integers(0, n - ln + 1))
+        cols[r] = sorted(set(range(start, start + ln)) | {r})
+    rp = np.zeros(n + 1, dtype=np.int32)
+    rp[1:] = np.cumsum([len(c) for c in cols])
+    ci = np.fromiter((c for row in cols for c in row), dtype=np.int32, count=int(rp[-1]))
+    v = rng.uniform(-1, 1, int(rp[-1]))
+    return host.CSR(n, n, int(rp[-1]), rp + base, ci + base, v, base)
+
+
+@pytest.mark.parametrize("precision", ["d", "s", "m"])
+@pytest.mark.parametrize("algo", ["auto", "tile"])
+def test_long_rows_are_split_into_segments(handle, precision, algo):
+    """Rows longer than a CTA's stage (2304 / 4352 entries) are cut into 2048-entry segments, one CTA each, whose
+    partial sums the last arrival adds in order: lengths around every boundary, first/last row, neighbours."""
+    n = 30000
+    lens = [2304, 2305, 2309, 4352, 4353, 4357, 6143, 6144, 6145, 8193, 20000, 29999, 4097, 2049 + 2304]
+    rows_at = [0, 1, 2, 77, 78, 500, 501, 9000, 9001, 15000, 15001, 29998, 29999, 12345]
+    handle.set_option("SPMV_ALGO", ALGO[algo])
+    try:
+        for base in (0, 1):
+            a = long_rows_matrix(n, lens, rows_at, base)
+            x = orc.dlarnv(a.n) - 0.5
+            check(handle, a, x, precision)
+            assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+            y0 = orc.dlarnv(a.m) - 0.5
+            check(handle, a, x, precision, alpha=-1.5, beta=0.25, y0=y0)
+            check(handle, a, x, precision)  # counters were reset by the previous products
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+
+
+def test_long_row_split_is_deterministic(handle):
+    a = host.gen_powerlaw(60000, 2.2, 64, 3, 20000, 4)
+    A = DeviceCSR(a, "d")
+    x = torch.from_numpy(orc.dlarnv(a.n) - 0.5).cuda()
+    y0 = handle.spmv(A, x).clone()
+    assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+    for _ in range(5):
+        assert torch.equal(handle.spmv(A, x), y0)
+
+
+def test_too_many_long_rows_fall_back_to_merge_path(handle):
+    n, ln = 4300, 4400  # more than 4096 rows longer than any stage
+    rp = (np.arange(n + 1, dtype=np.int64) * ln).astype(np.int32)
+    ci = ((np.arange(n)[:, None] * 7 + np.arange(ln)[None, :]) % n).astype(np.int32)
+    ci.sort(axis=1)
+    rng = np.random.default_rng(3)
+    a = host.CSR(n, n, n * ln, rp, ci.ravel().copy(), rng.uniform(-1, 1, n * ln), 0)
+    x = orc.dlarnv(a.n) - 0.5
+    check(handle, a, x, "d")
+    assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
+    handle.set_option("SPMV_ALGO", ALGO["tile"])  # forced: long rows stay CTA-per-row inside the tiles
+    try:
+        check(handle, a, x, "d")
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+
+
+PIPE_MATS = {
+    "stencil27_64": lambda: host.gen_stencil27(64, seed=2),            # banded: x prefix grows chunk by chunk
+    "lap2d_600": lambda: host.gen_laplace2d(600),
+    "powerlaw_300k": lambda: host.gen_powerlaw(300000, 2.2, 64, 3, 50000, 4),  # first rows reference all of x
+    "stencil27_64_base1": lambda: (lambda a: host.CSR(a.m, a.n, a.nnz, a.rowptr + 1, a.colidx + 1, a.values, 1))(host.gen_stencil27(64, seed=2)),
+}
+
+
+@pytest.mark.parametrize("name", sorted(PIPE_MATS))
+@pytest.mark.parametrize("chunks", [0, 1, 3, 32])
+@pytest.mark.parametrize("direct", [0, 1])
+def test_pipelined_host_product(handle, name, chunks, direct):
+    """rsg_matrix_spmv_host with beta == 0 overlaps x H2D, the product and y D2H over row chunks (HOST_CHUNKS):
+    every chunking must reproduce the oracle, from pageable and from page-locked caller buffers."""
+    a = PIPE_MATS[name]()
+    x = orc.dlarnv(a.n) - 0.5
+    handle.set_option("HOST_CHUNKS", chunks)
+    handle.set_option("HOST_Y_DIRECT", direct)  # 1: kernels store y into the page-locked host buffer; 0: D2H copies
+    try:
+        for p in ("d", "s", "m"):
+            xt = np.float32 if p == "s" else np.float64
+            ref = orc.spmv(a, x, p).astype(np.float64)
+            tol = 1e-12 if p != "s" else 2e-5
+            mat = handle.matrix_upload(a, p)
+            y = np.full(a.m, np.nan, dtype=xt)
+            handle.matrix_spmv_host(mat, x.astype(xt), y)
+            assert np.abs(y - ref).max() <= tol * np.abs(ref).max()
+            xp = torch.from_numpy(x.astype(xt)).pin_memory()
+            yp = torch.full((a.m,), float("nan"), dtype=xp.dtype).pin_memory()
+            for _ in range(3):  # repeated calls re-use streams / events
+                yp.fill_(float("nan"))
+                handle.matrix_spmv_host(mat, xp.numpy(), yp.numpy())
+                assert np.abs(yp.numpy() - ref).max() <= tol * np.abs(ref).max()
+            # beta != 0 takes the one-piece path: y = 2 A x - 0.5 y0
+            y0 = orc.dlarnv(a.m).astype(xt)
+            yb = y0.copy()
+            handle.matrix_spmv_host(mat, x.astype(xt), yb, alpha=2.0, beta=-0.5)
+            refb = 2.0 * ref - 0.5 * y0.astype(np.float64)
+            assert np.abs(yb - refb).max() <= 4 * tol * max(np.abs(ref).max(), 1.0)
+            handle.matrix_free(mat)
+    finally:
+        handle.set_option("HOST_CHUNKS", 0)
+        handle.set_option("HOST_Y_DIRECT", 0)
+
+
 def test_row_partition_bit_exact(handle):
     for a in (host.gen_laplace2d(50), host.gen_powerlaw(30000, 2.2, 64, 2, 9000, 4), SMALL["b1_ss_base1"]()):
         A = DeviceCSR(a, "d")
@@ -321,10 +431,7 @@ def test_full_size_configs(handle, name):
         y = check(handle, a, x, p)
         if p == "d":
             yd = y
-    if name == "C4":
-        assert handle.info("SPMV_ALGO_USED") == ALGO["merge"]
-    else:
-        assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+    assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]  # C4: its 4 rows of 100 002 entries are split into segments
     # linearity: A(2x + 1) = 2 A x + A 1
     A = DeviceCSR(a, "d")
     xd = torch.from_numpy(x).cuda()

@@ -136,3 +136,26 @@ def test_residual_property_ilu0_exact_on_tridiagonal():
     b = orc.dlarnv(n)
     _, _, y = orc.sptrsv_lu(a, lu, b)
     np.testing.assert_allclose(orc.spmv(a, y), b, rtol=1e-13, atol=1e-14)
+
+
+def test_oracle_pcg_solves_spd_systems():
+    """orc_pcg_d (checker of rsg_pcg_d): converges to the scipy direct solution, ILU(0) cuts the iteration count,
+    fp32 factors inside the fp64 iteration cost at most a couple of extra iterations."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    from respasol_b200 import host
+    g = host.gen_femlike(12)  # structurally symmetric, values not: take the symmetric part (still diagonally dominant)
+    G = sp.csr_matrix((g.values, g.colidx, g.rowptr), shape=(g.m, g.n))
+    M = ((G + G.T) * 0.5).tocsr()
+    M.sort_indices()
+    a = host.CSR(g.m, g.n, M.nnz, M.indptr.astype(np.int32), M.indices.astype(np.int32), M.data.copy(), 0)
+    assert abs(M - M.T).max() < 1e-14
+    b = orc.dlarnv(a.m) - 0.5
+    x_direct = spl.spsolve(M.tocsc(), b)
+    its = {}
+    for pre in (None, np.float64, np.float32):
+        lu = None if pre is None else orc.ilu0(a, pre)[2]
+        x, it, rel = orc.pcg(a, b, lu, rtol=1e-11)
+        assert rel <= 1e-11 and np.abs(x - x_direct).max() <= 1e-8 * np.abs(x_direct).max()
+        its[pre] = it
+    assert its[np.float64] < its[None] and its[np.float32] <= its[np.float64] + 2

@@ -54,7 +54,7 @@ def main():
     for v in range(8):
         for lanes in (0,):  # pipe: the "xhint" slot carries the forced lanes per row
             combos.append(("pipe", v, lanes, 1))
-    for v in range(8):
+    for v in range(10):
         for ts in (0,):  # tile: the "xhint" slot carries the tile size (0 = heuristic)
             combos.append(("tile", v, ts, 1))
     for v in range(6):
