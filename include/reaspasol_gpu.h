@@ -48,7 +48,8 @@ typedef enum {
     RSG_ZERO_PIVOT_STRUCTURAL = 5, /* A(j,j) missing  -- ilu0.cu:221-226 */
     RSG_ZERO_PIVOT_NUMERIC = 6,    /* U(j,j) == 0     -- ilu0.cu:278-282 */
     RSG_DEPENDENCY_TIMEOUT = 7,    /* watchdog in a dependency-flag wait fired (malformed input) */
-    RSG_UNSUPPORTED = 8
+    RSG_UNSUPPORTED = 8,
+    RSG_BREAKDOWN = 9              /* Krylov recurrence broke down (a scalar became 0, inf or NaN) */
 } rsg_status;
 
 /* ---- handle ---------------------------------------------------------------------------- */
@@ -72,7 +73,7 @@ typedef enum {
     RSG_OPT_SPMV_X_HINT = 8,    /* stream/pipe kernels: 1 = gather x with an L2 evict_last hint */
     RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* pipe kernel: tile size in rows per thread (0 = 1) */
     RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* pipe kernel: cap on resident CTAs per SM (0 = occupancy limit) */
-    RSG_OPT_TRSV_BATCH = 11,    /* sync-free solves: solution entries polled per round trip (1,2,4,8; 0 = default) */
+    RSG_OPT_TRSV_BATCH = 11,    /* sync-free solves: solution entries polled per round trip (1,2,4,8,16; 0 = default) */
     RSG_OPT_TRSV_GATE = 12,     /* sync-free solves: 1 = a row first polls only its deepest dependency, 2 = off, 0 = default */
     RSG_OPT_TRI_CTAS_PER_SM = 13, /* sync-free ILU0 / solves: cap on resident CTAs per SM (0 = default) */
     RSG_OPT_TRSV_BLOCK = 14,    /* sync-free solves: threads per CTA (multiple of 32, <= 256; 0 = default) */
@@ -195,6 +196,12 @@ int rsg_spmv_halo_fuse(rsg_handle_t handle, int nsend, const int *send_idx, int 
 int rsg_pcg_d(rsg_handle_t handle, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
               const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
               int *iters, double *relres);
+/* BiCGStab (van der Vorst 1992), right-preconditioned by the same ILU(0) factors, for matrices that are not
+ * symmetric positive definite (config 3's FEM-like matrix has unsymmetric values).  Same arguments and stopping
+ * rule; one iteration = 2 SpMV + 2 preconditioner applications + 5 fused vector kernels. */
+int rsg_bicgstab_d(rsg_handle_t handle, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                   const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                   int *iters, double *relres);
 
 /* ---- host-pointer convenience wrappers (allocate, H2D, run, D2H, free; synchronous) ------- */
 int spmv_csr_d_host(rsg_handle_t handle, int m, int n, int nnz, int base,

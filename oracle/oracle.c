@@ -378,3 +378,66 @@ int orc_pcg_d(int n, int base, const int *rowptr, const int *colidx, const doubl
     free(r); free(z); free(p); free(q); free(r32); free(z32); free(t32);
     return it;
 }
+
+/* ------------------------------------------------------------- BiCGStab ---
+ * van der Vorst's BiCGStab with right preconditioning K = LU (Saad, Alg. 9.7 / Barrett et al.,
+ * Templates, fig. 2.10), shadow residual = initial residual; checker of rsg_bicgstab_d.
+ * Convergence is tested on |r| once per iteration (no half-step test), like the GPU loop. */
+static void orc_apply_prec(int n, int base, const int *rowptr, const int *colidx, const void *lu, int lu_precision,
+                           const double *in, double *out, double *tmp, float *in32, float *out32, float *tmp32)
+{
+    if (lu_precision == 0) {
+        for (int i = 0; i < n; ++i) out[i] = in[i];
+    } else if (lu_precision == 's') {
+        for (int i = 0; i < n; ++i) in32[i] = (float)in[i];
+        orc_sptrsv_lu_s(n, base, rowptr, colidx, (const float *)lu, in32, tmp32, out32);
+        for (int i = 0; i < n; ++i) out[i] = (double)out32[i];
+    } else {
+        orc_sptrsv_lu_d(n, base, rowptr, colidx, (const double *)lu, in, tmp, out);
+    }
+}
+
+int orc_bicgstab_d(int n, int base, const int *rowptr, const int *colidx, const double *values,
+                   const void *lu, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                   double *relres)
+{
+    const size_t nb = sizeof(double) * (size_t)(n + 1);
+    double *r = malloc(nb), *rh = malloc(nb), *p = malloc(nb), *v = malloc(nb), *y = malloc(nb), *z = malloc(nb), *t = malloc(nb);
+    float *a32 = malloc(nb / 2), *b32 = malloc(nb / 2), *c32 = malloc(nb / 2);
+    orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, x, 0.0, v);
+    for (int i = 0; i < n; ++i) { r[i] = b[i] - v[i]; rh[i] = r[i]; }
+    double bb = orc_dot(n, b, b), rr = orc_dot(n, r, r);
+    if (!(bb > 0)) bb = 1.0;
+    const double stop = rtol * rtol * bb;
+    double rho = rr, rho_old = 1, alpha = 1, omega = 1;
+    int it = 0;
+    while (it < max_iters && rr > stop && isfinite(rr)) {
+        if (it == 0) {
+            for (int i = 0; i < n; ++i) p[i] = r[i];
+        } else {
+            const double beta = (rho / rho_old) * (alpha / omega);
+            for (int i = 0; i < n; ++i) p[i] = fma(beta, fma(-omega, v[i], p[i]), r[i]);
+        }
+        orc_apply_prec(n, base, rowptr, colidx, lu, lu_precision, p, y, t, a32, b32, c32);
+        orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, y, 0.0, v);
+        alpha = rho / orc_dot(n, rh, v);
+        for (int i = 0; i < n; ++i) r[i] = fma(-alpha, v[i], r[i]); /* s */
+        orc_apply_prec(n, base, rowptr, colidx, lu, lu_precision, r, z, t, a32, b32, c32);
+        orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, z, 0.0, t);
+        omega = orc_dot(n, t, r) / orc_dot(n, t, t);
+        rr = 0;
+        double rho_next = 0;
+        for (int i = 0; i < n; ++i) {
+            x[i] = fma(omega, z[i], fma(alpha, y[i], x[i]));
+            r[i] = fma(-omega, t[i], r[i]);
+            rr = fma(r[i], r[i], rr);
+            rho_next = fma(rh[i], r[i], rho_next);
+        }
+        rho_old = rho;
+        rho = rho_next;
+        ++it;
+    }
+    if (relres) *relres = sqrt(rr / bb);
+    free(r); free(rh); free(p); free(v); free(y); free(z); free(t); free(a32); free(b32); free(c32);
+    return it;
+}

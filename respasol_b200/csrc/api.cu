@@ -55,6 +55,7 @@ const char *rsg_status_string(int status)
     case RSG_ZERO_PIVOT_NUMERIC: return "numerical zero pivot";
     case RSG_DEPENDENCY_TIMEOUT: return "dependency wait timed out";
     case RSG_UNSUPPORTED: return "unsupported";
+    case RSG_BREAKDOWN: return "Krylov recurrence broke down";
     default: return "unknown status";
     }
 }

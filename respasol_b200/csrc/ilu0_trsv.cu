@@ -20,10 +20,11 @@
 namespace rsg {
 
 #define RSG_SPIN_LIMIT (1 << 22) // sweeps before a waiting row gives up (malformed schedule)
-// measured on config 3 (tools/tri_sweep.py, profiles/r1_tri_sweep.log): 8 entries per poll, no gate,
-// and only ~32 levels' worth of rows in flight -- every extra waiting row is polling traffic in L2
-// that slows the rows on the dependency chain down (2.8 ms with every row resident, 1.4 ms so).
-#define RSG_TRSV_DEFAULT_BATCH 8
+// measured on config 3 (tools/tri_sweep.py, profiles/r1_tri_sweep*.log): 16 entries per poll (a triangle of the
+// FEM-like matrix has up to 13 entries per row: one L2 round trip covers the whole row; 8 per poll needed two and
+// cost 1.39 ms against 1.05 ms), no gate, and only ~32 levels' worth of rows in flight -- every extra waiting row
+// is polling traffic in L2 that slows the rows on the dependency chain down (2.8 ms with every row resident).
+#define RSG_TRSV_DEFAULT_BATCH 16
 #define RSG_TRSV_DEFAULT_GATE 0
 
 // ------------------------------------------------------------------ flags / sentinels
@@ -503,15 +504,15 @@ int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
     fill_pending_kernel<T><<<(n + 255) / 256, 256, 0, st>>>(n, z, y);
     int per_sm = 0;
     int batch = h->opts[RSG_OPT_TRSV_BATCH];
-    if (batch != 1 && batch != 2 && batch != 4 && batch != 8) batch = RSG_TRSV_DEFAULT_BATCH;
+    if (batch != 1 && batch != 2 && batch != 4 && batch != 8 && batch != 16) batch = RSG_TRSV_DEFAULT_BATCH;
     const bool gate = h->opts[RSG_OPT_TRSV_GATE] ? h->opts[RSG_OPT_TRSV_GATE] == 1 : (RSG_TRSV_DEFAULT_GATE != 0);
     int block = h->opts[RSG_OPT_TRSV_BLOCK];
     if (block < 32 || block > 256 || (block & 31)) block = 64;
     typedef void (*kern_t)(int, int, const int *, const int *, const T *, const int *, const int *, const int *, const T *, T *, int *);
     kern_t kl = nullptr, ku = nullptr;
 #define RSG_PICK(BB, GG) { kl = trsv_kernel<T, false, BB, GG>; ku = trsv_kernel<T, true, BB, GG>; }
-    if (gate) { if (batch == 1) RSG_PICK(1, true) else if (batch == 2) RSG_PICK(2, true) else if (batch == 4) RSG_PICK(4, true) else RSG_PICK(8, true) }
-    else { if (batch == 1) RSG_PICK(1, false) else if (batch == 2) RSG_PICK(2, false) else if (batch == 4) RSG_PICK(4, false) else RSG_PICK(8, false) }
+    if (gate) { if (batch == 1) RSG_PICK(1, true) else if (batch == 2) RSG_PICK(2, true) else if (batch == 4) RSG_PICK(4, true) else if (batch == 16) RSG_PICK(16, true) else RSG_PICK(8, true) }
+    else { if (batch == 1) RSG_PICK(1, false) else if (batch == 2) RSG_PICK(2, false) else if (batch == 4) RSG_PICK(4, false) else if (batch == 16) RSG_PICK(16, false) else RSG_PICK(8, false) }
 #undef RSG_PICK
     RSG_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, ku, block, 0));
     per_sm = std::max(per_sm, 1);

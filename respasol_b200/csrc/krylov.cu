@@ -1,4 +1,5 @@
-// krylov.cu -- preconditioned conjugate gradients on the three hot-path calls: the loop the
+// krylov.cu -- preconditioned conjugate gradients (SPD) and BiCGStab (general) on the three hot-path calls
+// (SURVEY.md 8f-2): the loop the
 // reference benchmarks its kernels for (mixed-precision sparse solvers, /root/reference/README.md:5-7) but does
 // not contain.  q = A p is spmv_csr_d; z = M^-1 r is sptrsv_lu_d on fp64 ILU(0) factors, or sptrsv_lu_s on fp32
 // factors with r rounded to fp32 and z widened back (fp32 preconditioner inside an fp64 iteration); the vector
@@ -116,11 +117,100 @@ __global__ void __launch_bounds__(kVecThreads) cast_kernel(int n, const double *
     for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) b[i] = (float)a[i];
 }
 
+// ---- BiCGStab (van der Vorst 1992, right-preconditioned).  scalars: [0],[1] rho ping-pong, [2] rh.v, [3] rr, [4] bb,
+// [5] t.s, [6] t.t.  alpha = rho/rh.v and omega = t.s/t.t are recomputed from them by every kernel that needs them.
+enum { B_RHV = 2, B_RR = 3, B_BB = 4, B_TS = 5, B_TT = 6 };
+
+// p = r + beta (p - omega v), beta = (rho_new/rho_old)(alpha/omega); first pass: p = r.  (p32 = (float) p)
+__global__ void __launch_bounds__(kVecThreads) bicg_p_kernel(int n, const double *scal, int rho_slot, int first, const double *__restrict__ r,
+                                                             const double *__restrict__ v, double *__restrict__ p, float *__restrict__ p32)
+{
+    double beta = 0, omega = 0;
+    if (!first) {
+        const double rho_new = scal[rho_slot], rho_old = scal[rho_slot ^ 1];
+        const double alpha = rho_old / scal[B_RHV];
+        omega = scal[B_TS] / scal[B_TT];
+        beta = (rho_new / rho_old) * (alpha / omega);
+    }
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        const double pi = first ? r[i] : fma(beta, fma(-omega, v[i], p[i]), r[i]);
+        p[i] = pi;
+        if (p32) p32[i] = (float)pi;
+    }
+}
+
+// s = r - alpha v (in place on r), alpha = rho/rh.v;  (s32 = (float) s)
+__global__ void __launch_bounds__(kVecThreads) bicg_s_kernel(int n, const double *scal, int rho_slot, const double *__restrict__ v,
+                                                             double *__restrict__ r, float *__restrict__ s32)
+{
+    const double alpha = scal[rho_slot] / scal[B_RHV];
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        const double si = fma(-alpha, v[i], r[i]);
+        r[i] = si;
+        if (s32) s32[i] = (float)si;
+    }
+}
+
+// out0 = a.b, out1 = a.a
+__global__ void __launch_bounds__(kVecThreads) dot2_kernel(int n, const double *__restrict__ a, const double *__restrict__ b,
+                                                           double *partials, unsigned *ticket, double *out0, double *out1)
+{
+    double s0 = 0, s1 = 0;
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        const double ai = a[i];
+        s0 = fma(ai, b[i], s0);
+        s1 = fma(ai, ai, s1);
+    }
+    finish_dot(s0, partials, ticket, out0);
+    __syncthreads();
+    finish_dot(s1, partials + kMaxVecBlocks, ticket + 1, out1);
+}
+
+// x += alpha y + omega z;  r = s - omega t (s lives in r);  rr = r.r;  rho_next = rh.r
+__global__ void __launch_bounds__(kVecThreads) bicg_xr_kernel(int n, const double *scal, int rho_slot, const double *__restrict__ y,
+                                                              const double *__restrict__ z, const double *__restrict__ t,
+                                                              const double *__restrict__ rh, double *__restrict__ x, double *__restrict__ r,
+                                                              double *partials, unsigned *ticket, double *out_rr, double *out_rho)
+{
+    const double alpha = scal[rho_slot] / scal[B_RHV], omega = scal[B_TS] / scal[B_TT];
+    double s0 = 0, s1 = 0;
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        x[i] = fma(omega, z[i], fma(alpha, y[i], x[i]));
+        const double ri = fma(-omega, t[i], r[i]);
+        r[i] = ri;
+        s0 = fma(ri, ri, s0);
+        s1 = fma(rh[i], ri, s1);
+    }
+    finish_dot(s0, partials, ticket, out_rr);
+    __syncthreads();
+    finish_dot(s1, partials + kMaxVecBlocks, ticket + 1, out_rho);
+}
+
+__global__ void __launch_bounds__(kVecThreads) widen_kernel(int n, const float *__restrict__ a, double *__restrict__ b)
+{
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) b[i] = (double)a[i];
+}
+
 } // namespace rsg
 
 using namespace rsg;
 
 namespace {
+constexpr size_t kWsTail = 2 * kMaxVecBlocks * 8 + S_COUNT * 8 + 64; // partial sums (two dots), scalars, tickets
+
+int krylov_workspace(rsg_context *h, size_t bytes)
+{
+    if (h->krylov_bytes < bytes) {
+        if (h->krylov_ws) cudaFree(h->krylov_ws);
+        h->krylov_ws = nullptr;
+        h->krylov_bytes = 0;
+        if (cudaMalloc(&h->krylov_ws, bytes) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+        h->krylov_bytes = bytes;
+    }
+    if (!h->krylov_pin && cudaMallocHost(&h->krylov_pin, S_COUNT * sizeof(double)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+    return RSG_OK;
+}
+
 struct Guard {
     int prev = 0;
     explicit Guard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
@@ -143,15 +233,7 @@ extern "C" int rsg_pcg_d(rsg_handle_t h, int n, int nnz, int base, const int *ro
     const bool pre = lu_precision != 0, pre32 = lu_precision == 's';
     // workspace: r, z, p, q (fp64), r32, z32, t32 (fp32), partials, scalars, ticket
     const size_t nd = ((size_t)n + 3) & ~(size_t)3;
-    const size_t bytes = nd * 8 * 4 + nd * 4 * 3 + kMaxVecBlocks * 8 + S_COUNT * 8 + 64;
-    if (h->krylov_bytes < bytes) {
-        if (h->krylov_ws) cudaFree(h->krylov_ws);
-        h->krylov_ws = nullptr;
-        h->krylov_bytes = 0;
-        if (cudaMalloc(&h->krylov_ws, bytes) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
-        h->krylov_bytes = bytes;
-    }
-    if (!h->krylov_pin && cudaMallocHost(&h->krylov_pin, S_COUNT * sizeof(double)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+    RSG_TRY(krylov_workspace(h, nd * 8 * 4 + nd * 4 * 3 + kWsTail));
     char *w = static_cast<char *>(h->krylov_ws);
     double *r = reinterpret_cast<double *>(w); w += nd * 8;
     double *z = reinterpret_cast<double *>(w); w += nd * 8;
@@ -160,7 +242,7 @@ extern "C" int rsg_pcg_d(rsg_handle_t h, int n, int nnz, int base, const int *ro
     float *r32 = reinterpret_cast<float *>(w); w += nd * 4;
     float *z32 = reinterpret_cast<float *>(w); w += nd * 4;
     float *t32 = reinterpret_cast<float *>(w); w += nd * 4;
-    double *partials = reinterpret_cast<double *>(w); w += kMaxVecBlocks * 8;
+    double *partials = reinterpret_cast<double *>(w); w += 2 * kMaxVecBlocks * 8;
     double *scal = reinterpret_cast<double *>(w); w += S_COUNT * 8;
     unsigned *ticket = reinterpret_cast<unsigned *>(w);
     RSG_CUDA_TRY(cudaMemsetAsync(scal, 0, S_COUNT * 8 + 64, st));
@@ -213,5 +295,86 @@ extern "C" int rsg_pcg_d(rsg_handle_t h, int n, int nnz, int base, const int *ro
     RSG_CUDA_TRY(cudaGetLastError());
     if (iters) *iters = it;
     if (relres) *relres = std::sqrt(rr / bb);
-    return std::isfinite(rr) ? RSG_OK : RSG_ZERO_PIVOT_NUMERIC;
+    return std::isfinite(rr) ? RSG_OK : RSG_BREAKDOWN;
+}
+
+extern "C" int rsg_bicgstab_d(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                              const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                              int *iters, double *relres)
+{
+    if (!h || n < 0 || !rowptr || (n > 0 && (!b || !x || !values)) || max_iters < 0 ||
+        (lu_precision != 0 && lu_precision != 'd' && lu_precision != 's') || (lu_precision != 0 && !lu_values))
+        return RSG_BAD_ARG;
+    if (iters) *iters = 0;
+    if (relres) *relres = 0.0;
+    if (n == 0) return RSG_OK;
+    Guard g(h->device);
+    cudaStream_t st = h->stream;
+    const bool pre = lu_precision != 0, pre32 = lu_precision == 's';
+    const size_t nd = ((size_t)n + 3) & ~(size_t)3;
+    RSG_TRY(krylov_workspace(h, nd * 8 * 7 + nd * 4 * 3 + kWsTail));
+    char *w = static_cast<char *>(h->krylov_ws);
+    double *r = reinterpret_cast<double *>(w); w += nd * 8;  // r, then s in place
+    double *rh = reinterpret_cast<double *>(w); w += nd * 8; // shadow residual
+    double *p = reinterpret_cast<double *>(w); w += nd * 8;
+    double *v = reinterpret_cast<double *>(w); w += nd * 8;
+    double *y = reinterpret_cast<double *>(w); w += nd * 8;  // K^-1 p
+    double *z = reinterpret_cast<double *>(w); w += nd * 8;  // K^-1 s
+    double *t = reinterpret_cast<double *>(w); w += nd * 8;  // A z; scratch of the fp64 triangular solves before that
+    float *in32 = reinterpret_cast<float *>(w); w += nd * 4;
+    float *out32 = reinterpret_cast<float *>(w); w += nd * 4;
+    float *tmp32 = reinterpret_cast<float *>(w); w += nd * 4;
+    double *partials = reinterpret_cast<double *>(w); w += 2 * kMaxVecBlocks * 8;
+    double *scal = reinterpret_cast<double *>(w); w += S_COUNT * 8;
+    unsigned *ticket = reinterpret_cast<unsigned *>(w);
+    RSG_CUDA_TRY(cudaMemsetAsync(scal, 0, S_COUNT * 8 + 64, st));
+    const int grid = std::max(1, std::min(kMaxVecBlocks, std::min(h->sm_count * 8, (n + kVecThreads * 4 - 1) / (kVecThreads * 4))));
+    double *pin = h->krylov_pin;
+
+    // out = K^-1 in (in32 already holds (float) in when the factors are fp32)
+    auto precondition = [&](const double *in, double *out) -> int {
+        if (!pre) { RSG_CUDA_TRY(cudaMemcpyAsync(out, in, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st)); return RSG_OK; }
+        if (pre32) {
+            RSG_TRY(sptrsv_lu_s(h, n, nnz, base, rowptr, colidx, static_cast<const float *>(lu_values), in32, tmp32, out32));
+            widen_kernel<<<grid, kVecThreads, 0, st>>>(n, out32, out);
+            h->launches++;
+            return RSG_OK;
+        }
+        return sptrsv_lu_d(h, n, nnz, base, rowptr, colidx, static_cast<const double *>(lu_values), in, t, out);
+    };
+
+    RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, x, 0.0, v));
+    residual_kernel<<<grid, kVecThreads, 0, st>>>(n, b, v, r);
+    RSG_CUDA_TRY(cudaMemcpyAsync(rh, r, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+    dot_kernel<<<grid, kVecThreads, 0, st>>>(n, b, b, partials, ticket, scal + B_BB);
+    int slot = 0;
+    dot2_kernel<<<grid, kVecThreads, 0, st>>>(n, r, r, partials, ticket, scal + slot, scal + B_RR); // rho = rh.r = r.r
+    h->launches += 3;
+    RSG_CUDA_TRY(cudaMemcpyAsync(pin, scal, S_COUNT * sizeof(double), cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaStreamSynchronize(st));
+    const double bb = pin[B_BB] > 0 ? pin[B_BB] : 1.0;
+    double rr = pin[B_RR];
+    const double stop = rtol * rtol * bb;
+    int it = 0;
+    while (it < max_iters && rr > stop && std::isfinite(rr)) {
+        bicg_p_kernel<<<grid, kVecThreads, 0, st>>>(n, scal, slot, it == 0, r, v, p, pre32 ? in32 : nullptr);
+        RSG_TRY(precondition(p, y));
+        RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, y, 0.0, v));
+        dot_kernel<<<grid, kVecThreads, 0, st>>>(n, rh, v, partials, ticket, scal + B_RHV);
+        bicg_s_kernel<<<grid, kVecThreads, 0, st>>>(n, scal, slot, v, r, pre32 ? in32 : nullptr);
+        RSG_TRY(precondition(r, z));
+        RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, z, 0.0, t));
+        dot2_kernel<<<grid, kVecThreads, 0, st>>>(n, t, r, partials, ticket, scal + B_TS, scal + B_TT);
+        bicg_xr_kernel<<<grid, kVecThreads, 0, st>>>(n, scal, slot, y, z, t, rh, x, r, partials, ticket, scal + B_RR, scal + (slot ^ 1));
+        h->launches += 5;
+        slot ^= 1;
+        RSG_CUDA_TRY(cudaMemcpyAsync(pin + B_RR, scal + B_RR, sizeof(double), cudaMemcpyDeviceToHost, st));
+        RSG_CUDA_TRY(cudaStreamSynchronize(st));
+        rr = pin[B_RR];
+        ++it;
+    }
+    RSG_CUDA_TRY(cudaGetLastError());
+    if (iters) *iters = it;
+    if (relres) *relres = std::sqrt(rr / bb);
+    return std::isfinite(rr) ? RSG_OK : RSG_BREAKDOWN;
 }

@@ -203,7 +203,11 @@ class Handle:
                   self._p(z), self._p(y)), "sptrsv_lu")
         return z, y
 
-    def pcg(self, A: DeviceCSR, b, x=None, lu=None, max_iters=1000, rtol=1e-8):
+    def bicgstab(self, A: DeviceCSR, b, x=None, lu=None, max_iters=1000, rtol=1e-8):
+        """rsg_bicgstab_d: like pcg, for matrices that are not symmetric positive definite."""
+        return self.pcg(A, b, x, lu, max_iters, rtol, _fn="rsg_bicgstab_d")
+
+    def pcg(self, A: DeviceCSR, b, x=None, lu=None, max_iters=1000, rtol=1e-8, _fn="rsg_pcg_d"):
         """rsg_pcg_d: A (fp64 DeviceCSR) x = b, preconditioned by ILU(0) factors `lu` (fp64 or fp32 tensor, or None).
         Returns (x, iterations, relative residual)."""
         self._claim(A)
@@ -211,9 +215,9 @@ class Handle:
         x = torch.zeros_like(b) if x is None else x
         it, rel = C.c_int(0), C.c_double(0.0)
         prec = 0 if lu is None else (ord("d") if lu.dtype == torch.float64 else ord("s"))
-        _check(self.lib.rsg_pcg_d(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
-                                  self._p(lu), prec, self._p(b), self._p(x), int(max_iters), float(rtol), C.byref(it),
-                                  C.byref(rel)), "rsg_pcg_d")
+        _check(getattr(self.lib, _fn)(self.h, A.m, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
+                                      self._p(lu), prec, self._p(b), self._p(x), int(max_iters), float(rtol), C.byref(it),
+                                      C.byref(rel)), _fn)
         return x, it.value, rel.value
 
     def levels(self, which, n):

@@ -197,12 +197,17 @@ def cusparse_spsv_lu(A, lu, b, reps=1):
     return z, y, ms[0], ms[1]
 
 
-def pcg(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8):
+def bicgstab(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8):
+    """oracle BiCGStab (oracle.c: orc_bicgstab_d), same conventions as pcg"""
+    return pcg(a, b, lu, x0, max_iters, rtol, _fn="orc_bicgstab_d")
+
+
+def pcg(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8, _fn="orc_pcg_d"):
     """oracle PCG (oracle.c: orc_pcg_d) -> (x, iterations, relres); lu: None | fp64 | fp32 ILU(0) factor values"""
     x = np.zeros(a.m) if x0 is None else np.array(x0, dtype=np.float64)
     rel = C.c_double(0.0)
     prec = 0 if lu is None else (ord("d") if lu.dtype == np.float64 else ord("s"))
-    fn = lib().orc_pcg_d
+    fn = getattr(lib(), _fn)
     fn.restype = C.c_int
     vals = np.ascontiguousarray(a.values, dtype=np.float64)
     b = np.ascontiguousarray(b, dtype=np.float64)

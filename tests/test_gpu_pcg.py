@@ -90,3 +90,58 @@ def test_pcg_config3_full_size(handle):
         assert float((x - torch.from_numpy(xs).cuda()).abs().max()) <= 1e-7
         its[pre] = it
     assert abs(its["d"] - its["s"]) <= 2
+
+
+NONSYM = {
+    "femlike_22": lambda: host.gen_femlike(22),                 # symmetric pattern, unsymmetric values
+    "stencil27_24_perturbed": lambda: host.gen_stencil27(24, seed=2),
+    "lap2d_80": lambda: host.gen_laplace2d(80),                 # SPD works too
+}
+
+
+@pytest.mark.parametrize("name", sorted(NONSYM))
+def test_bicgstab_matches_oracle(handle, name):
+    """BiCGStab is less regular than CG: iteration counts of two correctly rounded runs may differ by a few; both
+    must converge, agree on x to 1e-6 and meet the true-residual bound."""
+    a = NONSYM[name]()
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n) - 0.5
+    b = orc.spmv(a, xs, "d")
+    bd = torch.from_numpy(b).cuda()
+    rtol = 1e-9
+    iters = {}
+    for pre in (None, "d", "s"):
+        lu = lu_ref = None
+        if pre:
+            F = DeviceCSR(a, pre)
+            st, _ = handle.ilu0_factor(F)
+            assert st == 0
+            lu = F.values
+            lu_ref = orc.ilu0(a, np.float64 if pre == "d" else np.float32)[2]
+        x, it, rel = handle.bicgstab(A, bd, lu=lu, max_iters=2000, rtol=rtol)
+        x_ref, it_ref, rel_ref = orc.bicgstab(a, b, lu_ref, max_iters=2000, rtol=rtol)
+        assert it < 2000 and it_ref < 2000 and abs(it - it_ref) <= max(3, it_ref // 10), (pre, it, it_ref)
+        assert rel <= rtol
+        xh = x.cpu().numpy()
+        assert np.abs(xh - x_ref).max() <= 1e-6 * np.abs(x_ref).max()
+        assert np.linalg.norm(b - orc.spmv(a, xh, "d")) / np.linalg.norm(b) <= 10 * rtol
+        iters[pre] = it
+    assert iters["d"] < iters[None] and iters["s"] <= iters["d"] + 3
+
+
+def test_bicgstab_config3_full_size(handle):
+    """config 3 as generated (FEM-like, 103 823 rows, unsymmetric values): ILU(0)-preconditioned BiCGStab, fp64 and
+    fp32 factors, reaches 1e-10."""
+    a = host.gen_femlike(47, 0.58, 3)
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n) - 0.5
+    b = torch.from_numpy(orc.spmv(a, xs, "d")).cuda()
+    its = {}
+    for pre in ("d", "s"):
+        F = DeviceCSR(a, pre)
+        handle.ilu0_factor(F)
+        x, it, rel = handle.bicgstab(A, b, lu=F.values, max_iters=500, rtol=1e-10)
+        assert rel <= 1e-10 and it < 500
+        assert float((x - torch.from_numpy(xs).cuda()).abs().max()) <= 1e-7
+        its[pre] = it
+    assert abs(its["d"] - its["s"]) <= 3

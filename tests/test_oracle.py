@@ -159,3 +159,21 @@ def test_oracle_pcg_solves_spd_systems():
         assert rel <= 1e-11 and np.abs(x - x_direct).max() <= 1e-8 * np.abs(x_direct).max()
         its[pre] = it
     assert its[np.float64] < its[None] and its[np.float32] <= its[np.float64] + 2
+
+
+def test_oracle_bicgstab_solves_unsymmetric_systems():
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    from respasol_b200 import host
+    a = host.gen_femlike(12)
+    M = sp.csr_matrix((a.values, a.colidx, a.rowptr), shape=(a.m, a.n))
+    assert abs(M - M.T).max() > 0.1  # unsymmetric values: CG does not apply
+    b = orc.dlarnv(a.m) - 0.5
+    x_direct = spl.spsolve(M.tocsc(), b)
+    its = {}
+    for pre in (None, np.float64, np.float32):
+        lu = None if pre is None else orc.ilu0(a, pre)[2]
+        x, it, rel = orc.bicgstab(a, b, lu, rtol=1e-11)
+        assert rel <= 1e-11 and np.abs(x - x_direct).max() <= 1e-8 * np.abs(x_direct).max()
+        its[pre] = it
+    assert its[np.float64] < its[None] and its[np.float32] <= its[np.float64] + 3

@@ -65,7 +65,7 @@ def main():
     z, y = torch.empty_like(b), torch.empty_like(b)
     y_first = None
     rows = []
-    for gate, batch, cap, block in itertools.product((1, 2), (1, 2, 4, 8), (0, 1, 2), (32, 64, 128, 256)):
+    for gate, batch, cap, block in itertools.product((1, 2), (4, 8, 16), (0, 1, 2), (32, 64, 128)):
         h.set_option("TRSV_GATE", gate)
         h.set_option("TRSV_BATCH", batch)
         h.set_option("TRI_CTAS_PER_SM", cap)
