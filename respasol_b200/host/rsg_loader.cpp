@@ -7,6 +7,13 @@
 // the whole file is read once and tokenised in memory with strtol/strtod -- the same glibc
 // conversions scanf uses, so parsed doubles are bit-identical -- and rowptr is allocated m+1
 // entries (the reference allocates `count`).
+// Ingest is parallel (the reference's single-thread fscanf loop is the wall-time bottleneck of
+// every driver): the entry region is cut at line boundaries into one chunk per OpenMP thread and tokenised
+// concurrently, the COO -> CSR counting sort runs over disjoint row ranges per thread (stable, so rows holding
+// duplicates enter the per-row sort in file order exactly as in the reference).  Anything irregular -- an entry
+// split across lines, a stray token, an out-of-range index, a count that disagrees with the header -- makes the
+// parallel pass give up and the sequential tokeniser, which reproduces the reference's behaviour token by token
+// including its error paths, takes over.
 #include "rsg_host.h"
 
 #include <algorithm>
@@ -16,9 +23,27 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <chrono>
 #include <vector>
 
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
 namespace {
+
+// RSG_LOADER_TRACE=1: stage timings on stderr
+struct Trace {
+    bool on = getenv("RSG_LOADER_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void lap(const char *what)
+    {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rsg_loader] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
 
 template <typename T> T *alloc64(size_t len)
 {
@@ -107,6 +132,105 @@ bool strictly_ascending(const int *key, int lo, int hi)
     return true;
 }
 
+// Parallel tokeniser of the entry region [p0, end): true on success (exactly `nnz` well-formed one-per-line entries).
+// field: 'R' real, 'I' integer, 'C' complex, 'P' pattern.  x/y come out as in the file (after the transpose swap).
+bool parse_entries_parallel(const char *p0, const char *end, char field, int nnz, int m, int n, int transpose,
+                            std::vector<int> &ci, std::vector<int> &cj, std::vector<double> &cv, bool *zero_based)
+{
+#ifndef _OPENMP
+    (void)p0; (void)end; (void)field; (void)nnz; (void)m; (void)n; (void)transpose; (void)ci; (void)cj; (void)cv; (void)zero_based;
+    return false;
+#else
+    const size_t len = (size_t)(end - p0);
+    int T = omp_get_max_threads();
+    if (const char *e = getenv("RSG_LOADER_THREADS")) T = atoi(e);
+    if (T < 2 || len < ((size_t)1 << 20)) return false;
+    T = std::min(T, 64);
+    std::vector<const char *> cut((size_t)T + 1);
+    cut[0] = p0;
+    cut[(size_t)T] = end;
+    for (int t = 1; t < T; ++t) {
+        const char *q = p0 + len * (size_t)t / (size_t)T;
+        while (q < end && *q != '\n') ++q;
+        cut[(size_t)t] = q < end ? q + 1 : end;
+    }
+    // pass 1: non-blank lines per chunk = entries per chunk when the file is regular; prefix sums give every
+    // thread its slice of the output arrays, so pass 2 writes in place (no per-thread buffers, no concatenation)
+    std::vector<size_t> off((size_t)T + 1, 0);
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+    for (int t = 0; t < T; ++t) {
+        const char *p = cut[(size_t)t], *pe = cut[(size_t)t + 1];
+        size_t lines = 0;
+        while (p < pe) {
+            const char *nl = static_cast<const char *>(memchr(p, '\n', (size_t)(pe - p)));
+            const char *le = nl ? nl : pe;
+            bool blank = true;
+            for (const char *q = p; q < le; ++q)
+                if (*q != ' ' && *q != '\t' && *q != '\r') { blank = false; break; }
+            lines += blank ? 0 : 1;
+            p = le + 1;
+        }
+        off[(size_t)t + 1] = lines;
+    }
+    for (int t = 0; t < T; ++t) off[(size_t)t + 1] += off[(size_t)t];
+    if (off[(size_t)T] != (size_t)nnz) return false;
+    ci.resize((size_t)nnz); cj.resize((size_t)nnz); cv.resize((size_t)nnz);
+    const bool pattern = field == 'P';
+    int bad_any = 0, zero_any = 0;
+#pragma omp parallel for schedule(static, 1) num_threads(T) reduction(| : bad_any, zero_any)
+    for (int t = 0; t < T; ++t) {
+        const char *p = cut[(size_t)t], *pe = cut[(size_t)t + 1];
+        size_t k = off[(size_t)t];
+        const size_t kend = off[(size_t)t + 1];
+        bool bad = false, zero = false;
+        auto blanks = [&](void) { while (p < pe && (*p == ' ' || *p == '\t' || *p == '\r')) ++p; };
+        while (p < pe && !bad) {
+            blanks();
+            if (p >= pe) break;
+            if (*p == '\n') { ++p; continue; }
+            char *q;
+            long long x = strtoll(p, &q, 10);
+            if (q == p) { bad = true; break; }
+            p = q; blanks();
+            if (p >= pe || *p == '\n') { bad = true; break; }
+            long long y = strtoll(p, &q, 10);
+            if (q == p) { bad = true; break; }
+            p = q;
+            double re = 1.0;
+            if (!pattern) {
+                blanks();
+                if (p >= pe || *p == '\n') { bad = true; break; }
+                if (field == 'I') { long long iv = strtoll(p, &q, 10); re = (double)iv; }
+                else re = strtod(p, &q);
+                if (q == p) { bad = true; break; }
+                p = q;
+                if (field == 'C') {
+                    blanks();
+                    if (p >= pe || *p == '\n') { bad = true; break; }
+                    (void)strtod(p, &q);
+                    if (q == p) { bad = true; break; }
+                    p = q;
+                }
+            }
+            blanks();
+            if (p < pe && *p != '\n') { bad = true; break; } // a stray token: not one entry per line
+            if (transpose) std::swap(x, y);
+            if (x < 0 || y < 0 || x > m || y > n || k >= kend) { bad = true; break; }
+            if (x == 0 || y == 0) zero = true;
+            ci[k] = (int)x; cj[k] = (int)y; cv[k] = re;
+            ++k;
+        }
+        if (k != kend) bad = true;
+        bad_any |= bad ? 1 : 0;
+        zero_any |= zero ? 1 : 0;
+    }
+    if (bad_any) { ci.clear(); cj.clear(); cv.clear(); return false; }
+    const bool zero = zero_any != 0;
+    *zero_based = zero;
+    return true;
+#endif
+}
+
 } // namespace
 
 extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputBase, int transpose, int flags)
@@ -115,6 +239,7 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
     matrix->rowptr = nullptr; matrix->colidx = nullptr; matrix->values = nullptr;
     matrix->m = matrix->n = matrix->nnz = 0; matrix->isSymmetric = 0;
 
+    Trace trace;
     FILE *fp = fopen(file, "rb");
     if (!fp) {
         // the reference exit(-1)s here (cpp:50-53); a library must not
@@ -133,6 +258,7 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
         fclose(fp);
     }
     Cursor cur{buf.data(), buf.data() + buf.size() - 1};
+    trace.lap("read file");
 
     // ---- banner: five whitespace-separated tokens on line 1 (mm_io.cpp:54-158)
     char kind = 0, field = 0, storage = 0;
@@ -189,7 +315,8 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
     std::vector<double> cv;
     ci.reserve((size_t)nnz); cj.reserve((size_t)nnz); cv.reserve((size_t)nnz);
     bool zero_based_file = false;
-    for (;;) {
+    const bool parsed = parse_entries_parallel(cur.p, cur.end, field, nnz, m, n, transpose, ci, cj, cv, &zero_based_file);
+    while (!parsed) { // sequential tokeniser: small files, irregular files, and every error path
         long long x, y;
         double re = 0, im = 0;
         const char *save = cur.p;
@@ -206,6 +333,7 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
         ci.push_back((int)x); cj.push_back((int)y); cv.push_back(pattern ? 1.0 : re);
         if (x == 0 || y == 0) zero_based_file = true;
     }
+    trace.lap(parsed ? "tokenise (parallel)" : "tokenise (sequential)");
     if (zero_based_file)
         for (size_t i = 0; i < ci.size(); ++i) { ci[i]++; cj[i]++; }
     if ((long long)ci.size() != nnz) {
@@ -246,6 +374,7 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
         for (size_t i = (size_t)nnz; i < stored; ++i)
             if (ci[i] > m || cj[i] > n) { fprintf(stderr, "Error: symmetric file is not square.\n"); return 0; }
 
+    trace.lap("checks / symmetric count");
     // ---- COO -> CSR: stable counting sort by row, then per-row sort by column (cpp:202-242)
     matrix->values = alloc64<double>(std::max(count, stored));
     matrix->colidx = alloc64<int>(std::max(count, stored));
@@ -260,13 +389,26 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
     for (size_t l = 0; l < stored; ++l) rowptr[ci[l]]++;
     for (int i = 0; i < m; ++i) rowptr[i + 1] += rowptr[i];
     {
+        // stable scatter: every thread owns a contiguous range of rows and walks the whole entry list for them,
+        // so entries of a row land in file order whatever the thread count
         std::vector<int> fill(rowptr, rowptr + m);
-        for (size_t l = 0; l < stored; ++l) {
-            const int dst = fill[ci[l] - 1]++;
-            matrix->values[dst] = cv[l];
-            matrix->colidx[dst] = cj[l] - 1 + outputBase;
+        int T = 1;
+#ifdef _OPENMP
+        T = stored >= ((size_t)1 << 18) ? std::min(omp_get_max_threads(), 64) : 1;
+#endif
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+        for (int t = 0; t < T; ++t) {
+            const int r0 = (int)((long long)m * t / T) + 1, r1 = (int)((long long)m * (t + 1) / T); // 1-based rows [r0, r1]
+            for (size_t l = 0; l < stored; ++l) {
+                const int r = ci[l];
+                if (r < r0 || r > r1) continue;
+                const int dst = fill[r - 1]++;
+                matrix->values[dst] = cv[l];
+                matrix->colidx[dst] = cj[l] - 1 + outputBase;
+            }
         }
     }
+    trace.lap("counting sort by row");
 #pragma omp parallel for schedule(dynamic, 1024)
     for (int i = 0; i < m; ++i) {
         const int lo = rowptr[i], hi = rowptr[i + 1] - 1;
@@ -275,6 +417,7 @@ extern "C" int rsg_load_matrix_market(const char *file, CSR *matrix, int outputB
     }
     if (outputBase != 0)
         for (int i = 0; i <= m; ++i) rowptr[i] += outputBase;
+    trace.lap("per-row column sort");
 
     matrix->m = m;
     matrix->n = n;
