@@ -129,6 +129,24 @@ int spmv_csr_mixed(rsg_handle_t handle, int m, int n, int nnz, int base,
                    const int *rowptr, const int *colidx, const float *values,
                    double alpha, const double *x, double beta, double *y);
 
+/* ---- transpose / CSC path ------------------------------------------------- */
+/* CSR -> CSC on the device: what the reference obtains by asking its loader for the transposed matrix
+ * (transpose = 1, loadMatrixMarket.cpp:79-81,124; test_superLU_MT.c:85).  colptr (n+1 ints), rowidx and values_out
+ * (stored-count entries each) are caller-allocated DEVICE arrays; indices keep `base`; inside a column the entries
+ * keep their row order (stable).  values / values_out may be NULL (pattern only).  Synchronous. */
+int rsg_csr2csc_d(rsg_handle_t handle, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
+                  const double *values, int *colptr, int *rowidx, double *values_out);
+int rsg_csr2csc_s(rsg_handle_t handle, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
+                  const float *values, int *colptr, int *rowidx, float *values_out);
+/* y = alpha*A^T*x + beta*y (x has m entries, y has n): CUSPARSE_OPERATION_TRANSPOSE of the SpMV call group
+ * (spmv.cu:184 passes NON_TRANSPOSE; this is the CSC product).  The transposed pattern is built once per matrix and
+ * cached in the handle; the values are re-gathered on every call, then the ordinary SpMV kernels run on the
+ * transposed pattern: deterministic, no atomics. */
+int spmv_csr_t_d(rsg_handle_t handle, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
+                 const double *values, double alpha, const double *x, double beta, double *y);
+int spmv_csr_t_s(rsg_handle_t handle, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
+                 const float *values, float alpha, const float *x, float beta, float *y);
+
 /* ---- ILU0 -------------------------------------------------------------------------------- */
 /* "Symbolic": diagonal positions, structural zero-pivot check, level sets of the lower pattern
  * (shared by the factorization and the L solve).  *zero_pivot_row = -1 or the first row with no

@@ -49,6 +49,10 @@ GPU_SYMBOLS = {
     "spmv_csr_d": (_I, _CSR_ARGS + [_P, _D, _P, _D, _P]),
     "spmv_csr_s": (_I, _CSR_ARGS + [_P, _F, _P, _F, _P]),
     "spmv_csr_mixed": (_I, _CSR_ARGS + [_P, _D, _P, _D, _P]),
+    "rsg_csr2csc_d": (_I, _CSR_ARGS + [_P, _P, _P, _P]),
+    "rsg_csr2csc_s": (_I, _CSR_ARGS + [_P, _P, _P, _P]),
+    "spmv_csr_t_d": (_I, _CSR_ARGS + [_P, _D, _P, _D, _P]),
+    "spmv_csr_t_s": (_I, _CSR_ARGS + [_P, _F, _P, _F, _P]),
     "rsg_ilu0_analysis": (_I, _TRI_ARGS + [c_int_p]),
     "ilu0_factor_d": (_I, _TRI_ARGS + [_P, c_int_p]),
     "ilu0_factor_s": (_I, _TRI_ARGS + [_P, c_int_p]),

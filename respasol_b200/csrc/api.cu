@@ -84,6 +84,7 @@ int rsg_create(rsg_handle_t *handle, int device)
     }
     h->spmv_plans.reserve(65);
     h->tri_plans.reserve(9);
+    h->transpose_plans.reserve(9);
     *handle = h;
     return RSG_OK;
 }
@@ -95,6 +96,7 @@ int rsg_destroy(rsg_handle_t h)
     cudaStreamSynchronize(h->stream);
     for (auto &p : h->spmv_plans) spmv_free_plan(p);
     for (auto &p : h->tri_plans) tri_free_plan(p);
+    for (auto &p : h->transpose_plans) transpose_free_plan(p);
     if (h->cub_tmp) cudaFree(h->cub_tmp);
     if (h->krylov_ws) cudaFree(h->krylov_ws);
     if (h->krylov_pin) cudaFreeHost(h->krylov_pin);
@@ -159,6 +161,8 @@ int rsg_forget_matrix(rsg_handle_t h, const int *rowptr)
         if (h->spmv_plans[i].rowptr == rowptr) { spmv_free_plan(h->spmv_plans[i]); h->spmv_plans.erase(h->spmv_plans.begin() + (long)i); }
     for (size_t i = h->tri_plans.size(); i-- > 0;)
         if (h->tri_plans[i].rowptr == rowptr) { tri_free_plan(h->tri_plans[i]); h->tri_plans.erase(h->tri_plans.begin() + (long)i); h->last_tri = -1; }
+    for (size_t i = h->transpose_plans.size(); i-- > 0;)
+        if (h->transpose_plans[i].rowptr == rowptr) transpose_drop_plan(h, i);
     return RSG_OK;
 }
 
@@ -194,6 +198,38 @@ int spmv_csr_mixed(rsg_handle_t h, int m, int n, int nnz, int base, const int *r
     if (!h) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
     return spmv_run<float, double>(h, m, n, nnz, base, rowptr, colidx, values, alpha, x, beta, y);
+}
+
+// ---- transpose (CSC) path ------------------------------------------------------------------
+int rsg_csr2csc_d(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                  int *colptr, int *rowidx, double *values_out)
+{
+    (void)nnz;
+    if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || !colptr) return RSG_BAD_ARG;
+    DeviceGuard g(h->device);
+    return csr2csc_run<double>(h, m, n, base, rowptr, colidx, values, colptr, rowidx, values_out);
+}
+int rsg_csr2csc_s(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx, const float *values,
+                  int *colptr, int *rowidx, float *values_out)
+{
+    (void)nnz;
+    if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || !colptr) return RSG_BAD_ARG;
+    DeviceGuard g(h->device);
+    return csr2csc_run<float>(h, m, n, base, rowptr, colidx, values, colptr, rowidx, values_out);
+}
+int spmv_csr_t_d(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                 double alpha, const double *x, double beta, double *y)
+{
+    if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || (n > 0 && !y)) return RSG_BAD_ARG;
+    DeviceGuard g(h->device);
+    return spmv_transposed_run<double>(h, m, n, nnz, base, rowptr, colidx, values, alpha, x, beta, y);
+}
+int spmv_csr_t_s(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx, const float *values,
+                 float alpha, const float *x, float beta, float *y)
+{
+    if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || (n > 0 && !y)) return RSG_BAD_ARG;
+    DeviceGuard g(h->device);
+    return spmv_transposed_run<float>(h, m, n, nnz, base, rowptr, colidx, values, alpha, x, beta, y);
 }
 
 // ---- ILU0 / SpTRSV ------------------------------------------------------------------------

@@ -109,6 +109,18 @@ struct TriPlan {
     size_t bytes = 0;
 };
 
+// ------------------------------------------------ transposed pattern (CSC) of a CSR matrix, cached per handle
+struct TransposePlan {
+    const int *rowptr = nullptr;
+    const int *colidx = nullptr;
+    int m = 0, n = 0, base = 0, nnz_hint = 0;
+    int nnz = 0, first = 0;
+    int *colptr = nullptr;    // n+1, carries the base
+    int *rowidx = nullptr;    // nnz, carries the base
+    int *perm = nullptr;      // nnz: entry (relative to `first`) that lands at k
+    void *values_t = nullptr; // nnz * 8 bytes, re-gathered per product
+};
+
 } // namespace rsg
 
 struct rsg_context {
@@ -124,6 +136,7 @@ struct rsg_context {
     int last_spmv_maxrow = 0;
     std::vector<rsg::SpmvPlan> spmv_plans;
     std::vector<rsg::TriPlan> tri_plans;
+    std::vector<rsg::TransposePlan> transpose_plans;
     int last_tri = -1;
     void *cub_tmp = nullptr;
     size_t cub_tmp_bytes = 0;
@@ -180,6 +193,16 @@ int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, c
 int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split = false);
 template <typename TV, typename TX>
 int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
+
+// transpose.cu
+void transpose_free_plan(TransposePlan &p);
+void transpose_drop_plan(rsg_context *h, size_t i);
+template <typename T>
+int csr2csc_run(rsg_context *h, int m, int n, int base, const int *rowptr, const int *colidx, const T *values, int *colptr,
+                int *rowidx, T *values_out);
+template <typename T>
+int spmv_transposed_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx, const T *values,
+                        T alpha, const T *x, T beta, T *y);
 
 // levels.cu
 int tri_get_plan(rsg_context *h, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,

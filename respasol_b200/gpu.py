@@ -140,6 +140,30 @@ class Handle:
                   alpha, self._p(x), beta, self._p(y)), "spmv_csr_" + A.precision)
         return y
 
+    def spmv_t(self, A: DeviceCSR, x, y=None, alpha=1.0, beta=0.0):
+        """y = alpha*A^T*x + beta*y through spmv_csr_t_d / spmv_csr_t_s (x: m entries, y: n entries)."""
+        self._claim(A)
+        assert A.precision in ("d", "s") and x.dtype == A.values.dtype and x.numel() >= A.m
+        if y is None:
+            y = torch.empty(A.n, dtype=x.dtype, device=x.device)
+        fn = self.lib.spmv_csr_t_d if A.precision == "d" else self.lib.spmv_csr_t_s
+        _check(fn(self.h, A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
+                  alpha, self._p(x), beta, self._p(y)), "spmv_csr_t_" + A.precision)
+        return y
+
+    def csr2csc(self, A: DeviceCSR):
+        """(colptr, rowidx, values) of A as CSC = CSR of A^T, built on the device."""
+        self._claim(A)
+        assert A.precision in ("d", "s")
+        cnt = int(A.rowptr[-1] - A.rowptr[0])
+        colptr = torch.empty(A.n + 1, dtype=torch.int32, device=A.device)
+        rowidx = torch.empty(max(cnt, 1), dtype=torch.int32, device=A.device)
+        vals = torch.empty(max(cnt, 1), dtype=A.values.dtype, device=A.device)
+        fn = self.lib.rsg_csr2csc_d if A.precision == "d" else self.lib.rsg_csr2csc_s
+        _check(fn(self.h, A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx), self._p(A.values),
+                  self._p(colptr), self._p(rowidx), self._p(vals)), "rsg_csr2csc")
+        return colptr, rowidx[:cnt], vals[:cnt]
+
     @staticmethod
     def ptr_array(addresses):
         """HOST array of device addresses (0 = NULL) in the form the C ABI takes; build once, pass many times."""
