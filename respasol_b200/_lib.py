@@ -87,6 +87,7 @@ HOST_SYMBOLS = {
     "rsg_gen_stencil27": (_I, [_I, _I, _I, _I, _I, C.c_uint64, C.POINTER(CCSR)]),
     "rsg_gen_femlike": (_I, [_I, _D, C.c_uint64, C.POINTER(CCSR)]),
     "rsg_gen_powerlaw": (_I, [_I, _D, _I, _I, _I, C.c_uint64, C.POINTER(CCSR)]),
+    "rsg_gen_banded": (_I, [_I, _I, _I, C.c_uint64, C.POINTER(CCSR)]),
     "rsg_dlarnv_u01": (None, [C.c_int64, C.POINTER(C.c_double)]),
 }
 

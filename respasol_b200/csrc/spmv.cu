@@ -412,6 +412,27 @@ __global__ void row_stats_kernel(int m, const int *__restrict__ rowptr, int *out
     if (blockIdx.x == 0 && threadIdx.x == 0) { out[1] = rowptr[0]; out[2] = rowptr[m]; }
 }
 
+// How scattered are the x gathers of NEIGHBOURING rows?  One warp per sampled group of 32 consecutive rows: lane l
+// takes the middle entry of row r0+l; out[3] += distinct 128-byte lines (of 8-byte x) among them, out[4] += rows
+// looked at.  A stencil or FEM ordering gives ~0.1 lines per row (thread-per-row gathers coalesce), hashed columns ~1.
+__global__ void scatter_stats_kernel(int m, int base, int groups, const int *__restrict__ rowptr, const int *__restrict__ colidx, int *out)
+{
+    const int g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (g >= groups) return;
+    const int ngroups32 = (m + 31) / 32;
+    const int r = (int)(((long long)g * ngroups32) / groups) * 32 + lane;
+    int line = -1 - lane; // distinct dummies for absent rows
+    bool valid = false;
+    if (r < m) {
+        const int a = rowptr[r], b = rowptr[r + 1];
+        if (b > a) { line = (colidx[a - base + ((b - a) >> 1)] - base) >> 4; valid = true; }
+    }
+    const unsigned peers = __match_any_sync(0xffffffffu, line);
+    const bool leader = valid && (lane == __ffs(peers) - 1);
+    const int distinct = __popc(__ballot_sync(0xffffffffu, leader)), rows = __popc(__ballot_sync(0xffffffffu, valid));
+    if (lane == 0 && rows > 0) { atomicAdd(out + 3, distinct); atomicAdd(out + 4, rows); }
+}
+
 __global__ void row_partition_kernel(int m, int base, const int *__restrict__ rowptr, int ngpu, int balanced, int *starts)
 {
     const int g = threadIdx.x;
@@ -473,18 +494,24 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
     SpmvPlan p;
     p.rowptr = rowptr; p.colidx = colidx; p.m = m; p.n = n; p.nnz_hint = nnz_hint; p.base = base; p.opt_sig = sig;
     cudaStream_t st = h->stream;
-    RSG_CUDA_TRY(cudaMemsetAsync(h->scratch_i, 0, 4 * sizeof(int), st));
+    RSG_CUDA_TRY(cudaMemsetAsync(h->scratch_i, 0, 8 * sizeof(int), st));
     if (m > 0) {
         const int blocks = std::min((m + 255) / 256, h->sm_count * 8);
         row_stats_kernel<<<blocks, 256, 0, st>>>(m, rowptr, h->scratch_i);
         h->launches++;
+        if (colidx && h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_AUTO) {
+            const int groups = std::min((m + 31) / 32, 4096);
+            scatter_stats_kernel<<<(groups * 32 + 255) / 256, 256, 0, st>>>(m, base, groups, rowptr, colidx, h->scratch_i);
+            h->launches++;
+        }
     } else {
         RSG_CUDA_TRY(cudaMemcpyAsync(h->scratch_i + 1, rowptr, sizeof(int), cudaMemcpyDeviceToDevice, st));
         RSG_CUDA_TRY(cudaMemcpyAsync(h->scratch_i + 2, rowptr, sizeof(int), cudaMemcpyDeviceToDevice, st));
     }
-    RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i, h->scratch_i, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i, h->scratch_i, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
     RSG_CUDA_TRY(cudaStreamSynchronize(st));
     p.max_row = h->pinned_i[0];
+    const double scatter = h->pinned_i[4] > 0 ? (double)h->pinned_i[3] / h->pinned_i[4] : 0.0; // x lines per row, neighbouring rows
     p.first = h->pinned_i[1] - base;
     p.nnz = h->pinned_i[2] - h->pinned_i[1];
     if (p.nnz < 0 || p.first < 0) return RSG_BAD_ARG;
@@ -508,6 +535,12 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         if (algo == RSG_SPMV_TILE) {
             const double avg = (double)p.nnz / std::max(m, 1);
             variant = avg < 12.0 ? 9 : (vbytes >= 8 ? 0 : 1);
+            // Rows of some length whose neighbours gather from unrelated x lines (hashed / badly ordered columns):
+            // thread-per-row gathers out of a staged tile no longer coalesce, and what helps is L1 capacity for x --
+            // the plain sub-warp-per-row kernel uses no shared memory and leaves all 228 KB to L1 (1.7-2.5x on the
+            // banded stand-ins of the 36-matrix sweep, profiles/r1_bench_spmv_sweep.*).  Not with dense rows (one
+            // sub-warp would crawl through them) and not when tiles must wait on halo flags.
+            if (scatter > 0.5 && avg >= 16.0 && p.max_row <= 4096 && h->opts[RSG_OPT_SPMV_HALO_START] == 0) algo = RSG_SPMV_VECTOR;
         }
     }
     if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)

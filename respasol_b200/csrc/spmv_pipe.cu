@@ -259,8 +259,7 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
                                                                make_evict_first_policy());
         if (tid == 0) {
             const int2 lr = ls.lrow[sg.w];
-            volatile TX *part = reinterpret_cast<volatile TX *>(ls.part + lr.x);
-            *reinterpret_cast<volatile TX *>(ls.part + seg_id) = tot;
+            *reinterpret_cast<volatile TX *>(ls.part + seg_id) = tot; // one 8-byte slot per segment, whatever TX is
             __threadfence();
             if (atomicAdd(ls.cnt + sg.w, 1) == lr.y - 1) {
                 __threadfence();
@@ -269,7 +268,6 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
                 store_y(y, sg.x, sum, alpha, beta);
                 ls.cnt[sg.w] = 0;
             }
-            (void)part;
         }
         return;
     }

@@ -105,6 +105,10 @@ def gen_powerlaw(m, alpha=2.2, maxlen=64, ndense=4, dense_len=100000, seed=4) ->
     return _gen(host_lib().rsg_gen_powerlaw, m, alpha, maxlen, ndense, dense_len, seed)
 
 
+def gen_banded(m, per_row, half_band, seed=7) -> CSR:
+    return _gen(host_lib().rsg_gen_banded, m, per_row, half_band, seed)
+
+
 def dlarnv_u01(n) -> np.ndarray:
     """x = LAPACKE_dlarnv(1, {0,0,0,1}, n) restated (test_spmv.c:75-76)."""
     x = np.empty(n, dtype=np.float64)

@@ -219,3 +219,47 @@ extern "C" int rsg_gen_powerlaw(int m, double alpha, int maxlen, int ndense, int
     out->rowptr[m] = k;
     return 1;
 }
+
+// Generic shape class for the sweep harness: m rows of `per_row` entries each -- the diagonal plus per_row-1
+// distinct columns at hashed offsets within +-half_band (clipped to the matrix; rows near the border are shorter
+// when the band runs out of distinct columns).  Values -(0.5+u), diagonal 1.05 * sum|offdiag|.
+extern "C" int rsg_gen_banded(int m, int per_row, int half_band, uint64_t seed, CSR *out)
+{
+    if (!out || m < 1 || per_row < 1 || half_band < 1) return 0;
+    half_band = std::min(half_band, m);
+    std::vector<int> rp((size_t)m + 1, 0);
+    std::vector<std::vector<int>> rows;
+    // two passes would double the hashing; rows are small, keep them
+    std::vector<int> ci;
+    ci.reserve((size_t)m * (size_t)per_row);
+    std::vector<int> cur;
+    for (int i = 0; i < m; ++i) {
+        cur.clear();
+        cur.push_back(i);
+        const int lo = std::max(0, i - half_band), hi = std::min(m - 1, i + half_band);
+        const int span = hi - lo + 1;
+        const int want = std::min(per_row, span);
+        for (uint64_t t = 0; (int)cur.size() < want && t < (uint64_t)per_row * 8; ++t) {
+            const int c = lo + (int)(hash3(seed, (uint64_t)i, t) % (uint64_t)span);
+            if (std::find(cur.begin(), cur.end(), c) == cur.end()) cur.push_back(c);
+        }
+        std::sort(cur.begin(), cur.end());
+        ci.insert(ci.end(), cur.begin(), cur.end());
+        rp[(size_t)i + 1] = (int)ci.size();
+    }
+    if (!alloc_csr(out, m, m, ci.size())) return 0;
+    std::memcpy(out->rowptr, rp.data(), sizeof(int) * ((size_t)m + 1));
+    std::memcpy(out->colidx, ci.data(), sizeof(int) * ci.size());
+    for (int i = 0; i < m; ++i) {
+        double sum = 0;
+        int dk = -1;
+        for (int k = rp[(size_t)i]; k < rp[(size_t)i + 1]; ++k) {
+            if (ci[(size_t)k] == i) { dk = k; continue; }
+            const double v = -(0.5 + u01(hash3(seed ^ 0x51ED270B, (uint64_t)i, (uint64_t)ci[(size_t)k])));
+            out->values[k] = v;
+            sum += std::fabs(v);
+        }
+        out->values[dk] = 1.05 * sum + 1e-3;
+    }
+    return 1;
+}

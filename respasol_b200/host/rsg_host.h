@@ -68,6 +68,10 @@ int rsg_gen_femlike(int N, double p, uint64_t seed, CSR *out);
  * columns + diagonal, plus ndense dense rows (and their transposed columns) of dense_len entries. */
 int rsg_gen_powerlaw(int m, double alpha, int maxlen, int ndense, int dense_len, uint64_t seed, CSR *out);
 
+/* Generic shape class (sweep harness): m rows x per_row entries (diagonal + hashed distinct columns within
+ * +-half_band), diagonally dominant values. */
+int rsg_gen_banded(int m, int per_row, int half_band, uint64_t seed, CSR *out);
+
 /* dlarnv(1,{0,0,0,1}) restated for the harness (test_spmv.c:75-76): 48-bit LCG, u = s*2^-48. */
 void rsg_dlarnv_u01(int64_t n, double *x);
 

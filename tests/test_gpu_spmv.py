@@ -348,6 +348,21 @@ def test_too_many_long_rows_fall_back_to_merge_path(handle):
         handle.set_option("SPMV_ALGO", 0)
 
 
+def test_auto_picks_the_unstaged_kernel_for_scattered_columns(handle):
+    """Rows of some length whose neighbours gather unrelated x lines (hashed columns inside a band) take the plain
+    sub-warp-per-row kernel (all of L1 for x); orderings with neighbour coherence and short or dense rows stay tiled."""
+    x_of = lambda a: orc.dlarnv(a.n) - 0.5
+    a = host.gen_banded(60000, 40, 6000)
+    for p in ("d", "s", "m"):
+        check(handle, a, x_of(a), p)
+        assert handle.info("SPMV_ALGO_USED") == ALGO["vector"]
+    check(handle, a, x_of(a), "d", alpha=-0.5, beta=2.0, y0=orc.dlarnv(a.m))
+    for b in (host.gen_stencil27(30, seed=2), host.gen_femlike(24), host.gen_banded(60000, 8, 6000),
+              host.gen_powerlaw(60000, 2.2, 64, 3, 20000, 4)):
+        check(handle, b, x_of(b), "d")
+        assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+
+
 PIPE_MATS = {
     "stencil27_64": lambda: host.gen_stencil27(64, seed=2),            # banded: x prefix grows chunk by chunk
     "lap2d_600": lambda: host.gen_laplace2d(600),
