@@ -70,7 +70,7 @@ typedef enum {
     RSG_OPT_TRSV_ALGO = 5,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_ILU0_ALGO = 6,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_SPMV_X_PERSIST = 7, /* 1: pin x in L2 with an access-policy window on the stream */
-    RSG_OPT_SPMV_X_HINT = 8,    /* stream/pipe kernels: 1 = gather x with an L2 evict_last hint */
+    RSG_OPT_SPMV_X_HINT = 8,    /* stream/pipe kernels: 1 = gather x with an L2 evict_last hint; tile kernel: 3 = older inner loop (A/B) */
     RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* pipe kernel: tile size in rows per thread (0 = 1) */
     RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* pipe kernel: cap on resident CTAs per SM (0 = occupancy limit) */
     RSG_OPT_TRSV_BATCH = 11,    /* sync-free solves: solution entries polled per round trip (1,2,4,8,16; 0 = default) */

@@ -432,6 +432,46 @@ __device__ __forceinline__ TX row_dot_lean(const TV *s_val, const int *s_col, in
     return s;
 }
 
+// Same sum, same order, fewer instructions: whole batches of B entries run without predicates (B independent
+// gathers, then B multiply-adds), only the last partial batch is predicated; the gather address is one IMAD.WIDE
+// off an opaque 64-bit base.  (row_dot_lean spends ~17 instructions per entry on a 27-point row: per-entry
+// predicates, a 4-instruction 64-bit address chain, and 16 register moves per batch for its software prefetch.)
+template <typename TV, typename TX, int G, int B>
+__device__ __forceinline__ TX row_dot_lean2(const TV *s_val, const int *s_col, int k, int e, const TX *xb)
+{
+    asm volatile("" : "+l"(xb));
+    TX s = 0;
+    while (k + (B - 1) * G < e) {
+        TX xv[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u) xv[u] = __ldg(xb + s_col[k + u * G]);
+#pragma unroll
+        for (int u = 0; u < B; ++u) s += (TX)s_val[k + u * G] * xv[u];
+        k += B * G;
+    }
+    if (k < e) {
+        TX xv[B];
+#pragma unroll
+        for (int u = 0; u < B; ++u) xv[u] = (k + u * G < e) ? __ldg(xb + s_col[k + u * G]) : (TX)0;
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (k + u * G < e) s += (TX)s_val[k + u * G] * xv[u];
+    }
+    return s;
+}
+
+template <typename TV, typename TX, int THREADS, int B>
+__device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
+                                                  int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
+                                                  TX alpha, TX beta)
+{
+    const TX *xb = x - base;
+    for (int i = threadIdx.x; i < nrows; i += THREADS) {
+        const TX s = row_dot_lean2<TV, TX, 1, B>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
+        store_y(y, row_glob + i, s, alpha, beta);
+    }
+}
+
 template <typename TV, typename TX, int THREADS, int G>
 __device__ __forceinline__ void reduce_rows_lean(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
                                                  int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,

@@ -94,7 +94,8 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
             if (qe > sb) { mbar_wait(s_aux, aux_parity); aux_parity ^= 1; }
         }
         const int nrows = pe - cur;
-        int g = reduce_opt;
+        int g = reduce_opt & 0xff;
+        const int mode = reduce_opt >> 8; // RSG_OPT_SPMV_X_HINT on the tile kernel: 3 = the older software-prefetching inner loop (A/B)
         if (g == 0) { // lanes per row from the tile's row-length statistics
             const int avg = (k1 - k0) / nrows;
             const int len = max(avg, mt.maxlen >> 3);
@@ -105,7 +106,11 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
         const int *rp = s_rp + cur;
         if (LEAN) {
             switch (g) {
-            case 1: reduce_rows_lean<TV, TX, NC, 1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            case 1: // thread per row: unpredicated whole batches (measured: 8 gathers per batch for fp64 x, 16 for fp32;
+                    // tools/ab_option.py SPMV_X_HINT 0 3: config 2 fp64 62.7 -> 60.4 us, fp32 48.2 -> 45.0 us)
+                if (mode == 3) reduce_rows_lean<TV, TX, NC, 1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+                else reduce_rows_lean2<TV, TX, NC, (sizeof(TX) == 4 ? 16 : 8)>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+                break;
             case 2: reduce_rows_lean<TV, TX, NC, 2>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
             case 4: reduce_rows_lean<TV, TX, NC, 4>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
             case 8: reduce_rows_lean<TV, TX, NC, 8>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
@@ -554,7 +559,7 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
     LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg};
     kern<<<p->nblk + fuse.ctas + ls.nseg, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc,
-                                                                      p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags,
+                                                                      p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE] | (h->opts[RSG_OPT_SPMV_X_HINT] << 8), h->wait_flags,
                                                                       h->wait_flags ? h->wait_n : 0, h->wait_epoch, fuse, ls);
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;

@@ -34,12 +34,27 @@ def main():
     args = ap.parse_args()
     a = host.gen_stencil27(args.grid, seed=2)
     n = a.n
+    out = {"bytes_each_way": n * 8}
+    # unbound first (wherever the scheduler put this thread), then from the GPU's own NUMA node
+    sys.path.insert(0, ROOT)
+    from bench import gpu_local_cpus
+    xu = torch.rand(n, dtype=torch.float64).pin_memory()
+    du = torch.empty(n, dtype=torch.float64, device="cuda")
+
+    def h2d_unbound():
+        du.copy_(xu, non_blocking=True)
+        torch.cuda.synchronize()
+    out["h2d_unbound_us"] = wall(h2d_unbound, args.reps)
+    near = gpu_local_cpus(0)
+    out["gpu_local_cpus"] = len(near) if near else 0
+    out["all_cpus"] = len(os.sched_getaffinity(0))
+    if near:
+        os.sched_setaffinity(0, near)
     xh = torch.rand(n, dtype=torch.float64).pin_memory()
     yh = torch.zeros(n, dtype=torch.float64).pin_memory()
     xd = torch.empty(n, dtype=torch.float64, device="cuda")
     yd = torch.ones(n, dtype=torch.float64, device="cuda")
     s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
-    out = {"bytes_each_way": n * 8}
 
     def h2d():
         xd.copy_(xh, non_blocking=True)
