@@ -459,18 +459,52 @@ def run_ours(args):
     xh_t = torch.from_numpy(np.ascontiguousarray(xfull)).pin_memory()
     yh_t = torch.zeros(full64.m, dtype=torch.float64).pin_memory()
     xh, yh = xh_t.numpy(), yh_t.numpy()
+    def pcie_link():
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            d = pynvml.nvmlDeviceGetHandleByIndex(dev.index if dev.index is not None else 0)
+            return "gen%d x%d" % (pynvml.nvmlDeviceGetCurrPcieLinkGeneration(d), pynvml.nvmlDeviceGetCurrPcieLinkWidth(d))
+        except Exception:  # noqa: BLE001
+            return "unknown"
+
+    def copy_alone_us(dst, src, reps=20):
+        for _ in range(3):
+            dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            dst.copy_(src, non_blocking=True)
+            torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / reps * 1e6
+
+    # the e2e products keep the SMs almost idle; make sure the device is out of its low-power state first
+    # (0.3 s of device-resident products), then look at what the PCIe link does on its own on this box
+    spin_x = torch.from_numpy(xfull).to(dev)
+    spin_y = torch.empty(full64.m, dtype=torch.float64, device=dev)
+    spin_A = DeviceCSR(full64, "d", dev)
+    t0 = time.perf_counter()
+    while time.perf_counter() - t0 < 0.3:
+        for _ in range(50):
+            h.spmv(spin_A, spin_x, spin_y)
+        torch.cuda.synchronize()
+    h2d_alone = copy_alone_us(spin_x, xh_t)
+    d2h_alone = copy_alone_us(yh_t, spin_y)
+    del spin_A
     for _ in range(3):
         h.matrix_spmv_host(mat, xh, yh)
-    e_steps = max(5, min(K, 50))
+    e_steps = max(50, min(K, 200))
     # PCIe time on a shared host is noisy from run to run (8 MB H2D measured between 157 and 287 us on this pool):
     # five rounds of e_steps products, the median round is reported, the spread is kept
     rounds = []
+    links = []
     for _ in range(5):
         barrier()
         t0 = time.perf_counter()
         for _ in range(e_steps):
             h.matrix_spmv_host(mat, xh, yh)
         rounds.append(allmax((time.perf_counter() - t0) / e_steps))
+        links.append(pcie_link())
     edt = sorted(rounds)[len(rounds) // 2]
     h.matrix_free(mat)
     os.sched_setaffinity(0, all_cpus)
@@ -480,6 +514,8 @@ def run_ours(args):
            "h2d_bytes_per_step": 8 * full64.n * world, "d2h_bytes_per_step": 8 * full64.m * world, "ms_per_step": edt * 1e3,
            "host_cpus": ("%d GPU-local of %d" % (len(near), len(all_cpus))) if near else "unbound",
            "ms_per_step_rounds": [round(r * 1e3, 4) for r in rounds],
+           "pcie": {"link_during_rounds": sorted(set(links)), "h2d_alone_us": round(h2d_alone, 1), "d2h_alone_us": round(d2h_alone, 1),
+                    "note": "plain cudaMemcpyAsync of the same 8 MB buffers on this box, measured just before the rounds"},
            "note": "rsg_matrix_spmv_host on every rank: matrix resident in HBM (uploaded once, as GPU/spmv.cu:111-118 does), "
                    "x H2D (from pinned host memory) + SpMV + y D2H (to pinned host memory) inside every timed step"}
     if world == 1:

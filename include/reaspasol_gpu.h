@@ -84,6 +84,8 @@ typedef enum {
                                    (x H2D | SpMV | y D2H overlap chunk by chunk); 0 = default (4), 1 = one piece */
     RSG_OPT_HOST_Y_DIRECT = 17, /* pipelined host-vector product: 1 = the kernels store y straight into the page-locked host
                                    buffer (mapped memory, no D2H copy stage); 0 = device memory + async D2H copies (default) */
+    RSG_OPT_HOST_GRAPH = 18,    /* pipelined host-vector product: 0/1 = replay the step from a CUDA graph once the same host buffers
+                                   and alpha are seen twice (one launch call instead of ~30 stream calls); 2 = never */
     RSG_OPT_COUNT_
 } rsg_option;
 

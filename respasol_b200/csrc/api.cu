@@ -530,7 +530,11 @@ int rsg_matrix_upload(rsg_handle_t h, char precision, int m, int n, int nnz, int
     }
     bool ev_ok = cudaStreamCreateWithFlags(&a->s_in, cudaStreamNonBlocking) == cudaSuccess &&
                  cudaStreamCreateWithFlags(&a->s_out, cudaStreamNonBlocking) == cudaSuccess &&
-                 cudaEventCreateWithFlags(&a->ev_start, cudaEventDisableTiming) == cudaSuccess;
+                 cudaStreamCreateWithFlags(&a->s_main, cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&a->ev_start, cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&a->ev_pre, cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&a->ev_join_in, cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&a->ev_join_out, cudaEventDisableTiming) == cudaSuccess;
     for (int c = 0; ev_ok && c < a->nchunk; ++c)
         ev_ok = cudaEventCreateWithFlags(&a->ev_in[c], cudaEventDisableTiming) == cudaSuccess &&
                 cudaEventCreateWithFlags(&a->ev_mul[c], cudaEventDisableTiming) == cudaSuccess;
@@ -587,33 +591,80 @@ int rsg_matrix_spmv_host(rsg_handle_t h, rsg_matrix_t a, double alpha, const voi
         RSG_CUDA_TRY(cudaMemcpyAsync(ydst, a->y, xs * (size_t)a->m, cudaMemcpyDeviceToHost, st));
         RSG_CUDA_TRY(cudaStreamSynchronize(st));
     } else {
-        // s_in carries x upward piece by piece; the handle's stream multiplies chunk c once its prefix of x has landed.
-        // y: s_out copies chunk c's slice back while chunk c+1 is multiplied; with HOST_Y_DIRECT = 1 the kernels store
-        // straight into the page-locked host buffer instead (mapped memory; measured slower: tools/e2e_breakdown.py)
+        // s_in carries x upward piece by piece; s_main multiplies chunk c once its prefix of x has landed; s_out copies
+        // chunk c's slice of y back while chunk c+1 is multiplied (HOST_Y_DIRECT = 1: the kernels store straight into the
+        // page-locked host buffer instead -- measured slower, tools/e2e_breakdown.py).  The ~30 stream calls of one step
+        // are captured into a CUDA graph the second time the same buffers and alpha come by; later steps are one launch.
         const bool direct = h->opts[RSG_OPT_HOST_Y_DIRECT] == 1;
         void *ydev = a->y;
         if (direct && cudaHostGetDevicePointer(&ydev, ydst, 0) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
-        RSG_CUDA_TRY(cudaEventRecord(a->ev_start, st));
-        RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_in, a->ev_start, 0));
-        if (!direct) RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_out, a->ev_start, 0));
-        int rc = RSG_OK;
-        for (int c = 0; c < a->nchunk && rc == RSG_OK; ++c) {
-            const size_t x0 = (size_t)a->chunk_x[c], x1 = (size_t)a->chunk_x[c + 1];
-            if (x1 > x0) RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(a->x) + xs * x0, xsrc + xs * x0, xs * (x1 - x0), cudaMemcpyHostToDevice, a->s_in));
-            RSG_CUDA_TRY(cudaEventRecord(a->ev_in[c], a->s_in));
+        auto issue = [&]() -> int { // fork from s_main, join back into it
+            RSG_CUDA_TRY(cudaEventRecord(a->ev_start, a->s_main));
+            RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_in, a->ev_start, 0));
+            RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_out, a->ev_start, 0));
+            for (int c = 0; c < a->nchunk; ++c) {
+                const size_t x0 = (size_t)a->chunk_x[c], x1 = (size_t)a->chunk_x[c + 1];
+                if (x1 > x0) RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(a->x) + xs * x0, xsrc + xs * x0, xs * (x1 - x0), cudaMemcpyHostToDevice, a->s_in));
+                RSG_CUDA_TRY(cudaEventRecord(a->ev_in[c], a->s_in));
+            }
+            cudaStream_t keep = h->stream;
+            h->stream = a->s_main; // the SpMV launches go where the pipeline lives
+            int rc = RSG_OK;
+            for (int c = 0; c < a->nchunk && rc == RSG_OK; ++c) {
+                const int r0 = a->chunk_row[c], r1 = a->chunk_row[c + 1];
+                if (cudaStreamWaitEvent(a->s_main, a->ev_in[c], 0) != cudaSuccess) { rc = RSG_CUDA_ERROR; break; }
+                if (r1 > r0) rc = matrix_rows_spmv_any(h, a, r0, r1, alpha, 0.0, ydev);
+                if (direct || rc != RSG_OK) continue;
+                if (cudaEventRecord(a->ev_mul[c], a->s_main) != cudaSuccess || cudaStreamWaitEvent(a->s_out, a->ev_mul[c], 0) != cudaSuccess ||
+                    (r1 > r0 && cudaMemcpyAsync(ydst + xs * (size_t)r0, static_cast<char *>(a->y) + xs * (size_t)r0, xs * (size_t)(r1 - r0),
+                                                cudaMemcpyDeviceToHost, a->s_out) != cudaSuccess))
+                    rc = RSG_CUDA_ERROR;
+            }
+            h->stream = keep;
+            RSG_TRY(rc);
+            RSG_CUDA_TRY(cudaEventRecord(a->ev_join_in, a->s_in));
+            RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_main, a->ev_join_in, 0));
+            RSG_CUDA_TRY(cudaEventRecord(a->ev_join_out, a->s_out));
+            RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_main, a->ev_join_out, 0));
+            return RSG_OK;
+        };
+        // order the step after whatever the handle's stream still has in flight
+        RSG_CUDA_TRY(cudaEventRecord(a->ev_pre, st));
+        RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_main, a->ev_pre, 0));
+        int sig = (direct ? 1 : 0) + a->nchunk * 2;
+        for (int o = 0; o < RSG_OPT_COUNT_; ++o) sig = sig * 31 + h->opts[o];
+        sig = sig * 31 + (int)spmv_plans_freed(); // a freed plan may be one the captured kernels point into
+        const bool want_graph = h->opts[RSG_OPT_HOST_GRAPH] != 2;
+        const bool same_as_graph = a->graph && a->g_x == xsrc && a->g_y == ydst && a->g_alpha == alpha && a->g_sig == sig;
+        if (want_graph && !same_as_graph && a->seen_x == xsrc && a->seen_y == ydst && a->seen_alpha == alpha && a->seen_sig == sig) {
+            // second visit of these buffers: capture (every kernel involved has been launched once, plans exist)
+            if (a->graph) { cudaGraphExecDestroy(a->graph); a->graph = nullptr; }
+            cudaGraph_t graph = nullptr;
+            const long long before = h->launches;
+            if (cudaStreamBeginCapture(a->s_main, cudaStreamCaptureModeRelaxed) == cudaSuccess) {
+                const int rc = issue();
+                const cudaError_t e = cudaStreamEndCapture(a->s_main, &graph);
+                if (rc == RSG_OK && e == cudaSuccess && graph && cudaGraphInstantiate(&a->graph, graph, 0) == cudaSuccess) {
+                    a->g_x = xsrc; a->g_y = ydst; a->g_alpha = alpha; a->g_sig = sig;
+                    a->g_kernels = (int)(h->launches - before);
+                } else {
+                    (void)cudaGetLastError();
+                    a->graph = nullptr;
+                }
+                if (graph) cudaGraphDestroy(graph);
+            } else {
+                (void)cudaGetLastError();
+            }
+            h->launches = before; // captured, not run
         }
-        for (int c = 0; c < a->nchunk && rc == RSG_OK; ++c) {
-            const int r0 = a->chunk_row[c], r1 = a->chunk_row[c + 1];
-            RSG_CUDA_TRY(cudaStreamWaitEvent(st, a->ev_in[c], 0));
-            if (r1 > r0) rc = matrix_rows_spmv_any(h, a, r0, r1, alpha, 0.0, ydev);
-            if (direct) continue;
-            RSG_CUDA_TRY(cudaEventRecord(a->ev_mul[c], st));
-            RSG_CUDA_TRY(cudaStreamWaitEvent(a->s_out, a->ev_mul[c], 0));
-            if (r1 > r0) RSG_CUDA_TRY(cudaMemcpyAsync(ydst + xs * (size_t)r0, static_cast<char *>(a->y) + xs * (size_t)r0, xs * (size_t)(r1 - r0), cudaMemcpyDeviceToHost, a->s_out));
+        a->seen_x = xsrc; a->seen_y = ydst; a->seen_alpha = alpha; a->seen_sig = sig;
+        if (want_graph && a->graph && a->g_x == xsrc && a->g_y == ydst && a->g_alpha == alpha && a->g_sig == sig) {
+            RSG_CUDA_TRY(cudaGraphLaunch(a->graph, a->s_main));
+            h->launches += a->g_kernels;
+        } else {
+            RSG_TRY(issue());
         }
-        cudaError_t e1 = direct ? cudaSuccess : cudaStreamSynchronize(a->s_out), e2 = cudaStreamSynchronize(st), e3 = cudaStreamSynchronize(a->s_in);
-        RSG_TRY(rc);
-        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
+        if (cudaStreamSynchronize(a->s_main) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
     }
     if (!y_pinned) std::memcpy(y_host, a->pin_y, xs * (size_t)a->m);
     return RSG_OK;
@@ -633,7 +684,12 @@ int rsg_matrix_free(rsg_handle_t h, rsg_matrix_t a)
     if (a->pin_y) cudaFreeHost(a->pin_y);
     if (a->s_in) cudaStreamDestroy(a->s_in);
     if (a->s_out) cudaStreamDestroy(a->s_out);
+    if (a->s_main) cudaStreamDestroy(a->s_main);
+    if (a->graph) cudaGraphExecDestroy(a->graph);
     if (a->ev_start) cudaEventDestroy(a->ev_start);
+    if (a->ev_pre) cudaEventDestroy(a->ev_pre);
+    if (a->ev_join_in) cudaEventDestroy(a->ev_join_in);
+    if (a->ev_join_out) cudaEventDestroy(a->ev_join_out);
     for (int c = 0; c < rsg_matrix::kMaxChunks; ++c) {
         if (a->ev_in[c]) cudaEventDestroy(a->ev_in[c]);
         if (a->ev_mul[c]) cudaEventDestroy(a->ev_mul[c]);

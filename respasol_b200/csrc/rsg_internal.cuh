@@ -74,6 +74,7 @@ struct SpmvPlan {
     double *seg_part = nullptr;
     int *seg_cnt = nullptr;
     int nseg = 0, nlong = 0;
+    int lanes_hint = 0;        // tile kernel: 2 = the stage holds about half as many rows as the CTA has threads -> two lanes per row
     // merge-path kernel
     int merge_items = 0;   // rows+entries per CTA
     int ntiles = 0;
@@ -167,8 +168,13 @@ struct rsg_matrix {
     int nchunk;                   // 1 = not pipelined
     int chunk_row[kMaxChunks + 1]; // first row of every chunk
     int chunk_x[kMaxChunks + 1];   // chunk c may start once x[0 .. chunk_x[c+1]) is on the device (monotone)
-    cudaStream_t s_in, s_out;
-    cudaEvent_t ev_start, ev_in[kMaxChunks], ev_mul[kMaxChunks];
+    cudaStream_t s_in, s_out, s_main; // x upward, y downward, products (forked from / joined into s_main)
+    cudaEvent_t ev_start, ev_in[kMaxChunks], ev_mul[kMaxChunks], ev_pre, ev_join_in, ev_join_out;
+    // the whole pipelined step as one CUDA graph, captured on the second call with the same buffers and scalars
+    cudaGraphExec_t graph;
+    const void *g_x, *g_y, *seen_x, *seen_y;
+    double g_alpha, seen_alpha;
+    int g_sig, seen_sig, g_kernels;
 };
 
 namespace rsg {
@@ -179,6 +185,7 @@ int ensure_cub_tmp(rsg_context *h, size_t bytes);
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
                   bool force_rebuild, SpmvPlan **out, int vbytes = 8);
 void spmv_free_plan(SpmvPlan &p);
+long long spmv_plans_freed();
 template <typename TV, typename TX>
 int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
              const TV *values, TX alpha, const TX *x, TX beta, TX *y);

@@ -460,8 +460,12 @@ static const Variant kStreamVariants[] = {{256, 4096}, {128, 4096}, {128, 2048},
 static const int kNumStreamVariants = (int)(sizeof(kStreamVariants) / sizeof(kStreamVariants[0]));
 static constexpr int kStreamW = 2;
 
+static long long g_plans_freed = 0; // bumps whenever device arrays of a plan go away (captured graphs key on it)
+long long spmv_plans_freed() { return g_plans_freed; }
+
 void spmv_free_plan(SpmvPlan &p)
 {
+    ++g_plans_freed;
     cudaFree(p.blk_row); cudaFree(p.sblk); cudaFree(p.pdesc); cudaFree(p.rp0); cudaFree(p.seg); cudaFree(p.lrow); cudaFree(p.seg_part); cudaFree(p.seg_cnt); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
     p = SpmvPlan();
 }
@@ -470,7 +474,7 @@ static int plan_signature(const rsg_context *h)
 {
     return h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW] +
            h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD] * 7919 + h->opts[RSG_OPT_SPMV_REDUCE] * 104729 +
-           h->opts[RSG_OPT_SPMV_HALO_START] * 31;
+           h->opts[RSG_OPT_SPMV_HALO_START] * 31 + (h->opts[RSG_OPT_SPMV_X_HINT] == 4 ? 1299709 : 0);
 }
 
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,

@@ -472,6 +472,26 @@ __device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_
     }
 }
 
+// G lanes per row with the same unpredicated batches (lane l takes entries l, l+G, ...)
+template <typename TV, typename TX, int THREADS, int G, int B>
+__device__ __forceinline__ void reduce_rows_lean2g(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
+                                                   int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
+                                                   TX alpha, TX beta)
+{
+    constexpr int GROUPS = THREADS / G;
+    const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+    const TX *xb = x - base;
+    const int iters = (nrows + GROUPS - 1) / GROUPS;
+    for (int it = 0; it < iters; ++it) {
+        const int i = it * GROUPS + gid;
+        TX s = 0;
+        if (i < nrows) s = row_dot_lean2<TV, TX, G, B>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
+    }
+}
+
 template <typename TV, typename TX, int THREADS, int G>
 __device__ __forceinline__ void reduce_rows_lean(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
                                                  int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,

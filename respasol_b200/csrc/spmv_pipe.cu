@@ -95,13 +95,15 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
         }
         const int nrows = pe - cur;
         int g = reduce_opt & 0xff;
-        const int mode = reduce_opt >> 8; // RSG_OPT_SPMV_X_HINT on the tile kernel: 3 = the older software-prefetching inner loop (A/B)
+        const bool prefer2 = (reduce_opt >> 16) & 1; // plan: about threads/2 rows per tile
+        const int mode = (reduce_opt >> 8) & 0xff; // RSG_OPT_SPMV_X_HINT on the tile kernel: 3 = the older software-prefetching inner loop (A/B)
         if (g == 0) { // lanes per row from the tile's row-length statistics
             const int avg = (k1 - k0) / nrows;
             const int len = max(avg, mt.maxlen >> 3);
             g = len <= 40 ? 1 : len <= 80 ? 4 : len <= 160 ? 8 : len <= 320 ? 16 : 32;
             while (g < 32 && nrows * g * 2 <= NC) g <<= 1; // few rows: spread them over the CTA
             if (g == 2) g = (avg <= 40 && mt.maxlen <= 64) ? 1 : 4;
+            if (prefer2 && g == 1 && mt.maxlen <= 64 && nrows * 2 <= NC) g = 2;
         }
         const int *rp = s_rp + cur;
         if (LEAN) {
@@ -111,7 +113,10 @@ __device__ __forceinline__ void pipe_general_tile(unsigned char *sp, const PipeM
                 if (mode == 3) reduce_rows_lean<TV, TX, NC, 1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
                 else reduce_rows_lean2<TV, TX, NC, (sizeof(TX) == 4 ? 16 : 8)>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
                 break;
-            case 2: reduce_rows_lean<TV, TX, NC, 2>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
+            case 2:
+                if (mode == 3) reduce_rows_lean<TV, TX, NC, 2>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+                else reduce_rows_lean2g<TV, TX, NC, 2, 8>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+                break;
             case 4: reduce_rows_lean<TV, TX, NC, 4>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
             case 8: reduce_rows_lean<TV, TX, NC, 8>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
             case 16: reduce_rows_lean<TV, TX, NC, 16>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
@@ -474,6 +479,13 @@ int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split)
     if (rpt <= 0) rpt = 1;
     int lanes = h->opts[RSG_OPT_SPMV_REDUCE]; // forced lanes per row: size the tile for threads/lanes rows
     if (lanes < 1 || lanes > 32) lanes = 1;
+    if (p.algo == RSG_SPMV_TILE && h->opts[RSG_OPT_SPMV_REDUCE] == 0 && avg >= 12.0 && h->opts[RSG_OPT_SPMV_X_HINT] != 4) { // X_HINT 4: A/B switch
+        // rows the stage can hold vs threads of the CTA: config 2 in fp64 fits 66 rows of 27 entries under 128
+        // threads -- with one thread per row half the CTA idles.  Two lanes per row (tile sized for threads/2 rows)
+        // keeps every thread busy: 63.5 -> 61.4 us (tools/ab_option.py SPMV_REDUCE 0 2)
+        const double rows_fit = tmax / (avg + w);
+        if (v.threads / rows_fit >= 1.5 && v.threads / rows_fit < 3.0) { lanes = 2; p.lanes_hint = 2; }
+    }
     long long want = (long long)((avg + w) * (v.threads / lanes) * rpt + 0.5);
     int tile = (int)std::min<long long>(tmax, std::max<long long>(want, 512));
     if (h->opts[RSG_OPT_SPMV_LONG_ROW] > 0) tile = std::min(tmax, std::max(64, h->opts[RSG_OPT_SPMV_LONG_ROW]));
@@ -559,7 +571,7 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
     LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg};
     kern<<<p->nblk + fuse.ctas + ls.nseg, THREADS, smem, h->stream>>>(p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc,
-                                                                      p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE] | (h->opts[RSG_OPT_SPMV_X_HINT] << 8), h->wait_flags,
+                                                                      p->first + p->nnz, h->opts[RSG_OPT_SPMV_REDUCE] | (h->opts[RSG_OPT_SPMV_X_HINT] << 8) | (p->lanes_hint == 2 ? 1 << 16 : 0), h->wait_flags,
                                                                       h->wait_flags ? h->wait_n : 0, h->wait_epoch, fuse, ls);
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;

@@ -392,10 +392,26 @@ def test_pipelined_host_product(handle, name, chunks, direct):
             assert np.abs(y - ref).max() <= tol * np.abs(ref).max()
             xp = torch.from_numpy(x.astype(xt)).pin_memory()
             yp = torch.full((a.m,), float("nan"), dtype=xp.dtype).pin_memory()
-            for _ in range(3):  # repeated calls re-use streams / events
+            for _ in range(4):  # repeated calls re-use streams / events; from the second one on the step is a CUDA graph
                 yp.fill_(float("nan"))
                 handle.matrix_spmv_host(mat, xp.numpy(), yp.numpy())
                 assert np.abs(yp.numpy() - ref).max() <= tol * np.abs(ref).max()
+            # new x in the same buffer (graph replay reads the buffer, not a snapshot), then other buffers, then alpha
+            xp.mul_(-2.0)
+            handle.matrix_spmv_host(mat, xp.numpy(), yp.numpy())
+            assert np.abs(yp.numpy() + 2.0 * ref).max() <= 2 * tol * np.abs(ref).max()
+            xq = torch.from_numpy(x.astype(xt)).pin_memory()
+            yq = torch.zeros(a.m, dtype=xp.dtype).pin_memory()
+            for _ in range(3):
+                handle.matrix_spmv_host(mat, xq.numpy(), yq.numpy())
+                assert np.abs(yq.numpy() - ref).max() <= tol * np.abs(ref).max()
+            for _ in range(3):
+                handle.matrix_spmv_host(mat, xq.numpy(), yq.numpy(), alpha=0.5)
+                assert np.abs(yq.numpy() - 0.5 * ref).max() <= tol * np.abs(ref).max()
+            handle.set_option("HOST_GRAPH", 2)
+            handle.matrix_spmv_host(mat, xq.numpy(), yq.numpy())
+            handle.set_option("HOST_GRAPH", 0)
+            assert np.abs(yq.numpy() - ref).max() <= tol * np.abs(ref).max()
             # beta != 0 takes the one-piece path: y = 2 A x - 0.5 y0
             y0 = orc.dlarnv(a.m).astype(xt)
             yb = y0.copy()

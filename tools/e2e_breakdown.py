@@ -75,13 +75,14 @@ def main():
     out["d2h_us"] = wall(d2h, args.reps)
     out["h2d_and_d2h_concurrent_us"] = wall(both, args.reps)
     h = Handle(0)
-    for direct in (1, 0):
-        h.set_option("HOST_Y_DIRECT", direct)
+    for direct in (1, 0, 2):
+        h.set_option("HOST_Y_DIRECT", direct if direct < 2 else 0)
+        h.set_option("HOST_GRAPH", 2 if direct < 2 else 0)
         for chunks in (1, 2, 4, 6, 8, 12, 16, 32):
             h.set_option("HOST_CHUNKS", chunks)
             mat = h.matrix_upload(a, "d")
             xn, yn = xh.numpy(), yh.numpy()
-            out["spmv_host_%s_chunks_%d_us" % ("ydirect" if direct == 1 else "ycopy", chunks)] = wall(lambda: h.matrix_spmv_host(mat, xn, yn), args.reps)
+            out["spmv_host_%s_chunks_%d_us" % ({1: "ydirect", 0: "ycopy", 2: "ycopy_graph"}[direct], chunks)] = wall(lambda: h.matrix_spmv_host(mat, xn, yn), args.reps)
             h.matrix_free(mat)
     print(json.dumps(out, indent=1))
 
