@@ -36,10 +36,30 @@ extern "C" int cref_version(void) { return CUSPARSE_VERSION; }
 // prec: 0 = fp64, 1 = fp32.  alg: 0 default, 1 CSR_ALG1, 2 CSR_ALG2.  flush/flush_bytes: optional device
 // scratch written between repetitions (outside the event pair) so every product starts with a cold L2.
 // us[0] = mean, us[1] = median, us[2] = min over `reps` products (after `warm` untimed ones).
+static int spmv_any(int transpose, int prec, int alg, int m, int n, int nnz, const int *rowptr, const int *colidx,
+                    const void *values, const void *x, void *y, int warm, int reps, void *flush,
+                    size_t flush_bytes, float *us);
+
 extern "C" int cref_spmv(int prec, int alg, int m, int n, int nnz, const int *rowptr, const int *colidx,
                          const void *values, const void *x, void *y, int warm, int reps, void *flush,
                          size_t flush_bytes, float *us)
 {
+    return spmv_any(0, prec, alg, m, n, nnz, rowptr, colidx, values, x, y, warm, reps, flush, flush_bytes, us);
+}
+
+// y (n entries) = A^T x (m entries): CUSPARSE_OPERATION_TRANSPOSE of the same call group
+extern "C" int cref_spmv_t(int prec, int alg, int m, int n, int nnz, const int *rowptr, const int *colidx,
+                           const void *values, const void *x, void *y, int warm, int reps, void *flush,
+                           size_t flush_bytes, float *us)
+{
+    return spmv_any(1, prec, alg, m, n, nnz, rowptr, colidx, values, x, y, warm, reps, flush, flush_bytes, us);
+}
+
+static int spmv_any(int transpose, int prec, int alg, int m, int n, int nnz, const int *rowptr, const int *colidx,
+                    const void *values, const void *x, void *y, int warm, int reps, void *flush,
+                    size_t flush_bytes, float *us)
+{
+    const cusparseOperation_t op = transpose ? CUSPARSE_OPERATION_TRANSPOSE : CUSPARSE_OPERATION_NON_TRANSPOSE;
     cusparseHandle_t h;
     SP(cusparseCreate(&h));
     cudaDataType dt = prec ? CUDA_R_32F : CUDA_R_64F;
@@ -47,28 +67,28 @@ extern "C" int cref_spmv(int prec, int alg, int m, int n, int nnz, const int *ro
     cusparseDnVecDescr_t vx, vy;
     SP(cusparseCreateCsr(&A, m, n, nnz, (void *)rowptr, (void *)colidx, (void *)values, CUSPARSE_INDEX_32I,
                          CUSPARSE_INDEX_32I, CUSPARSE_INDEX_BASE_ZERO, dt));
-    SP(cusparseCreateDnVec(&vx, n, (void *)x, dt));
-    SP(cusparseCreateDnVec(&vy, m, y, dt));
+    SP(cusparseCreateDnVec(&vx, transpose ? m : n, (void *)x, dt));
+    SP(cusparseCreateDnVec(&vy, transpose ? n : m, y, dt));
     double ad = 1.0, bd = 0.0;
     float af = 1.0f, bf = 0.0f;
     const void *alpha = prec ? (const void *)&af : (const void *)&ad;
     const void *beta = prec ? (const void *)&bf : (const void *)&bd;
     cusparseSpMVAlg_t a = alg == 1 ? CUSPARSE_SPMV_CSR_ALG1 : alg == 2 ? CUSPARSE_SPMV_CSR_ALG2 : CUSPARSE_SPMV_ALG_DEFAULT;
     size_t bs = 0;
-    SP(cusparseSpMV_bufferSize(h, CUSPARSE_OPERATION_NON_TRANSPOSE, alpha, A, vx, beta, vy, dt, a, &bs));
+    SP(cusparseSpMV_bufferSize(h, op, alpha, A, vx, beta, vy, dt, a, &bs));
     void *buf = nullptr;
     CK(cudaMalloc(&buf, bs ? bs : 16));
-    SP(cusparseSpMV_preprocess(h, CUSPARSE_OPERATION_NON_TRANSPOSE, alpha, A, vx, beta, vy, dt, a, buf));
+    SP(cusparseSpMV_preprocess(h, op, alpha, A, vx, beta, vy, dt, a, buf));
     if (warm < 1 && reps < 1) warm = 1; // a plain product when no timing is asked for
     for (int i = 0; i < warm; ++i)
-        SP(cusparseSpMV(h, CUSPARSE_OPERATION_NON_TRANSPOSE, alpha, A, vx, beta, vy, dt, a, buf));
+        SP(cusparseSpMV(h, op, alpha, A, vx, beta, vy, dt, a, buf));
     CK(cudaDeviceSynchronize());
     std::vector<float> t(reps > 0 ? reps : 0);
     Timer tm;
     for (int i = 0; i < reps; ++i) {
         if (flush) CK(cudaMemsetAsync(flush, i & 0xff, flush_bytes, 0));
         tm.start();
-        SP(cusparseSpMV(h, CUSPARSE_OPERATION_NON_TRANSPOSE, alpha, A, vx, beta, vy, dt, a, buf));
+        SP(cusparseSpMV(h, op, alpha, A, vx, beta, vy, dt, a, buf));
         t[i] = tm.stop() * 1000.0f;
     }
     if (reps > 0 && us) {

@@ -53,6 +53,14 @@ def spmv_case(h, name, a, reps, flush, out):
             err = float((y - y_ref).abs().max() / y_ref.abs().max())
             row["rel_diff_vs_%s" % an] = err
             best = us[1] if best is None else min(best, us[1])
+        if prec == "d":  # the transposed product: ours (cached transposed pattern + value gather, deterministic) vs op = T
+            xt_ = torch.from_numpy(orc.dlarnv(a.m) - 0.5).cuda()
+            yt_ = torch.empty(a.n, dtype=torch.float64, device="cuda")
+            h.spmv_t(A, xt_, yt_)
+            row["transposed_ours_us_mean_med_min"] = time_ours(lambda: h.spmv_t(A, xt_, yt_), reps, flush)
+            yr_, ust = orc.cusparse_spmv(A, xt_, warm=5, reps=reps, flush=flush, transpose=True)
+            row["transposed_cusparse_us_mean_med_min"] = ust
+            row["transposed_rel_diff"] = float((yt_ - yr_).abs().max() / yr_.abs().max())
         row["ours_GBps"] = A.bytes() / ours[1] / 1e3
         row["cusparse_best_GBps"] = A.bytes() / best / 1e3
         row["speedup_vs_best_cusparse"] = best / ours[1]

@@ -152,6 +152,7 @@ def cusparse():
         _cus = C.CDLL(CUSPARSE_LIB)
         _cus.cref_spmv.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + \
             [C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        _cus.cref_spmv_t.argtypes = _cus.cref_spmv.argtypes
         _cus.cref_ilu0.argtypes = [C.c_int] * 4 + [C.c_void_p] * 5
         _cus.cref_spsv_lu.argtypes = [C.c_int] * 3 + [C.c_void_p] * 6 + [C.c_int, C.c_void_p]
     return _cus
@@ -162,13 +163,14 @@ def _cus_prec(t):
     return {torch.float64: 0, torch.float32: 1}[t.dtype]
 
 
-def cusparse_spmv(A, x, y=None, alg=0, warm=0, reps=0, flush=None):
-    """cusparseSpMV on a DeviceCSR ('d' or 's', base 0) -> (y, [mean, median, min] us or None)."""
+def cusparse_spmv(A, x, y=None, alg=0, warm=0, reps=0, flush=None, transpose=False):
+    """cusparseSpMV on a DeviceCSR ('d' or 's', base 0) -> (y, [mean, median, min] us or None); transpose: y = A^T x."""
     import torch
     assert A.base == 0 and A.values.dtype == x.dtype
-    y = torch.empty(A.m, dtype=x.dtype, device=x.device) if y is None else y
+    y = torch.empty(A.n if transpose else A.m, dtype=x.dtype, device=x.device) if y is None else y
     us = (C.c_float * 3)()
-    st = cusparse().cref_spmv(_cus_prec(x), alg, A.m, A.n, A.stored, A.rowptr.data_ptr(), A.colidx.data_ptr(),
+    fn = cusparse().cref_spmv_t if transpose else cusparse().cref_spmv
+    st = fn(_cus_prec(x), alg, A.m, A.n, A.stored, A.rowptr.data_ptr(), A.colidx.data_ptr(),
                               A.values.data_ptr(), x.data_ptr(), y.data_ptr(), warm, reps,
                               flush.data_ptr() if flush is not None else None,
                               flush.numel() * flush.element_size() if flush is not None else 0, us)

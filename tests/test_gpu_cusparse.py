@@ -157,3 +157,16 @@ def test_config2_full_size_matches_cusparse(handle):
         y = handle.spmv(A, x)
         y_ref, _ = orc.cusparse_spmv(A, x)
         assert float((y - y_ref).abs().max()) <= tol * float(y_ref.abs().max())
+
+
+@pytest.mark.parametrize("name", ["stencil27_40", "femlike_24", "powerlaw_20k"])
+def test_transposed_product_matches_cusparse(handle, name):
+    """spmv_csr_t_d/s against cusparseSpMV(CUSPARSE_OPERATION_TRANSPOSE) on the same arrays"""
+    a = SPMV_MATS[name]()
+    x64 = orc.dlarnv(a.m) - 0.5
+    for prec, tol in (("d", 1e-12), ("s", 3e-5)):
+        A = DeviceCSR(a, prec)
+        x = torch.from_numpy(x64).cuda().to(A.values.dtype)
+        y = handle.spmv_t(A, x)
+        y_ref, _ = orc.cusparse_spmv(A, x, transpose=True)
+        assert float((y - y_ref).abs().max()) <= tol * float(y_ref.abs().max())
