@@ -86,6 +86,12 @@ typedef enum {
                                    buffer (mapped memory, no D2H copy stage); 0 = device memory + async D2H copies (default) */
     RSG_OPT_HOST_GRAPH = 18,    /* pipelined host-vector product: 0/1 = replay the step from a CUDA graph once the same host buffers
                                    and alpha are seen twice (one launch call instead of ~30 stream calls); 2 = never */
+    RSG_OPT_TRANSPOSE_STATIC = 19, /* spmv_csr_t_*: 1 = the caller promises the values behind a given `values` pointer do not
+                                   change between calls (an iterative solver on a fixed matrix): the transposed copy is
+                                   gathered once per (pattern, values pointer, precision) and the product costs what the
+                                   untransposed one does; 0 = read the values through the cached permutation on every call
+                                   (default, always right: fused kernel, or gather + product when a column is longer
+                                   than 2048 entries); 2 = always gather + product (A/B) */
     RSG_OPT_COUNT_
 } rsg_option;
 
@@ -142,8 +148,8 @@ int rsg_csr2csc_s(rsg_handle_t handle, int m, int n, int nnz, int base, const in
                   const float *values, int *colptr, int *rowidx, float *values_out);
 /* y = alpha*A^T*x + beta*y (x has m entries, y has n): CUSPARSE_OPERATION_TRANSPOSE of the SpMV call group
  * (spmv.cu:184 passes NON_TRANSPOSE; this is the CSC product).  The transposed pattern is built once per matrix and
- * cached in the handle; the values are re-gathered on every call, then the ordinary SpMV kernels run on the
- * transposed pattern: deterministic, no atomics. */
+ * cached in the handle; the values are read through that permutation on every call (unless RSG_OPT_TRANSPOSE_STATIC = 1,
+ * see there): deterministic, no atomics. */
 int spmv_csr_t_d(rsg_handle_t handle, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
                  const double *values, double alpha, const double *x, double beta, double *y);
 int spmv_csr_t_s(rsg_handle_t handle, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,

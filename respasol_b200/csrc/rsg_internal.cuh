@@ -120,6 +120,9 @@ struct TransposePlan {
     int *rowidx = nullptr;    // nnz, carries the base
     int *perm = nullptr;      // nnz: entry (relative to `first`) that lands at k
     void *values_t = nullptr; // nnz * 8 bytes, re-gathered per product
+    const void *gathered_from = nullptr; // values pointer (and element size) values_t currently mirrors:
+    int gathered_size = 0;               // consulted only under RSG_OPT_TRANSPOSE_STATIC
+    int max_col = -1;                    // longest column of A (-1 unknown)
 };
 
 } // namespace rsg

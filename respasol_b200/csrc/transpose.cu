@@ -5,8 +5,11 @@
 // column indices (CUB) carrying the entry positions, so inside a column the entries keep their row order, which is
 // what the loader's per-row sort of the transposed matrix yields (bit-identical for matrices without duplicate
 // coordinates; tests/test_gpu_transpose.py).  The transposed product then runs the ordinary SpMV kernels on the
-// transposed pattern (deterministic, no atomics); the pattern and the permutation are cached per handle, the values
-// are re-gathered on every call because they may have changed (e.g. after a factorization).
+// transposed pattern (deterministic, no atomics); the pattern and the permutation are cached per handle.  The values
+// may have changed between calls (e.g. after a factorization), so by default they are read through the permutation
+// inside the product (spmv_t_fused_kernel) or, for patterns with long columns, re-gathered into a transposed copy on
+// every call -- unless the caller sets RSG_OPT_TRANSPOSE_STATIC = 1 and so promises they do not change: then the copy
+// is made once and the product is the tile kernel's.
 #include <cub/device/device_radix_sort.cuh>
 
 #include "rsg_internal.cuh"
@@ -53,6 +56,54 @@ template <typename T>
 __global__ void tr_gather_kernel(int nnz, const int *__restrict__ perm, const T *__restrict__ values, T *__restrict__ out)
 {
     for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < nnz; k += gridDim.x * blockDim.x) out[k] = values[perm[k]];
+}
+
+// y = alpha*A^T*x + beta*y with the values fetched THROUGH the permutation, so no transposed copy of them is written
+// and read back: per stored entry 4 B (row index) + 4 B (perm) + 8/4 B (value, each sector shared by the neighbouring
+// columns) instead of the 20 B gather pass + 12 B product.  G lanes per column of A, straight from global memory;
+// fixed summation order (lane-strided partial sums, xor tree), so the result is deterministic.  Only for patterns
+// whose longest column is short (a lane walks its share serially): the caller falls back to gather + tile kernel.
+template <typename T, int G>
+__global__ void __launch_bounds__(256)
+spmv_t_fused_kernel(int ncols, int base, const int *__restrict__ colptr, const int *__restrict__ rowidx, const int *__restrict__ perm,
+                    const T *__restrict__ values, const T *__restrict__ x, T *__restrict__ y, T alpha, T beta)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = t / G, lane = t % G;
+    T s = 0;
+    if (c < ncols) {
+        const int e = colptr[c + 1] - base;
+        int k = colptr[c] - base + lane;
+        for (; k + 3 * G < e; k += 4 * G) { // four independent entry chains in flight per lane
+            const int p0 = perm[k], p1 = perm[k + G], p2 = perm[k + 2 * G], p3 = perm[k + 3 * G];
+            const int r0 = rowidx[k] - base, r1 = rowidx[k + G] - base, r2 = rowidx[k + 2 * G] - base, r3 = rowidx[k + 3 * G] - base;
+            const T a0 = __ldg(values + p0), a1 = __ldg(values + p1), a2 = __ldg(values + p2), a3 = __ldg(values + p3);
+            const T x0 = __ldg(x + r0), x1 = __ldg(x + r1), x2 = __ldg(x + r2), x3 = __ldg(x + r3);
+            s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+        }
+        if (k < e) { // the tail as one predicated batch, so its loads overlap as well
+            int pp[4], rr[4];
+            T aa[4], xx[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool ok = k + j * G < e;
+                pp[j] = ok ? perm[k + j * G] : 0;
+                rr[j] = ok ? rowidx[k + j * G] - base : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool ok = k + j * G < e;
+                aa[j] = ok ? __ldg(values + pp[j]) : (T)0;
+                xx[j] = ok ? __ldg(x + rr[j]) : (T)0;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (k + j * G < e) s += aa[j] * xx[j];
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (c < ncols && lane == 0) y[c] = (beta == (T)0) ? alpha * s : alpha * s + beta * y[c];
 }
 
 void transpose_free_plan(TransposePlan &p)
@@ -137,6 +188,8 @@ int csr2csc_run(rsg_context *h, int m, int n, int base, const int *rowptr, const
     return rc;
 }
 
+constexpr int kFusedMaxColumn = 2048; // longest column the fused kernel takes (a lane walks column/G entries serially)
+
 template <typename T>
 int spmv_transposed_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx, const T *values,
                         T alpha, const T *x, T beta, T *y)
@@ -158,14 +211,42 @@ int spmv_transposed_run(rsg_context *h, int m, int n, int nnz_hint, int base, co
         }
         const int rc = build_transpose(h, m, n, q.nnz, q.first, base, rowptr, colidx, q.colptr, q.rowidx, q.perm);
         if (rc != RSG_OK) { transpose_free_plan(q); return rc; }
+        if (q.nnz > 0) { // longest column of A, from the SpMV plan of the transposed pattern (built here, used by the fallback)
+            SpmvPlan *sp = nullptr;
+            const int rc2 = spmv_get_plan(h, n, m, q.nnz, base, q.colptr, q.rowidx, false, &sp, (int)sizeof(T));
+            q.max_col = rc2 == RSG_OK ? sp->max_row : -1;
+        }
         h->transpose_plans.push_back(q);
         p = &h->transpose_plans.back();
     }
     if (p->nnz > 0) {
         if (!values) return RSG_BAD_ARG;
-        tr_gather_kernel<T><<<std::min((p->nnz + 255) / 256, h->sm_count * 16), 256, 0, h->stream>>>(p->nnz, p->perm, values + p->first,
-                                                                                                   static_cast<T *>(p->values_t));
-        h->launches++;
+        const int mode = h->opts[RSG_OPT_TRANSPOSE_STATIC];
+        if (mode == 0 && p->max_col >= 0 && p->max_col <= kFusedMaxColumn && !h->wait_flags && !h->fuse.ctas) {
+            const double avg = (double)p->nnz / std::max(n, 1);
+            int lanes = h->opts[RSG_OPT_SPMV_REDUCE];
+            if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32)
+                lanes = avg <= 8 ? 1 : avg <= 14 ? 2 : avg <= 56 ? 4 : avg <= 160 ? 8 : avg <= 512 ? 16 : 32;
+            const int threads = 256;
+#define RSG_TF(G)                                                                                                   \
+    spmv_t_fused_kernel<T, G><<<(int)(((long long)n * G + threads - 1) / threads), threads, 0, h->stream>>>(          \
+        n, base, p->colptr, p->rowidx, p->perm, values + p->first, x, y, alpha, beta)
+            if (lanes == 1) RSG_TF(1); else if (lanes == 2) RSG_TF(2); else if (lanes == 4) RSG_TF(4); else if (lanes == 8) RSG_TF(8); else if (lanes == 16) RSG_TF(16); else RSG_TF(32);
+#undef RSG_TF
+            h->launches++;
+            h->last_spmv_algo = RSG_SPMV_VECTOR;
+            h->last_spmv_maxrow = p->max_col;
+            RSG_CUDA_TRY(cudaGetLastError());
+            return RSG_OK;
+        }
+        const bool fresh = mode == 1 && p->gathered_from == values && p->gathered_size == (int)sizeof(T);
+        if (!fresh) {
+            tr_gather_kernel<T><<<std::min((p->nnz + 255) / 256, h->sm_count * 16), 256, 0, h->stream>>>(
+                p->nnz, p->perm, values + p->first, static_cast<T *>(p->values_t));
+            h->launches++;
+            p->gathered_from = values;
+            p->gathered_size = (int)sizeof(T);
+        }
     }
     // A^T is n x m: its "rows" are A's columns
     return spmv_run<T, T>(h, n, m, p->nnz, base, p->colptr, p->rowidx, static_cast<const T *>(p->values_t), alpha, x, beta, y);

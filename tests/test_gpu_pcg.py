@@ -4,6 +4,8 @@ Dot products are summed in a different order on the GPU, so the iterates agree t
 count must match the oracle's within one, the solutions to 1e-6 relative (rtol is 1e-9), and the TRUE residual
 |b - A x| / |b| must meet 10 rtol.  The preconditioned runs must take fewer iterations than the plain one, and the
 fp32-factor run (mixed precision, the reference README's theme) about as many as the fp64-factor run."""
+import ctypes as C
+
 import numpy as np
 import pytest
 import torch
@@ -145,3 +147,32 @@ def test_bicgstab_config3_full_size(handle):
         assert float((x - torch.from_numpy(xs).cuda()).abs().max()) <= 1e-7
         its[pre] = it
     assert abs(its["d"] - its["s"]) <= 3
+
+
+@pytest.mark.parametrize("solver", ["pcg", "bicgstab"])
+def test_krylov_edge_cases(handle, solver):
+    from respasol_b200.gpu import RsgError
+    run = getattr(handle, solver)
+    # empty system: nothing to do, no device work
+    e = host.CSR(0, 0, 0, np.zeros(1, np.int32), np.zeros(0, np.int32), np.zeros(0))
+    E = DeviceCSR(e, "d")
+    l0 = handle.info("KERNEL_LAUNCHES")
+    x, it, rel = run(E, torch.zeros(0, dtype=torch.float64, device="cuda"))
+    assert it == 0 and rel == 0.0 and handle.info("KERNEL_LAUNCHES") == l0
+    # zero right-hand side with a zero initial guess: converged before the first iteration
+    a = sym_femlike(8) if solver == "pcg" else host.gen_femlike(8)
+    A = DeviceCSR(a, "d")
+    x, it, rel = run(A, torch.zeros(a.m, dtype=torch.float64, device="cuda"))
+    assert it == 0 and rel == 0.0 and float(x.abs().max()) == 0.0
+    # max_iters = 0: the initial residual is reported, x untouched
+    b = torch.from_numpy(orc.dlarnv(a.m)).cuda()
+    x, it, rel = run(A, b, max_iters=0)
+    assert it == 0 and abs(rel - 1.0) <= 1e-14 and float(x.abs().max()) == 0.0
+    # a precision letter the interface does not know
+    it_c, rel_c = C.c_int(0), C.c_double(0.0)
+    fn = getattr(handle.lib, "rsg_%s_d" % solver)
+    st = fn(handle.h, A.m, A.stored, A.base, handle._p(A.rowptr), handle._p(A.colidx), handle._p(A.values), handle._p(A.values),
+            ord("q"), handle._p(b), handle._p(x), 5, 1e-8, C.byref(it_c), C.byref(rel_c))
+    assert st == 1  # RSG_BAD_ARG
+    with pytest.raises(RsgError):
+        run(A, b, max_iters=-1)

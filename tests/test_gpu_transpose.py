@@ -95,3 +95,70 @@ def test_transpose_config2_full_size(handle):
     At.uid = DeviceCSR._next_uid
     rp2, ci2, v2 = handle.csr2csc(At)
     assert torch.equal(rp2, A.rowptr) and torch.equal(ci2, A.colidx) and torch.equal(v2, A.values)
+
+
+def test_transposed_product_value_modes(handle):
+    """RSG_OPT_TRANSPOSE_STATIC: 0 = values read through the permutation inside the product (one launch), 2 = gather +
+    product (two launches), 1 = the caller promises static values: gathered once per (pattern, values pointer), then one
+    launch.  All three agree to rounding, each is deterministic, and modes 0 / 2 see a change of the values."""
+    a = host.gen_stencil27(24, seed=5)
+    A = DeviceCSR(a, "d")
+    x = torch.from_numpy(orc.dlarnv(a.m) - 0.5).cuda()
+    scale = 1e-13 * float(handle.spmv_t(A, x).abs().max())
+
+    def run(mode, M=A):
+        handle.set_option("TRANSPOSE_STATIC", mode)
+        try:
+            l0 = handle.info("KERNEL_LAUNCHES")
+            y = handle.spmv_t(M, x).clone()
+            return y, handle.info("KERNEL_LAUNCHES") - l0
+        finally:
+            handle.set_option("TRANSPOSE_STATIC", 0)
+    y0, n0 = run(0)
+    y0b, _ = run(0)
+    y2, n2 = run(2)
+    y1, _ = run(1)
+    y1b, n1 = run(1)
+    assert n0 == 1 and n2 == 2 and n1 == 1
+    assert torch.equal(y0, y0b) and torch.equal(y1, y1b) and torch.equal(y1, y2)   # 1 and 2 run the same product kernel
+    assert float((y0 - y2).abs().max()) <= scale
+    B = DeviceCSR(a, "d")                     # another values pointer on another pattern: gathered afresh under mode 1
+    B.values.mul_(4.0)                        # a power of two: the scaled product is exact
+    assert torch.equal(run(1, B)[0], 4.0 * y1)
+    A.values.mul_(2.0)
+    assert torch.equal(run(0)[0], 2.0 * y0) and torch.equal(run(2)[0], 2.0 * y2)
+    # a pattern with a column too long for the fused kernel (the transpose of a matrix with two 5000-entry rows) falls back
+    # to gather + product on its own
+    import scipy.sparse as sp
+    p = host.gen_powerlaw(6000, 2.2, 48, 2, 5000, 4)
+    S = sp.csr_matrix((p.values, p.colidx.astype(np.int64) - p.base, p.rowptr.astype(np.int64) - p.base), shape=(p.m, p.n))
+    St = S.T.tocsr()
+    St.sort_indices()
+    q = host.CSR(p.n, p.m, St.nnz, St.indptr.astype(np.int32), St.indices.astype(np.int32), St.data.copy(), 0)
+    Q = DeviceCSR(q, "d")
+    xq = torch.from_numpy(orc.dlarnv(q.m) - 0.5).cuda()
+    handle.spmv_t(Q, xq)                      # builds the plans
+    l0 = handle.info("KERNEL_LAUNCHES")
+    yq = handle.spmv_t(Q, xq)
+    assert handle.info("KERNEL_LAUNCHES") - l0 >= 2 and handle.info("SPMV_MAX_ROW") >= 5000
+    ref = orc.spmv(p, xq.cpu().numpy(), "d")  # (S^T)^T x = S x
+    assert np.abs(yq.cpu().numpy() - ref).max() <= 1e-12 * np.abs(ref).max()
+
+
+def test_transpose_edge_cases(handle):
+    # no stored entries: A^T x = 0 (or beta*y), csr2csc gives an all-base colptr
+    e = host.CSR(3, 5, 0, np.zeros(4, np.int32), np.zeros(0, np.int32), np.zeros(0))
+    E = DeviceCSR(e, "d")
+    x = torch.ones(3, dtype=torch.float64, device="cuda")
+    y = torch.full((5,), 7.0, dtype=torch.float64, device="cuda")
+    out = handle.spmv_t(E, x, y, alpha=1.0, beta=0.5)
+    assert torch.equal(out.cpu(), torch.full((5,), 3.5, dtype=torch.float64))
+    colptr, rowidx, vals = handle.csr2csc(E)
+    assert colptr.cpu().tolist() == [0] * 6 and rowidx.numel() == 0 and vals.numel() == 0
+    # one-based, rectangular, a single row
+    r = host.CSR(1, 4, 3, np.array([1, 4], np.int32), np.array([1, 3, 4], np.int32), np.array([2.0, -1.0, 4.0]), 1)
+    R = DeviceCSR(r, "d")
+    out = handle.spmv_t(R, torch.tensor([3.0], dtype=torch.float64, device="cuda"))
+    assert out.cpu().tolist() == [6.0, 0.0, -3.0, 12.0]
+    colptr, rowidx, vals = handle.csr2csc(R)
+    assert colptr.cpu().tolist() == [1, 2, 2, 3, 4] and rowidx.cpu().tolist() == [1, 1, 1] and vals.cpu().tolist() == [2.0, -1.0, 4.0]
