@@ -383,21 +383,50 @@ __global__ void spmv_scalar_kernel(int m, int base, const int *__restrict__ rowp
     store_y(y, r, s, alpha, beta);
 }
 
+// G lanes per row straight from global memory.  Entries are taken in batches of four per lane (all index loads, then
+// all value / x loads, then the multiply-adds), the tail as one predicated batch, so a lane keeps eight gathers in
+// flight instead of two; summation order is fixed (lane-strided partial sums, xor tree).
 template <typename TV, typename TX, int G>
-__global__ void spmv_vector_kernel(int m, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
-                                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y,
-                                   TX alpha, TX beta)
+__global__ void __launch_bounds__(256)
+spmv_vector_kernel(int m, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
+                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta)
 {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int r = t / G, lane = t % G;
     TX s = 0;
-    if (r < m)
-        for (int k = rowptr[r] - base + lane; k < rowptr[r + 1] - base; k += G)
-            s += (TX)values[k] * __ldg(x + (colidx[k] - base));
+    if (r < m) {
+        const int e = rowptr[r + 1] - base;
+        int k = rowptr[r] - base + lane;
+        for (; k + 3 * G < e; k += 4 * G) {
+            const int c0 = colidx[k] - base, c1 = colidx[k + G] - base, c2 = colidx[k + 2 * G] - base, c3 = colidx[k + 3 * G] - base;
+            const TX a0 = (TX)values[k], a1 = (TX)values[k + G], a2 = (TX)values[k + 2 * G], a3 = (TX)values[k + 3 * G];
+            const TX x0 = __ldg(x + c0), x1 = __ldg(x + c1), x2 = __ldg(x + c2), x3 = __ldg(x + c3);
+            s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+        }
+        if (k < e) {
+            int cc[4];
+            TX aa[4], xx[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool ok = k + j * G < e;
+                cc[j] = ok ? colidx[k + j * G] - base : 0;
+                aa[j] = ok ? (TX)values[k + j * G] : (TX)0;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) xx[j] = (k + j * G < e) ? __ldg(x + cc[j]) : (TX)0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (k + j * G < e) s += aa[j] * xx[j];
+        }
+    }
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
     if (r < m && lane == 0) store_y(y, r, s, alpha, beta);
 }
+
+// lanes per row of the VECTOR kernel by average row length (measured: profiles/r1_vector_lanes_sweep.txt -- fewer
+// lanes than entries/4 would suggest: what counts is gathers in flight per lane, and each lane batches four entries)
+static inline int vector_lanes(double avg) { return avg <= 15.5 ? 2 : avg <= 34 ? 4 : avg <= 128 ? 8 : avg <= 512 ? 16 : 32; }
 
 // ------------------------------------------------------------------ statistics
 // out[0] = max row length, out[1] = rowptr[0], out[2] = rowptr[m]
@@ -539,12 +568,19 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         if (algo == RSG_SPMV_TILE) {
             const double avg = (double)p.nnz / std::max(m, 1);
             variant = avg < 12.0 ? 9 : (vbytes >= 8 ? 0 : 1);
-            // Rows of some length whose neighbours gather from unrelated x lines (hashed / badly ordered columns):
-            // thread-per-row gathers out of a staged tile no longer coalesce, and what helps is L1 capacity for x --
-            // the plain sub-warp-per-row kernel uses no shared memory and leaves all 228 KB to L1 (1.7-2.5x on the
-            // banded stand-ins of the 36-matrix sweep, profiles/r1_bench_spmv_sweep.*).  Not with dense rows (one
-            // sub-warp would crawl through them) and not when tiles must wait on halo flags.
-            if (scatter > 0.5 && avg >= 16.0 && p.max_row <= 4096 && h->opts[RSG_OPT_SPMV_HALO_START] == 0) algo = RSG_SPMV_VECTOR;
+            // Two cases go to the plain sub-warp-per-row kernel instead (batched loads, no shared memory, so all 228 KB
+            // of the SM stay L1 for x; profiles/r1_vector_lanes_sweep.txt, profiles/r1_auto_vs_vector.txt):
+            //  * rows whose neighbours gather from unrelated x lines (hashed / badly ordered columns): thread-per-row
+            //    gathers out of a staged tile no longer coalesce and L1 capacity for x is what helps (1.7-2.5x on the
+            //    banded stand-ins of the 36-matrix sweep);
+            //  * small matrices (a few MB, L2-resident after the first product): the tile kernel's per-CTA set-up
+            //    (barrier, bulk copies, a 512-row stage) is a visible part of a 10 us product (config 3: 11.9 -> 10.5 us).
+            // Not with dense rows (a lane walks its share of the row serially: the kernel widens to at most 32 lanes)
+            // and not when tiles must wait on halo flags.
+            const int vl = vector_lanes(avg);
+            const bool no_halo = h->opts[RSG_OPT_SPMV_HALO_START] == 0;
+            const int longest_ok = (scatter > 0.5 && avg >= 16.0) ? 4096 : 128 * vl;
+            if (no_halo && (scatter > 0.5 || p.nnz < 4500000) && p.max_row <= longest_ok) algo = RSG_SPMV_VECTOR;
         }
     }
     if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)
@@ -758,12 +794,24 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
         RSG_TRY((launch_merge<TV, TX>(h, p, vec, values, alpha, x, beta, y)));
         break;
     case RSG_SPMV_VECTOR: {
-        const int avg = p->nnz / std::max(m, 1);
+        const double avg = (double)p->nnz / std::max(m, 1);
         const int threads = 256;
 #define RSG_VEC(G)                                                                                          \
     spmv_vector_kernel<TV, TX, G><<<(int)(((long long)m * G + threads - 1) / threads), threads, 0, h->stream>>>( \
         m, base, rowptr, colidx, values, x, y, alpha, beta)
-        if (avg <= 6) RSG_VEC(4); else if (avg <= 24) RSG_VEC(8); else if (avg <= 64) RSG_VEC(16); else RSG_VEC(32);
+        int lanes = h->opts[RSG_OPT_SPMV_REDUCE]; // 0 = by row lengths; a power of two forces it (A/B)
+        if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32) {
+            lanes = vector_lanes(avg);
+            while (lanes < 32 && p->max_row > 128 * lanes) lanes *= 2; // the longest row bounds a lane's serial walk
+        }
+        switch (lanes) {
+        case 1: RSG_VEC(1); break;
+        case 2: RSG_VEC(2); break;
+        case 4: RSG_VEC(4); break;
+        case 8: RSG_VEC(8); break;
+        case 16: RSG_VEC(16); break;
+        default: RSG_VEC(32); break;
+        }
 #undef RSG_VEC
         h->last_spmv_blocks = 0;
         h->launches++;

@@ -349,18 +349,25 @@ def test_too_many_long_rows_fall_back_to_merge_path(handle):
 
 
 def test_auto_picks_the_unstaged_kernel_for_scattered_columns(handle):
-    """Rows of some length whose neighbours gather unrelated x lines (hashed columns inside a band) take the plain
-    sub-warp-per-row kernel (all of L1 for x); orderings with neighbour coherence and short or dense rows stay tiled."""
+    """Rows whose neighbours gather unrelated x lines (hashed columns inside a band) take the plain sub-warp-per-row
+    kernel (all of L1 for x), and so do small matrices without dense rows (the tile kernel's per-CTA set-up shows in a
+    10 us product); large matrices with neighbour coherence and anything with dense rows stay tiled."""
     x_of = lambda a: orc.dlarnv(a.n) - 0.5
     a = host.gen_banded(60000, 40, 6000)
     for p in ("d", "s", "m"):
         check(handle, a, x_of(a), p)
         assert handle.info("SPMV_ALGO_USED") == ALGO["vector"]
     check(handle, a, x_of(a), "d", alpha=-0.5, beta=2.0, y0=orc.dlarnv(a.m))
-    for b in (host.gen_stencil27(30, seed=2), host.gen_femlike(24), host.gen_banded(60000, 8, 6000),
-              host.gen_powerlaw(60000, 2.2, 64, 3, 20000, 4)):
+    for b in (host.gen_stencil27(30, seed=2), host.gen_femlike(24), host.gen_banded(60000, 8, 6000)):
+        check(handle, b, x_of(b), "d")
+        assert handle.info("SPMV_ALGO_USED") == ALGO["vector"]
+    for b in (host.gen_stencil27(60, seed=2), host.gen_laplace2d(1000), host.gen_powerlaw(60000, 2.2, 64, 3, 20000, 4)):
         check(handle, b, x_of(b), "d")
         assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+    # one row far longer than the rest in a small matrix: the sub-warp kernel would crawl through it
+    c = host.gen_powerlaw(20000, 2.2, 48, 1, 3000, 4)
+    check(handle, c, x_of(c), "d")
+    assert handle.info("SPMV_ALGO_USED") == ALGO["tile"] and handle.info("SPMV_MAX_ROW") >= 3000
 
 
 PIPE_MATS = {
