@@ -386,7 +386,7 @@ __global__ void spmv_scalar_kernel(int m, int base, const int *__restrict__ rowp
 // G lanes per row straight from global memory.  Entries are taken in batches of four per lane (all index loads, then
 // all value / x loads, then the multiply-adds), the tail as one predicated batch, so a lane keeps eight gathers in
 // flight instead of two; summation order is fixed (lane-strided partial sums, xor tree).
-template <typename TV, typename TX, int G>
+template <typename TV, typename TX, int G, int B>
 __global__ void __launch_bounds__(256)
 spmv_vector_kernel(int m, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
                    const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta)
@@ -397,25 +397,29 @@ spmv_vector_kernel(int m, int base, const int *__restrict__ rowptr, const int *_
     if (r < m) {
         const int e = rowptr[r + 1] - base;
         int k = rowptr[r] - base + lane;
-        for (; k + 3 * G < e; k += 4 * G) {
-            const int c0 = colidx[k] - base, c1 = colidx[k + G] - base, c2 = colidx[k + 2 * G] - base, c3 = colidx[k + 3 * G] - base;
-            const TX a0 = (TX)values[k], a1 = (TX)values[k + G], a2 = (TX)values[k + 2 * G], a3 = (TX)values[k + 3 * G];
-            const TX x0 = __ldg(x + c0), x1 = __ldg(x + c1), x2 = __ldg(x + c2), x3 = __ldg(x + c3);
-            s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+        for (; k + (B - 1) * G < e; k += B * G) {
+            int cc[B];
+            TX aa[B], xx[B];
+#pragma unroll
+            for (int j = 0; j < B; ++j) { cc[j] = colidx[k + j * G] - base; aa[j] = (TX)values[k + j * G]; }
+#pragma unroll
+            for (int j = 0; j < B; ++j) xx[j] = __ldg(x + cc[j]);
+#pragma unroll
+            for (int j = 0; j < B; ++j) s += aa[j] * xx[j];
         }
         if (k < e) {
-            int cc[4];
-            TX aa[4], xx[4];
+            int cc[B];
+            TX aa[B], xx[B];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < B; ++j) {
                 const bool ok = k + j * G < e;
                 cc[j] = ok ? colidx[k + j * G] - base : 0;
                 aa[j] = ok ? (TX)values[k + j * G] : (TX)0;
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) xx[j] = (k + j * G < e) ? __ldg(x + cc[j]) : (TX)0;
+            for (int j = 0; j < B; ++j) xx[j] = (k + j * G < e) ? __ldg(x + cc[j]) : (TX)0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int j = 0; j < B; ++j)
                 if (k + j * G < e) s += aa[j] * xx[j];
         }
     }
@@ -580,7 +584,7 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
             const int vl = vector_lanes(avg);
             const bool no_halo = h->opts[RSG_OPT_SPMV_HALO_START] == 0;
             const int longest_ok = (scatter > 0.5 && avg >= 16.0) ? 4096 : 128 * vl;
-            if (no_halo && (scatter > 0.5 || p.nnz < 4500000) && p.max_row <= longest_ok) algo = RSG_SPMV_VECTOR;
+            if (no_halo && (scatter > 0.5 || p.nnz < 4500000) && p.max_row <= longest_ok) { algo = RSG_SPMV_VECTOR; variant = 0; }
         }
     }
     if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)
@@ -796,9 +800,16 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     case RSG_SPMV_VECTOR: {
         const double avg = (double)p->nnz / std::max(m, 1);
         const int threads = 256;
-#define RSG_VEC(G)                                                                                          \
-    spmv_vector_kernel<TV, TX, G><<<(int)(((long long)m * G + threads - 1) / threads), threads, 0, h->stream>>>( \
+#define RSG_VEC_B(G, B)                                                                                        \
+    spmv_vector_kernel<TV, TX, G, B><<<(int)(((long long)m * G + threads - 1) / threads), threads, 0, h->stream>>>( \
         m, base, rowptr, colidx, values, x, y, alpha, beta)
+#define RSG_VEC(G)                                                                                             \
+    do {                                                                                                       \
+        if (vb == 8) RSG_VEC_B(G, 8); else if (vb == 2) RSG_VEC_B(G, 2); else RSG_VEC_B(G, 4);                  \
+    } while (0)
+        // entries per lane and batch: 8 with 4-byte x (45.0 vs 51.6 us on config 2), 4 with 8-byte x (64.6 vs 67.8 us);
+        // RSG_OPT_SPMV_VARIANT 1 / 2 / 3 force 8 / 2 / 4 (profiles/r1_vector_batch_lanes.txt)
+        const int vb = p->variant == 1 ? 8 : p->variant == 2 ? 2 : p->variant == 3 ? 4 : (sizeof(TX) == 4 ? 8 : 4);
         int lanes = h->opts[RSG_OPT_SPMV_REDUCE]; // 0 = by row lengths; a power of two forces it (A/B)
         if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32) {
             lanes = vector_lanes(avg);
@@ -812,6 +823,7 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
         case 16: RSG_VEC(16); break;
         default: RSG_VEC(32); break;
         }
+#undef RSG_VEC_B
 #undef RSG_VEC
         h->last_spmv_blocks = 0;
         h->launches++;

@@ -63,7 +63,7 @@ __global__ void tr_gather_kernel(int nnz, const int *__restrict__ perm, const T 
 // columns) instead of the 20 B gather pass + 12 B product.  G lanes per column of A, straight from global memory;
 // fixed summation order (lane-strided partial sums, xor tree), so the result is deterministic.  Only for patterns
 // whose longest column is short (a lane walks its share serially): the caller falls back to gather + tile kernel.
-template <typename T, int G>
+template <typename T, int G, int B>
 __global__ void __launch_bounds__(256)
 spmv_t_fused_kernel(int ncols, int base, const int *__restrict__ colptr, const int *__restrict__ rowidx, const int *__restrict__ perm,
                     const T *__restrict__ values, const T *__restrict__ x, T *__restrict__ y, T alpha, T beta)
@@ -74,30 +74,33 @@ spmv_t_fused_kernel(int ncols, int base, const int *__restrict__ colptr, const i
     if (c < ncols) {
         const int e = colptr[c + 1] - base;
         int k = colptr[c] - base + lane;
-        for (; k + 3 * G < e; k += 4 * G) { // four independent entry chains in flight per lane
-            const int p0 = perm[k], p1 = perm[k + G], p2 = perm[k + 2 * G], p3 = perm[k + 3 * G];
-            const int r0 = rowidx[k] - base, r1 = rowidx[k + G] - base, r2 = rowidx[k + 2 * G] - base, r3 = rowidx[k + 3 * G] - base;
-            const T a0 = __ldg(values + p0), a1 = __ldg(values + p1), a2 = __ldg(values + p2), a3 = __ldg(values + p3);
-            const T x0 = __ldg(x + r0), x1 = __ldg(x + r1), x2 = __ldg(x + r2), x3 = __ldg(x + r3);
-            s += a0 * x0; s += a1 * x1; s += a2 * x2; s += a3 * x3;
+        for (; k + (B - 1) * G < e; k += B * G) { // B independent entry chains in flight per lane
+            int pp[B], rr[B];
+            T aa[B], xx[B];
+#pragma unroll
+            for (int j = 0; j < B; ++j) { pp[j] = perm[k + j * G]; rr[j] = rowidx[k + j * G] - base; }
+#pragma unroll
+            for (int j = 0; j < B; ++j) { aa[j] = __ldg(values + pp[j]); xx[j] = __ldg(x + rr[j]); }
+#pragma unroll
+            for (int j = 0; j < B; ++j) s += aa[j] * xx[j];
         }
         if (k < e) { // the tail as one predicated batch, so its loads overlap as well
-            int pp[4], rr[4];
-            T aa[4], xx[4];
+            int pp[B], rr[B];
+            T aa[B], xx[B];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < B; ++j) {
                 const bool ok = k + j * G < e;
                 pp[j] = ok ? perm[k + j * G] : 0;
                 rr[j] = ok ? rowidx[k + j * G] - base : 0;
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < B; ++j) {
                 const bool ok = k + j * G < e;
                 aa[j] = ok ? __ldg(values + pp[j]) : (T)0;
                 xx[j] = ok ? __ldg(x + rr[j]) : (T)0;
             }
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
+            for (int j = 0; j < B; ++j)
                 if (k + j * G < e) s += aa[j] * xx[j];
         }
     }
@@ -229,7 +232,7 @@ int spmv_transposed_run(rsg_context *h, int m, int n, int nnz_hint, int base, co
                 lanes = avg <= 8 ? 1 : avg <= 14 ? 2 : avg <= 56 ? 4 : avg <= 160 ? 8 : avg <= 512 ? 16 : 32;
             const int threads = 256;
 #define RSG_TF(G)                                                                                                   \
-    spmv_t_fused_kernel<T, G><<<(int)(((long long)n * G + threads - 1) / threads), threads, 0, h->stream>>>(          \
+    spmv_t_fused_kernel<T, G, (sizeof(T) == 4 ? 8 : 4)><<<(int)(((long long)n * G + threads - 1) / threads), threads, 0, h->stream>>>(          \
         n, base, p->colptr, p->rowidx, p->perm, values + p->first, x, y, alpha, beta)
             if (lanes == 1) RSG_TF(1); else if (lanes == 2) RSG_TF(2); else if (lanes == 4) RSG_TF(4); else if (lanes == 8) RSG_TF(8); else if (lanes == 16) RSG_TF(16); else RSG_TF(32);
 #undef RSG_TF

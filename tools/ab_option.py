@@ -22,8 +22,11 @@ ap.add_argument("b", type=int)
 ap.add_argument("--configs", default="C2")
 ap.add_argument("--prec", default="d,s")
 ap.add_argument("--reps", type=int, default=300)
+ap.add_argument("--set", default="", help="fixed options for both arms: NAME=VAL,NAME=VAL")
 args = ap.parse_args()
 h = Handle(0)
+for kv in filter(None, args.set.split(",")):
+    h.set_option(kv.split("=")[0], int(kv.split("=")[1]))
 for cname in args.configs.split(","):
     a = matrix(cname)
     x = orc.dlarnv(a.n) - 0.5
