@@ -577,14 +577,16 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
             //  * rows whose neighbours gather from unrelated x lines (hashed / badly ordered columns): thread-per-row
             //    gathers out of a staged tile no longer coalesce and L1 capacity for x is what helps (1.7-2.5x on the
             //    banded stand-ins of the 36-matrix sweep);
-            //  * small matrices (a few MB, L2-resident after the first product): the tile kernel's per-CTA set-up
-            //    (barrier, bulk copies, a 512-row stage) is a visible part of a 10 us product (config 3: 11.9 -> 10.5 us).
+            //  * matrices whose entries fit in half of L2 (resident after the first product of a solver loop): the tile
+            //    kernel's per-CTA set-up (barrier, bulk copies, a 512-row stage) is a visible part of a 10-20 us product
+            //    (config 3: 11.9 -> 10.5 us cold; warm, 5-point 1000x1000: 18.5 -> 14.4 us).
             // Not with dense rows (a lane walks its share of the row serially: the kernel widens to at most 32 lanes)
             // and not when tiles must wait on halo flags.
             const int vl = vector_lanes(avg);
             const bool no_halo = h->opts[RSG_OPT_SPMV_HALO_START] == 0;
             const int longest_ok = (scatter > 0.5 && avg >= 16.0) ? 4096 : 128 * vl;
-            if (no_halo && (scatter > 0.5 || p.nnz < 4500000) && p.max_row <= longest_ok) { algo = RSG_SPMV_VECTOR; variant = 0; }
+            const bool l2_resident = (long long)p.nnz * (vbytes + 4) < (64LL << 20); // entries in half of the 126 MB L2
+            if (no_halo && (scatter > 0.5 || l2_resident) && p.max_row <= longest_ok) { algo = RSG_SPMV_VECTOR; variant = 0; }
         }
     }
     if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)
@@ -809,12 +811,13 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     } while (0)
         // entries per lane and batch: 8 with 4-byte x (45.0 vs 51.6 us on config 2), 4 with 8-byte x (64.6 vs 67.8 us);
         // RSG_OPT_SPMV_VARIANT 1 / 2 / 3 force 8 / 2 / 4 (profiles/r1_vector_batch_lanes.txt)
-        const int vb = p->variant == 1 ? 8 : p->variant == 2 ? 2 : p->variant == 3 ? 4 : (sizeof(TX) == 4 ? 8 : 4);
         int lanes = h->opts[RSG_OPT_SPMV_REDUCE]; // 0 = by row lengths; a power of two forces it (A/B)
         if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32) {
             lanes = vector_lanes(avg);
             while (lanes < 32 && p->max_row > 128 * lanes) lanes *= 2; // the longest row bounds a lane's serial walk
         }
+        // a batch of 8 only pays when a lane has more than 4 entries to take (5-point rows, fp32: 16.4 us with 4, 18.5 with 8)
+        const int vb = p->variant == 1 ? 8 : p->variant == 2 ? 2 : p->variant == 3 ? 4 : (sizeof(TX) == 4 && avg > 4.0 * lanes ? 8 : 4);
         switch (lanes) {
         case 1: RSG_VEC(1); break;
         case 2: RSG_VEC(2); break;
