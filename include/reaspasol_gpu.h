@@ -229,6 +229,16 @@ int rsg_bicgstab_d(rsg_handle_t handle, int n, int nnz, int base, const int *row
                    const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
                    int *iters, double *relres);
 
+/* Restarted flexible GMRES(30) (Saad & Schultz 1986; the preconditioned basis is kept, so fp32 factors cost no
+ * accuracy), right-preconditioned by the same ILU(0) factors, modified Gram-Schmidt.
+ * Same arguments and stopping rule as rsg_pcg_d; an iteration is one Arnoldi step = 1 SpMV + 1 preconditioner
+ * application + (j+2) fused subtract-and-dot launches at step j of the cycle; the host reads the Hessenberg column
+ * once per step; *relres is the rotated right-hand side's residual estimate (the true residual is recomputed at
+ * each restart).  No counterpart in the reference (README.md:5-7 names the use only); SURVEY.md 8f-2. */
+int rsg_gmres_d(rsg_handle_t handle, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                int *iters, double *relres);
+
 /* ---- host-pointer convenience wrappers (allocate, H2D, run, D2H, free; synchronous) ------- */
 int spmv_csr_d_host(rsg_handle_t handle, int m, int n, int nnz, int base,
                     const int *rowptr, const int *colidx, const double *values,

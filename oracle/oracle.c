@@ -441,3 +441,85 @@ int orc_bicgstab_d(int n, int base, const int *rowptr, const int *colidx, const 
     free(r); free(rh); free(p); free(v); free(y); free(z); free(t); free(a32); free(b32); free(c32);
     return it;
 }
+
+/* ---------------------------------------------------------------- GMRES ---
+ * Restarted flexible GMRES(30) with right preconditioning K = LU (Saad & Schultz 1986; Saad, Iterative Methods,
+ * Alg. 9.6: the preconditioned basis Z is kept, so an fp32 preconditioner -- not a linear operator once its input is
+ * rounded -- costs no accuracy), modified Gram-Schmidt, Givens rotations on the host-size Hessenberg matrix; checker of rsg_gmres_d.  One
+ * iteration = one Arnoldi step; |r| is the rotated right-hand side's last entry, the true residual is recomputed
+ * at every restart.  The reference has no Krylov loop (README.md:5-7 names the use only). */
+#define ORC_GMRES_RESTART 30
+int orc_gmres_d(int n, int base, const int *rowptr, const int *colidx, const double *values,
+                const void *lu, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                double *relres)
+{
+    enum { R = ORC_GMRES_RESTART };
+    const size_t nd = (size_t)n + 1;
+    double *V = malloc(sizeof(double) * nd * (R + 1)), *w = malloc(sizeof(double) * nd), *Z = malloc(sizeof(double) * nd * R),
+           *t = malloc(sizeof(double) * nd);
+    float *a32 = malloc(sizeof(float) * nd), *b32 = malloc(sizeof(float) * nd), *c32 = malloc(sizeof(float) * nd);
+    double H[R + 1][R], cs[R], sn[R], g[R + 1], yv[R];
+    double bb = orc_dot(n, b, b), rr = 0;
+    if (!(bb > 0)) bb = 1.0;
+    const double stop = rtol * rtol * bb;
+    int it = 0;
+    for (;;) {
+        orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, x, 0.0, w);
+        for (int i = 0; i < n; ++i) V[i] = b[i] - w[i];
+        rr = orc_dot(n, V, V);
+        if (!(rr > stop) || !isfinite(rr) || it >= max_iters) break;
+        const double inv0 = 1.0 / sqrt(rr);
+        for (int i = 0; i < n; ++i) V[i] *= inv0;
+        g[0] = sqrt(rr);
+        for (int i = 1; i <= R; ++i) g[i] = 0;
+        int k = 0;
+        for (int j = 0; j < R && it < max_iters; ++j) {
+            double *vj = V + nd * j;
+            double *z = Z + nd * j; /* flexible variant: z_j = K^-1 v_j is kept, x += Z y */
+            orc_apply_prec(n, base, rowptr, colidx, lu, lu_precision, vj, z, t, a32, b32, c32);
+            orc_spmv_csr_d(n, base, rowptr, colidx, values, 1.0, z, 0.0, w);
+            for (int i = 0; i <= j; ++i) {
+                const double *vi = V + nd * i;
+                const double h = orc_dot(n, w, vi);
+                H[i][j] = h;
+                for (int q = 0; q < n; ++q) w[q] = fma(-h, vi[q], w[q]);
+            }
+            const double ww = orc_dot(n, w, w), hn = sqrt(ww);
+            for (int i = 0; i < j; ++i) {
+                const double tmp = cs[i] * H[i][j] + sn[i] * H[i + 1][j];
+                H[i + 1][j] = -sn[i] * H[i][j] + cs[i] * H[i + 1][j];
+                H[i][j] = tmp;
+            }
+            const double d = hypot(H[j][j], hn);
+            if (d == 0) break;
+            cs[j] = H[j][j] / d;
+            sn[j] = hn / d;
+            H[j][j] = d;
+            g[j + 1] = -sn[j] * g[j];
+            g[j] = cs[j] * g[j];
+            ++it;
+            k = j + 1;
+            rr = g[j + 1] * g[j + 1];
+            if (!(rr > stop) || !isfinite(rr) || hn == 0) break;
+            if (j + 1 < R && it < max_iters) {
+                const double inv = 1.0 / sqrt(ww);
+                double *vn = V + nd * (j + 1);
+                for (int q = 0; q < n; ++q) vn[q] = w[q] * inv;
+            }
+        }
+        for (int i = k - 1; i >= 0; --i) {
+            double s = g[i];
+            for (int q = i + 1; q < k; ++q) s -= H[i][q] * yv[q];
+            yv[i] = s / H[i][i];
+        }
+        for (int q = 0; q < n; ++q) {
+            double s = 0;
+            for (int i = 0; i < k; ++i) s = fma(yv[i], Z[nd * i + q], s);
+            x[q] += s;
+        }
+        if (!(rr > stop) || !isfinite(rr) || it >= max_iters || k == 0) break;
+    }
+    if (relres) *relres = sqrt(rr / bb);
+    free(V); free(w); free(Z); free(t); free(a32); free(b32); free(c32);
+    return it;
+}

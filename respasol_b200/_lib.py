@@ -73,6 +73,7 @@ GPU_SYMBOLS = {
     "rsg_matrix_free": (_I, [_P, _P]),
     "rsg_pcg_d": (_I, _TRI_ARGS + [_P, _P, _I, _P, _P, _I, _D, c_int_p, C.POINTER(_D)]),
     "rsg_bicgstab_d": (_I, _TRI_ARGS + [_P, _P, _I, _P, _P, _I, _D, c_int_p, C.POINTER(_D)]),
+    "rsg_gmres_d": (_I, _TRI_ARGS + [_P, _P, _I, _P, _P, _I, _D, c_int_p, C.POINTER(_D)]),
     "rsg_halo_push": (_I, [_P, _I, _I, _P, _P, _I, _P, _P, _I]),
     "rsg_spmv_halo_wait": (_I, [_P, _P, _I, _I]),
     "rsg_spmv_halo_fuse": (_I, [_P, _I, _P, _I, _P, _P, _I]),

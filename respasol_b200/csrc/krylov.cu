@@ -191,6 +191,45 @@ __global__ void __launch_bounds__(kVecThreads) widen_kernel(int n, const float *
     for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) b[i] = (double)a[i];
 }
 
+// ---- GMRES(30): modified Gram-Schmidt step.  w -= h_prev v_prev (when v_prev);  out = w . v_next (v_next == w: |w|^2).
+// One launch per basis vector: the subtraction of vector i-1 rides on the pass that takes the dot with vector i.
+// (w and v_next may alias: no __restrict__ on them.)
+__global__ void __launch_bounds__(kVecThreads) gmres_mgs_kernel(int n, const double *h_prev, const double *v_prev, const double *v_next,
+                                                                double *w, double *partials, unsigned *ticket, double *out)
+{
+    const double hp = v_prev ? *h_prev : 0.0;
+    const bool norm = v_next == w;
+    double s = 0;
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        double wi = w[i];
+        if (v_prev) { wi = fma(-hp, v_prev[i], wi); w[i] = wi; }
+        s = fma(wi, norm ? wi : v_next[i], s);
+    }
+    finish_dot(s, partials, ticket, out);
+}
+
+// v = w / sqrt(*ww)  (v32 = (float) v; v may be w)
+__global__ void __launch_bounds__(kVecThreads) gmres_scale_kernel(int n, const double *ww, const double *w, double *v, float *__restrict__ v32)
+{
+    const double inv = 1.0 / sqrt(*ww);
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        const double vi = w[i] * inv;
+        v[i] = vi;
+        if (v32) v32[i] = (float)vi;
+    }
+}
+
+// x += sum_j y[j] Z_j
+__global__ void __launch_bounds__(kVecThreads) gmres_update_x_kernel(int n, int k, const double *__restrict__ y, const double *__restrict__ Z,
+                                                                     size_t ld, double *__restrict__ x)
+{
+    for (int i = blockIdx.x * kVecThreads + threadIdx.x; i < n; i += gridDim.x * kVecThreads) {
+        double s = 0;
+        for (int j = 0; j < k; ++j) s = fma(y[j], Z[(size_t)j * ld + i], s);
+        x[i] += s;
+    }
+}
+
 } // namespace rsg
 
 using namespace rsg;
@@ -373,6 +412,140 @@ extern "C" int rsg_bicgstab_d(rsg_handle_t h, int n, int nnz, int base, const in
         rr = pin[B_RR];
         ++it;
     }
+    RSG_CUDA_TRY(cudaGetLastError());
+    if (iters) *iters = it;
+    if (relres) *relres = std::sqrt(rr / bb);
+    return std::isfinite(rr) ? RSG_OK : RSG_BREAKDOWN;
+}
+
+// Restarted flexible GMRES(kGmresRestart), right-preconditioned (Saad & Schultz 1986; Saad Alg. 9.6): the preconditioned
+// vectors z_j = K^-1 v_j are kept and x += Z y, so fp32 factors (whose input is rounded) cost no accuracy.  Both bases stay in HBM; the Hessenberg
+// column of one Arnoldi step is built on the device by j+2 fused subtract-and-dot launches and read back in ONE copy; the
+// Givens rotations and the small triangular solve run on the host.
+static constexpr int kGmresRestart = 30;
+
+extern "C" int rsg_gmres_d(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                           const void *lu_values, int lu_precision, const double *b, double *x, int max_iters, double rtol,
+                           int *iters, double *relres)
+{
+    if (!h || n < 0 || !rowptr || (n > 0 && (!b || !x || !values)) || max_iters < 0 ||
+        (lu_precision != 0 && lu_precision != 'd' && lu_precision != 's') || (lu_precision != 0 && !lu_values))
+        return RSG_BAD_ARG;
+    if (iters) *iters = 0;
+    if (relres) *relres = 0.0;
+    if (n == 0) return RSG_OK;
+    constexpr int R = kGmresRestart;
+    Guard g(h->device);
+    cudaStream_t st = h->stream;
+    const bool pre = lu_precision != 0, pre32 = lu_precision == 's';
+    const size_t nd = ((size_t)n + 3) & ~(size_t)3;
+    // workspace: bases V (R+1 vectors) and Z (R), w, t (fp64), three fp32 vectors, Hessenberg column, y, partials, scalars, ticket
+    RSG_TRY(krylov_workspace(h, nd * 8 * (2 * R + 3) + nd * 4 * 3 + (size_t)(2 * R + 4) * 8 + kWsTail));
+    char *w_ = static_cast<char *>(h->krylov_ws);
+    double *V = reinterpret_cast<double *>(w_); w_ += nd * 8 * (R + 1);
+    double *w = reinterpret_cast<double *>(w_); w_ += nd * 8;
+    double *Z = reinterpret_cast<double *>(w_); w_ += nd * 8 * R;
+    double *t = reinterpret_cast<double *>(w_); w_ += nd * 8;
+    float *in32 = reinterpret_cast<float *>(w_); w_ += nd * 4;
+    float *out32 = reinterpret_cast<float *>(w_); w_ += nd * 4;
+    float *tmp32 = reinterpret_cast<float *>(w_); w_ += nd * 4;
+    double *hcol = reinterpret_cast<double *>(w_); w_ += (R + 2) * 8;
+    double *ycoef = reinterpret_cast<double *>(w_); w_ += (R + 2) * 8;
+    double *partials = reinterpret_cast<double *>(w_); w_ += 2 * kMaxVecBlocks * 8;
+    double *scal = reinterpret_cast<double *>(w_); w_ += S_COUNT * 8;
+    unsigned *ticket = reinterpret_cast<unsigned *>(w_);
+    RSG_CUDA_TRY(cudaMemsetAsync(scal, 0, S_COUNT * 8 + 64, st));
+    const int grid = std::max(1, std::min(kMaxVecBlocks, std::min(h->sm_count * 8, (n + kVecThreads * 4 - 1) / (kVecThreads * 4))));
+    struct Pinned {
+        double *p = nullptr;
+        ~Pinned() { if (p) cudaFreeHost(p); }
+    } pin;
+    if (cudaMallocHost(&pin.p, sizeof(double) * (2 * R + 4)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+    double *ph = pin.p, *py = pin.p + R + 2;
+
+    auto precondition = [&](const double *in, double *out) -> int { // in32 already holds (float) in with fp32 factors
+        if (!pre) { RSG_CUDA_TRY(cudaMemcpyAsync(out, in, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st)); return RSG_OK; }
+        if (pre32) {
+            RSG_TRY(sptrsv_lu_s(h, n, nnz, base, rowptr, colidx, static_cast<const float *>(lu_values), in32, tmp32, out32));
+            widen_kernel<<<grid, kVecThreads, 0, st>>>(n, out32, out);
+            h->launches++;
+            return RSG_OK;
+        }
+        return sptrsv_lu_d(h, n, nnz, base, rowptr, colidx, static_cast<const double *>(lu_values), in, t, out);
+    };
+
+    double H[R + 1][R], cs[R], sn[R], gv[R + 1], yv[R];
+    dot_kernel<<<grid, kVecThreads, 0, st>>>(n, b, b, partials, ticket, scal + S_BB);
+    h->launches++;
+    double bb = 1.0, stop = 0.0, rr = 0.0;
+    int it = 0;
+    bool first = true;
+    for (;;) {
+        // true residual at every (re)start: V_0 = b - A x
+        RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, x, 0.0, w));
+        residual_kernel<<<grid, kVecThreads, 0, st>>>(n, b, w, V);
+        dot_kernel<<<grid, kVecThreads, 0, st>>>(n, V, V, partials, ticket, hcol);
+        h->launches += 2;
+        RSG_CUDA_TRY(cudaMemcpyAsync(ph, hcol, sizeof(double), cudaMemcpyDeviceToHost, st));
+        if (first) RSG_CUDA_TRY(cudaMemcpyAsync(ph + 1, scal + S_BB, sizeof(double), cudaMemcpyDeviceToHost, st));
+        RSG_CUDA_TRY(cudaStreamSynchronize(st));
+        if (first) { bb = ph[1] > 0 ? ph[1] : 1.0; stop = rtol * rtol * bb; first = false; }
+        rr = ph[0];
+        if (!(rr > stop) || !std::isfinite(rr) || it >= max_iters) break;
+        gmres_scale_kernel<<<grid, kVecThreads, 0, st>>>(n, hcol, V, V, pre32 ? in32 : nullptr);
+        h->launches++;
+        gv[0] = std::sqrt(rr);
+        for (int i = 1; i <= R; ++i) gv[i] = 0;
+        int k = 0;
+        for (int j = 0; j < R && it < max_iters; ++j) {
+            double *vj = V + nd * (size_t)j, *z = Z + nd * (size_t)j;
+            RSG_TRY(precondition(vj, z));
+            RSG_TRY(spmv_csr_d(h, n, n, nnz, base, rowptr, colidx, values, 1.0, z, 0.0, w));
+            for (int i = 0; i <= j; ++i)
+                gmres_mgs_kernel<<<grid, kVecThreads, 0, st>>>(n, i ? hcol + i - 1 : nullptr, i ? V + nd * (size_t)(i - 1) : nullptr,
+                                                               V + nd * (size_t)i, w, partials, ticket, hcol + i);
+            gmres_mgs_kernel<<<grid, kVecThreads, 0, st>>>(n, hcol + j, vj, w, w, partials, ticket, hcol + j + 1);
+            h->launches += j + 2;
+            RSG_CUDA_TRY(cudaMemcpyAsync(ph, hcol, sizeof(double) * (size_t)(j + 2), cudaMemcpyDeviceToHost, st));
+            RSG_CUDA_TRY(cudaStreamSynchronize(st));
+            for (int i = 0; i <= j; ++i) H[i][j] = ph[i];
+            const double hn = std::sqrt(ph[j + 1]);
+            for (int i = 0; i < j; ++i) {
+                const double tmp = cs[i] * H[i][j] + sn[i] * H[i + 1][j];
+                H[i + 1][j] = -sn[i] * H[i][j] + cs[i] * H[i + 1][j];
+                H[i][j] = tmp;
+            }
+            const double d = std::hypot(H[j][j], hn);
+            if (d == 0) break;
+            cs[j] = H[j][j] / d;
+            sn[j] = hn / d;
+            H[j][j] = d;
+            gv[j + 1] = -sn[j] * gv[j];
+            gv[j] = cs[j] * gv[j];
+            ++it;
+            k = j + 1;
+            rr = gv[j + 1] * gv[j + 1];
+            if (!(rr > stop) || !std::isfinite(rr) || hn == 0) break;
+            if (j + 1 < R && it < max_iters) {
+                gmres_scale_kernel<<<grid, kVecThreads, 0, st>>>(n, hcol + j + 1, w, V + nd * (size_t)(j + 1), pre32 ? in32 : nullptr);
+                h->launches++;
+            }
+        }
+        // x += Z y,  H y = g
+        for (int i = k - 1; i >= 0; --i) {
+            double s = gv[i];
+            for (int q = i + 1; q < k; ++q) s -= H[i][q] * yv[q];
+            yv[i] = s / H[i][i];
+        }
+        if (k > 0) {
+            for (int i = 0; i < k; ++i) py[i] = yv[i];
+            RSG_CUDA_TRY(cudaMemcpyAsync(ycoef, py, sizeof(double) * (size_t)k, cudaMemcpyHostToDevice, st));
+            gmres_update_x_kernel<<<grid, kVecThreads, 0, st>>>(n, k, ycoef, Z, nd, x);
+            h->launches++;
+        }
+        if (!(rr > stop) || !std::isfinite(rr) || it >= max_iters || k == 0) break;
+    }
+    RSG_CUDA_TRY(cudaStreamSynchronize(st));
     RSG_CUDA_TRY(cudaGetLastError());
     if (iters) *iters = it;
     if (relres) *relres = std::sqrt(rr / bb);

@@ -231,6 +231,10 @@ class Handle:
         """rsg_bicgstab_d: like pcg, for matrices that are not symmetric positive definite."""
         return self.pcg(A, b, x, lu, max_iters, rtol, _fn="rsg_bicgstab_d")
 
+    def gmres(self, A: DeviceCSR, b, x=None, lu=None, max_iters=1000, rtol=1e-8):
+        """rsg_gmres_d: restarted GMRES(30), right-preconditioned; an iteration is one Arnoldi step."""
+        return self.pcg(A, b, x, lu, max_iters, rtol, _fn="rsg_gmres_d")
+
     def pcg(self, A: DeviceCSR, b, x=None, lu=None, max_iters=1000, rtol=1e-8, _fn="rsg_pcg_d"):
         """rsg_pcg_d: A (fp64 DeviceCSR) x = b, preconditioned by ILU(0) factors `lu` (fp64 or fp32 tensor, or None).
         Returns (x, iterations, relative residual)."""

@@ -204,6 +204,11 @@ def bicgstab(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8):
     return pcg(a, b, lu, x0, max_iters, rtol, _fn="orc_bicgstab_d")
 
 
+def gmres(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8):
+    """oracle GMRES(30) (oracle.c: orc_gmres_d), same conventions as pcg; an iteration is one Arnoldi step"""
+    return pcg(a, b, lu, x0, max_iters, rtol, _fn="orc_gmres_d")
+
+
 def pcg(a, b, lu=None, x0=None, max_iters=1000, rtol=1e-8, _fn="orc_pcg_d"):
     """oracle PCG (oracle.c: orc_pcg_d) -> (x, iterations, relres); lu: None | fp64 | fp32 ILU(0) factor values"""
     x = np.zeros(a.m) if x0 is None else np.array(x0, dtype=np.float64)

@@ -149,7 +149,59 @@ def test_bicgstab_config3_full_size(handle):
     assert abs(its["d"] - its["s"]) <= 3
 
 
-@pytest.mark.parametrize("solver", ["pcg", "bicgstab"])
+@pytest.mark.parametrize("name", sorted(NONSYM))
+def test_gmres_matches_oracle(handle, name):
+    """Flexible GMRES(30): same Arnoldi steps as the oracle (dot products summed in a different, fixed order), so the
+    iteration counts agree to +-2, the solutions to 1e-6 and the true residual meets the bound; several restarts without
+    a preconditioner."""
+    a = NONSYM[name]()
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n) - 0.5
+    b = orc.spmv(a, xs, "d")
+    bd = torch.from_numpy(b).cuda()
+    rtol = 1e-9
+    iters = {}
+    for pre in (None, "d", "s"):
+        lu = lu_ref = None
+        if pre:
+            F = DeviceCSR(a, pre)
+            st, _ = handle.ilu0_factor(F)
+            assert st == 0
+            lu = F.values
+            lu_ref = orc.ilu0(a, np.float64 if pre == "d" else np.float32)[2]
+        x, it, rel = handle.gmres(A, bd, lu=lu, max_iters=2000, rtol=rtol)
+        x_ref, it_ref, rel_ref = orc.gmres(a, b, lu_ref, max_iters=2000, rtol=rtol)
+        assert it < 2000 and it_ref < 2000 and abs(it - it_ref) <= 2, (pre, it, it_ref)
+        assert rel <= rtol
+        xh = x.cpu().numpy()
+        assert np.abs(xh - x_ref).max() <= 1e-6 * np.abs(x_ref).max()
+        assert np.linalg.norm(b - orc.spmv(a, xh, "d")) / np.linalg.norm(b) <= 10 * rtol
+        iters[pre] = it
+    assert iters["d"] < iters[None] and iters["s"] <= iters["d"] + 2
+    # iteration cap inside a cycle: x carries the partial cycle, the estimate is the true residual
+    x7, it7, rel7 = handle.gmres(A, bd, max_iters=7, rtol=rtol)
+    assert it7 == 7 and 0 < rel7 < 1
+    assert abs(np.linalg.norm(b - orc.spmv(a, x7.cpu().numpy(), "d")) / np.linalg.norm(b) - rel7) <= 1e-9
+
+
+def test_gmres_config3_full_size(handle):
+    """config 3 as generated: ILU(0)-preconditioned flexible GMRES(30), fp64 and fp32 factors, reaches 1e-10."""
+    a = host.gen_femlike(47, 0.58, 3)
+    A = DeviceCSR(a, "d")
+    xs = orc.dlarnv(a.n) - 0.5
+    b = torch.from_numpy(orc.spmv(a, xs, "d")).cuda()
+    its = {}
+    for pre in ("d", "s"):
+        F = DeviceCSR(a, pre)
+        handle.ilu0_factor(F)
+        x, it, rel = handle.gmres(A, b, lu=F.values, max_iters=500, rtol=1e-10)
+        assert rel <= 1e-10 and it < 500
+        assert float((x - torch.from_numpy(xs).cuda()).abs().max()) <= 1e-7
+        its[pre] = it
+    assert abs(its["d"] - its["s"]) <= 2
+
+
+@pytest.mark.parametrize("solver", ["pcg", "bicgstab", "gmres"])
 def test_krylov_edge_cases(handle, solver):
     from respasol_b200.gpu import RsgError
     run = getattr(handle, solver)

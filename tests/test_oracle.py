@@ -177,3 +177,32 @@ def test_oracle_bicgstab_solves_unsymmetric_systems():
         assert rel <= 1e-11 and np.abs(x - x_direct).max() <= 1e-8 * np.abs(x_direct).max()
         its[pre] = it
     assert its[np.float64] < its[None] and its[np.float32] <= its[np.float64] + 3
+
+
+def test_oracle_gmres_solves_unsymmetric_systems():
+    """orc_gmres_d (restarted GMRES(30), right-preconditioned) against a sparse direct solve and scipy's own GMRES;
+    enough iterations without a preconditioner to go through several restarts."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    from respasol_b200 import host
+    a = host.gen_femlike(12)
+    M = sp.csr_matrix((a.values, a.colidx, a.rowptr), shape=(a.m, a.n))
+    b = orc.dlarnv(a.m) - 0.5
+    x_direct = spl.spsolve(M.tocsc(), b)
+    its = {}
+    for pre in (None, np.float64, np.float32):
+        lu = None if pre is None else orc.ilu0(a, pre)[2]
+        x, it, rel = orc.gmres(a, b, lu, rtol=1e-11)
+        assert rel <= 1e-11 and np.abs(x - x_direct).max() <= 1e-8 * np.abs(x_direct).max(), (pre, it, rel)
+        assert np.linalg.norm(b - M @ x) <= 1e-10 * np.linalg.norm(b)
+        its[pre] = it
+    assert its[np.float64] < its[None] and its[np.float32] <= its[np.float64] + 2
+    # iteration cap: the estimate after exactly 7 Arnoldi steps, x updated with the partial cycle
+    x7, it7, rel7 = orc.gmres(a, b, None, max_iters=7, rtol=1e-11)
+    assert it7 == 7 and 0 < rel7 < 1
+    assert abs(np.linalg.norm(b - M @ x7) / np.linalg.norm(b) - rel7) <= 1e-10
+    # scipy's GMRES(30) without a preconditioner takes the same number of inner steps to the same tolerance (+-2)
+    cnt = [0]
+    spl.gmres(M, b, rtol=1e-11, atol=0.0, restart=30, maxiter=100, callback=lambda r: cnt.__setitem__(0, cnt[0] + 1),
+              callback_type="pr_norm")
+    assert abs(cnt[0] - its[None]) <= 2, (cnt[0], its[None])
