@@ -175,6 +175,9 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        # the box sets NCCL_DEBUG=VERSION, which prints a banner on STDOUT ahead of the JSON line: keep stdout to the one line
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            del os.environ["NCCL_DEBUG"]  # WARN and above print the banner too
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus or world == 1 and args.gpus == 1, "launch with torchrun --nproc-per-node N for --gpus N"
 
