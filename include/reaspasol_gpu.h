@@ -26,6 +26,8 @@
  *     (the analogue of dBuffer / pBuffer, spmv.cu:164, ilu0.cu:193-194).
  *   - `nnz` is advisory: the stored-entry count is rowptr[m]-rowptr[0].  When they disagree
  *     (the reference loader's symmetric-file defect) the rowptr value is used.
+ *   - ILU0 and SpTRSV need the columns of every row in ascending order (what the loader produces); an unsorted row makes
+ *     the analysis, factor and solve calls return RSG_BAD_ARG.  SpMV accepts any order.
  *   - One handle = one device + one stream; calls on a handle are not re-entrant.
  *   - Every function returns an rsg_status (0 = OK).  The library never exit()s or prints.
  */
@@ -56,7 +58,7 @@ typedef enum {
 int rsg_create(rsg_handle_t *handle, int device);
 int rsg_destroy(rsg_handle_t handle);
 int rsg_set_stream(rsg_handle_t handle, void *cuda_stream); /* cudaStream_t; NULL = default */
-int rsg_synchronize(rsg_handle_t handle);
+int rsg_synchronize(rsg_handle_t handle); /* RSG_DEPENDENCY_TIMEOUT if a device-side wait gave up since the last call */
 const char *rsg_status_string(int status);
 int rsg_version(void);
 
@@ -70,9 +72,9 @@ typedef enum {
     RSG_OPT_TRSV_ALGO = 5,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_ILU0_ALGO = 6,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_SPMV_X_PERSIST = 7, /* 1: pin x in L2 with an access-policy window on the stream */
-    RSG_OPT_SPMV_X_HINT = 8,    /* stream/pipe kernels: 1 = gather x with an L2 evict_last hint; tile kernel: 3 = older inner loop (A/B) */
-    RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* pipe kernel: tile size in rows per thread (0 = 1) */
-    RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* pipe kernel: cap on resident CTAs per SM (0 = occupancy limit) */
+    RSG_OPT_SPMV_X_HINT = 8,    /* tile kernel plan: 4 = never size tiles for two lanes per row (A/B); other values unused */
+    RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* tile kernel: tile size in rows per thread (0 = 1) */
+    RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* unused since the persistent kernel was retired */
     RSG_OPT_TRSV_BATCH = 11,    /* sync-free solves: solution entries polled per round trip (1,2,4,8,16; 0 = default) */
     RSG_OPT_TRSV_GATE = 12,     /* sync-free solves: 1 = a row first polls only its deepest dependency, 2 = off, 0 = default */
     RSG_OPT_TRI_CTAS_PER_SM = 13, /* sync-free ILU0 / solves: cap on resident CTAs per SM (0 = default) */
@@ -92,6 +94,11 @@ typedef enum {
                                    untransposed one does; 0 = read the values through the cached permutation on every call
                                    (default, always right: fused kernel, or gather + product when a column is longer
                                    than 2048 entries); 2 = always gather + product (A/B) */
+    RSG_OPT_SPMV_WIN_BYTES = 20, /* window kernel: shared memory per CTA the plan aims at (bytes; 0 = default 44 KB) */
+    RSG_OPT_SPMV_WIN_STREAM_PCT = 21, /* window kernel: share of that given to the entries (values + 16-bit columns), percent (0 = 64) */
+    RSG_OPT_SPMV_WIN_GAP = 22,  /* window kernel plan: runs of x separated by up to this many unused 4-column granules are merged (0 = 3) */
+    RSG_OPT_WAIT_SPINS = 23,    /* polls a device-side dependency / halo wait may spend before it gives up and the next
+                                   synchronising call returns RSG_DEPENDENCY_TIMEOUT (0 = default 2^22, i.e. seconds) */
     RSG_OPT_COUNT_
 } rsg_option;
 
@@ -101,9 +108,11 @@ typedef enum {
     RSG_SPMV_MERGE = 2,    /* merge-path, for skewed row lengths */
     RSG_SPMV_VECTOR = 3,   /* plain sub-warp-per-row, scalar loads (any alignment) */
     RSG_SPMV_SCALAR = 4,   /* plain thread-per-row, scalar loads */
-    RSG_SPMV_STREAM = 5,   /* TMA bulk-staged tiles, one tile per CTA; thread-, sub-warp-, warp-, CTA-per-row */
-    RSG_SPMV_PIPE = 6,     /* persistent CTAs, multi-stage TMA ring (mbarrier pipeline); same reductions */
-    RSG_SPMV_TILE = 7      /* one TMA-staged tile per CTA (row pointers staged too), many small CTAs per SM */
+    RSG_SPMV_STREAM = 5,   /* retired (round 1's first TMA kernel): selects RSG_SPMV_TILE */
+    RSG_SPMV_PIPE = 6,     /* retired (persistent multi-stage TMA ring, measured slower everywhere): selects RSG_SPMV_TILE */
+    RSG_SPMV_TILE = 7,     /* one TMA-staged tile per CTA (row pointers staged too), many small CTAs per SM; long rows split */
+    RSG_SPMV_WINDOW = 8    /* TMA-staged tile + its x window in shared memory, 16-bit window-local columns built at plan time
+                              (stencil / FEM / banded patterns; falls back to TILE when a pattern has no compact windows) */
 } rsg_spmv_algo;
 
 typedef enum {
@@ -202,7 +211,9 @@ int rsg_halo_push(rsg_handle_t handle, int elem_bytes, int nsend, const int *sen
  * RSG_OPT_SPMV_HALO_START wait (acquire, system scope) until flags[i] >= epoch for all i < nflags
  * (flags: DEVICE pointer, nflags <= RSG_MAX_PEERS), while all other tiles run at once: the exchange
  * overlaps the product without splitting it.  Needs the TILE kernel (AUTO picks it for regular rows);
- * other kernels return RSG_UNSUPPORTED.  A wait gives up after ~1 s (result then undefined). */
+ * (the last tile waits too, marked or not, so a rank never runs more than one step ahead of a neighbour).  Needs the
+ * WINDOW or TILE kernel (AUTO picks them for regular rows); other kernels return RSG_UNSUPPORTED.  A wait that gives up
+ * (RSG_OPT_WAIT_SPINS polls) raises a flag that rsg_synchronize returns as RSG_DEPENDENCY_TIMEOUT. */
 int rsg_spmv_halo_wait(rsg_handle_t handle, const int *flags, int nflags, int epoch);
 /* One-shot: the NEXT spmv_csr_* call also performs the push of rsg_halo_push itself -- its first few CTAs
  * store x[send_idx[j]] (x = that call's x) into the peers' slots and release `epoch` to their flags, the

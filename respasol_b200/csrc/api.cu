@@ -39,6 +39,16 @@ __global__ void cast_d2f_kernel(size_t n, const double *__restrict__ a, float *_
 
 } // namespace
 
+int rsg::check_err_flag(rsg_context *h)
+{
+    cudaStream_t st = h->stream;
+    RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i + 63, h->err_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    RSG_CUDA_TRY(cudaStreamSynchronize(st));
+    if (h->pinned_i[63] == 0) return RSG_OK;
+    RSG_CUDA_TRY(cudaMemsetAsync(h->err_flag, 0, sizeof(int), st));
+    return RSG_DEPENDENCY_TIMEOUT;
+}
+
 extern "C" {
 
 int rsg_version(void) { return 100; }
@@ -82,6 +92,7 @@ int rsg_create(rsg_handle_t *handle, int device)
         delete h;
         return RSG_ALLOC_FAILED;
     }
+    h->err_flag = h->scratch_i + 60;
     h->spmv_plans.reserve(65);
     h->tri_plans.reserve(9);
     h->transpose_plans.reserve(9);
@@ -118,8 +129,7 @@ int rsg_synchronize(rsg_handle_t h)
 {
     if (!h) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    RSG_CUDA_TRY(cudaStreamSynchronize(h->stream));
-    return RSG_OK;
+    return check_err_flag(h); // synchronises the stream; a device-side wait that gave up surfaces here
 }
 
 int rsg_set_option(rsg_handle_t h, int option, int value)
@@ -171,9 +181,9 @@ int rsg_spmv_analysis(rsg_handle_t h, int m, int n, int nnz, int base, const int
 {
     if (!h || m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr) return RSG_BAD_ARG;
     DeviceGuard g(h->device);
-    SpmvPlan *p = nullptr; // one plan per stored-value size (fp64 / fp32+mixed): the tile shape differs
-    RSG_TRY(spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p, 8));
-    return spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p, 4);
+    SpmvPlan *p = nullptr; // one plan per (stored-value size, vector element size): the tile shapes differ
+    RSG_TRY(spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p, 0x88));
+    return spmv_get_plan(h, m, n, nnz, base, rowptr, colidx, true, &p, 0x44); // the mixed plan (0x84) is built on first use
 }
 
 int spmv_csr_d(rsg_handle_t h, int m, int n, int nnz, int base, const int *rowptr, const int *colidx,
@@ -239,6 +249,7 @@ int rsg_ilu0_analysis(rsg_handle_t h, int n, int nnz, int base, const int *rowpt
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
     RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, true, &p));
+    if (p->unsorted) return RSG_BAD_ARG; // columns must ascend inside every row (see the header)
     if (zero_pivot_row) *zero_pivot_row = p->missing_diag_row;
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
     // both patterns in one launch: the L and U dependency chains overlap, and the harness asks for
@@ -252,6 +263,7 @@ int rsg_sptrsv_analysis(rsg_handle_t h, int n, int nnz, int base, const int *row
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
     RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
+    if (p->unsorted) return RSG_BAD_ARG;
     if (p->missing_diag_row >= 0) return RSG_ZERO_PIVOT_STRUCTURAL;
     return tri_build_levels(h, p, -1);
 }
@@ -263,6 +275,7 @@ int ilu0_factor_impl(rsg_handle_t h, int n, int nnz, int base, const int *rowptr
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
     RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
+    if (p->unsorted) return RSG_BAD_ARG;
     return ilu0_run<T>(h, p, values, zp);
 }
 
@@ -282,6 +295,7 @@ int sptrsv_impl(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, con
     DeviceGuard g(h->device);
     TriPlan *p = nullptr;
     RSG_TRY(tri_get_plan(h, n, nnz, base, rowptr, colidx, false, &p));
+    if (p->unsorted) return RSG_BAD_ARG;
     return trsv_run<T>(h, p, lu, b, z, y);
 }
 
@@ -541,10 +555,11 @@ int rsg_matrix_upload(rsg_handle_t h, char precision, int m, int n, int nnz, int
     if (!ev_ok) { (void)cudaGetLastError(); rsg_matrix_free(h, a); return RSG_CUDA_ERROR; }
     // plans of the whole matrix and of every chunk view now, so that no product pays for an analysis
     SpmvPlan *pl = nullptr;
-    rc = spmv_get_plan(h, m, n, a->nnz, base, a->rowptr, a->colidx, false, &pl, (int)vs);
+    const int pkey = (int)vs | ((int)xs << 4);
+    rc = spmv_get_plan(h, m, n, a->nnz, base, a->rowptr, a->colidx, false, &pl, pkey);
     for (int c = 0; rc == RSG_OK && a->nchunk > 1 && c < a->nchunk; ++c)
         rc = spmv_get_plan(h, a->chunk_row[c + 1] - a->chunk_row[c], n, a->nnz, base, a->rowptr + a->chunk_row[c], a->colidx,
-                           false, &pl, (int)vs);
+                           false, &pl, pkey);
     if (rc != RSG_OK) { rsg_matrix_free(h, a); return rc; }
     *matrix = a;
     return RSG_OK;

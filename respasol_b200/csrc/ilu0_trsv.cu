@@ -19,7 +19,7 @@
 
 namespace rsg {
 
-#define RSG_SPIN_LIMIT (1 << 22) // sweeps before a waiting row gives up (malformed schedule)
+// a waiting row gives up after `spin_limit` sweeps (RSG_OPT_WAIT_SPINS, default 2^22: a malformed schedule or input)
 // measured on config 3 (tools/tri_sweep.py, profiles/r1_tri_sweep*.log): 16 entries per poll (a triangle of the
 // FEM-like matrix has up to 13 entries per row: one L2 round trip covers the whole row; 8 per poll needed two and
 // cost 1.39 ms against 1.05 ms), no gate, and only ~32 levels' worth of rows in flight -- every extra waiting row
@@ -98,7 +98,7 @@ template <> __device__ __forceinline__ float div_t(float a, float b) { return __
 template <typename T>
 __device__ __noinline__ void ilu0_row_generic(int lane, int i, int rs, int len, int nl, int base, const int *__restrict__ rowptr,
                                               const int *__restrict__ colidx, T *values, const int *__restrict__ diag_pos,
-                                              const int *done, int epoch, int *ctl)
+                                              const int *done, int epoch, int *ctl, int spin_limit, int *err)
 {
     const int *rc = colidx + rs;
     volatile T *rv = values + rs;
@@ -113,7 +113,7 @@ __device__ __noinline__ void ilu0_row_generic(int lane, int i, int rs, int len, 
         int spins = 0;
         while (!__all_sync(0xffffffffu, ready)) {
             if (!ready) ready = (ld_acquire(done + k) == epoch);
-            if (++spins > RSG_SPIN_LIMIT) { if (lane == 0) atomicExch(ctl + 1, 1); break; }
+            if (++spins > spin_limit) { if (lane == 0) { atomicExch(ctl + 1, 1); atomicExch(err, 1); } break; }
         }
         __syncwarp();
         if (mine) {
@@ -151,7 +151,7 @@ __device__ __noinline__ void ilu0_row_generic(int lane, int i, int rs, int len, 
 template <typename T, int WARPS, int WCAP, int LCAP>
 __global__ void __launch_bounds__(WARPS * 32)
 ilu0_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx, T *values,
-            const int *__restrict__ diag_pos, const int *__restrict__ order, int *done, int epoch, int *ctl)
+            const int *__restrict__ diag_pos, const int *__restrict__ order, int *done, int epoch, int *ctl, int spin_limit, int *err)
 {
     constexpr unsigned short NONE = 0xffff;
     __shared__ int s_col[WARPS][WCAP];            // row i: raw column indices
@@ -202,7 +202,7 @@ ilu0_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restri
             fast = tot <= LCAP;
         }
         if (!fast) {
-            ilu0_row_generic<T>(lane, i, rs, len, nl, base, rowptr, colidx, values, diag_pos, done, epoch, ctl);
+            ilu0_row_generic<T>(lane, i, rs, len, nl, base, rowptr, colidx, values, diag_pos, done, epoch, ctl, spin_limit, err);
         } else {
             // ---- structure only: match every upper entry of every row k against row i
             for (int c = lane; c < tot; c += 32) {
@@ -238,7 +238,7 @@ ilu0_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restri
                     int run = pend ? __ffs((int)pend) - 1 : 32;
                     run = min(run, cnt - processed);
                     if (run == 0) {
-                        if (++spins > RSG_SPIN_LIMIT) { if (lane == 0) atomicExch(ctl + 1, 1); timed_out = true; break; }
+                        if (++spins > spin_limit) { if (lane == 0) { atomicExch(ctl + 1, 1); atomicExch(err, 1); } timed_out = true; break; }
                         continue;
                     }
                     __syncwarp(); // the acquiring lanes' observations now order every lane's loads below
@@ -310,7 +310,7 @@ template <typename T, bool UPPER, int B, bool GATE>
 __global__ void __launch_bounds__(256)
 trsv_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
             const T *__restrict__ lu, const int *__restrict__ diag_pos, const int *__restrict__ order,
-            const int *__restrict__ crit, const T *__restrict__ rhs, T *sol, int *ctl)
+            const int *__restrict__ crit, const T *__restrict__ rhs, T *sol, int *ctl, int spin_limit, int *err)
 {
     typedef Pending<T> P;
     const int lane = threadIdx.x & 31;
@@ -366,7 +366,7 @@ trsv_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restri
                     if (head < nb) break; // a dependency is still pending: next sweep
                 }
             }
-            if (++spins > RSG_SPIN_LIMIT) { atomicExch(ctl + 1, 1); break; }
+            if (++spins > spin_limit) { atomicExch(ctl + 1, 1); atomicExch(err, 1); break; }
         }
     }
 }
@@ -444,13 +444,13 @@ int ilu0_run(rsg_context *h, TriPlan *p, T *values, int *zero_pivot_row)
     if (h->opts[RSG_OPT_TRI_CTAS_PER_SM] > 0) per_sm = std::min(per_sm, h->opts[RSG_OPT_TRI_CTAS_PER_SM]);
     const int grid = std::max(1, std::min(h->sm_count * per_sm, (p->n + WARPS - 1) / WARPS));
     kern<<<grid, WARPS * 32, 0, st>>>(p->n, p->base, p->rowptr, p->colidx, values, p->diag_pos, p->order[0], p->done,
-                                      p->epoch, p->ctl);
+                                      p->epoch, p->ctl, wait_spins(h), h->err_flag);
     h->launches++;
     RSG_CUDA_TRY(cudaGetLastError());
     if (!zero_pivot_row) return RSG_OK;
     RSG_CUDA_TRY(cudaMemcpyAsync(h->pinned_i + 12, p->ctl, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
     RSG_CUDA_TRY(cudaStreamSynchronize(st));
-    if (h->pinned_i[13]) return RSG_DEPENDENCY_TIMEOUT;
+    if (h->pinned_i[13]) { (void)check_err_flag(h); return RSG_DEPENDENCY_TIMEOUT; }
     if (h->pinned_i[14] != 0x7fffffff) {
         *zero_pivot_row = h->pinned_i[14];
         return RSG_ZERO_PIVOT_NUMERIC;
@@ -508,7 +508,7 @@ int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
     const bool gate = h->opts[RSG_OPT_TRSV_GATE] ? h->opts[RSG_OPT_TRSV_GATE] == 1 : (RSG_TRSV_DEFAULT_GATE != 0);
     int block = h->opts[RSG_OPT_TRSV_BLOCK];
     if (block < 32 || block > 256 || (block & 31)) block = 64;
-    typedef void (*kern_t)(int, int, const int *, const int *, const T *, const int *, const int *, const int *, const T *, T *, int *);
+    typedef void (*kern_t)(int, int, const int *, const int *, const T *, const int *, const int *, const int *, const T *, T *, int *, int, int *);
     kern_t kl = nullptr, ku = nullptr;
 #define RSG_PICK(BB, GG) { kl = trsv_kernel<T, false, BB, GG>; ku = trsv_kernel<T, true, BB, GG>; }
     if (gate) { if (batch == 1) RSG_PICK(1, true) else if (batch == 2) RSG_PICK(2, true) else if (batch == 4) RSG_PICK(4, true) else if (batch == 16) RSG_PICK(16, true) else RSG_PICK(8, true) }
@@ -526,8 +526,8 @@ int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
         grid = (int)std::min<long long>((long long)h->sm_count * per_sm, std::max<long long>(h->sm_count, want));
     }
     grid = std::max(1, std::min(grid, (n + block - 1) / block));
-    kl<<<grid, block, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[0], p->crit[0], b, z, p->ctl);
-    ku<<<grid, block, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[1], p->crit[1], z, y, p->ctl + 4);
+    kl<<<grid, block, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[0], p->crit[0], b, z, p->ctl, wait_spins(h), h->err_flag);
+    ku<<<grid, block, 0, st>>>(n, p->base, p->rowptr, p->colidx, lu, p->diag_pos, p->order[1], p->crit[1], z, y, p->ctl + 4, wait_spins(h), h->err_flag);
     h->launches += 3;
     RSG_CUDA_TRY(cudaGetLastError());
     return RSG_OK;

@@ -246,7 +246,7 @@ int krylov_workspace(rsg_context *h, size_t bytes)
         if (cudaMalloc(&h->krylov_ws, bytes) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
         h->krylov_bytes = bytes;
     }
-    if (!h->krylov_pin && cudaMallocHost(&h->krylov_pin, S_COUNT * sizeof(double)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
+    if (!h->krylov_pin && cudaMallocHost(&h->krylov_pin, (S_COUNT + 2 * 30 + 8) * sizeof(double)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
     return RSG_OK;
 }
 
@@ -334,7 +334,8 @@ extern "C" int rsg_pcg_d(rsg_handle_t h, int n, int nnz, int base, const int *ro
     RSG_CUDA_TRY(cudaGetLastError());
     if (iters) *iters = it;
     if (relres) *relres = std::sqrt(rr / bb);
-    return std::isfinite(rr) ? RSG_OK : RSG_BREAKDOWN;
+    if (!std::isfinite(rr)) return check_err_flag(h) == RSG_DEPENDENCY_TIMEOUT ? RSG_DEPENDENCY_TIMEOUT : RSG_BREAKDOWN; // a hung solve leaves sentinel NaNs
+    return RSG_OK;
 }
 
 extern "C" int rsg_bicgstab_d(rsg_handle_t h, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
@@ -415,7 +416,8 @@ extern "C" int rsg_bicgstab_d(rsg_handle_t h, int n, int nnz, int base, const in
     RSG_CUDA_TRY(cudaGetLastError());
     if (iters) *iters = it;
     if (relres) *relres = std::sqrt(rr / bb);
-    return std::isfinite(rr) ? RSG_OK : RSG_BREAKDOWN;
+    if (!std::isfinite(rr)) return check_err_flag(h) == RSG_DEPENDENCY_TIMEOUT ? RSG_DEPENDENCY_TIMEOUT : RSG_BREAKDOWN; // a hung solve leaves sentinel NaNs
+    return RSG_OK;
 }
 
 // Restarted flexible GMRES(kGmresRestart), right-preconditioned (Saad & Schultz 1986; Saad Alg. 9.6): the preconditioned
@@ -456,12 +458,8 @@ extern "C" int rsg_gmres_d(rsg_handle_t h, int n, int nnz, int base, const int *
     unsigned *ticket = reinterpret_cast<unsigned *>(w_);
     RSG_CUDA_TRY(cudaMemsetAsync(scal, 0, S_COUNT * 8 + 64, st));
     const int grid = std::max(1, std::min(kMaxVecBlocks, std::min(h->sm_count * 8, (n + kVecThreads * 4 - 1) / (kVecThreads * 4))));
-    struct Pinned {
-        double *p = nullptr;
-        ~Pinned() { if (p) cudaFreeHost(p); }
-    } pin;
-    if (cudaMallocHost(&pin.p, sizeof(double) * (2 * R + 4)) != cudaSuccess) { (void)cudaGetLastError(); return RSG_ALLOC_FAILED; }
-    double *ph = pin.p, *py = pin.p + R + 2;
+    static_assert(kGmresRestart <= 30, "krylov_pin is sized for a restart length of 30");
+    double *ph = h->krylov_pin + S_COUNT, *py = ph + R + 2; // grow-once pinned mirror (no allocation per call)
 
     auto precondition = [&](const double *in, double *out) -> int { // in32 already holds (float) in with fp32 factors
         if (!pre) { RSG_CUDA_TRY(cudaMemcpyAsync(out, in, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, st)); return RSG_OK; }
@@ -549,5 +547,6 @@ extern "C" int rsg_gmres_d(rsg_handle_t h, int n, int nnz, int base, const int *
     RSG_CUDA_TRY(cudaGetLastError());
     if (iters) *iters = it;
     if (relres) *relres = std::sqrt(rr / bb);
-    return std::isfinite(rr) ? RSG_OK : RSG_BREAKDOWN;
+    if (!std::isfinite(rr)) return check_err_flag(h) == RSG_DEPENDENCY_TIMEOUT ? RSG_DEPENDENCY_TIMEOUT : RSG_BREAKDOWN; // a hung solve leaves sentinel NaNs
+    return RSG_OK;
 }

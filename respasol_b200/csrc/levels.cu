@@ -27,7 +27,9 @@ __device__ __forceinline__ void st_relaxed(int *p, int v)
     asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-// diag_pos[i] = zero-based position of a_ii, or -1; stats[0] = min row without diagonal (init INT_MAX)
+// diag_pos[i] = zero-based position of a_ii, or -1; stats[0] = min row without diagonal (init INT_MAX);
+// stats[2] = 1 when some row's columns are not ascending (the factorization and the solves split a row at its
+// diagonal and binary-search it: such input is refused with RSG_BAD_ARG instead of giving wrong factors)
 __global__ void diag_pos_kernel(int n, int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
                                 int *__restrict__ diag_pos, int *stats)
 {
@@ -50,6 +52,9 @@ __global__ void diag_pos_kernel(int n, int base, const int *__restrict__ rowptr,
     }
     diag_pos[i] = pos;
     if (pos < 0) atomicMin(stats, i);
+    bool descending = false;
+    for (int k = lo + 1; k < hi; ++k) descending |= colidx[k] < colidx[k - 1];
+    if (descending) stats[2] = 1;
 }
 
 // Both patterns in ONE launch: CTAs with an even index walk the lower pattern (rows ascending),
@@ -234,6 +239,7 @@ int tri_get_plan(rsg_context *h, int n, int nnz_hint, int base, const int *rowpt
     const int *r = h->pinned_i + 16;
     p.missing_diag_row = (r[0] == 0x7fffffff) ? -1 : r[0];
     p.max_row = r[1];
+    p.unsorted = r[2] != 0;
     p.nnz = n > 0 ? r[5] - r[4] : 0;
     h->tri_plans.push_back(p);
     h->last_tri = (int)h->tri_plans.size() - 1;

@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <atomic>
 #include <vector>
 
 #include "../../include/reaspasol_gpu.h"
@@ -22,6 +23,17 @@
     } while (0)
 
 namespace rsg {
+
+// cudaFuncSetAttribute applies to the CURRENT device only: one bit per device remembers what has been configured
+// (a single process may drive several GPUs through several handles -- rsg_spmv_multi_*).
+struct PerDeviceOnce {
+    std::atomic<unsigned long long> mask{0};
+    bool need(int device)
+    {
+        const unsigned long long bit = 1ull << (device & 63);
+        return (mask.fetch_or(bit) & bit) == 0;
+    }
+};
 
 // x-halo push folded into the SpMV launch (rsg_spmv_halo_fuse): the first `ctas` CTAs of the grid store
 // x[send_idx[j]] into the peers' halo slots and release `epoch` to their flags, the rest are the tiles.
@@ -64,9 +76,8 @@ struct SpmvPlan {
     int tile = 0;          // merged items (rows + entries) per CTA
     int nblk = 0;
     int *blk_row = nullptr;    // nblk+1 row indices
-    int2 *sblk = nullptr;      // stream kernel: nblk+1 (first row, zero-based entry offset)
-    int4 *pdesc = nullptr;     // pipe kernel: nblk+1 (first row, zero-based entry offset, longest row, 0)
-    int *rp0 = nullptr;        // pipe kernel: zero-based padded copy of rowptr
+    int4 *pdesc = nullptr;     // tile kernel: nblk+1 (first row, zero-based entry offset, longest row, halo mark)
+    int *rp0 = nullptr;        // tile / window kernels: zero-based padded copy of rowptr
     int rp0_len = 0;
     // tile kernel: split long rows (LongSplit)
     int4 *seg = nullptr;
@@ -74,6 +85,11 @@ struct SpmvPlan {
     double *seg_part = nullptr;
     int *seg_cnt = nullptr;
     int nseg = 0, nlong = 0;
+    // window kernel (spmv_window.cu): 128-byte tile records, 16-bit window-local column indices
+    int4 *wdesc = nullptr;
+    uint16_t *widx = nullptr;
+    int wsmem = 0, wthreads = 0, whalo = 0, first8 = 0;
+    int vbytes = 0, xbytes = 0; // stored-value / vector element sizes the plan was shaped for
     int lanes_hint = 0;        // tile kernel: 2 = the stage holds about half as many rows as the CTA has threads -> two lanes per row
     // merge-path kernel
     int merge_items = 0;   // rows+entries per CTA
@@ -92,6 +108,7 @@ struct TriPlan {
     int nnz_hint = 0;              // the caller's nnz argument (part of the key)
     int *diag_pos = nullptr;       // zero-based position of a_ii in colidx/values, -1 if missing
     int missing_diag_row = -1;     // first row without a diagonal entry
+    bool unsorted = false;         // some row's columns are not ascending: ILU0 / SpTRSV refuse it (RSG_BAD_ARG)
     int max_row = 0;
     bool have[2] = {false, false}; // [0]=L (lower pattern), [1]=U (upper pattern)
     int nlevels[2] = {0, 0};
@@ -145,6 +162,7 @@ struct rsg_context {
     void *cub_tmp = nullptr;
     size_t cub_tmp_bytes = 0;
     int *scratch_i = nullptr; // small device scratch (stats), 64 ints
+    int *err_flag = nullptr;  // = scratch_i + 60: raised by a device-side dependency wait that gave up
     int *pinned_i = nullptr;  // small pinned host mirror, 64 ints
     const int *wait_flags = nullptr;   // one-shot halo wait for the next SpMV (rsg_spmv_halo_wait)
     int wait_n = 0, wait_epoch = 0;
@@ -185,8 +203,13 @@ namespace rsg {
 int ensure_cub_tmp(rsg_context *h, size_t bytes);
 
 // spmv.cu
+// pkey: stored-value bytes | vector-element bytes << 4 (0x88 fp64, 0x44 fp32, 0x84 mixed; a bare 8 / 4 means both alike)
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
-                  bool force_rebuild, SpmvPlan **out, int vbytes = 8);
+                  bool force_rebuild, SpmvPlan **out, int pkey = 8);
+// polls a device-side flag wait may spend before it gives up (RSG_OPT_WAIT_SPINS; default 2^22: seconds)
+inline int wait_spins(const rsg_context *h) { const int v = h->opts[RSG_OPT_WAIT_SPINS]; return v > 0 ? v : (1 << 22); }
+// RSG_DEPENDENCY_TIMEOUT if a kernel of this handle raised the flag since the last check (synchronises the stream)
+int check_err_flag(rsg_context *h);
 void spmv_free_plan(SpmvPlan &p);
 long long spmv_plans_freed();
 template <typename TV, typename TX>
@@ -195,14 +218,16 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
 int row_partition(rsg_context *h, int m, int base, const int *rowptr, int ngpu, int balanced,
                   int *row_starts_host);
 
-// spmv_pipe.cu
-int pipe_num_variants();
+// spmv_tile.cu
 int tile_num_variants();
 template <typename TV, typename TX>
 int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split = false);
+
+// spmv_window.cu
+int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool strict);
 template <typename TV, typename TX>
-int pipe_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
+int window_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 
 // transpose.cu
 void transpose_free_plan(TransposePlan &p);

@@ -12,7 +12,8 @@
 //             the tile is reduced CTA-per-row straight from global memory.
 //   merge     Merge-path (rows+entries split evenly over CTAs and threads, carry fix-up):
 //             for skewed row lengths, where one dense row would pin a single CTA.
-//   vector    plain sub-warp-per-row, scalar loads, any alignment (fallback / cross-check)
+//   window / tile   the TMA-staged kernels (spmv_window.cu, spmv_tile.cu); this file holds the plan logic that picks them
+//   vector    plain sub-warp-per-row, batched scalar loads, any alignment (scattered columns, small matrices)
 //   scalar    plain thread-per-row (fallback / cross-check)
 // TX is the vector / accumulation type, TV the stored-value type: (double,double) fp64,
 // (float,float) fp32, (float,double) the mixed variant.
@@ -89,163 +90,6 @@ spmv_rowblock_kernel(int base, const int *__restrict__ rowptr, const int *__rest
     }
 }
 
-
-// ------------------------------------------------------------------ stream kernel (TMA-staged)
-// The dominant kernel.  The entries of a CTA tile are brought into shared memory RAW (colidx and
-// values, not products) by two 1-D bulk async copies (cp.async.bulk -> UBLKCP, completion on an
-// mbarrier): one elected thread issues the whole tile, so the bytes in flight per SM do not
-// depend on what the other threads are doing, and several CTAs per SM keep one tile loading
-// while another one reduces.  x is gathered in the REDUCTION phase: with one thread per row
-// (short rows) lane l of a warp reads x[col(r0+l, k)], which for banded/stencil patterns is a
-// contiguous run -- 2-3 cache lines per warp load instead of ~11 when gathering in entry order
-// (the L1 wavefront rate, ~1 line per cycle per SM, is what bounds an entry-order gather of a
-// 27-point stencil at ~3 TB/s).  A thread-per-row sum runs left to right like the oracle's.
-// Longer rows take 2..32 lanes each (shuffle reduction); a row beyond the staging capacity is
-// reduced CTA-per-row straight from global memory.
-// W: weight of a row in the tile partition (items = entries + W*rows <= TILE => rows <= TILE/W)
-template <int TILE, int W> struct StreamShape {
-    static constexpr int CAP = TILE + TILE / 8; // staged entries per pass
-    static constexpr int ROWS = TILE / W;       // rows per tile
-    template <typename TV> static constexpr size_t smem()
-    {
-        return (sizeof(TV) + sizeof(int)) * (size_t)(CAP + 8) + sizeof(int) * (size_t)(ROWS + 4) + 16;
-    }
-};
-
-template <typename TV, typename TX, int THREADS, int TILE, int W, int XH>
-__global__ void __launch_bounds__(THREADS)
-spmv_stream_kernel(int base, const int *__restrict__ rowptr, const int *__restrict__ colidx,
-                   const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
-                   const int2 *__restrict__ blk, int reduce_opt)
-{
-    typedef StreamShape<TILE, W> Shape;
-    constexpr int CAP = Shape::CAP;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    TV *s_val = reinterpret_cast<TV *>(smem_raw);                                   // CAP + 8
-    int *s_col = reinterpret_cast<int *>(s_val + CAP + 8);                          // CAP + 8
-    int *s_rp = s_col + CAP + 8;                                                    // ROWS + 1 (+ pad)
-    uint64_t *bar = reinterpret_cast<uint64_t *>(s_rp + ((Shape::ROWS + 4) & ~1)); // 8-byte aligned
-    __shared__ int s_maxlen;
-    const int tid = threadIdx.x;
-    const int2 c0 = blk[blockIdx.x], c1 = blk[blockIdx.x + 1];
-    const int r0 = c0.x, nr = c1.x - c0.x;
-    if (nr <= 0) return;
-    const uint64_t spol = make_evict_first_policy();
-    uint64_t xpol = 0;
-    if (XH) xpol = make_evict_last_policy();
-    // the first pass can be issued before the row pointers arrive when the whole tile fits
-    const int kb = c0.y, ke = c1.y; // zero-based entry range of the tile
-    const bool single = (ke - (kb & ~3)) <= CAP;
-    if (tid == 0) {
-        s_maxlen = 0;
-        mbar_init(bar, 1);
-    }
-    __syncthreads();
-    uint32_t parity = 0;
-    bool issued = false;
-    if (single) {
-        const int sb = kb & ~3, qe = ke & ~3;
-        if (tid == 0 && qe > sb) {
-            const uint32_t nq = (uint32_t)(qe - sb);
-            mbar_expect_tx(bar, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
-            bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), bar, spol);
-            bulk_g2s(s_col, colidx + sb, nq * (uint32_t)sizeof(int), bar, spol);
-        }
-        issued = true;
-    }
-    {
-        int ml = 0;
-        for (int i = tid; i <= nr; i += THREADS) {
-            const int a = rowptr[r0 + i] - base;
-            s_rp[i] = a;
-            if (i < nr) ml = max(ml, rowptr[r0 + i + 1] - base - a);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ml = max(ml, __shfl_xor_sync(0xffffffffu, ml, o));
-        if ((tid & 31) == 0 && ml > 0) atomicMax(&s_maxlen, ml);
-    }
-    __syncthreads();
-    const int maxlen = s_maxlen;
-    int cur = 0;
-    while (cur < nr) {
-        const int k0 = s_rp[cur];
-        const int sb = k0 & ~3;
-        int pe;
-        if (s_rp[nr] - sb <= CAP) {
-            pe = nr;
-        } else { // largest pe in [cur,nr] with s_rp[pe]-sb <= CAP
-            int lo = cur, hi = nr;
-            while (lo < hi) {
-                const int mid = (lo + hi + 1) >> 1;
-                if (s_rp[mid] - sb <= CAP) lo = mid; else hi = mid - 1;
-            }
-            pe = lo;
-        }
-        if (pe == cur) { // this row alone exceeds the staging capacity: CTA-per-row
-            const TX tot = cta_row_sum<TV, TX, THREADS, 1, true>(k0, s_rp[cur + 1], colidx, values, x, base,
-                                                                 reinterpret_cast<TX *>(smem_raw), spol);
-            if (tid == 0) store_y(y, r0 + cur, tot, alpha, beta);
-            cur += 1;
-            continue;
-        }
-        const int k1 = s_rp[pe];
-        const int qe = k1 & ~3;
-        if (!issued) {
-            if (tid == 0 && qe > sb) {
-                const uint32_t nq = (uint32_t)(qe - sb);
-                mbar_expect_tx(bar, nq * (uint32_t)(sizeof(TV) + sizeof(int)));
-                bulk_g2s(s_val, values + sb, nq * (uint32_t)sizeof(TV), bar, spol);
-                bulk_g2s(s_col, colidx + sb, nq * (uint32_t)sizeof(int), bar, spol);
-            }
-        }
-        issued = false;
-        { // ragged tail (< 4 entries) by plain loads
-            const int k = max(qe, sb) + tid;
-            if (tid < 4 && k < k1) { s_val[k - sb] = values[k]; s_col[k - sb] = colidx[k]; }
-        }
-        __syncthreads();
-        if (qe > sb) { mbar_wait(bar, parity); parity ^= 1; }
-        const int nrows = pe - cur;
-        int g = reduce_opt;
-        if (g == 0) { // row-length bin of this tile: lanes per row
-            const int avg = (k1 - k0) / nrows;
-            const int len = max(avg, maxlen >> 3);
-            g = len <= 40 ? 1 : len <= 80 ? 4 : len <= 160 ? 8 : len <= 320 ? 16 : 32;
-            while (g < 32 && nrows * g * 2 <= THREADS) g <<= 1; // few rows: spread them over the CTA
-            if (g == 2) g = (avg <= 40 && maxlen <= 64) ? 1 : 4;
-        }
-        const int *rp = s_rp + cur;
-        switch (g) {
-        case 1: reduce_rows_lean<TV, TX, THREADS, 1>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
-        case 2: reduce_rows_lean<TV, TX, THREADS, 2>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
-        case 4: reduce_rows_lean<TV, TX, THREADS, 4>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
-        case 8: reduce_rows_lean<TV, TX, THREADS, 8>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
-        case 16: reduce_rows_lean<TV, TX, THREADS, 16>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
-        default: reduce_rows_lean<TV, TX, THREADS, 32>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
-        }
-        cur = pe;
-        if (cur < nr) __syncthreads();
-    }
-}
-
-// blk[b] = (first row of tile b, its zero-based entry offset); item coordinate = entries + w*rows
-__global__ void stream_partition_kernel(int m, int base, const int *__restrict__ rowptr, int tile, int w, int nblk, int2 *blk)
-{
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b > nblk) return;
-    int r = m;
-    if (b < nblk) {
-        const int rp0 = rowptr[0];
-        const long long target = (long long)b * tile;
-        int lo = 0, hi = m;
-        while (lo < hi) {
-            const int mid = lo + ((hi - lo) >> 1);
-            if ((long long)(rowptr[mid] - rp0) + (long long)w * mid < target) lo = mid + 1; else hi = mid;
-        }
-        r = lo;
-    }
-    blk[b] = make_int2(r, rowptr[r] - base);
-}
 
 // first row r in [0,m] with (rowptr[r]-rowptr[0]) + r >= target  (merged-item coordinate)
 __device__ __forceinline__ int first_row_at_item(const int *__restrict__ rowptr, int m, long long target)
@@ -488,10 +332,6 @@ struct Variant { int threads, tile; };
 static const Variant kVariants[] = {{256, 4096}, {128, 2048}, {256, 2048}, {512, 8192}, {128, 1024}};
 static const int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 static const int kMergeThreads = 256, kMergeIpt = 8;
-// stream kernel shapes (threads, entries+W*rows per CTA); W = kStreamW
-static const Variant kStreamVariants[] = {{256, 4096}, {128, 4096}, {128, 2048}, {256, 8192}, {512, 8192}, {256, 2048}};
-static const int kNumStreamVariants = (int)(sizeof(kStreamVariants) / sizeof(kStreamVariants[0]));
-static constexpr int kStreamW = 2;
 
 static long long g_plans_freed = 0; // bumps whenever device arrays of a plan go away (captured graphs key on it)
 long long spmv_plans_freed() { return g_plans_freed; }
@@ -499,21 +339,26 @@ long long spmv_plans_freed() { return g_plans_freed; }
 void spmv_free_plan(SpmvPlan &p)
 {
     ++g_plans_freed;
-    cudaFree(p.blk_row); cudaFree(p.sblk); cudaFree(p.pdesc); cudaFree(p.rp0); cudaFree(p.seg); cudaFree(p.lrow); cudaFree(p.seg_part); cudaFree(p.seg_cnt); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
+    cudaFree(p.blk_row); cudaFree(p.wdesc); cudaFree(p.widx); cudaFree(p.pdesc); cudaFree(p.rp0); cudaFree(p.seg); cudaFree(p.lrow); cudaFree(p.seg_part); cudaFree(p.seg_cnt); cudaFree(p.coords); cudaFree(p.carry_row); cudaFree(p.carry_val);
     p = SpmvPlan();
 }
 
 static int plan_signature(const rsg_context *h)
 {
-    return h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW] +
-           h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD] * 7919 + h->opts[RSG_OPT_SPMV_REDUCE] * 104729 +
-           h->opts[RSG_OPT_SPMV_HALO_START] * 31 + (h->opts[RSG_OPT_SPMV_X_HINT] == 4 ? 1299709 : 0);
+    int sig = h->opts[RSG_OPT_SPMV_ALGO] * 1000003 + h->opts[RSG_OPT_SPMV_VARIANT] * 10007 + h->opts[RSG_OPT_SPMV_LONG_ROW] +
+              h->opts[RSG_OPT_SPMV_ROWS_PER_THREAD] * 7919 + h->opts[RSG_OPT_SPMV_REDUCE] * 104729 +
+              h->opts[RSG_OPT_SPMV_HALO_START] * 31 + (h->opts[RSG_OPT_SPMV_X_HINT] == 4 ? 1299709 : 0);
+    sig = sig * 31 + h->opts[RSG_OPT_SPMV_WIN_BYTES];
+    sig = sig * 31 + h->opts[RSG_OPT_SPMV_WIN_STREAM_PCT];
+    sig = sig * 31 + h->opts[RSG_OPT_SPMV_WIN_GAP];
+    return sig;
 }
 
 int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const int *rowptr, const int *colidx,
-                  bool force_rebuild, SpmvPlan **out, int vbytes)
+                  bool force_rebuild, SpmvPlan **out, int pkey)
 {
-    const int sig = plan_signature(h) + vbytes * 15485863; // the tile shape depends on the stored-value size
+    const int vbytes = pkey & 15, xbytes = (pkey >> 4) ? (pkey >> 4) : (pkey & 15);
+    const int sig = plan_signature(h) + (vbytes + 16 * xbytes) * 15485863; // tile shapes depend on the element sizes
     for (size_t i = 0; i < h->spmv_plans.size(); ++i) {
         SpmvPlan &p = h->spmv_plans[i];
         if (p.rowptr == rowptr && p.colidx == colidx && p.m == m && p.n == n && p.nnz_hint == nnz_hint && p.base == base &&
@@ -530,13 +375,14 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
     }
     SpmvPlan p;
     p.rowptr = rowptr; p.colidx = colidx; p.m = m; p.n = n; p.nnz_hint = nnz_hint; p.base = base; p.opt_sig = sig;
+    p.vbytes = vbytes; p.xbytes = xbytes;
     cudaStream_t st = h->stream;
     RSG_CUDA_TRY(cudaMemsetAsync(h->scratch_i, 0, 8 * sizeof(int), st));
     if (m > 0) {
         const int blocks = std::min((m + 255) / 256, h->sm_count * 8);
         row_stats_kernel<<<blocks, 256, 0, st>>>(m, rowptr, h->scratch_i);
         h->launches++;
-        if (colidx && h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_AUTO) {
+        if (colidx && (h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_AUTO || h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_WINDOW)) {
             const int groups = std::min((m + 31) / 32, 4096);
             scatter_stats_kernel<<<(groups * 32 + 255) / 256, 256, 0, st>>>(m, base, groups, rowptr, colidx, h->scratch_i);
             h->launches++;
@@ -555,9 +401,13 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
 
     int algo = h->opts[RSG_OPT_SPMV_ALGO];
     int variant = h->opts[RSG_OPT_SPMV_VARIANT];
+    if (algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE) { algo = RSG_SPMV_TILE; variant = 0; } // retired kernels
     const bool aligned = (((uintptr_t)colidx) & 15) == 0;
     const bool auto_algo = algo == RSG_SPMV_AUTO;
-    if (algo == RSG_SPMV_AUTO) {
+    const double avg = (double)p.nnz / std::max(m, 1);
+    bool try_window = algo == RSG_SPMV_WINDOW;
+    if (algo == RSG_SPMV_WINDOW) { algo = RSG_SPMV_TILE; variant = avg < 12.0 ? 5 : (vbytes >= 8 ? 0 : 1); } // what a declined window plan becomes
+    if (auto_algo) {
         // A row reduced by one CTA streams at one SM's share of the bandwidth (~1/148); past
         // roughly nnz/64 entries that single row outlasts the rest of the product: merge-path.
         const int cap = RowBlockShape<4096>::CAP;
@@ -570,35 +420,50 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         // power-law rows; configs 1 and 4) are bound by the latency of the x gathers, not by the stream: a small
         // stage (128 threads x 1152 entries, 15 KB) keeps ~60 warps resident per SM
         if (algo == RSG_SPMV_TILE) {
-            const double avg = (double)p.nnz / std::max(m, 1);
-            variant = avg < 12.0 ? 9 : (vbytes >= 8 ? 0 : 1);
+            variant = avg < 12.0 ? 5 : (vbytes >= 8 ? 0 : 1);
+            // Neighbouring rows that read neighbouring x (stencil / FEM / banded orderings: scatter statistic ~0.1):
+            // the WINDOW kernel -- the tile's x window travels to shared memory with the tile, no gather is left on the
+            // critical path (spmv_window.cu).  It declines patterns without compact windows.
+            if (scatter <= 0.5 && m >= 64) try_window = true;
             // Two cases go to the plain sub-warp-per-row kernel instead (batched loads, no shared memory, so all 228 KB
             // of the SM stay L1 for x; profiles/r1_vector_lanes_sweep.txt, profiles/r1_auto_vs_vector.txt):
             //  * rows whose neighbours gather from unrelated x lines (hashed / badly ordered columns): thread-per-row
             //    gathers out of a staged tile no longer coalesce and L1 capacity for x is what helps (1.7-2.5x on the
             //    banded stand-ins of the 36-matrix sweep);
-            //  * matrices whose entries fit in half of L2 (resident after the first product of a solver loop): the tile
-            //    kernel's per-CTA set-up (barrier, bulk copies, a 512-row stage) is a visible part of a 10-20 us product
-            //    (config 3: 11.9 -> 10.5 us cold; warm, 5-point 1000x1000: 18.5 -> 14.4 us).
+            //  * matrices whose entries fit in half of L2 (resident after the first product of a solver loop) and that the
+            //    window kernel declined: the tile kernel's per-CTA set-up is a visible part of a 10-20 us product.
             // Not with dense rows (a lane walks its share of the row serially: the kernel widens to at most 32 lanes)
             // and not when tiles must wait on halo flags.
             const int vl = vector_lanes(avg);
             const bool no_halo = h->opts[RSG_OPT_SPMV_HALO_START] == 0;
             const int longest_ok = (scatter > 0.5 && avg >= 16.0) ? 4096 : 128 * vl;
-            const bool l2_resident = (long long)p.nnz * (vbytes + 4) < (64LL << 20); // entries in half of the 126 MB L2
+            const bool l2_resident = (long long)p.nnz * (vbytes + 4) < (long long)h->l2_bytes / 2;
             if (no_halo && (scatter > 0.5 || l2_resident) && p.max_row <= longest_ok) { algo = RSG_SPMV_VECTOR; variant = 0; }
         }
     }
-    if ((algo == RSG_SPMV_STREAM || algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && !aligned)
-        algo = RSG_SPMV_ROWBLOCK; // bulk copies need 16-byte aligned arrays
-    const int nvar = algo == RSG_SPMV_STREAM ? kNumStreamVariants : algo == RSG_SPMV_PIPE ? pipe_num_variants()
-                   : algo == RSG_SPMV_TILE ? tile_num_variants() : kNumVariants;
+    if (try_window && aligned && m > 0 && p.nnz > 0) {
+        SpmvPlan wp = p;
+        wp.algo = RSG_SPMV_WINDOW;
+        wp.variant = h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_WINDOW ? h->opts[RSG_OPT_SPMV_VARIANT] : 0;
+        const int rc = window_build_plan(h, wp, vbytes, xbytes, auto_algo);
+        if (rc == RSG_OK) {
+            RSG_CUDA_TRY(cudaGetLastError());
+            h->spmv_plans.push_back(wp);
+            *out = &h->spmv_plans.back();
+            return RSG_OK;
+        }
+        cudaFree(wp.wdesc); cudaFree(wp.widx); cudaFree(wp.rp0);
+        (void)cudaGetLastError();
+        if (rc != RSG_UNSUPPORTED) return rc;
+    }
+    if (algo == RSG_SPMV_TILE && !aligned) algo = RSG_SPMV_ROWBLOCK; // bulk copies need 16-byte aligned arrays
+    const int nvar = algo == RSG_SPMV_TILE ? tile_num_variants() : kNumVariants;
     if (variant < 0 || variant >= nvar) variant = 0;
     p.variant = variant;
-    p.tile = algo == RSG_SPMV_STREAM ? kStreamVariants[variant].tile : kVariants[variant].tile;
+    p.tile = kVariants[algo == RSG_SPMV_TILE ? 0 : variant].tile;
     p.algo = algo;
     const long long items = (long long)m + p.nnz;
-    if ((algo == RSG_SPMV_PIPE || algo == RSG_SPMV_TILE) && m > 0) {
+    if (algo == RSG_SPMV_TILE && m > 0) {
         const SpmvPlan bare = p; // nothing allocated yet
         const int rc = pipe_build_plan(h, p, auto_algo);
         if (rc == RSG_UNSUPPORTED && auto_algo) { // too many long rows to split: merge-path
@@ -616,13 +481,6 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         RSG_CUDA_TRY(cudaMalloc(&p.blk_row, sizeof(int) * ((size_t)p.nblk + 1)));
         p.bytes += sizeof(int) * ((size_t)p.nblk + 1);
         rowblock_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, rowptr, p.tile, p.nblk, p.blk_row);
-        h->launches++;
-    } else if (algo == RSG_SPMV_STREAM && m > 0) {
-        const long long witems = (long long)kStreamW * m + p.nnz;
-        p.nblk = (int)((witems + p.tile - 1) / p.tile);
-        RSG_CUDA_TRY(cudaMalloc(&p.sblk, sizeof(int2) * ((size_t)p.nblk + 1)));
-        p.bytes += sizeof(int2) * ((size_t)p.nblk + 1);
-        stream_partition_kernel<<<(p.nblk + 1 + 255) / 256, 256, 0, st>>>(m, base, rowptr, p.tile, kStreamW, p.nblk, p.sblk);
         h->launches++;
     } else if (algo == RSG_SPMV_MERGE && m > 0) {
         p.merge_items = kMergeThreads * kMergeIpt;
@@ -645,10 +503,9 @@ static int launch_rowblock_one(rsg_context *h, const SpmvPlan *p, const TV *valu
 {
     auto kern = spmv_rowblock_kernel<TV, TX, THREADS, TILE, HINT, VEC>;
     const size_t smem = sizeof(TX) * (RowBlockShape<TILE>::CAP + 4) + sizeof(int) * (TILE + 1);
-    static bool configured = false; // per instantiation
-    if (!configured) {
+    static PerDeviceOnce configured; // function attributes are per device (and per instantiation)
+    if (configured.need(h->device)) {
         RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
     }
     kern<<<p->nblk, THREADS, smem, h->stream>>>(p->base, p->rowptr, p->colidx, values, x, y, alpha, beta, p->blk_row,
                                                h->opts[RSG_OPT_SPMV_REDUCE]);
@@ -677,42 +534,6 @@ static int launch_rowblock(rsg_context *h, const SpmvPlan *p, bool vec, const TV
     case 3: return launch_rowblock_shape<TV, TX, 512, 8192>(h, p, vec, values, alpha, x, beta, y);
     case 4: return launch_rowblock_shape<TV, TX, 128, 1024>(h, p, vec, values, alpha, x, beta, y);
     default: return launch_rowblock_shape<TV, TX, 256, 4096>(h, p, vec, values, alpha, x, beta, y);
-    }
-}
-
-template <typename TV, typename TX, int THREADS, int TILE>
-static int launch_stream_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
-{
-    const size_t smem = StreamShape<TILE, kStreamW>::template smem<TV>();
-    const int xh = h->opts[RSG_OPT_SPMV_X_HINT];
-    static bool configured = false; // per instantiation
-    if (!configured) {
-        RSG_CUDA_TRY(cudaFuncSetAttribute(spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 0>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        RSG_CUDA_TRY(cudaFuncSetAttribute(spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 1>,
-                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
-    }
-    if (xh)
-        spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 1><<<p->nblk, THREADS, smem, h->stream>>>(
-            p->base, p->rowptr, p->colidx, values, x, y, alpha, beta, p->sblk, h->opts[RSG_OPT_SPMV_REDUCE]);
-    else
-        spmv_stream_kernel<TV, TX, THREADS, TILE, kStreamW, 0><<<p->nblk, THREADS, smem, h->stream>>>(
-            p->base, p->rowptr, p->colidx, values, x, y, alpha, beta, p->sblk, h->opts[RSG_OPT_SPMV_REDUCE]);
-    h->launches++;
-    return RSG_OK;
-}
-
-template <typename TV, typename TX>
-static int launch_stream(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
-{
-    switch (p->variant) {
-    case 1: return launch_stream_one<TV, TX, 128, 4096>(h, p, values, alpha, x, beta, y);
-    case 2: return launch_stream_one<TV, TX, 128, 2048>(h, p, values, alpha, x, beta, y);
-    case 3: return launch_stream_one<TV, TX, 256, 8192>(h, p, values, alpha, x, beta, y);
-    case 4: return launch_stream_one<TV, TX, 512, 8192>(h, p, values, alpha, x, beta, y);
-    case 5: return launch_stream_one<TV, TX, 256, 2048>(h, p, values, alpha, x, beta, y);
-    default: return launch_stream_one<TV, TX, 256, 4096>(h, p, values, alpha, x, beta, y);
     }
 }
 
@@ -770,13 +591,23 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     if (m < 0 || n < 0 || (base != 0 && base != 1) || !rowptr || (m > 0 && !y)) return RSG_BAD_ARG;
     if (m == 0) return RSG_OK;
     SpmvPlan *p = nullptr;
-    RSG_TRY(spmv_get_plan(h, m, n, nnz_hint, base, rowptr, colidx, false, &p, (int)sizeof(TV)));
+    constexpr int pkey = (int)sizeof(TV) | ((int)sizeof(TX) << 4);
+    RSG_TRY(spmv_get_plan(h, m, n, nnz_hint, base, rowptr, colidx, false, &p, pkey));
     if (p->nnz > 0 && (!colidx || !values || !x)) return RSG_BAD_ARG;
+    if (p->algo == RSG_SPMV_WINDOW && ((((uintptr_t)x) | ((uintptr_t)values)) & 15) != 0) {
+        // the x segments and the values travel by 16-byte bulk copies: an odd view of x takes the tile / row-block plan
+        const int keep_algo = h->opts[RSG_OPT_SPMV_ALGO], keep_var = h->opts[RSG_OPT_SPMV_VARIANT];
+        h->opts[RSG_OPT_SPMV_ALGO] = ((((uintptr_t)values) & 15) == 0) ? RSG_SPMV_TILE : RSG_SPMV_ROWBLOCK;
+        h->opts[RSG_OPT_SPMV_VARIANT] = h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_TILE ? (p->nnz < 12LL * m ? 5 : (sizeof(TV) >= 8 ? 0 : 1)) : 0;
+        const int rc = spmv_get_plan(h, m, n, nnz_hint, base, rowptr, colidx, false, &p, pkey);
+        h->opts[RSG_OPT_SPMV_ALGO] = keep_algo; h->opts[RSG_OPT_SPMV_VARIANT] = keep_var;
+        RSG_TRY(rc);
+    }
     h->last_spmv_algo = p->algo;
     h->last_spmv_maxrow = p->max_row;
     RSG_TRY(set_x_persistence(h, x, sizeof(TX) * (size_t)n));
     const bool vec = (((uintptr_t)colidx | (uintptr_t)values) & 15) == 0;
-    if ((h->wait_flags || h->fuse.ctas) && p->algo != RSG_SPMV_TILE) { h->wait_flags = nullptr; h->fuse.ctas = 0; return RSG_UNSUPPORTED; }
+    if ((h->wait_flags || h->fuse.ctas) && p->algo != RSG_SPMV_TILE && p->algo != RSG_SPMV_WINDOW) { h->wait_flags = nullptr; h->fuse.ctas = 0; return RSG_UNSUPPORTED; }
     switch (p->algo) {
     case RSG_SPMV_ROWBLOCK:
         h->last_spmv_blocks = p->nblk;
@@ -786,14 +617,8 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
         if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays
         RSG_TRY((tile_launch<TV, TX>(h, p, values, alpha, x, beta, y)));
         break;
-    case RSG_SPMV_PIPE:
-        if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays
-        RSG_TRY((pipe_launch<TV, TX>(h, p, values, alpha, x, beta, y)));
-        break;
-    case RSG_SPMV_STREAM:
-        if ((((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // plan was made for aligned arrays
-        h->last_spmv_blocks = p->nblk;
-        RSG_TRY((launch_stream<TV, TX>(h, p, values, alpha, x, beta, y)));
+    case RSG_SPMV_WINDOW:
+        RSG_TRY((window_launch<TV, TX>(h, p, values, alpha, x, beta, y)));
         break;
     case RSG_SPMV_MERGE:
         h->last_spmv_blocks = p->ntiles;

@@ -131,6 +131,70 @@ __device__ __forceinline__ void stage_products(int k0, int k1, const int *__rest
     }
 }
 
+// ------------------------------------------------------------------ multi-GPU halo helpers (tile + window kernels)
+// Coherent x gather for tiles that read entries a peer stores over NVLink while this kernel is resident: a plain
+// ld.global (PTX defines ld.global.nc / __ldg only for data that is read-only for the kernel's lifetime).
+__device__ __forceinline__ double ld_x_coherent(const double *p)
+{
+    double r;
+    asm volatile("ld.global.f64 %0, [%1];" : "=d"(r) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ float ld_x_coherent(const float *p)
+{
+    float r;
+    asm volatile("ld.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+    return r;
+}
+
+// The first `fuse.ctas` CTAs of a product's grid: store this rank's boundary entries of x into the peers' halo slots
+// (plain stores into P2P-mapped memory), then the last of them to finish releases `epoch` to the peers' flags.
+template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_push(const HaloFuse &fuse, const TX *__restrict__ x)
+{
+    __shared__ int s_last;
+    const int tid = threadIdx.x;
+    for (int j = blockIdx.x * THREADS + tid; j < fuse.nsend; j += fuse.ctas * THREADS) {
+        const TX v = x[fuse.send_idx[j]];
+#pragma unroll 1
+        for (int q = 0; q < fuse.npeers; ++q) {
+            TX *d = static_cast<TX *>(fuse.dst[q]);
+            if (d) d[j] = v;
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) {
+        const int done = atomicAdd(fuse.counter, 1);
+        s_last = (done == fuse.ctas - 1);
+        if (s_last) *fuse.counter = 0;
+    }
+    __syncthreads();
+    if (s_last && tid < fuse.npeers && fuse.flag[tid]) {
+        __threadfence_system();
+        asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(fuse.flag[tid]), "r"(fuse.epoch) : "memory");
+    }
+}
+
+// Threads tid < n each await flags[tid] >= epoch (acquire, system scope).  A wait that gives up (max_spins polls with
+// back-off; the default 2^22 is seconds) raises *err_flag, which the next synchronising call of the handle turns into
+// RSG_DEPENDENCY_TIMEOUT.  The caller follows with a block barrier.
+__device__ __forceinline__ void halo_flag_wait(const int *flags, int n, int epoch, int *err_flag, int max_spins)
+{
+    const int tid = threadIdx.x;
+    if (tid < n) {
+        int spins = 0, v;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(flags + tid) : "memory");
+            if (v >= epoch) break;
+            if (++spins >= max_spins) { if (err_flag) atomicExch(err_flag, 1); break; }
+            if (spins > 64) __nanosleep(spins > 4096 ? 400 : 40);
+        }
+    }
+}
+
+// x gather of a row reduction: read-only path, or coherent when peers write x while the kernel runs
+template <bool COH, typename TX> __device__ __forceinline__ TX ld_xg(const TX *p) { return COH ? ld_x_coherent(p) : __ldg(p); }
+
 // barrier over the first THREADS threads of the CTA: id 0 = __syncthreads (whole CTA), otherwise a
 // named barrier (kernels with a producer warp that does not take part)
 template <int BARID, int THREADS> __device__ __forceinline__ void group_sync()
@@ -140,7 +204,7 @@ template <int BARID, int THREADS> __device__ __forceinline__ void group_sync()
 }
 
 // CTA-wide sum of a_k*x[col_k] over [k0,k1), result valid in thread 0 (CTA-per-row path).
-template <typename TV, typename TX, int THREADS, int HINT, bool VEC, int BARID = 0>
+template <typename TV, typename TX, int THREADS, int HINT, bool VEC, int BARID = 0, bool COH = false>
 __device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict__ colidx,
                                           const TV *__restrict__ values, const TX *__restrict__ x,
                                           int base, TX *s_red, uint64_t pol)
@@ -157,20 +221,20 @@ __device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict_
                 int4 c = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
                 TV v[4];
                 ld_values4<HINT>(values + (q << 2), pol, v);
-                acc += (TX)v[0] * __ldg(x + (c.x - base));
-                acc2 += (TX)v[1] * __ldg(x + (c.y - base));
-                acc += (TX)v[2] * __ldg(x + (c.z - base));
-                acc2 += (TX)v[3] * __ldg(x + (c.w - base));
+                acc += (TX)v[0] * ld_xg<COH>(x + (c.x - base));
+                acc2 += (TX)v[1] * ld_xg<COH>(x + (c.y - base));
+                acc += (TX)v[2] * ld_xg<COH>(x + (c.z - base));
+                acc2 += (TX)v[3] * ld_xg<COH>(x + (c.w - base));
             }
             acc += acc2;
             // ragged ends
-            for (int k = k0 + tid; k < ks; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
-            for (int k = ke + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+            for (int k = k0 + tid; k < ks; k += THREADS) acc += (TX)values[k] * ld_xg<COH>(x + (colidx[k] - base));
+            for (int k = ke + tid; k < k1; k += THREADS) acc += (TX)values[k] * ld_xg<COH>(x + (colidx[k] - base));
         } else {
-            for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+            for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * ld_xg<COH>(x + (colidx[k] - base));
         }
     } else {
-        for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * __ldg(x + (colidx[k] - base));
+        for (int k = k0 + tid; k < k1; k += THREADS) acc += (TX)values[k] * ld_xg<COH>(x + (colidx[k] - base));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -255,173 +319,22 @@ __device__ __forceinline__ uint64_t make_evict_last_policy()
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
-// x gather: read-only path (L1-allocating); XH = 1 adds an L2 evict_last hint so the streamed
-// matrix does not push x out of L2
-// (asm volatile on purpose: __ldg is an invariant load the compiler may sink past the barrier
-// that separates "issue all gathers" from "use them")
-template <int XH> __device__ __forceinline__ double ld_x(const double *p, uint64_t pol)
-{
-    double r;
-    if (XH == 0) asm volatile("ld.global.nc.f64 %0, [%1];" : "=d"(r) : "l"(p));
-    else asm volatile("ld.global.nc.L2::cache_hint.f64 %0, [%1], %2;" : "=d"(r) : "l"(p), "l"(pol));
-    return r;
-}
-template <int XH> __device__ __forceinline__ float ld_x(const float *p, uint64_t pol)
-{
-    float r;
-    if (XH == 0) asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(r) : "l"(p));
-    else asm volatile("ld.global.nc.L2::cache_hint.f32 %0, [%1], %2;" : "=f"(r) : "l"(p), "l"(pol));
-    return r;
-}
-
-// NOTE on code shape (measured with cuobjdump): ptxas only keeps many gathers in flight when
-// (a) the kernel states its residency (__launch_bounds__(T, minBlocks)) -- otherwise it aims at 32
-// registers and sinks every load next to its use -- and (b) the loads are NOT predicated (there
-// are 7 predicate registers): out-of-range slots therefore re-read the row's last entry (same
-// cache line as the previous load) and their product is dropped by a select.
-
-// sum over the staged entries k, k+G, k+2G, ... < e of s_val[.] * x[s_col[.]], in that order.
-// Software-pipelined: the x gathers of batch i+1 (B per lane) are issued before batch i is
-// consumed, so up to 2B independent loads are in flight per lane.  FULL batches run without any
-// clamp, predicate or select (6 instructions per entry: LDS col, IMAD.WIDE, LDG, LDS val, MUL,
-// ADD); only the last partial batch of a row pays for the clamped indices and the selects.
-template <typename TV, typename TX, int G, int B, int XH>
-__device__ __forceinline__ TX row_dot(const TV *s_val, const int *s_col, int k, int e, const TX *xb, uint64_t xpol)
-{
-    TX s = 0;
-    if (k >= e) return s;
-    const int last = k + ((e - 1 - k) / G) * G; // this lane's last entry
-    constexpr int SPAN = (B - 1) * G;
-    TX xa[B];
-    if (k + SPAN <= last) {
-#pragma unroll
-        for (int u = 0; u < B; ++u) xa[u] = ld_x<XH>(xb + s_col[k + u * G], xpol);
-    } else {
-#pragma unroll
-        for (int u = 0; u < B; ++u) xa[u] = ld_x<XH>(xb + s_col[min(k + u * G, last)], xpol);
-    }
-    for (;;) {
-        const int kn = k + B * G;
-        TX xn[B];
-        if (kn + SPAN <= last) {
-#pragma unroll
-            for (int u = 0; u < B; ++u) xn[u] = ld_x<XH>(xb + s_col[kn + u * G], xpol);
-        } else if (kn <= last) {
-#pragma unroll
-            for (int u = 0; u < B; ++u) xn[u] = ld_x<XH>(xb + s_col[min(kn + u * G, last)], xpol);
-        }
-        if (k + SPAN <= last) {
-#pragma unroll
-            for (int u = 0; u < B; ++u) s += (TX)s_val[k + u * G] * xa[u];
-        } else {
-#pragma unroll
-            for (int u = 0; u < B; ++u) {
-                const TX p = (TX)s_val[min(k + u * G, last)] * xa[u];
-                s += (k + u * G <= last) ? p : (TX)0;
-            }
-        }
-        if (kn > last) break;
-#pragma unroll
-        for (int u = 0; u < B; ++u) xa[u] = xn[u];
-        k = kn;
-    }
-    return s;
-}
-
-// one thread, one row, every gather of the row in flight at once: the first B1 entries are
-// issued back to back before any of them is used; a longer row continues with the pipelined
-// loop.  Left-to-right summation like the oracle (adding +0 for the unused slots changes nothing).
-template <typename TV, typename TX, int B1, int XH>
-__device__ __forceinline__ TX row_dot_oneshot(const TV *s_val, const int *s_col, int k, int e, const TX *xb, uint64_t xpol)
-{
-    TX s = 0;
-    if (k >= e) return s;
-    const int last = e - 1;
-    TX xa[B1];
-#pragma unroll
-    for (int u = 0; u < B1; ++u) xa[u] = ld_x<XH>(xb + s_col[min(k + u, last)], xpol);
-#pragma unroll
-    for (int u = 0; u < B1; ++u) {
-        const TX p = (TX)s_val[min(k + u, last)] * xa[u];
-        s += (k + u <= last) ? p : (TX)0;
-    }
-    k += B1;
-    if (k <= last) { // rest of a long row: pipelined batches of 8, same order
-        TX xr[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) xr[u] = ld_x<XH>(xb + s_col[min(k + u, last)], xpol);
-        while (k <= last) {
-            const int kn = k + 8;
-            TX xn[8];
-            if (kn <= last) {
-#pragma unroll
-                for (int u = 0; u < 8; ++u) xn[u] = ld_x<XH>(xb + s_col[min(kn + u, last)], xpol);
-            }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const TX p = (TX)s_val[min(k + u, last)] * xr[u];
-                s += (k + u <= last) ? p : (TX)0;
-            }
-#pragma unroll
-            for (int u = 0; u < 8; ++u) xr[u] = xn[u];
-            k = kn;
-        }
-    }
-    return s;
-}
-
-// ---- one thread, one row of at most 32 entries, split in two phases so that the gathers of the
-// NEXT tile's row can be in flight while the current row is consumed (cross-tile pipelining):
-//   row_issue32    : every x gather of the row is issued (groups of 4, no use of the results)
-//   row_consume32  : s = sum_k val_k * x_k, left to right like the oracle
-// Entries k..last (inclusive) index the stage's s_col / s_val; last < k means "no row".
-template <typename TX, int XH>
-__device__ __forceinline__ void row_issue32(const int *s_col, int k, int last, const TX *xb, uint64_t xpol, TX (&xv)[32])
-{
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        if (k + 4 * b <= last) {
-#pragma unroll
-            for (int v = 0; v < 4; ++v) xv[4 * b + v] = ld_x<XH>(xb + s_col[min(k + 4 * b + v, last)], xpol);
-        }
-    }
-}
-template <typename TV, typename TX>
-__device__ __forceinline__ TX row_consume32(const TV *s_val, int k, int last, const TX (&xv)[32])
-{
-    TX s = 0;
-#pragma unroll
-    for (int b = 0; b < 8; ++b) {
-        if (k + 4 * b + 3 <= last) {
-#pragma unroll
-            for (int v = 0; v < 4; ++v) s += (TX)s_val[k + 4 * b + v] * xv[4 * b + v];
-        } else if (k + 4 * b <= last) {
-#pragma unroll
-            for (int v = 0; v < 4; ++v) {
-                const TX p = (TX)s_val[min(k + 4 * b + v, last)] * xv[4 * b + v];
-                s += (k + 4 * b + v <= last) ? p : (TX)0;
-            }
-        }
-    }
-    return s;
-}
-
 // "lean" variant of row_dot for kernels that run MANY warps per SM (stream kernel: no residency
 // hint in __launch_bounds__, so ptxas keeps it at 32-40 registers and 7 CTAs fit an SM): predicated
 // __ldg gathers, a few in flight per lane; the latency is hidden by occupancy instead.  Measured
 // faster than the register-hungry batched form whenever the latter costs resident warps.
-template <typename TV, typename TX, int G, int B>
+template <typename TV, typename TX, int G, int B, bool COH = false>
 __device__ __forceinline__ TX row_dot_lean(const TV *s_val, const int *s_col, int k, int e, const TX *xb)
 {
     TX s = 0;
     TX xa[B];
 #pragma unroll
-    for (int u = 0; u < B; ++u) xa[u] = (k + u * G < e) ? __ldg(xb + s_col[k + u * G]) : (TX)0;
+    for (int u = 0; u < B; ++u) xa[u] = (k + u * G < e) ? ld_xg<COH>(xb + s_col[k + u * G]) : (TX)0;
     while (k < e) {
         const int kn = k + B * G;
         TX xn[B];
 #pragma unroll
-        for (int u = 0; u < B; ++u) xn[u] = (kn + u * G < e) ? __ldg(xb + s_col[kn + u * G]) : (TX)0;
+        for (int u = 0; u < B; ++u) xn[u] = (kn + u * G < e) ? ld_xg<COH>(xb + s_col[kn + u * G]) : (TX)0;
 #pragma unroll
         for (int u = 0; u < B; ++u)
             if (k + u * G < e) s += (TX)s_val[k + u * G] * xa[u];
@@ -436,7 +349,7 @@ __device__ __forceinline__ TX row_dot_lean(const TV *s_val, const int *s_col, in
 // gathers, then B multiply-adds), only the last partial batch is predicated; the gather address is one IMAD.WIDE
 // off an opaque 64-bit base.  (row_dot_lean spends ~17 instructions per entry on a 27-point row: per-entry
 // predicates, a 4-instruction 64-bit address chain, and 16 register moves per batch for its software prefetch.)
-template <typename TV, typename TX, int G, int B>
+template <typename TV, typename TX, int G, int B, bool COH = false>
 __device__ __forceinline__ TX row_dot_lean2(const TV *s_val, const int *s_col, int k, int e, const TX *xb)
 {
     asm volatile("" : "+l"(xb));
@@ -444,7 +357,7 @@ __device__ __forceinline__ TX row_dot_lean2(const TV *s_val, const int *s_col, i
     while (k + (B - 1) * G < e) {
         TX xv[B];
 #pragma unroll
-        for (int u = 0; u < B; ++u) xv[u] = __ldg(xb + s_col[k + u * G]);
+        for (int u = 0; u < B; ++u) xv[u] = ld_xg<COH>(xb + s_col[k + u * G]);
 #pragma unroll
         for (int u = 0; u < B; ++u) s += (TX)s_val[k + u * G] * xv[u];
         k += B * G;
@@ -452,7 +365,7 @@ __device__ __forceinline__ TX row_dot_lean2(const TV *s_val, const int *s_col, i
     if (k < e) {
         TX xv[B];
 #pragma unroll
-        for (int u = 0; u < B; ++u) xv[u] = (k + u * G < e) ? __ldg(xb + s_col[k + u * G]) : (TX)0;
+        for (int u = 0; u < B; ++u) xv[u] = (k + u * G < e) ? ld_xg<COH>(xb + s_col[k + u * G]) : (TX)0;
 #pragma unroll
         for (int u = 0; u < B; ++u)
             if (k + u * G < e) s += (TX)s_val[k + u * G] * xv[u];
@@ -460,20 +373,20 @@ __device__ __forceinline__ TX row_dot_lean2(const TV *s_val, const int *s_col, i
     return s;
 }
 
-template <typename TV, typename TX, int THREADS, int B>
+template <typename TV, typename TX, int THREADS, int B, bool COH = false>
 __device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
                                                   int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
                                                   TX alpha, TX beta)
 {
     const TX *xb = x - base;
     for (int i = threadIdx.x; i < nrows; i += THREADS) {
-        const TX s = row_dot_lean2<TV, TX, 1, B>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
+        const TX s = row_dot_lean2<TV, TX, 1, B, COH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
         store_y(y, row_glob + i, s, alpha, beta);
     }
 }
 
 // G lanes per row with the same unpredicated batches (lane l takes entries l, l+G, ...)
-template <typename TV, typename TX, int THREADS, int G, int B>
+template <typename TV, typename TX, int THREADS, int G, int B, bool COH = false>
 __device__ __forceinline__ void reduce_rows_lean2g(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
                                                    int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
                                                    TX alpha, TX beta)
@@ -485,14 +398,14 @@ __device__ __forceinline__ void reduce_rows_lean2g(const TV *s_val, const int *s
     for (int it = 0; it < iters; ++it) {
         const int i = it * GROUPS + gid;
         TX s = 0;
-        if (i < nrows) s = row_dot_lean2<TV, TX, G, B>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
+        if (i < nrows) s = row_dot_lean2<TV, TX, G, B, COH>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
 #pragma unroll
         for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
         if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
     }
 }
 
-template <typename TV, typename TX, int THREADS, int G>
+template <typename TV, typename TX, int THREADS, int G, bool COH = false>
 __device__ __forceinline__ void reduce_rows_lean(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
                                                  int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
                                                  TX alpha, TX beta)
@@ -501,7 +414,7 @@ __device__ __forceinline__ void reduce_rows_lean(const TV *s_val, const int *s_c
     const TX *xb = x - base;
     if (G == 1) {
         for (int i = tid; i < nrows; i += THREADS) {
-            const TX s = row_dot_lean<TV, TX, 1, 8>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
+            const TX s = row_dot_lean<TV, TX, 1, 8, COH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
             store_y(y, row_glob + i, s, alpha, beta);
         }
     } else {
@@ -511,39 +424,7 @@ __device__ __forceinline__ void reduce_rows_lean(const TV *s_val, const int *s_c
         for (int it = 0; it < iters; ++it) {
             const int i = it * GROUPS + gid;
             TX s = 0;
-            if (i < nrows) s = row_dot_lean<TV, TX, G, 4>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
-#pragma unroll
-            for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
-        }
-    }
-}
-
-// rows of one pass out of the staged raw entries; G lanes per row.  G == 1 keeps the oracle's
-// summation order (left to right, multiply then add).  B1 > 0: whole-row-in-flight gathers.
-template <typename TV, typename TX, int THREADS, int G, int XH, int B1 = 0>
-__device__ __forceinline__ void reduce_rows_gather(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
-                                                   int row_glob, const TX *__restrict__ x, int base, uint64_t xpol,
-                                                   TX *__restrict__ y, TX alpha, TX beta)
-{
-    const int tid = threadIdx.x;
-    const TX *xb = x - base;
-    asm volatile("" : "+l"(xb)); // opaque: keeps the gather address a single IMAD.WIDE (col, 8, xb)
-    if (G == 1) {
-        for (int i = tid; i < nrows; i += THREADS) {
-            TX s;
-            if (B1 >= 32) s = row_dot_oneshot<TV, TX, (B1 > 0 ? B1 : 8), XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
-            else s = row_dot<TV, TX, 1, 8, XH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb, xpol);
-            store_y(y, row_glob + i, s, alpha, beta);
-        }
-    } else {
-        constexpr int GROUPS = THREADS / G;
-        const int gid = tid / G, lane = tid % G;
-        const int iters = (nrows + GROUPS - 1) / GROUPS;
-        for (int it = 0; it < iters; ++it) {
-            const int i = it * GROUPS + gid;
-            TX s = 0;
-            if (i < nrows) s = row_dot<TV, TX, G, (G <= 4 ? 8 : 4), XH>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb, xpol);
+            if (i < nrows) s = row_dot_lean<TV, TX, G, 4, COH>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
 #pragma unroll
             for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
             if (i < nrows && lane == 0) store_y(y, row_glob + i, s, alpha, beta);

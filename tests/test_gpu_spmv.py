@@ -64,7 +64,7 @@ SMALL = {
 
 @pytest.mark.parametrize("name", sorted(SMALL))
 @pytest.mark.parametrize("precision", ["d", "s", "m"])
-@pytest.mark.parametrize("algo", ["auto", "tile", "pipe", "stream", "rowblock", "merge", "vector", "scalar"])
+@pytest.mark.parametrize("algo", ["auto", "window", "tile", "rowblock", "merge", "vector", "scalar"])
 def test_spmv_small(handle, name, precision, algo):
     a = SMALL[name]()
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -85,7 +85,7 @@ def test_golden_b1ss_values(handle):
 
 
 @pytest.mark.parametrize("precision", ["d", "s", "m"])
-@pytest.mark.parametrize("algo", ["tile", "pipe", "stream", "rowblock", "merge", "vector"])
+@pytest.mark.parametrize("algo", ["window", "tile", "rowblock", "merge", "vector"])
 def test_alpha_beta(handle, precision, algo):
     a = host.gen_stencil27(9, 10, 11, seed=5)
     handle.set_option("SPMV_ALGO", ALGO[algo])
@@ -123,40 +123,108 @@ def test_rowblock_variants(handle, variant, reduce):
         handle.set_option("SPMV_REDUCE", 0)
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 3, 4, 5])
+WINDOWED = {
+    "lap2d_37": lambda: host.gen_laplace2d(37),
+    "stencil27_11": lambda: host.gen_stencil27(11, 12, 13, seed=4),
+    "stencil27_slab": lambda: host.gen_stencil27(12, 12, 30, 10, 20, seed=2),
+    "femlike_14": lambda: host.gen_femlike(14, 0.7, 9),
+    "b1_ss_base1": lambda: host.load_matrix_market(os.path.join(GOLD, "b1_ss.mtx"), 1),
+    "bcspwr01": lambda: host.load_matrix_market(os.path.join(GOLD, "bcspwr01.mtx")),
+    "rect": lambda: host.load_matrix_market(os.path.join(GOLD, "rect.mtx")),
+    "empty_rows": lambda: host.load_matrix_market(os.path.join(GOLD, "empty_rows.mtx")),
+}
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2])
 @pytest.mark.parametrize("reduce", [0, 1, 2, 4, 8, 16, 32])
-def test_stream_variants(handle, variant, reduce):
-    """every compiled tile shape x every lanes-per-row reduction of the TMA-staged kernel"""
-    handle.set_option("SPMV_ALGO", ALGO["stream"])
+@pytest.mark.parametrize("win_bytes", [0, 8192, 20000, 90000])
+def test_window_variants(handle, variant, reduce, win_bytes):
+    """every CTA width x every lanes-per-row reduction x tile budgets (many small tiles ... few fat ones) of the
+    x-window kernel; thread-per-row sums left to right like the oracle: bit-exact"""
+    handle.set_option("SPMV_ALGO", ALGO["window"])
     handle.set_option("SPMV_VARIANT", variant)
     handle.set_option("SPMV_REDUCE", reduce)
+    handle.set_option("SPMV_WIN_BYTES", win_bytes)
     try:
-        for a in (host.gen_femlike(14, 0.7, 9), host.gen_powerlaw(6000, 2.2, 48, 2, 700 + 611 * variant, 4)):
+        for name in sorted(WINDOWED):
+            a = WINDOWED[name]()
             x = orc.dlarnv(a.n) - 0.5
             for p in ("d", "s", "m"):
                 check(handle, a, x, p)
-        if reduce == 1:  # thread-per-row sums left to right like the oracle: bit-exact
-            a = host.gen_stencil27(11, 12, 13, seed=4)
-            x = orc.dlarnv(a.n) - 0.5
-            A = DeviceCSR(a, "d")
-            y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
-            assert np.array_equal(y, orc.spmv(a, x, "d"))
+            if a.m >= 64:
+                assert handle.info("SPMV_ALGO_USED") == ALGO["window"], name
+            if reduce == 1:
+                A = DeviceCSR(a, "d")
+                y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
+                assert np.array_equal(y, orc.spmv(a, x, "d")), name
     finally:
         handle.set_option("SPMV_ALGO", 0)
         handle.set_option("SPMV_VARIANT", 0)
         handle.set_option("SPMV_REDUCE", 0)
+        handle.set_option("SPMV_WIN_BYTES", 0)
 
 
-@pytest.mark.parametrize("variant", list(range(10)))
+def test_window_ragged_ends_and_views(handle):
+    """x lengths that are not multiples of 4 (the last entries of x travel by plain loads), entry counts that are not
+    multiples of 8 (the last entries of a tile too), row-slab views whose first entry is not entry 0, a gap setting
+    that merges every run into one, and an x view that is not 16-byte aligned (falls back to the tile plan)."""
+    handle.set_option("SPMV_ALGO", ALGO["window"])
+    try:
+        for n in (61, 62, 63, 64, 65, 67, 130):
+            rng = np.random.default_rng(n)
+            m = n + 3
+            rows = []
+            for i in range(m):  # banded rows that reach the last columns, ragged lengths
+                c0 = min(max(0, i - 3), n - 1)
+                cs = sorted(set(range(c0, min(n, c0 + 1 + int(rng.integers(0, 7))))) | {n - 1 - (i % 3)})
+                rows.append(cs)
+            rp = np.zeros(m + 1, dtype=np.int32); rp[1:] = np.cumsum([len(r) for r in rows])
+            ci = np.fromiter((c for r in rows for c in r), dtype=np.int32, count=int(rp[-1]))
+            a = host.CSR(m, n, int(rp[-1]), rp, ci, rng.uniform(-1, 1, int(rp[-1])), 0)
+            x = orc.dlarnv(n) - 0.5
+            for p in ("d", "s", "m"):
+                check(handle, a, x, p, alpha=1.25, beta=-0.5, y0=orc.dlarnv(m) - 0.5)
+            assert handle.info("SPMV_ALGO_USED") == ALGO["window"]
+        a = host.gen_stencil27(12, 12, 30, 10, 20, seed=2)
+        x = orc.dlarnv(a.n) - 0.5
+        A = DeviceCSR(a, "d")
+        xd = torch.from_numpy(x).cuda()
+        ref = orc.spmv(a, x, "d")
+        for r0, r1 in ((0, a.m), (5, 700), (333, a.m), (1001, 1002)):
+            y = handle.spmv(A.view_rows(r0, r1), xd).cpu().numpy()
+            assert np.array_equal(y, ref[r0:r1]), (r0, r1)
+        for gap in (1, 100000):
+            handle.set_option("SPMV_WIN_GAP", gap)
+            assert np.array_equal(handle.spmv(DeviceCSR(a, "d"), xd).cpu().numpy(), ref)
+        handle.set_option("SPMV_WIN_GAP", 0)
+        xo = torch.empty(a.n + 1, dtype=torch.float64, device="cuda")
+        xo[1:] = xd
+        y = handle.spmv(A, xo[1:]).cpu().numpy()
+        assert np.abs(y - ref).max() <= 1e-12 * np.abs(ref).max()
+        assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+    finally:
+        handle.set_option("SPMV_ALGO", 0)
+        handle.set_option("SPMV_WIN_GAP", 0)
+
+
+def test_window_declines_scattered_patterns(handle):
+    """hashed columns / dense rows have no compact x windows: the plan falls back (AUTO: vector or tile), results unchanged"""
+    a = host.gen_powerlaw(20000, 2.2, 64, 2, 9000, 4)
+    x = orc.dlarnv(a.n) - 0.5
+    for algo in ("window", "auto"):
+        handle.set_option("SPMV_ALGO", ALGO[algo])
+        check(handle, a, x, "d")
+        assert handle.info("SPMV_ALGO_USED") != ALGO["window"]
+    handle.set_option("SPMV_ALGO", 0)
+
+
+@pytest.mark.parametrize("variant", list(range(8)))
 @pytest.mark.parametrize("reduce", [0, 1, 4, 32])
 @pytest.mark.parametrize("rpt", [0, 3])
-@pytest.mark.parametrize("algo", ["pipe", "tile"])
-def test_pipe_variants(handle, variant, reduce, rpt, algo):
-    if algo == "pipe" and variant >= 8:
-        pytest.skip("the pipe kernel has 8 shapes")
-    """every compiled shape of the pipelined (persistent, stage ring) and tile (one tile per CTA) kernels:
-    fitting tiles, multi-pass tiles (rows longer than the tile slack), CTA-per-row rows, a ragged last quad"""
-    handle.set_option("SPMV_ALGO", ALGO[algo])
+def test_tile_variants(handle, variant, reduce, rpt):
+    """every compiled shape of the tile kernel (one tile per CTA): fitting tiles, multi-pass tiles (rows longer than
+    the tile slack), CTA-per-row rows, a ragged last quad.  (The retired pipe / stream enum values select it too.)"""
+    handle.set_option("SPMV_ALGO", ALGO["pipe" if variant == 0 and rpt == 3 else "stream" if variant == 0 else "tile"])
     handle.set_option("SPMV_VARIANT", variant)
     handle.set_option("SPMV_REDUCE", reduce)
     handle.set_option("SPMV_ROWS_PER_THREAD", rpt)
@@ -167,6 +235,7 @@ def test_pipe_variants(handle, variant, reduce, rpt, algo):
             x = orc.dlarnv(a.n) - 0.5
             for p in ("d", "s", "m"):
                 check(handle, a, x, p)
+            assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
         if reduce == 1:  # thread-per-row sums left to right like the oracle: bit-exact
             a = host.gen_stencil27(11, 12, 13, seed=4)
             x = orc.dlarnv(a.n) - 0.5
@@ -183,8 +252,7 @@ def test_pipe_variants(handle, variant, reduce, rpt, algo):
 def test_pipe_tiny_tiles_and_slabs(handle):
     """tile size forced down to 64 items: many tiles per CTA, empty tiles inside long rows, slab views
     whose first entry is not entry 0"""
-    for algo in ("pipe", "tile"):
-        _tiny_tiles(handle, algo)
+    _tiny_tiles(handle, "tile")
 
 
 def _tiny_tiles(handle, algo):
@@ -208,9 +276,8 @@ def test_cache_hints(handle, hint, persist):
     handle.set_option("SPMV_CACHE_HINT", hint)
     handle.set_option("SPMV_X_PERSIST", persist)
     try:
-        for algo in ("pipe", "stream", "rowblock", "merge"):
+        for algo in ("window", "tile", "rowblock", "merge"):
             handle.set_option("SPMV_ALGO", ALGO[algo])
-            handle.set_option("SPMV_X_HINT", persist)
             check(handle, a, orc.dlarnv(a.n), "d")
             check(handle, a, orc.dlarnv(a.n), "m")
     finally:
@@ -224,7 +291,7 @@ def test_long_rows_cta_per_row_and_merge(handle):
     # rows far longer than a tile: the row-block kernel falls to CTA-per-row, AUTO picks the tile kernel with split rows
     a = host.gen_powerlaw(60000, 2.2, 32, 3, 50000, 7)
     x = orc.dlarnv(a.n) - 0.5
-    for algo in ("pipe", "stream", "rowblock", "merge", "tile", "auto"):
+    for algo in ("window", "rowblock", "merge", "tile", "auto"):
         handle.set_option("SPMV_ALGO", ALGO[algo])
         for p in ("d", "s", "m"):
             check(handle, a, x, p)
@@ -244,7 +311,7 @@ def test_unaligned_views_take_scalar_path(handle):
     A.colidx, A.values = ci[1:], va[1:]
     x = orc.dlarnv(a.n)
     ref = orc.spmv(a, x)
-    for algo in ("auto", "pipe", "stream", "rowblock", "merge"):  # pipe/stream fall back to rowblock's scalar staging
+    for algo in ("auto", "window", "tile", "rowblock", "merge"):  # window / tile fall back to rowblock's scalar staging
         handle.set_option("SPMV_ALGO", ALGO[algo])
         y = handle.spmv(A, torch.from_numpy(x).cuda()).cpu().numpy()
         assert np.abs(y - ref).max() <= 1e-12 * np.abs(ref).max()
@@ -260,7 +327,7 @@ def test_empty_and_degenerate(handle):
     e = host.CSR(5, 5, 0, np.zeros(6, np.int32), np.zeros(0, np.int32), np.zeros(0))
     E = DeviceCSR(e, "d")
     E.colidx = torch.zeros(1, dtype=torch.int32, device="cuda"); E.values = torch.zeros(1, dtype=torch.float64, device="cuda")
-    for algo in ("pipe", "stream", "rowblock", "merge", "vector", "scalar"):
+    for algo in ("window", "tile", "rowblock", "merge", "vector", "scalar"):
         handle.set_option("SPMV_ALGO", ALGO[algo])
         y = handle.spmv(E, torch.ones(5, dtype=torch.float64, device="cuda"),
                         torch.full((5,), 7.0, dtype=torch.float64, device="cuda"))
@@ -358,12 +425,15 @@ def test_auto_picks_the_unstaged_kernel_for_scattered_columns(handle):
         check(handle, a, x_of(a), p)
         assert handle.info("SPMV_ALGO_USED") == ALGO["vector"]
     check(handle, a, x_of(a), "d", alpha=-0.5, beta=2.0, y0=orc.dlarnv(a.m))
-    for b in (host.gen_stencil27(30, seed=2), host.gen_femlike(24), host.gen_banded(60000, 8, 6000)):
+    b = host.gen_banded(60000, 8, 6000)
+    check(handle, b, x_of(b), "d")
+    assert handle.info("SPMV_ALGO_USED") == ALGO["vector"]
+    for b in (host.gen_stencil27(30, seed=2), host.gen_femlike(24), host.gen_stencil27(60, seed=2)):  # neighbour coherence: x windows
         check(handle, b, x_of(b), "d")
-        assert handle.info("SPMV_ALGO_USED") == ALGO["vector"]
-    for b in (host.gen_stencil27(60, seed=2), host.gen_powerlaw(60000, 2.2, 64, 3, 20000, 4)):
-        check(handle, b, x_of(b), "d")
-        assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
+        assert handle.info("SPMV_ALGO_USED") == ALGO["window"]
+    b = host.gen_powerlaw(60000, 2.2, 64, 3, 20000, 4)
+    check(handle, b, x_of(b), "d")
+    assert handle.info("SPMV_ALGO_USED") == ALGO["tile"]
     # one row far longer than the rest in a small matrix: the sub-warp kernel would crawl through it
     c = host.gen_powerlaw(20000, 2.2, 48, 1, 3000, 4)
     check(handle, c, x_of(c), "d")
@@ -469,9 +539,9 @@ def test_full_size_configs(handle, name):
         y = check(handle, a, x, p)
         if p == "d":
             yd = y
-    # C1 is L2-resident with short rows: the batched sub-warp kernel; C2 streams: tiles; C4: tiles, its 4 rows of
-    # 100 002 entries split into segments
-    assert handle.info("SPMV_ALGO_USED") == (ALGO["vector"] if name == "C1" else ALGO["tile"])
+    # C1 and C2 are stencils: the x-window kernel; C4 (hashed columns, 4 rows of 100 002 entries): tiles, the long
+    # rows split into segments
+    assert handle.info("SPMV_ALGO_USED") == (ALGO["tile"] if name == "C4" else ALGO["window"])
     # linearity: A(2x + 1) = 2 A x + A 1
     A = DeviceCSR(a, "d")
     xd = torch.from_numpy(x).cuda()
@@ -520,11 +590,16 @@ def test_halo_push_kernel(handle, dtype):
 
 
 @pytest.mark.gpu
-def test_halo_push_signal_and_in_kernel_wait(handle):
-    """Two ranks emulated on one device: rank 0's block (columns relabelled by HaloPlan) is multiplied while
-    'rank 1' pushes its boundary entries LATE, from another stream.  The tiles that read halo columns must
-    wait for the arrival flag (rsg_spmv_halo_wait); the result must equal the oracle's rows of the full product."""
+@pytest.mark.parametrize("algo", ["window", "tile"])
+def test_halo_push_signal_and_in_kernel_wait(handle, algo):
+    """Two ranks emulated on one device, in ONE stream (kernels that spin on each other must never be separate
+    launches on one GPU): 'rank 1' pushes its boundary entries and signals, then rank 0's block (columns relabelled
+    by HaloPlan) is multiplied with the wait armed -- its halo tiles acquire the flag, copy / gather the pushed
+    entries, and the result must equal the oracle's rows of the full product.  Then the fused form (the product's
+    own first CTAs push and signal), the one-shot property, and a wait that can never be satisfied: it must give
+    up and surface as RSG_DEPENDENCY_TIMEOUT at the next rsg_synchronize."""
     from respasol_b200.dist import HaloPlan
+    from respasol_b200.gpu import RsgError
     full = host.gen_stencil27(24, 24, 40, seed=2)
     starts = np.array([0, full.m // 2, full.m])
     plans = [HaloPlan(full.rows(int(starts[r]), int(starts[r + 1])), starts, r) for r in range(2)]
@@ -534,6 +609,7 @@ def test_halo_push_signal_and_in_kernel_wait(handle):
     p0, p1 = plans
     x = orc.dlarnv(full.n) - 0.5
     ref = orc.spmv(full, x, "d")[:p0.n_local]
+    handle.set_option("SPMV_ALGO", ALGO[algo])
     handle.set_option("SPMV_HALO_START", p0.halo_base)
     try:
         A = DeviceCSR(p0.remapped, "d")
@@ -545,27 +621,15 @@ def test_halo_push_signal_and_in_kernel_wait(handle):
         flags = torch.zeros(32, dtype=torch.int32, device="cuda")
         slot = x_ext[p0.halo_base + 1 * p0.width:].data_ptr()             # rank 1's slot in rank 0's halo
         other = Handle(0)
-        side = torch.cuda.Stream()
         y = torch.empty(p0.n_local, dtype=torch.float64, device="cuda")
-        # first launches load their modules, which may wait for running kernels: do that before anything spins
-        with torch.cuda.stream(side):
-            other.use_current_stream()
-            torch.cuda._sleep(1000)
-            other.halo_push(send1, x1, [slot], [flags[8:].data_ptr()], 1)
-        torch.cuda.synchronize()
         for epoch in (1, 2):
             x_ext[p0.halo_base:].fill_(float("nan"))
-            torch.cuda.synchronize()
-            # flags[0] (this rank's own signal) is set up front, flags[1] arrives while the product runs
-            flags[0] = epoch
-            torch.cuda.synchronize()
+            flags[0] = epoch                                              # this rank's own signal
+            other.halo_push(send1, x1, [slot], [flags[1:].data_ptr()], epoch)
             handle.spmv_halo_wait(flags, 2, epoch)
             handle.spmv(A, x_ext, y)
-            with torch.cuda.stream(side):
-                other.use_current_stream()
-                torch.cuda._sleep(2_000_000)  # ~1 ms: the product is long spinning by now
-                other.halo_push(send1, x1, [slot], [flags[1:].data_ptr()], epoch)
-            torch.cuda.synchronize()
+            handle.synchronize()
+            assert handle.info("SPMV_ALGO_USED") == ALGO[algo]
             assert int(flags[1].item()) == epoch
             got = y.cpu().numpy()
             assert np.abs(got - ref).max() <= 1e-12 * np.abs(ref).max()
@@ -579,7 +643,7 @@ def test_halo_push_signal_and_in_kernel_wait(handle):
         handle.spmv_halo_wait(flags, 2, 7)
         y.fill_(0)
         handle.spmv(A, x_ext, y)
-        torch.cuda.synchronize()
+        handle.synchronize()
         assert int(peer_flags[0].item()) == 7
         want = torch.from_numpy(x[:p0.n_local][p0.my_send]).cuda()
         assert torch.equal(peer_halo[p1.halo_base:p1.halo_base + len(p0.my_send)], want)
@@ -587,8 +651,18 @@ def test_halo_push_signal_and_in_kernel_wait(handle):
         # one-shot: the next plain product neither pushes nor waits
         peer_flags.zero_()
         handle.spmv(A, x_ext, y)
-        torch.cuda.synchronize()
+        handle.synchronize()
         assert int(peer_flags[0].item()) == 0 and np.abs(y.cpu().numpy() - ref).max() <= 1e-12 * np.abs(ref).max()
+        # a flag that never arrives: the wait gives up after RSG_OPT_WAIT_SPINS polls and the handle reports it once
+        handle.set_option("WAIT_SPINS", 3000)
+        handle.spmv_halo_wait(flags, 2, 1000)
+        handle.spmv(A, x_ext, y)
+        with pytest.raises(RsgError) as ei:
+            handle.synchronize()
+        assert ei.value.status == 7  # RSG_DEPENDENCY_TIMEOUT
+        handle.synchronize()
         other.close()
     finally:
+        handle.set_option("WAIT_SPINS", 0)
+        handle.set_option("SPMV_ALGO", 0)
         handle.set_option("SPMV_HALO_START", 0)
