@@ -94,7 +94,7 @@ typedef enum {
                                    untransposed one does; 0 = read the values through the cached permutation on every call
                                    (default, always right: fused kernel, or gather + product when a column is longer
                                    than 2048 entries); 2 = always gather + product (A/B) */
-    RSG_OPT_SPMV_WIN_BYTES = 20, /* window kernel: shared memory per CTA the plan aims at (bytes; 0 = default 44 KB) */
+    RSG_OPT_SPMV_WIN_BYTES = 20, /* window kernel: shared memory per CTA the plan aims at (bytes; 0 = default 36 KB) */
     RSG_OPT_SPMV_WIN_STREAM_PCT = 21, /* window kernel: share of that given to the entries (values + 16-bit columns), percent (0 = 64) */
     RSG_OPT_SPMV_WIN_GAP = 22,  /* window kernel plan: runs of x separated by up to this many unused 4-column granules are merged (0 = 3) */
     RSG_OPT_WAIT_SPINS = 23,    /* polls a device-side dependency / halo wait may spend before it gives up and the next

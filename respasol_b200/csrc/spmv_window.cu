@@ -172,9 +172,10 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     int g = reduce_opt & 0xff;
     if (g == 0) { // lanes per row from the tile's row lengths
         const int avg = nk / nr;
+        // rows of up to 40 entries: ALWAYS a thread per row, so that their sums run left to right like the oracle's
+        // whatever the tile they fall into (bit-exact, and independent of how the matrix was cut)
         g = avg <= 40 ? 1 : avg <= 80 ? 4 : avg <= 160 ? 8 : avg <= 320 ? 16 : 32;
-        while (g < 32 && nr * g * 2 <= THREADS) g <<= 1; // few rows: spread them over the CTA
-        if (g == 2 && avg <= 12) g = 1;
+        while (g > 1 && g < 32 && nr * g * 2 <= THREADS) g <<= 1; // few long rows: spread them over the CTA
     }
     switch (g) {
     case 1: win_rows<TV, TX, THREADS, 1>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
@@ -350,7 +351,7 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     const int m = p.m;
     const int eb = vbytes + 2;
     int target = h->opts[RSG_OPT_SPMV_WIN_BYTES]; // shared memory per CTA aimed at
-    if (target <= 0) target = 44 * 1024;
+    if (target <= 0) target = 36 * 1024; // 6 CTAs per SM (tools/spmv_sweep.py: 28-45 KB within 1 % on fp64, best for fp32 / mixed)
     target = std::min(std::max(target, 8 * 1024), 160 * 1024);
     int pct = h->opts[RSG_OPT_SPMV_WIN_STREAM_PCT]; // share of it given to the entries (the rest: x window, row pointers)
     if (pct <= 0) pct = 64;
