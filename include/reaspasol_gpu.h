@@ -40,6 +40,8 @@ extern "C" {
 
 typedef struct rsg_context *rsg_handle_t;
 typedef struct rsg_matrix *rsg_matrix_t;
+typedef struct rsg_dist *rsg_dist_t;   /* one rank's side of the row-block product (one process or thread per GPU) */
+typedef struct rsg_multi *rsg_multi_t; /* a whole matrix over N devices of one process */
 
 typedef enum {
     RSG_OK = 0,
@@ -221,6 +223,46 @@ int rsg_spmv_halo_wait(rsg_handle_t handle, const int *flags, int nflags, int ep
  * TILE kernel only. */
 int rsg_spmv_halo_fuse(rsg_handle_t handle, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
                        int *const *peer_flags, int epoch);
+
+/* Same as rsg_spmv_halo_fuse; peer q is sent only the entries j in [peer_lo[q], peer_hi[q]) of the send list (NULL: all):
+ * each boundary plane goes to the neighbour that reads it, not to every reader. */
+int rsg_spmv_halo_fuse_ranges(rsg_handle_t handle, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
+                              int *const *peer_flags, const int *peer_lo, const int *peer_hi, int epoch);
+
+/* ---- multi-GPU row-block SpMV (SURVEY.md 8b "multi-GPU entry point", 8e) -------------------------------------------- */
+/* One rank's side, everything a step needs bound ONCE (the product of /root/reference/GPU/spmv.cu:184-186 for this
+ * rank's row block, plus the exchange step north_star names).  The block's CSR has its columns relabelled into
+ * [local entries | pad | npeers halo slots] (halo_start = first halo column); x lives in TWO images of that layout
+ * (x_images[0..1], peer-mapped), used in turn so that a rank one step ahead never overwrites a halo a neighbour still reads.
+ * peer_slots / peer_flags: HOST arrays of 2*npeers DEVICE pointers, image-major ([p*npeers + q]): where peer q keeps THIS
+ * rank's slot of its image-p halo (NULL: q reads nothing from this rank) and the arrival flag it awaits from this rank
+ * (NULL: not a neighbour).  wait_flags[p]: this rank's own nwait flags of image p.  precision 'd' | 's' | 'm'. */
+int rsg_dist_create(rsg_handle_t handle, char precision, int m, int n_ext, int nnz, int base, const int *rowptr,
+                    const int *colidx, const void *values, void *const *x_images, int halo_start, int nsend,
+                    const int *send_idx, int npeers, void *const *peer_slots, int *const *peer_flags, const int *peer_lo,
+                    const int *peer_hi, const int *const *wait_flags, int nwait, rsg_dist_t *dist);
+/* y = A_block * x: ONE kernel launch on the handle's stream -- its first CTAs push this rank's boundary entries of x
+ * (image of this step) into the peers' slots and release the step number to their flags, its halo tiles (and always its
+ * last tile) acquire the neighbours' flags before they read x.  Asynchronous. */
+int rsg_dist_step(rsg_dist_t dist, void *y);
+void *rsg_dist_x(rsg_dist_t dist); /* DEVICE pointer of the x image the NEXT step reads (write the local entries there) */
+int rsg_dist_destroy(rsg_dist_t dist);
+
+/* A whole square CSR matrix (HOST arrays, values fp64 like the reference's struct CSR) over ngpu devices of this process:
+ * row blocks (row_starts: ngpu+1 cuts, or NULL for the nnz-balanced cuts of rsg_get_row_partition), halo relabelling,
+ * peer access, one handle and one rsg_dist per device, one host thread per device issuing its steps.  devices: ngpu
+ * ordinals (NULL: 0..ngpu-1).  RSG_UNSUPPORTED without peer access between the devices. */
+int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, int n, int nnz, int base,
+                          const int *rowptr_host, const int *colidx_host, const double *values_host,
+                          const int *row_starts, rsg_multi_t *multi);
+int rsg_spmv_multi_set_x(rsg_multi_t multi, const void *x_host);            /* n entries: fp64 ('d','m') or fp32 ('s') */
+int rsg_spmv_multi_step(rsg_multi_t multi, int nsteps);                     /* nsteps products, asynchronous */
+int rsg_spmv_multi_time(rsg_multi_t multi, int nsteps, double *us_per_step); /* timed on the devices, slowest device */
+int rsg_spmv_multi_get_y(rsg_multi_t multi, void *y_host);                  /* waits, gathers the m entries of y */
+/* what: 0 ranks, 1 halo bytes all ranks receive per step, 2 rsg_spmv_algo of rank 0's last product, 3 halo slot width;
+ * row_starts (may be NULL): ngpu+1 ints */
+int rsg_spmv_multi_info(rsg_multi_t multi, int what, long long *value, int *row_starts);
+int rsg_spmv_multi_destroy(rsg_multi_t multi);
 
 /* ---- preconditioned conjugate gradients on the three calls above -------------------------- */
 /* Solves A x = b for a symmetric positive definite CSR matrix (device arrays; x holds the initial guess on entry).

@@ -1,0 +1,471 @@
+// dist.cu -- the multi-GPU entry points of the C ABI ("multi-GPU entry point takes an array of
+// handles"; 8e: row-block SpMV across the box).  No counterpart in the reference, whose harness drives one GPU
+// (/root/reference/GPU/spmv.cu:174-207); this is the shape a C++ caller of that harness needs to reach 8 GPUs.
+//
+//   rsg_dist_*        ONE rank's side of the row-block product, everything a step needs bound once: the block's
+//                     CSR with relabelled columns, the two x images ([local | halo], peer-mapped), the peers' halo
+//                     slots / arrival flags and the range of the send list each peer reads.  rsg_dist_step = arm the
+//                     fused push + the in-kernel wait + launch the product: ONE library call, ONE kernel launch per
+//                     step.  Used by the one-process-per-GPU path (respasol_b200/dist.py under torchrun, memory mapped
+//                     through torch symmetric memory / CUDA IPC) and by rsg_spmv_multi_* below.
+//   rsg_spmv_multi_*  a whole matrix over N devices of ONE process: partition (the rsg_get_row_partition formula, or the
+//                     caller's cuts), halo relabelling, peer access (cudaDeviceEnablePeerAccess), one handle + one
+//                     rsg_dist per device, one host thread per device issuing its steps.  bin/test_spmv --gpus N.
+//
+// Protocol (unchanged from round 1, now in one place): step e uses image p = (e-1) & 1.  A rank's launch first stores
+// its boundary entries of image p into the readers' image-p halo slots and releases e to their flags; tiles that read
+// halo columns (and, always, the last tile) acquire flags[p][i] >= e from every neighbour.  A rank therefore never runs
+// more than one step ahead of a neighbour, which is what makes two images enough.
+#include "rsg_internal.cuh"
+
+#include <cstring>
+#include <map>
+#include <new>
+#include <thread>
+
+using namespace rsg;
+
+struct rsg_dist {
+    rsg_context *h = nullptr;
+    char precision = 'd';
+    int m = 0, n_ext = 0, nnz = 0, base = 0, halo_start = 0;
+    const int *rowptr = nullptr, *colidx = nullptr;
+    const void *values = nullptr;
+    void *x_image[2] = {nullptr, nullptr};
+    HaloFuse fuse[2];
+    const int *wait_flags[2] = {nullptr, nullptr};
+    int nwait = 0, epoch = 0;
+};
+
+namespace {
+
+struct DevGuard {
+    int prev = -1;
+    explicit DevGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DevGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+inline int halo_base_of(int n_local) { return (n_local + 31) / 32 * 32; } // the halo starts on its own 128/256-byte line
+
+} // namespace
+
+extern "C" {
+
+int rsg_dist_create(rsg_handle_t h, char precision, int m, int n_ext, int nnz, int base, const int *rowptr, const int *colidx,
+                    const void *values, void *const *x_images, int halo_start, int nsend, const int *send_idx, int npeers,
+                    void *const *peer_slots, int *const *peer_flags, const int *peer_lo, const int *peer_hi,
+                    const int *const *wait_flags, int nwait, rsg_dist_t *out)
+{
+    if (!h || !out || m < 0 || n_ext < 0 || !rowptr || !x_images || !x_images[0] || !x_images[1] || npeers < 0 || npeers > RSG_MAX_PEERS ||
+        nwait < 0 || nwait > RSG_MAX_PEERS || (precision != 'd' && precision != 's' && precision != 'm') ||
+        (npeers > 0 && (!peer_slots || !peer_flags)) || (nwait > 0 && (!wait_flags || !wait_flags[0] || !wait_flags[1])) ||
+        (nsend > 0 && !send_idx))
+        return RSG_BAD_ARG;
+    *out = nullptr;
+    rsg_dist *d = new (std::nothrow) rsg_dist();
+    if (!d) return RSG_ALLOC_FAILED;
+    d->h = h; d->precision = precision; d->m = m; d->n_ext = n_ext; d->nnz = nnz; d->base = base; d->halo_start = halo_start;
+    d->rowptr = rowptr; d->colidx = colidx; d->values = values;
+    d->nwait = nwait;
+    for (int p = 0; p < 2; ++p) {
+        d->x_image[p] = x_images[p];
+        d->wait_flags[p] = nwait > 0 ? wait_flags[p] : nullptr;
+        HaloFuse &f = d->fuse[p];
+        std::memset(&f, 0, sizeof(f));
+        for (int q = 0; q < npeers; ++q) { // image-major: [p * npeers + q]
+            f.dst[q] = peer_slots[p * npeers + q];
+            f.flag[q] = peer_flags[p * npeers + q];
+            f.lo[q] = peer_lo ? peer_lo[q] : 0;
+            f.hi[q] = peer_hi ? peer_hi[q] : nsend;
+        }
+        f.send_idx = send_idx;
+        f.counter = h->scratch_i + 62;
+        f.nsend = nsend; f.npeers = npeers; f.ctas = npeers > 0 ? 1 : 0;
+    }
+    // the plan of this block, halo tiles marked, now (so that no step pays for an analysis)
+    DevGuard g(h->device);
+    const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
+    h->opts[RSG_OPT_SPMV_HALO_START] = halo_start;
+    SpmvPlan *pl = nullptr;
+    const int pkey = precision == 'd' ? 0x88 : precision == 's' ? 0x44 : 0x84;
+    const int rc = m > 0 ? spmv_get_plan(h, m, n_ext, nnz, base, rowptr, colidx, false, &pl, pkey) : RSG_OK;
+    h->opts[RSG_OPT_SPMV_HALO_START] = keep;
+    if (rc != RSG_OK) { delete d; return rc; }
+    *out = d;
+    return RSG_OK;
+}
+
+int rsg_dist_destroy(rsg_dist_t d)
+{
+    if (!d) return RSG_BAD_ARG;
+    delete d;
+    return RSG_OK;
+}
+
+void *rsg_dist_x(rsg_dist_t d) { return d ? d->x_image[d->epoch & 1] : nullptr; } // the image the NEXT step reads
+
+int rsg_dist_step(rsg_dist_t d, void *y)
+{
+    if (!d || (d->m > 0 && !y)) return RSG_BAD_ARG;
+    rsg_context *h = d->h;
+    DevGuard g(h->device);
+    const int p = d->epoch & 1; // step e = epoch + 1 uses image (e - 1) & 1
+    d->epoch += 1;
+    if (d->fuse[p].npeers > 0) {
+        h->fuse = d->fuse[p];
+        h->fuse.epoch = d->epoch;
+    }
+    if (d->nwait > 0) { h->wait_flags = d->wait_flags[p]; h->wait_n = d->nwait; h->wait_epoch = d->epoch; }
+    const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
+    h->opts[RSG_OPT_SPMV_HALO_START] = d->halo_start; // part of the plan's key
+    int rc;
+    if (d->precision == 'd')
+        rc = spmv_run<double, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const double *>(d->values), 1.0,
+                                      static_cast<const double *>(d->x_image[p]), 0.0, static_cast<double *>(y));
+    else if (d->precision == 's')
+        rc = spmv_run<float, float>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const float *>(d->values), 1.0f,
+                                    static_cast<const float *>(d->x_image[p]), 0.0f, static_cast<float *>(y));
+    else
+        rc = spmv_run<float, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const float *>(d->values), 1.0,
+                                     static_cast<const double *>(d->x_image[p]), 0.0, static_cast<double *>(y));
+    h->opts[RSG_OPT_SPMV_HALO_START] = keep;
+    h->wait_flags = nullptr;
+    h->fuse.ctas = 0;
+    return rc;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// Single process, N devices.
+struct rsg_multi {
+    int P = 0;
+    char precision = 'd';
+    int m = 0, n = 0, base = 0;
+    size_t vs = 8, xs = 8;
+    std::vector<int> dev, row_start, n_local, hbase;
+    int width = 1;
+    size_t stride = 0; // elements per x image
+    std::vector<rsg_context *> h;
+    std::vector<rsg_dist *> d;
+    std::vector<cudaStream_t> stream;
+    std::vector<cudaEvent_t> ev0, ev1;
+    // per device allocations
+    std::vector<int *> rowptr, colidx, send_idx, flags;
+    std::vector<void *> values, x, y;
+    long long bytes_received_per_step = 0; // sum over ranks of the halo entries they read, in bytes
+    long long halo_tiles = 0;
+};
+
+namespace {
+
+void multi_free(rsg_multi *M)
+{
+    for (int r = 0; r < M->P; ++r) {
+        if ((size_t)r >= M->dev.size()) break;
+        DevGuard g(M->dev[r]);
+        if ((size_t)r < M->stream.size() && M->stream[r]) cudaStreamSynchronize(M->stream[r]);
+        if ((size_t)r < M->d.size() && M->d[r]) rsg_dist_destroy(M->d[r]);
+        if ((size_t)r < M->h.size() && M->h[r]) rsg_destroy(M->h[r]);
+        if ((size_t)r < M->rowptr.size()) cudaFree(M->rowptr[r]);
+        if ((size_t)r < M->colidx.size()) cudaFree(M->colidx[r]);
+        if ((size_t)r < M->send_idx.size()) cudaFree(M->send_idx[r]);
+        if ((size_t)r < M->flags.size()) cudaFree(M->flags[r]);
+        if ((size_t)r < M->values.size()) cudaFree(M->values[r]);
+        if ((size_t)r < M->x.size()) cudaFree(M->x[r]);
+        if ((size_t)r < M->y.size()) cudaFree(M->y[r]);
+        if ((size_t)r < M->ev0.size() && M->ev0[r]) cudaEventDestroy(M->ev0[r]);
+        if ((size_t)r < M->ev1.size() && M->ev1[r]) cudaEventDestroy(M->ev1[r]);
+        if ((size_t)r < M->stream.size() && M->stream[r]) cudaStreamDestroy(M->stream[r]);
+    }
+    delete M;
+}
+
+// one host thread per device: what a C++ caller with N GPUs does anyway, and the only way N launch queues fill at once
+template <typename F> int for_each_rank(rsg_multi *M, F fn)
+{
+    std::vector<int> rc((size_t)M->P, RSG_OK);
+    if (M->P == 1) { rc[0] = fn(0); return rc[0]; }
+    std::vector<std::thread> th;
+    th.reserve((size_t)M->P);
+    for (int r = 0; r < M->P; ++r) th.emplace_back([&, r]() { cudaSetDevice(M->dev[r]); rc[(size_t)r] = fn(r); });
+    for (auto &t : th) t.join();
+    for (int r = 0; r < M->P; ++r)
+        if (rc[(size_t)r] != RSG_OK) return rc[(size_t)r];
+    return RSG_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, int n, int nnz, int base, const int *rowptr,
+                          const int *colidx, const double *values, const int *row_starts, rsg_multi_t *out)
+{
+    (void)nnz;
+    if (!out || ngpu < 1 || ngpu > RSG_MAX_PEERS || m < 0 || n < 0 || m != n || !rowptr || (base != 0 && base != 1) ||
+        (precision != 'd' && precision != 's' && precision != 'm'))
+        return RSG_BAD_ARG; // square matrices: x is distributed like the rows (the reference harness assumes square too, spmv.cu:50-51)
+    *out = nullptr;
+    int count = 0;
+    RSG_CUDA_TRY(cudaGetDeviceCount(&count));
+    rsg_multi *M = new (std::nothrow) rsg_multi();
+    if (!M) return RSG_ALLOC_FAILED;
+    const int P = ngpu;
+    M->P = P; M->precision = precision; M->m = m; M->n = n; M->base = base;
+    M->vs = precision == 'd' ? 8 : 4; M->xs = precision == 's' ? 4 : 8;
+    M->dev.resize((size_t)P);
+    for (int r = 0; r < P; ++r) {
+        M->dev[(size_t)r] = devices ? devices[r] : r;
+        if (M->dev[(size_t)r] < 0 || M->dev[(size_t)r] >= count) { delete M; return RSG_BAD_ARG; }
+    }
+    // ---- partition: the caller's cuts, or nnz-balanced split points (rsg_get_row_partition's formula, 64-bit)
+    std::vector<int> &rs = M->row_start;
+    rs.assign((size_t)P + 1, 0);
+    const long long first = rowptr[0], total = (long long)rowptr[m] - first;
+    for (int g = 1; g < P; ++g) {
+        if (row_starts) rs[(size_t)g] = row_starts[g];
+        else {
+            const long long target = (long long)g * total / P + first;
+            rs[(size_t)g] = (int)(std::lower_bound(rowptr, rowptr + m + 1, target, [](int v, long long t) { return (long long)v < t; }) - rowptr);
+        }
+        if (rs[(size_t)g] < rs[(size_t)g - 1] || rs[(size_t)g] > m) { delete M; return RSG_BAD_ARG; }
+    }
+    rs[(size_t)P] = m;
+    for (int g = 0; g < P && P > 1; ++g)
+        if (rs[(size_t)g + 1] == rs[(size_t)g]) { delete M; return RSG_BAD_ARG; } // a rank without rows would never signal its neighbours
+    auto owner = [&](int c) { return (int)(std::upper_bound(rs.begin(), rs.end(), c) - rs.begin()) - 1; };
+    // ---- what every rank reads from the others, what every owner publishes
+    std::vector<std::vector<int>> need((size_t)P), send((size_t)P);
+    for (int r = 0; r < P; ++r) {
+        const int lo = rs[(size_t)r], hi = rs[(size_t)r + 1];
+        std::vector<int> &nd = need[(size_t)r];
+        for (long long k = rowptr[lo] - base; k < rowptr[hi] - base; ++k) {
+            const int c = colidx[k] - base;
+            if (c < 0 || c >= n) { delete M; return RSG_BAD_ARG; }
+            if (c < lo || c >= hi) nd.push_back(c);
+        }
+        std::sort(nd.begin(), nd.end());
+        nd.erase(std::unique(nd.begin(), nd.end()), nd.end());
+    }
+    for (int o = 0; o < P; ++o) {
+        std::vector<int> &s = send[(size_t)o];
+        for (int q = 0; q < P; ++q)
+            if (q != o) for (int c : need[(size_t)q]) if (c >= rs[(size_t)o] && c < rs[(size_t)o + 1]) s.push_back(c - rs[(size_t)o]);
+        std::sort(s.begin(), s.end());
+        s.erase(std::unique(s.begin(), s.end()), s.end());
+        M->width = std::max(M->width, (int)s.size());
+    }
+    const int width = M->width;
+    M->n_local.resize((size_t)P); M->hbase.resize((size_t)P);
+    size_t stride = 0;
+    for (int r = 0; r < P; ++r) {
+        M->n_local[(size_t)r] = rs[(size_t)r + 1] - rs[(size_t)r];
+        M->hbase[(size_t)r] = halo_base_of(M->n_local[(size_t)r]);
+        stride = std::max(stride, (size_t)M->hbase[(size_t)r] + (size_t)P * (size_t)width);
+        M->bytes_received_per_step += (long long)need[(size_t)r].size() * (long long)M->xs;
+    }
+    stride = (stride + 31) / 32 * 32;
+    M->stride = stride;
+    // reads[q] = owners q reads from; neighbours[q] = ranks q exchanges entries with, in either direction (sorted)
+    std::vector<std::vector<int>> reads((size_t)P), nb((size_t)P);
+    for (int q = 0; q < P; ++q) {
+        std::vector<char> hit((size_t)P, 0);
+        for (int c : need[(size_t)q]) hit[(size_t)owner(c)] = 1;
+        for (int o = 0; o < P; ++o) if (hit[(size_t)o] && o != q) reads[(size_t)q].push_back(o);
+    }
+    for (int q = 0; q < P; ++q) {
+        std::vector<char> is((size_t)P, 0);
+        for (int o : reads[(size_t)q]) is[(size_t)o] = 1;
+        for (int o = 0; o < P; ++o) for (int t : reads[(size_t)o]) if (t == q) is[(size_t)o] = 1;
+        for (int o = 0; o < P; ++o) if (is[(size_t)o]) nb[(size_t)q].push_back(o);
+    }
+    // ---- devices: peer access, handles, arrays
+    M->h.assign((size_t)P, nullptr); M->d.assign((size_t)P, nullptr); M->stream.assign((size_t)P, nullptr);
+    M->ev0.assign((size_t)P, nullptr); M->ev1.assign((size_t)P, nullptr);
+    M->rowptr.assign((size_t)P, nullptr); M->colidx.assign((size_t)P, nullptr); M->send_idx.assign((size_t)P, nullptr);
+    M->flags.assign((size_t)P, nullptr); M->values.assign((size_t)P, nullptr); M->x.assign((size_t)P, nullptr); M->y.assign((size_t)P, nullptr);
+    int prev = 0;
+    cudaGetDevice(&prev);
+    int rc = RSG_OK;
+    for (int r = 0; r < P && rc == RSG_OK; ++r) {
+        cudaSetDevice(M->dev[(size_t)r]);
+        for (int q = 0; q < P; ++q) {
+            if (q == r || M->dev[(size_t)q] == M->dev[(size_t)r]) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, M->dev[(size_t)r], M->dev[(size_t)q]);
+            if (!can) { rc = RSG_UNSUPPORTED; break; }
+            const cudaError_t e = cudaDeviceEnablePeerAccess(M->dev[(size_t)q], 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { rc = RSG_CUDA_ERROR; break; }
+            (void)cudaGetLastError();
+        }
+        if (rc != RSG_OK) break;
+        rc = rsg_create(&M->h[(size_t)r], M->dev[(size_t)r]);
+        if (rc != RSG_OK) break;
+        if (cudaStreamCreateWithFlags(&M->stream[(size_t)r], cudaStreamNonBlocking) != cudaSuccess ||
+            cudaEventCreate(&M->ev0[(size_t)r]) != cudaSuccess || cudaEventCreate(&M->ev1[(size_t)r]) != cudaSuccess) { rc = RSG_CUDA_ERROR; break; }
+        rsg_set_stream(M->h[(size_t)r], M->stream[(size_t)r]);
+        const int lo = rs[(size_t)r], hi = rs[(size_t)r + 1], ml = hi - lo;
+        const long long k0 = rowptr[lo] - base, k1 = rowptr[hi] - base;
+        const size_t cnt = (size_t)(k1 - k0);
+        // relabel: own columns -> local index; others -> halo_base + owner * width + position in the owner's send list
+        std::vector<int> rp((size_t)ml + 1), ci(cnt ? cnt : 1);
+        for (int i = 0; i <= ml; ++i) rp[(size_t)i] = (int)((long long)rowptr[lo + i] - base - k0);
+        for (size_t k = 0; k < cnt; ++k) {
+            const int c = colidx[k0 + (long long)k] - base;
+            if (c >= lo && c < hi) ci[k] = c - lo;
+            else {
+                const int o = owner(c);
+                const std::vector<int> &s = send[(size_t)o];
+                const int pos = (int)(std::lower_bound(s.begin(), s.end(), c - rs[(size_t)o]) - s.begin());
+                ci[k] = M->hbase[(size_t)r] + o * width + pos;
+            }
+        }
+        bool ok = cudaMalloc(&M->rowptr[(size_t)r], sizeof(int) * ((size_t)ml + 1)) == cudaSuccess &&
+                  cudaMalloc(&M->colidx[(size_t)r], sizeof(int) * (cnt ? cnt : 1)) == cudaSuccess &&
+                  cudaMalloc(&M->values[(size_t)r], M->vs * (cnt ? cnt : 1)) == cudaSuccess &&
+                  cudaMalloc(&M->x[(size_t)r], M->xs * 2 * stride) == cudaSuccess &&
+                  cudaMalloc(&M->y[(size_t)r], M->xs * (size_t)(ml ? ml : 1)) == cudaSuccess &&
+                  cudaMalloc(&M->flags[(size_t)r], sizeof(int) * 64) == cudaSuccess &&
+                  cudaMalloc(&M->send_idx[(size_t)r], sizeof(int) * (send[(size_t)r].size() ? send[(size_t)r].size() : 1)) == cudaSuccess;
+        if (!ok) { (void)cudaGetLastError(); rc = RSG_ALLOC_FAILED; break; }
+        ok = cudaMemcpy(M->rowptr[(size_t)r], rp.data(), sizeof(int) * ((size_t)ml + 1), cudaMemcpyHostToDevice) == cudaSuccess &&
+             (cnt == 0 || cudaMemcpy(M->colidx[(size_t)r], ci.data(), sizeof(int) * cnt, cudaMemcpyHostToDevice) == cudaSuccess) &&
+             cudaMemset(M->x[(size_t)r], 0, M->xs * 2 * stride) == cudaSuccess && cudaMemset(M->flags[(size_t)r], 0, sizeof(int) * 64) == cudaSuccess &&
+             (send[(size_t)r].empty() || cudaMemcpy(M->send_idx[(size_t)r], send[(size_t)r].data(), sizeof(int) * send[(size_t)r].size(), cudaMemcpyHostToDevice) == cudaSuccess);
+        if (ok && cnt) {
+            if (M->vs == 8) ok = cudaMemcpy(M->values[(size_t)r], values + k0, 8 * cnt, cudaMemcpyHostToDevice) == cudaSuccess;
+            else { // fp32 storage: cast on the host like the harness (spmv.cu:63-67)
+                std::vector<float> vf(cnt);
+                for (size_t k = 0; k < cnt; ++k) vf[k] = (float)values[k0 + (long long)k];
+                ok = cudaMemcpy(M->values[(size_t)r], vf.data(), 4 * cnt, cudaMemcpyHostToDevice) == cudaSuccess;
+            }
+        }
+        if (!ok) { (void)cudaGetLastError(); rc = RSG_CUDA_ERROR; break; }
+    }
+    // ---- per rank: the peers' slots / flags, the send-list range each peer reads, the dist context
+    for (int r = 0; r < P && rc == RSG_OK; ++r) {
+        std::vector<void *> slots((size_t)(2 * P), nullptr);
+        std::vector<int *> pflags((size_t)(2 * P), nullptr);
+        std::vector<int> plo((size_t)P, 0), phi((size_t)P, 0);
+        const std::vector<int> &s = send[(size_t)r];
+        for (int q = 0; q < P; ++q) {
+            if (q == r) continue;
+            const bool q_reads_r = std::find(reads[(size_t)q].begin(), reads[(size_t)q].end(), r) != reads[(size_t)q].end();
+            const auto it = std::find(nb[(size_t)q].begin(), nb[(size_t)q].end(), r);
+            if (q_reads_r) { // bounding range, inside r's send list, of what q needs from r
+                int lo = (int)s.size(), hi = 0;
+                for (int c : need[(size_t)q])
+                    if (c >= rs[(size_t)r] && c < rs[(size_t)r + 1]) {
+                        const int pos = (int)(std::lower_bound(s.begin(), s.end(), c - rs[(size_t)r]) - s.begin());
+                        lo = std::min(lo, pos); hi = std::max(hi, pos + 1);
+                    }
+                plo[(size_t)q] = lo; phi[(size_t)q] = hi;
+            }
+            for (int p = 0; p < 2; ++p) {
+                if (q_reads_r)
+                    slots[(size_t)(p * P + q)] = static_cast<char *>(M->x[(size_t)q]) + M->xs * ((size_t)p * stride + (size_t)M->hbase[(size_t)q] + (size_t)r * (size_t)width);
+                if (it != nb[(size_t)q].end())
+                    pflags[(size_t)(p * P + q)] = M->flags[(size_t)q] + 32 * p + (int)(it - nb[(size_t)q].begin());
+            }
+        }
+        void *ximg[2] = {M->x[(size_t)r], static_cast<char *>(M->x[(size_t)r]) + M->xs * stride};
+        const int *wf[2] = {M->flags[(size_t)r], M->flags[(size_t)r] + 32};
+        const int ml = M->n_local[(size_t)r];
+        cudaSetDevice(M->dev[(size_t)r]);
+        rc = rsg_dist_create(M->h[(size_t)r], precision, ml, M->hbase[(size_t)r] + P * width, 0, 0, M->rowptr[(size_t)r], M->colidx[(size_t)r],
+                             M->values[(size_t)r], ximg, P > 1 ? M->hbase[(size_t)r] : 0, (int)s.size(), M->send_idx[(size_t)r], P > 1 ? P : 0,
+                             slots.data(), pflags.data(), plo.data(), phi.data(), wf, P > 1 ? (int)nb[(size_t)r].size() : 0, &M->d[(size_t)r]);
+    }
+    cudaSetDevice(prev);
+    if (rc != RSG_OK) { multi_free(M); return rc; }
+    *out = M;
+    return RSG_OK;
+}
+
+int rsg_spmv_multi_destroy(rsg_multi_t M)
+{
+    if (!M) return RSG_BAD_ARG;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    multi_free(M);
+    cudaSetDevice(prev);
+    return RSG_OK;
+}
+
+/* x_host: n entries (fp64 for 'd' / 'm', fp32 for 's'); every rank's slice goes into both of its images */
+int rsg_spmv_multi_set_x(rsg_multi_t M, const void *x_host)
+{
+    if (!M || (M->n > 0 && !x_host)) return RSG_BAD_ARG;
+    const int rc = for_each_rank(M, [&](int r) -> int {
+        const size_t nl = (size_t)M->n_local[(size_t)r];
+        const char *src = static_cast<const char *>(x_host) + M->xs * (size_t)M->row_start[(size_t)r];
+        for (int p = 0; p < 2 && nl; ++p)
+            RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(M->x[(size_t)r]) + M->xs * (size_t)p * M->stride, src, M->xs * nl,
+                                         cudaMemcpyHostToDevice, M->stream[(size_t)r]));
+        RSG_CUDA_TRY(cudaStreamSynchronize(M->stream[(size_t)r]));
+        return RSG_OK;
+    });
+    return rc;
+}
+
+/* nsteps products y = A x on every device (asynchronous: returns once every device's launches are queued) */
+int rsg_spmv_multi_step(rsg_multi_t M, int nsteps)
+{
+    if (!M || nsteps < 0) return RSG_BAD_ARG;
+    return for_each_rank(M, [&](int r) -> int {
+        for (int s = 0; s < nsteps; ++s) RSG_TRY(rsg_dist_step(M->d[(size_t)r], M->y[(size_t)r]));
+        return RSG_OK;
+    });
+}
+
+/* nsteps products timed on the devices (CUDA events on every device's stream, all devices released together):
+ * *us_per_step = the slowest device's elapsed time / nsteps */
+int rsg_spmv_multi_time(rsg_multi_t M, int nsteps, double *us_per_step)
+{
+    if (!M || nsteps < 1 || !us_per_step) return RSG_BAD_ARG;
+    std::vector<float> ms((size_t)M->P, 0.f);
+    RSG_TRY(for_each_rank(M, [&](int r) -> int { RSG_CUDA_TRY(cudaStreamSynchronize(M->stream[(size_t)r])); return RSG_OK; }));
+    RSG_TRY(for_each_rank(M, [&](int r) -> int {
+        RSG_CUDA_TRY(cudaEventRecord(M->ev0[(size_t)r], M->stream[(size_t)r]));
+        for (int s = 0; s < nsteps; ++s) RSG_TRY(rsg_dist_step(M->d[(size_t)r], M->y[(size_t)r]));
+        RSG_CUDA_TRY(cudaEventRecord(M->ev1[(size_t)r], M->stream[(size_t)r]));
+        RSG_CUDA_TRY(cudaStreamSynchronize(M->stream[(size_t)r]));
+        RSG_CUDA_TRY(cudaEventElapsedTime(&ms[(size_t)r], M->ev0[(size_t)r], M->ev1[(size_t)r]));
+        return check_err_flag(M->h[(size_t)r]);
+    }));
+    float worst = 0.f;
+    for (float v : ms) worst = std::max(worst, v);
+    *us_per_step = (double)worst * 1e3 / nsteps;
+    return RSG_OK;
+}
+
+/* waits for every device, then gathers y (m entries) to the host; RSG_DEPENDENCY_TIMEOUT if a halo wait gave up */
+int rsg_spmv_multi_get_y(rsg_multi_t M, void *y_host)
+{
+    if (!M || (M->m > 0 && !y_host)) return RSG_BAD_ARG;
+    return for_each_rank(M, [&](int r) -> int {
+        const size_t nl = (size_t)M->n_local[(size_t)r];
+        if (nl) RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(y_host) + M->xs * (size_t)M->row_start[(size_t)r], M->y[(size_t)r], M->xs * nl,
+                                             cudaMemcpyDeviceToHost, M->stream[(size_t)r]));
+        return check_err_flag(M->h[(size_t)r]);
+    });
+}
+
+/* what: 0 = ranks, 1 = halo bytes all ranks together receive per step, 2 = SpMV kernel (rsg_spmv_algo) of rank 0,
+ * 3 = halo width (entries per rank slot); row_starts (may be NULL): ngpu+1 ints */
+int rsg_spmv_multi_info(rsg_multi_t M, int what, long long *value, int *row_starts)
+{
+    if (!M || !value) return RSG_BAD_ARG;
+    switch (what) {
+    case 0: *value = M->P; break;
+    case 1: *value = M->bytes_received_per_step; break;
+    case 2: *value = M->h[0]->last_spmv_algo; break;
+    case 3: *value = M->width; break;
+    default: return RSG_BAD_ARG;
+    }
+    if (row_starts) for (int g = 0; g <= M->P; ++g) row_starts[g] = M->row_start[(size_t)g];
+    return RSG_OK;
+}
+
+} // extern "C"

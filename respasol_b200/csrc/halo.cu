@@ -86,8 +86,17 @@ extern "C" int rsg_spmv_halo_wait(rsg_handle_t h, const int *flags, int nflags, 
     return RSG_OK;
 }
 
+extern "C" int rsg_spmv_halo_fuse_ranges(rsg_handle_t h, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
+                                         int *const *peer_flags, const int *peer_lo, const int *peer_hi, int epoch);
+
 extern "C" int rsg_spmv_halo_fuse(rsg_handle_t h, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
                                   int *const *peer_flags, int epoch)
+{
+    return rsg_spmv_halo_fuse_ranges(h, nsend, send_idx, npeers, peer_slots, peer_flags, nullptr, nullptr, epoch);
+}
+
+extern "C" int rsg_spmv_halo_fuse_ranges(rsg_handle_t h, int nsend, const int *send_idx, int npeers, void *const *peer_slots,
+                                         int *const *peer_flags, const int *peer_lo, const int *peer_hi, int epoch)
 {
     if (!h || nsend < 0 || npeers < 0 || npeers > RSG_MAX_PEERS || epoch <= 0 || !peer_flags) return RSG_BAD_ARG;
     if (nsend > 0 && (!send_idx || !peer_slots)) return RSG_BAD_ARG;
@@ -95,6 +104,8 @@ extern "C" int rsg_spmv_halo_fuse(rsg_handle_t h, int nsend, const int *send_idx
     for (int q = 0; q < RSG_MAX_PEERS; ++q) {
         f.dst[q] = (q < npeers && peer_slots) ? peer_slots[q] : nullptr;
         f.flag[q] = q < npeers ? peer_flags[q] : nullptr;
+        f.lo[q] = (q < npeers && peer_lo) ? peer_lo[q] : 0;
+        f.hi[q] = (q < npeers && peer_hi) ? peer_hi[q] : nsend;
     }
     f.send_idx = send_idx;
     f.counter = h->scratch_i + 62;

@@ -40,6 +40,7 @@ struct PerDeviceOnce {
 struct HaloFuse {
     void *dst[RSG_MAX_PEERS];
     int *flag[RSG_MAX_PEERS];
+    int lo[RSG_MAX_PEERS], hi[RSG_MAX_PEERS]; // peer q reads only the entries j in [lo[q], hi[q]) of the send list
     const int *send_idx;
     int *counter;
     int nsend, npeers, epoch, ctas;

@@ -158,7 +158,7 @@ template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_pu
 #pragma unroll 1
         for (int q = 0; q < fuse.npeers; ++q) {
             TX *d = static_cast<TX *>(fuse.dst[q]);
-            if (d) d[j] = v;
+            if (d && j >= fuse.lo[q] && j < fuse.hi[q]) d[j] = v; // each boundary entry only to the peers that read it
         }
     }
     __threadfence_system();

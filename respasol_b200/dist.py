@@ -90,6 +90,17 @@ class HaloPlan:
         self.my_send = send[self.rank]
         lo, hi = rs[self.rank], rs[self.rank + 1]  # peers that read at least one of this rank's entries
         self.readers = [q for q, nb in enumerate(needs_by_rank) if q != self.rank and np.any((nb >= lo) & (nb < hi))]
+        # peer q reads only a part of my send list: the bounding range [lo_q, hi_q) of its entries' positions in it
+        # (a slab of a stencil: the lower neighbour reads the first plane, the upper one the last)
+        self.send_range = []
+        for q, nb in enumerate(needs_by_rank):
+            mine = nb[(nb >= lo) & (nb < hi)] - lo if q != self.rank else np.zeros(0, np.int64)
+            if len(mine):
+                pos = np.searchsorted(self.my_send, mine)
+                self.send_range.append((int(pos.min()), int(pos.max()) + 1))
+            else:
+                self.send_range.append((0, 0))
+        self.recv_entries = int(len(self.need))  # halo entries this rank receives per step
         # neighbours[q] (identical on every rank): the ranks q exchanges entries with, in either direction.
         # A rank signals and awaits exactly its neighbours -- enough to keep it within one step of each of them.
         reads = [[o for o in range(P) if o != q and np.any((nb >= rs[o]) & (nb < rs[o + 1]))] for q, nb in enumerate(needs_by_rank)]
@@ -159,7 +170,8 @@ class RowBlockSpmv:
             self.send_idx = torch.from_numpy(plan.my_send).to(device)
             self.pack = torch.zeros(plan.width, dtype=dtype, device=device)
             self.halo = self.x_ext[plan.halo_base:]
-            self.exchange_bytes = plan.width * self.P * self.x_ext.element_size()
+            # what this rank RECEIVES per step (the entries it reads from other ranks), not the size of the halo buffer
+            self.exchange_bytes = plan.recv_entries * self.x_ext.element_size()
         elif mode == "allgather":
             self.width = int(np.diff(self.row_starts).max())
             # padded equal slices: global column c of owner o lives at o*width + (c - start[o])
@@ -215,8 +227,37 @@ class RowBlockSpmv:
             self.flag_slots = [to_c.ptr_array(v) for v in self.flag_slots]
         self.flag_views = [self.flags[32 * p:] for p in range(2)]
         self.send_idx32 = torch.from_numpy(plan.my_send.astype(np.int32)).to(device)
+        self.cdist = None
+        owner = getattr(self.p2p[0], "__self__", None)
+        if len(self.p2p) > 2 and owner is not None and hasattr(self.p2p[2].__self__, "dist_create"):
+            # fused mode: everything a step needs is bound once inside the library (rsg_dist_create); a step is ONE call
+            hnd = self.p2p[2].__self__
+            raw_slots = [[(ptrs[q] + offs[p][q] * esz) if q in plan.readers else 0 for q in range(self.P)] for p in range(2)]
+            raw_flags = [[(fptrs[q] + 4 * (32 * p + nb[q].index(self.rank))) if q in nb[self.rank] else 0
+                          for q in range(self.P)] for p in range(2)]
+            self.cdist = hnd.dist_create(self.A, [im.data_ptr() for im in self.images], plan.halo_base, self.send_idx32,
+                                         raw_slots, raw_flags, [r[0] for r in plan.send_range], [r[1] for r in plan.send_range],
+                                         [v.data_ptr() for v in self.flag_views], self.n_wait)
+            self.cdist_step = hnd.dist_step
         torch.cuda.synchronize(device)
         self.symm.barrier(channel=0)
+
+    def describe(self):
+        """what the exchange step of this operator is, for the bench line"""
+        if self.p2p is not None:
+            how = ("FUSED into the SpMV launch (rsg_dist_step: the product's first CTAs push this rank's boundary entries into the "
+                   "readers' halo slots and signal, its halo tiles await the neighbours' flags before they copy x)"
+                   if len(self.p2p) > 2 else "rsg_halo_push on a side stream, arrival flags awaited inside the product's halo tiles"
+                   if self.p2p[1] else "rsg_halo_push + symmetric-memory barrier")
+            mode = "x-halo push over NVLink peer memory, " + how
+        elif self.mode == "halo":
+            mode = "packed x-halo all-gather (NCCL)"
+        else:
+            mode = "full x all-gather (NCCL)"
+        if self.split:
+            mode += "; exchange on a side stream overlapped with the %d interior rows, boundary rows follow" % self.interior_rows
+        return {"mode": mode, "bytes_received_per_rank_per_step": int(self.exchange_bytes),
+                "neighbours": int(getattr(self, "n_wait", 0))}
 
     def set_x(self, x_local):
         """x_local: this rank's slice of x (device tensor)."""
@@ -284,6 +325,12 @@ class RowBlockSpmv:
             self.graph.replay()
             return self.y
         if self.split is None:
+            if getattr(self, "cdist", None) is not None:  # push + signal + wait + product: one library call, one launch
+                self.cdist_step(self.cdist, self.y)
+                self.epoch += 1
+                self.x_ext = self.images[self.parity]
+                self.parity ^= 1
+                return self.y
             self.exchange()
             self.spmv_fn(self.A, self.x_ext, self.y)
             if getattr(self, "join_side", False):  # x may be rewritten once the step returns

@@ -190,6 +190,30 @@ class Handle:
         _check(self.lib.rsg_spmv_halo_fuse(self.h, int(send_idx.numel()), self._p(send_idx), len(slots), slots, flags,
                                            int(epoch)), "rsg_spmv_halo_fuse")
 
+    def dist_create(self, A, x_images, halo_start, send_idx, peer_slots, peer_flags, peer_lo, peer_hi, wait_flags, nwait):
+        """rsg_dist_create: bind one rank's side of the row-block product once.  peer_slots / peer_flags: [image][peer] device
+        addresses (0 = NULL); x_images / wait_flags: the two images' device addresses."""
+        self._claim(A)
+        npeers = len(peer_slots[0])
+        assert len(peer_slots) == 2 and len(peer_flags) == 2 and len(peer_flags[0]) == npeers
+        slots = self.ptr_array([p for img in peer_slots for p in img])
+        flags = self.ptr_array([p for img in peer_flags for p in img])
+        lo = (C.c_int * npeers)(*[int(v) for v in peer_lo])
+        hi = (C.c_int * npeers)(*[int(v) for v in peer_hi])
+        ximg = self.ptr_array(x_images)
+        wf = self.ptr_array(wait_flags)
+        d = C.c_void_p()
+        _check(self.lib.rsg_dist_create(self.h, A.precision.encode(), A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx),
+                                        self._p(A.values), ximg, int(halo_start), int(send_idx.numel()), self._p(send_idx), npeers,
+                                        slots, flags, lo, hi, wf, int(nwait), C.byref(d)), "rsg_dist_create")
+        return d
+
+    def dist_step(self, d, y):
+        _check(self.lib.rsg_dist_step(d, self._p(y)), "rsg_dist_step")
+
+    def dist_destroy(self, d):
+        _check(self.lib.rsg_dist_destroy(d), "rsg_dist_destroy")
+
     def spmv_halo_wait(self, flags, nflags, epoch):
         """One-shot: tiles of the next spmv that read columns >= SPMV_HALO_START wait for flags[i] >= epoch."""
         _check(self.lib.rsg_spmv_halo_wait(self.h, self._p(flags), int(nflags), int(epoch)), "rsg_spmv_halo_wait")

@@ -17,6 +17,7 @@ struct HarnessArgs {
     int repeat = 50;      // REPEAT in GPU/spmv.cu:174
     int warmup = 0;       // the reference has none
     int algo = 0;
+    int gpus = 1;         // --gpus=N: row-block product over N devices of this process (rsg_spmv_multi_*)
     bool stats = false;   // extra lines after the reference's own output
     bool expand_symmetric = false;
 };
@@ -43,14 +44,18 @@ inline bool parse_args(int argc, char **argv, HarnessArgs *a)
         if (const char *v = val("--precision=")) a->precision = v[0];
         else if (const char *v = val("--repeat=")) a->repeat = atoi(v);
         else if (const char *v = val("--warmup=")) a->warmup = atoi(v);
+        else if (const char *v = val("--gpus=")) a->gpus = atoi(v);
+        else if (s == "--gpus" && i + 1 < argc) a->gpus = atoi(argv[++i]);
         else if (const char *v = val("--kernel=")) {
             a->algo = !strcmp(v, "rowblock") ? RSG_SPMV_ROWBLOCK : !strcmp(v, "merge") ? RSG_SPMV_MERGE
-                    : !strcmp(v, "vector") ? RSG_SPMV_VECTOR : !strcmp(v, "scalar") ? RSG_SPMV_SCALAR : RSG_SPMV_AUTO;
+                    : !strcmp(v, "vector") ? RSG_SPMV_VECTOR : !strcmp(v, "scalar") ? RSG_SPMV_SCALAR
+                    : !strcmp(v, "tile") ? RSG_SPMV_TILE : !strcmp(v, "window") ? RSG_SPMV_WINDOW : RSG_SPMV_AUTO;
         } else if (s == "--stats") a->stats = true;
         else if (s == "--expand-symmetric") a->expand_symmetric = true;
     }
     if (a->precision != 'd' && a->precision != 's' && a->precision != 'm') a->precision = 'd';
     if (a->repeat < 1) a->repeat = 1;
+    if (a->gpus < 1) a->gpus = 1;
     return true;
 }
 

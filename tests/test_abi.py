@@ -12,7 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def header_functions():
     text = open(os.path.join(ROOT, "include", "reaspasol_gpu.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    names = re.findall(r"^\s*(?:const\s+char\s*\*\s*|int\s+)(\w+)\s*\(", text, flags=re.M)
+    names = re.findall(r"^\s*(?:const\s+char\s*\*\s*|void\s*\*\s*|int\s+)(\w+)\s*\(", text, flags=re.M)
     return sorted(set(names))
 
 
