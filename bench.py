@@ -543,12 +543,16 @@ def run_ours(args):
         t = torch.tensor([extra_steps], dtype=torch.int64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         extra_steps = int(t.item())
-    c0 = time.perf_counter()
     for i in range(extra_steps):
         step(K + i)
-    host_issue_us = (time.perf_counter() - c0) / max(extra_steps, 1) * 1e6
     torch.cuda.synchronize()
     w1b = time.time()
+    barrier()
+    c0 = time.perf_counter()  # what the host needs to ISSUE a step: a short burst into an empty launch queue
+    for i in range(64):
+        step(K + extra_steps + i)
+    host_issue_us = (time.perf_counter() - c0) / 64 * 1e6
+    torch.cuda.synchronize()
     barrier()
     clocks = sampler.summary(w0, max(w1, w1b))
     extra["host_issue_us_per_step"] = round(host_issue_us, 2)

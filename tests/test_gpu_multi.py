@@ -1,0 +1,119 @@
+"""Multi-GPU row-block SpMV through the C ABI (rsg_spmv_multi_*: one process, N devices).
+
+The N > 1 cases need N real devices (kernels that wait on each other must never share one GPU): they skip on a
+one-GPU box and run under `gpurun --gpus 2` / on the 8-GPU box.  The one-rank case runs everywhere and pins the host
+logic of the entry points (partition, relabelling, scatter / gather).  Full y against the oracle, bit-exact where the
+rows are summed left to right like the oracle (window kernel, rows up to 40 entries)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+import orc
+from respasol_b200 import host
+from respasol_b200._lib import gpu_lib
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "respasol_b200", "bin")
+
+
+def ndev():
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+def multi_product(a, x, ngpu, precision="d", row_starts=None, steps=3):
+    lib = gpu_lib()
+    M = C.c_void_p()
+    rs = None if row_starts is None else np.ascontiguousarray(row_starts, dtype=np.int32)
+    st = lib.rsg_spmv_multi_create(ngpu, None, precision.encode(), a.m, a.n, a.stored, a.base, a.rowptr.ctypes.data,
+                                   a.colidx.ctypes.data, np.ascontiguousarray(a.values, dtype=np.float64).ctypes.data,
+                                   None if rs is None else rs.ctypes.data, C.byref(M))
+    assert st == 0, lib.rsg_status_string(st)
+    xt = np.float32 if precision == "s" else np.float64
+    xh = np.ascontiguousarray(x, dtype=xt)
+    y = np.zeros(a.m, dtype=xt)
+    try:
+        assert lib.rsg_spmv_multi_set_x(M, xh.ctypes.data) == 0
+        assert lib.rsg_spmv_multi_step(M, steps) == 0          # several steps: both x images, epochs 1..steps
+        assert lib.rsg_spmv_multi_get_y(M, y.ctypes.data) == 0
+        us = C.c_double(0)
+        assert lib.rsg_spmv_multi_time(M, 5, C.byref(us)) == 0 and us.value > 0
+        y2 = np.zeros(a.m, dtype=xt)
+        assert lib.rsg_spmv_multi_get_y(M, y2.ctypes.data) == 0
+        assert np.array_equal(y, y2)
+        v = C.c_longlong(0)
+        cuts = np.zeros(ngpu + 1, dtype=np.int32)
+        assert lib.rsg_spmv_multi_info(M, 0, C.byref(v), cuts.ctypes.data) == 0 and v.value == ngpu
+        assert cuts[0] == 0 and cuts[-1] == a.m and np.all(np.diff(cuts) > 0)
+        if row_starts is None:
+            assert np.array_equal(cuts, orc.row_partition(a, ngpu))  # the oracle's nnz-balanced cuts, bit-exact
+    finally:
+        assert lib.rsg_spmv_multi_destroy(M) == 0
+    return y
+
+
+@pytest.mark.parametrize("ngpu", [1, 2, 4, 8])
+@pytest.mark.parametrize("precision", ["d", "s", "m"])
+def test_multi_gpu_product_matches_the_oracle(ngpu, precision):
+    if ndev() < ngpu:
+        pytest.skip("needs %d devices" % ngpu)
+    for a in (host.gen_stencil27(30, 30, 48, seed=2), host.gen_laplace2d(300), host.gen_femlike(20, 0.6, 5)):
+        x = orc.dlarnv(a.n) - 0.5
+        y = multi_product(a, x, ngpu, precision)
+        ref = orc.spmv(a, x, precision)
+        if precision == "d":
+            assert np.array_equal(y, ref)
+        else:
+            assert np.abs(y.astype(np.float64) - ref.astype(np.float64)).max() <= (5e-5 if precision == "s" else 1e-12) * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("ngpu", [2, 4])
+def test_multi_gpu_one_directional_pattern_and_changing_x(ngpu):
+    """An upwind (lower-bidiagonal-by-planes) pattern: rank r reads only from rank r-1, so rank 0 feeds a neighbour but
+    reads nothing -- it must still not run ahead (its last tile awaits the flags).  x changes between steps, so a stale
+    or early halo would show."""
+    if ndev() < ngpu:
+        pytest.skip("needs %d devices" % ngpu)
+    n, band = 40000, 700
+    rows = np.arange(n)
+    rp = np.zeros(n + 1, dtype=np.int32)
+    lens = np.where(rows < band, 1, 2)
+    rp[1:] = np.cumsum(lens)
+    ci = np.concatenate([[r] if r < band else [r - band, r] for r in range(n)]).astype(np.int32)
+    a = host.CSR(n, n, int(rp[-1]), rp, ci, np.random.default_rng(1).uniform(0.5, 1.5, int(rp[-1])), 0)
+    lib = gpu_lib()
+    M = C.c_void_p()
+    assert lib.rsg_spmv_multi_create(ngpu, None, b"d", n, n, a.stored, 0, rp.ctypes.data, ci.ctypes.data, a.values.ctypes.data, None, C.byref(M)) == 0
+    try:
+        y = np.zeros(n)
+        for it in range(6):
+            x = orc.dlarnv(n) + it
+            assert lib.rsg_spmv_multi_set_x(M, x.ctypes.data) == 0
+            assert lib.rsg_spmv_multi_step(M, 1) == 0
+            assert lib.rsg_spmv_multi_get_y(M, y.ctypes.data) == 0
+            assert np.array_equal(y, orc.spmv(a, x, "d")), it
+    finally:
+        lib.rsg_spmv_multi_destroy(M)
+
+
+@pytest.mark.parametrize("ngpu", [1, 2])
+def test_harness_gpus_flag(tmp_path, ngpu):
+    """bin/test_spmv --gpus N prints the reference's two stdout lines (GPU/spmv.cu:203-207,260)"""
+    if ndev() < ngpu:
+        pytest.skip("needs %d devices" % ngpu)
+    p = tmp_path / "s27.mtx"
+    host.write_matrix_market(p, host.gen_stencil27(24, seed=2))
+    r = subprocess.run([os.path.join(BIN, "test_spmv"), str(p), "--gpus=%d" % ngpu, "--stats", "--repeat=20", "--warmup=2"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.strip().splitlines()
+    assert re.fullmatch(r"DOUBLE PRECISION SPMV solve time \(microseconds\) = (\d+\.\d{6})", lines[0]), r.stdout
+    m = re.fullmatch(r"Error= (\d\.\d{6}e[+-]\d{2})", lines[1])
+    assert m and float(m.group(1)) <= 1e-12, r.stdout
+    if ngpu > 1:
+        assert "gpus=%d" % ngpu in lines[2]
