@@ -211,3 +211,52 @@ def test_config3_full_size(handle):
     assert np.all(np.abs(r) <= 200 * 2.0 ** -53 * (abs(L) @ (abs(U) @ np.abs(yh))) + 1e-300)
     # (3) M^-1 A is a contraction towards the identity for this diagonally dominant matrix
     assert float((y - x).abs().max() / x.abs().max()) < 1.0
+
+
+def test_hung_solve_reports_dependency_timeout(handle):
+    """A right-hand side that carries the pending sentinel (a NaN payload no arithmetic produces) makes row 0 look
+    unwritten for ever: its dependants give up after RSG_OPT_WAIT_SPINS sweeps and the next synchronising call
+    returns RSG_DEPENDENCY_TIMEOUT instead of RSG_OK (round 1 returned RSG_OK with NaNs in y)."""
+    from respasol_b200.gpu import RsgError
+    a = host.gen_laplace2d(20)
+    A = DeviceCSR(a, "d")
+    handle.ilu0_factor(A)
+    b = torch.ones(a.m, dtype=torch.float64, device="cuda")
+    sentinel = torch.tensor([0xFFF8DEADBEEF0001 - (1 << 64)], dtype=torch.int64, device="cuda").view(torch.float64)
+    b[0:1] = sentinel
+    handle.set_option("WAIT_SPINS", 2000)
+    try:
+        handle.sptrsv_lu(A, A.values, b)
+        with pytest.raises(RsgError) as ei:
+            handle.synchronize()
+        assert ei.value.status == 7  # RSG_DEPENDENCY_TIMEOUT
+        handle.synchronize()  # reported once
+        good = torch.ones(a.m, dtype=torch.float64, device="cuda")
+        z, y = handle.sptrsv_lu(A, A.values, good)
+        handle.synchronize()
+        assert bool(torch.isfinite(y).all())
+    finally:
+        handle.set_option("WAIT_SPINS", 0)
+
+
+def test_unsorted_rows_are_refused(handle):
+    """ILU0 / SpTRSV split a row at its diagonal and binary-search it: a row whose columns do not ascend is refused with
+    RSG_BAD_ARG by the analysis, factor and solve calls (the header states the contract); SpMV takes any order."""
+    from respasol_b200.gpu import RsgError
+    a = host.gen_laplace2d(12)
+    ci = a.colidx.copy()
+    vals = a.values.copy()
+    r = 40
+    k0, k1 = int(a.rowptr[r]), int(a.rowptr[r + 1])
+    ci[k0:k1] = ci[k0:k1][::-1]
+    vals[k0:k1] = vals[k0:k1][::-1]
+    b = host.CSR(a.m, a.n, a.nnz, a.rowptr, ci, vals, a.base)
+    B = DeviceCSR(b, "d")
+    for call in (lambda: handle.ilu0_analysis(B), lambda: handle.sptrsv_analysis(B), lambda: handle.ilu0_factor(B),
+                 lambda: handle.sptrsv_lu(B, B.values, torch.ones(b.m, dtype=torch.float64, device="cuda"))):
+        with pytest.raises(RsgError) as ei:
+            call()
+        assert ei.value.status == 1  # RSG_BAD_ARG
+    x = orc.dlarnv(a.n)
+    y = handle.spmv(B, torch.from_numpy(x).cuda()).cpu().numpy()
+    assert np.abs(y - orc.spmv(a, x, "d")).max() <= 1e-12
