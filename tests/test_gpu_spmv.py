@@ -666,3 +666,37 @@ def test_halo_push_signal_and_in_kernel_wait(handle, algo):
         handle.set_option("WAIT_SPINS", 0)
         handle.set_option("SPMV_ALGO", 0)
         handle.set_option("SPMV_HALO_START", 0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("algo", ["window", "tile", "vector", "merge"])
+@pytest.mark.parametrize("precision", ["d", "s", "m"])
+def test_guard_bands(handle, algo, precision):
+    """compute-sanitizer is closed on this pool (profiles/r2_sanitizer_closed.txt): the arrays of a product are embedded in
+    larger buffers whose guard bands hold NaN values, wild column indices and canaries.  A read past an array's end poisons
+    the result (or faults), a write outside y kills a canary.  Offsets keep the 16-byte alignment the bulk copies need."""
+    G = 64  # guard elements on each side
+    for a in (host.gen_stencil27(13, 11, 9, seed=3), host.gen_laplace2d(31), host.gen_powerlaw(4000, 2.2, 40, 2, 3100, 4)):
+        vt = torch.float64 if precision == "d" else torch.float32
+        xt = torch.float32 if precision == "s" else torch.float64
+        A = DeviceCSR(a, precision)
+        rp = torch.full((a.m + 1 + 2 * G,), 2 ** 30, dtype=torch.int32, device="cuda")
+        ci = torch.full((a.stored + 2 * G,), 2 ** 30, dtype=torch.int32, device="cuda")
+        va = torch.full((a.stored + 2 * G,), float("nan"), dtype=vt, device="cuda")
+        xg = torch.full((a.n + 2 * G,), float("nan"), dtype=xt, device="cuda")
+        yg = torch.full((a.m + 2 * G,), -77.0, dtype=xt, device="cuda")
+        rp[G:G + a.m + 1] = A.rowptr; ci[G:G + a.stored] = A.colidx; va[G:G + a.stored] = A.values
+        x = orc.dlarnv(a.n) - 0.5
+        xg[G:G + a.n] = torch.from_numpy(x).cuda().to(xt)
+        A.rowptr, A.colidx, A.values = rp[G:G + a.m + 1], ci[G:G + a.stored], va[G:G + a.stored]
+        handle.set_option("SPMV_ALGO", ALGO[algo])
+        try:
+            handle.spmv(A, xg[G:G + a.n], yg[G:G + a.m])
+            handle.synchronize()
+        finally:
+            handle.set_option("SPMV_ALGO", 0)
+        assert bool((yg[:G] == -77.0).all()) and bool((yg[G + a.m:] == -77.0).all()), "write outside y"
+        got = yg[G:G + a.m].cpu().numpy().astype(np.float64)
+        ref = orc.spmv(a, x, precision).astype(np.float64)
+        assert np.isfinite(got).all(), "a guard-band NaN reached the result"
+        assert np.abs(got - ref).max() <= (1e-12 if precision == "d" else 5e-5) * np.abs(ref).max()
