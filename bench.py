@@ -37,6 +37,8 @@ GRID = 100          # configs[1]: 27-point stencil on 100^3
 GRID5 = 134         # configs[4]: 27-point stencil on 134^3 = 64 000 000 entries
 REPLICAS = 2
 METRIC = "SpMV achieved HBM GB/s (fp64 CSR, algorithmic bytes / device time)"
+LAUNCH_NOTE = ("back-to-back products of a static matrix, as in the reference's timed loop (GPU/spmv.cu:174-207); programmatic dependent "
+               "launch with the values promised static (RSG_OPT_SPMV_PDL = 2) unless --pdl says otherwise")
 
 
 def peaks():
@@ -52,10 +54,11 @@ def job_config(n_gpus):
     if n_gpus == 1:
         return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 100^3 (1000000 rows, 26463592 entries) -- BASELINE configs[1]",
                 "l2_policy": "inputs larger than L2: %d resident replicas of the matrix and vectors are rotated" % REPLICAS,
-                "parallelism": "single GPU"}
+                "parallelism": "single GPU", "launch": LAUNCH_NOTE}
     return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 134^3 (2406104 rows, 64000000 entries) -- BASELINE configs[4], strong scaling",
             "l2_policy": "inputs larger than L2 up to N = 4; %d resident replicas of every rank's block are rotated at every N" % REPLICAS,
-            "parallelism": "row blocks of whole planes over %d GPUs; x halo pushed over NVLink peer memory by the product's own launch" % n_gpus}
+            "parallelism": "row blocks of whole planes over %d GPUs; x halo pushed over NVLink peer memory by the product's own launch" % n_gpus,
+            "launch": LAUNCH_NOTE}
 
 
 def all_host_cpus():
@@ -435,6 +438,10 @@ def run_ours(args):
         return -allmax(-v)
 
     h = Handle(local_rank)
+    # every matrix of this bench is static while its products are timed (the reference harness's loop, spmv.cu:174-207,
+    # is 50 products of one matrix): the promise RSG_OPT_SPMV_PDL = 2 lets a product's CTAs fetch their tiles while the
+    # previous product drains.  --pdl 0 / 1 run the same workload without the promise / without dependent launches.
+    h.set_option("SPMV_PDL", args.pdl)
     K, W = args.steps, max(args.warmup, 3)
     peak, peak_src = peaks()
     sampler = ClockSampler(local_rank)
@@ -621,6 +628,15 @@ def run_ours(args):
         reps = max(20, min(K, 500))
         extra["spmv_fp64"] = {"GBps": achieved, "us": per_launch_ms * 1e3, "GFLOPs": 2.0 * a.stored / (per_launch_ms * 1e-3) * 1e-9,
                               "frac_of_measured_peak": achieved / peak, "algo": algo_used}
+        ab = {}
+        for mode in (1, 0, 2):  # plain launches / dependent launch, plan data early / + values early
+            h.set_option("SPMV_PDL", mode)
+            for i in range(4):
+                step(i)
+            t, _, _ = timed_loop(torch, step, reps, lambda: None)
+            ab["pdl_%d_us" % mode] = t / reps * 1e3
+        h.set_option("SPMV_PDL", args.pdl)
+        extra["spmv_fp64"]["launch_modes_us"] = ab
         for p in ("s", "m"):
             _, us, b, R, _ = cold_rate(torch, h, lambda: full, lambda m_: xfull, p, reps)
             extra["spmv_" + {"s": "fp32", "m": "mixed"}[p]] = {"GBps": b / us * 1e-3, "us": us, "GFLOPs": 2.0 * full.stored / us * 1e-3,
@@ -863,6 +879,7 @@ def main():
     ap.add_argument("--graph", action="store_true", help="N>1: replay each step from a CUDA graph (NCCL exchange only)")
     ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-side", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
+    ap.add_argument("--pdl", type=int, default=2, choices=[0, 1, 2], help="RSG_OPT_SPMV_PDL for the timed products (2 = matrix values promised static)")
     ap.add_argument("--cpu-leg", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.cpu_leg:

@@ -101,6 +101,11 @@ typedef enum {
     RSG_OPT_SPMV_WIN_GAP = 22,  /* window kernel plan: runs of x separated by up to this many unused 4-column granules are merged (0 = 3) */
     RSG_OPT_WAIT_SPINS = 23,    /* polls a device-side dependency / halo wait may spend before it gives up and the next
                                    synchronising call returns RSG_DEPENDENCY_TIMEOUT (0 = default 2^22, i.e. seconds) */
+    RSG_OPT_SPMV_PDL = 24,      /* window kernel, programmatic dependent launch: 0 (default) = a product's CTAs may start while the
+                                   previous kernel of the stream drains, reading only plan-owned data (tile records, row pointers,
+                                   16-bit columns) before they wait for it; 2 = the matrix VALUES too -- the caller promises that
+                                   nothing queued ahead of the product writes them (a solver loop on a fixed matrix, the harness's
+                                   50 timed products, spmv.cu:174-207); 1 = plain launches */
     RSG_OPT_COUNT_
 } rsg_option;
 

@@ -192,6 +192,10 @@ __device__ __forceinline__ void halo_flag_wait(const int *flags, int n, int epoc
     }
 }
 
+// Programmatic dependent launch (PTX griddepcontrol; no-ops in a kernel that was launched without the attribute)
+__device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // x gather of a row reduction: read-only path, or coherent when peers write x while the kernel runs
 template <bool COH, typename TX> __device__ __forceinline__ TX ld_xg(const TX *p) { return COH ? ld_x_coherent(p) : __ldg(p); }
 

@@ -97,13 +97,21 @@ __device__ __forceinline__ void win_rows(const TV *s_val, const uint16_t *s_idx,
 template <typename TV, typename TX, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
-                   int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch, int *err_flag, int max_spins, const HaloFuse fuse)
+                   int reduce_opt, int early_values, const int *wait_flags, int wait_n, int wait_epoch, int *err_flag, int max_spins,
+                   const HaloFuse fuse)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(16) int4 s_desc[kWinRecInt4];
     __shared__ __align__(8) uint64_t s_bar;
     const int tid = threadIdx.x;
+    // Programmatic dependent launch: the NEXT kernel of the stream may start its CTAs as soon as every CTA of this grid
+    // has got here (they fill the SM slots this grid's last wave frees), and this grid was allowed to start the same way:
+    // everything up to grid_dependency_wait() below reads plan-owned, immutable data only (tile record, row pointers,
+    // 16-bit columns -- and the values when the caller promised them static), so descriptor latency, the launch gap and
+    // the ramp of a product hide behind the tail of the one before it.
+    grid_launch_dependents();
     if ((int)blockIdx.x < fuse.ctas) { // fused exchange: publish this rank's boundary entries of x to the peers
+        grid_dependency_wait(); // x is what the work before this launch produced
         halo_fuse_push<TX, THREADS>(fuse, x);
         return;
     }
@@ -135,10 +143,13 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
         mbar_expect_tx(&s_bar, nrp * 4u + nstage * (uint32_t)(sizeof(TV) + 2) + (uint32_t)xtma * (uint32_t)sizeof(TX));
         bulk_g2s(smem + L.o_rp, w.rp0 + ra, nrp * 4u, &s_bar, spol);
         if (nstage) {
-            bulk_g2s(s_val, values + sb, nstage * (uint32_t)sizeof(TV), &s_bar, spol);
             bulk_g2s(s_idx, w.widx + (sb - w.first8), nstage * 2u, &s_bar, spol);
+            if (early_values) bulk_g2s(s_val, values + sb, nstage * (uint32_t)sizeof(TV), &s_bar, spol);
         }
     }
+    grid_dependency_wait(); // from here on: x, y and (unless promised static) the values -- what earlier work may have written
+    if (tid == 0 && nr > 0 && nstage && !early_values)
+        bulk_g2s(s_val, values + sb, nstage * (uint32_t)sizeof(TV), &s_bar, make_evict_first_policy());
     if (must_wait) {
         // x entries of this tile are written by peers over NVLink: wait for their arrival flags (the matrix part of
         // the tile is already in flight), THEN copy the segments -- the copy is the first read of that memory
@@ -402,6 +413,20 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     p.wsmem = (h->pinned_i[32] + 127) & ~127;
     p.whalo = h->pinned_i[34];
     p.wthreads = threads;
+    if (p.whalo > 0 && p.whalo < p.nblk) {
+        // multi-GPU: tiles that read a peer's entries go to the END of the grid (records are self-contained, so the order is
+        // free): by the time they are dispatched the neighbours' pushes have long landed, instead of the first wave
+        // spinning on flags while interior tiles wait for an SM slot.  Stable on both sides; done once, on the host.
+        std::vector<int4> rec((size_t)p.nblk * kWinRecInt4), out_rec((size_t)p.nblk * kWinRecInt4);
+        RSG_CUDA_TRY(cudaMemcpy(rec.data(), p.wdesc, sizeof(int4) * rec.size(), cudaMemcpyDeviceToHost));
+        size_t at = 0;
+        for (int pass = 0; pass < 2; ++pass)
+            for (int b = 0; b < p.nblk; ++b) {
+                const bool halo = ((rec[(size_t)b * kWinRecInt4].z >> 24) & 1) != 0;
+                if ((pass == 1) == halo) { std::copy_n(rec.begin() + (size_t)b * kWinRecInt4, kWinRecInt4, out_rec.begin() + at); at += kWinRecInt4; }
+            }
+        RSG_CUDA_TRY(cudaMemcpy(p.wdesc, out_rec.data(), sizeof(int4) * out_rec.size(), cudaMemcpyHostToDevice));
+    }
     p.bytes += sizeof(int4) * kWinRecInt4 * (size_t)p.nblk + sizeof(uint16_t) * widx_len + sizeof(int) * (size_t)p.rp0_len;
     return RSG_OK;
 }
@@ -419,8 +444,25 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
     HaloFuse fuse = h->fuse;
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
     WinArgs w = {p->wdesc, p->rp0, p->widx, p->first8, p->first + p->nnz, p->n, p->nblk};
-    kern<<<p->nblk + fuse.ctas, THREADS, (size_t)p->wsmem, h->stream>>>(w, values, x, y, alpha, beta, h->opts[RSG_OPT_SPMV_REDUCE], h->wait_flags,
-                                                                         h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse);
+    // RSG_OPT_SPMV_PDL: 0 = programmatic dependent launch, plan data only ahead of the dependency; 1 = plain launch;
+    // 2 = the values too (the caller promises that nothing queued before the product writes them)
+    int pdl = h->opts[RSG_OPT_SPMV_PDL];
+    if (pdl != 1) { // a stream that is being captured keeps plain launches (the e2e graph of rsg_matrix_spmv_host)
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(h->stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { (void)cudaGetLastError(); pdl = 1; }
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(p->nblk + fuse.ctas));
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = (size_t)p->wsmem;
+    cfg.stream = h->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl != 1 ? 1 : 0;
+    RSG_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, w, values, x, y, alpha, beta, h->opts[RSG_OPT_SPMV_REDUCE], pdl == 2 ? 1 : 0, h->wait_flags,
+                                    h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse));
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;
     h->launches++;

@@ -16,7 +16,7 @@ OPT = dict(SPMV_ALGO=0, SPMV_REDUCE=1, SPMV_LONG_ROW=2, SPMV_VARIANT=3, SPMV_CAC
            TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7, SPMV_X_HINT=8,
            SPMV_ROWS_PER_THREAD=9, SPMV_CTAS_PER_SM=10, TRSV_BATCH=11, TRSV_GATE=12,
            TRI_CTAS_PER_SM=13, TRSV_BLOCK=14, SPMV_HALO_START=15, HOST_CHUNKS=16, HOST_Y_DIRECT=17, HOST_GRAPH=18, TRANSPOSE_STATIC=19,
-           SPMV_WIN_BYTES=20, SPMV_WIN_STREAM_PCT=21, SPMV_WIN_GAP=22, WAIT_SPINS=23)
+           SPMV_WIN_BYTES=20, SPMV_WIN_STREAM_PCT=21, SPMV_WIN_GAP=22, WAIT_SPINS=23, SPMV_PDL=24)
 ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4, stream=5, pipe=6, tile=7, window=8)
 INFO = dict(KERNEL_LAUNCHES=0, SPMV_ALGO_USED=1, SPMV_ROW_BLOCKS=2, SPMV_MAX_ROW=3, LEVELS_L=4, LEVELS_U=5,
             SM_COUNT=6, WORKSPACE_BYTES=7)

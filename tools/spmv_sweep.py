@@ -47,6 +47,8 @@ for wb in (28672, 36864, 45056, 56320, 75776):
     DEFAULT.append("window:SPMV_WIN_BYTES=%d" % wb)
 for pct in (56, 72):
     DEFAULT.append("window:SPMV_WIN_STREAM_PCT=%d" % pct)
+DEFAULT += ["window:SPMV_PDL=1", "window:SPMV_PDL=2", "window:SPMV_PDL=2,SPMV_WIN_BYTES=28672", "window:SPMV_PDL=2,SPMV_WIN_BYTES=45056",
+            "window:SPMV_PDL=2,SPMV_VARIANT=1,SPMV_WIN_BYTES=22528", "window:SPMV_PDL=2,SPMV_VARIANT=2,SPMV_WIN_BYTES=75776"]
 DEFAULT += ["window:SPMV_VARIANT=1,SPMV_WIN_BYTES=22528", "window:SPMV_VARIANT=1,SPMV_WIN_BYTES=28672",
             "window:SPMV_VARIANT=2,SPMV_WIN_BYTES=75776", "window:SPMV_VARIANT=2,SPMV_WIN_BYTES=110592",
             "window:SPMV_REDUCE=2", "window:SPMV_REDUCE=4",
