@@ -362,13 +362,19 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     const int m = p.m;
     const int eb = vbytes + 2;
     int target = h->opts[RSG_OPT_SPMV_WIN_BYTES]; // shared memory per CTA aimed at
-    if (target <= 0) target = 36 * 1024; // 6 CTAs per SM (tools/spmv_sweep.py: 28-45 KB within 1 % on fp64, best for fp32 / mixed)
+    int threads = p.variant == 1 ? 64 : p.variant == 2 ? 256 : 128;
+    if (target <= 0) {
+        target = 36 * 1024; // 6 CTAs per SM (tools/spmv_sweep.py: 28-45 KB within 1 % on fp64, best for fp32 / mixed)
+        // A product of only a few waves of such tiles (configs 1 and 3, a rank's share of config 5 on 8 GPUs) is ramp- and
+        // tail-bound: finer tiles with 64-thread CTAs (profiles/r2_window_pdl_sweep.jsonl: C1 13.4 -> 12.8 us, C3 8.5 -> 7.7 us)
+        const long long tiles36 = ((long long)p.nnz * eb + 4LL * m) / ((long long)target * 64 / 100) + 1;
+        if (p.variant == 0 && tiles36 < 6LL * 6 * h->sm_count) { target = 22 * 1024; threads = 64; }
+    }
     target = std::min(std::max(target, 8 * 1024), 160 * 1024);
     int pct = h->opts[RSG_OPT_SPMV_WIN_STREAM_PCT]; // share of it given to the entries (the rest: x window, row pointers)
     if (pct <= 0) pct = 64;
     const long long budget = std::max<long long>(1024, (long long)target * pct / 100);
     if ((long long)p.max_row * eb * 2 > budget) return RSG_UNSUPPORTED; // long rows: the tile kernel splits them
-    const int threads = p.variant == 1 ? 64 : p.variant == 2 ? 256 : 128;
     // rows per tile: at most 8 per thread (5-point rows: 4)
     const int rw = (int)std::max<long long>(4, budget / (8LL * threads));
     const long long total = (long long)p.nnz * eb + (long long)rw * m;
