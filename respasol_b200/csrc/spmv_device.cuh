@@ -153,12 +153,24 @@ template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_pu
 {
     __shared__ int s_last;
     const int tid = threadIdx.x;
-    for (int j = blockIdx.x * THREADS + tid; j < fuse.nsend; j += fuse.ctas * THREADS) {
-        const TX v = x[fuse.send_idx[j]];
+    // four entries per thread, their two dependent loads (index, then x) issued back to back: the push is latency, not bandwidth
+    const int stride = fuse.ctas * THREADS;
+    for (int j0 = blockIdx.x * THREADS + tid; j0 < fuse.nsend; j0 += 4 * stride) {
+        int idx[4];
+        TX v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) idx[u] = (j0 + u * stride < fuse.nsend) ? fuse.send_idx[j0 + u * stride] : -1;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = idx[u] >= 0 ? x[idx[u]] : (TX)0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int j = j0 + u * stride;
+            if (idx[u] < 0) continue;
 #pragma unroll 1
-        for (int q = 0; q < fuse.npeers; ++q) {
-            TX *d = static_cast<TX *>(fuse.dst[q]);
-            if (d && j >= fuse.lo[q] && j < fuse.hi[q]) d[j] = v; // each boundary entry only to the peers that read it
+            for (int q = 0; q < fuse.npeers; ++q) {
+                TX *d = static_cast<TX *>(fuse.dst[q]);
+                if (d && j >= fuse.lo[q] && j < fuse.hi[q]) d[j] = v[u]; // each boundary entry only to the peers that read it
+            }
         }
     }
     __threadfence_system();

@@ -412,7 +412,10 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
         if (COH_OK) RSG_CUDA_TRY(cudaFuncSetAttribute(kern_coh, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     HaloFuse fuse = h->fuse;
-    if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
+    // four boundary entries per thread, issued together: the push is a chain of two dependent loads and a remote store per
+    // entry, so with few threads walking many entries it outlasts the whole product (measured: 32 CTAs x 9 entries per
+    // thread, one at a time = 18 us for a 14 us product)
+    if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(1024, (fuse.nsend + 4 * THREADS - 1) / (4 * THREADS)));
     LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg};
     const int ropt = h->opts[RSG_OPT_SPMV_REDUCE] | (p->lanes_hint == 2 ? 1 << 16 : 0);
     (multi ? kern_coh : kern)<<<p->nblk + fuse.ctas + ls.nseg, THREADS, smem, h->stream>>>(

@@ -448,7 +448,10 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
         RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     }
     HaloFuse fuse = h->fuse;
-    if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(32, (fuse.nsend + THREADS - 1) / THREADS));
+    // four boundary entries per thread, issued together: the push is a chain of two dependent loads and a remote store per
+    // entry, so with few threads walking many entries it outlasts the whole product (measured: 32 CTAs x 9 entries per
+    // thread, one at a time = 18 us for a 14 us product)
+    if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(1024, (fuse.nsend + 4 * THREADS - 1) / (4 * THREADS)));
     WinArgs w = {p->wdesc, p->rp0, p->widx, p->first8, p->first + p->nnz, p->n, p->nblk};
     // RSG_OPT_SPMV_PDL: 0 = programmatic dependent launch, plan data only ahead of the dependency; 1 = plain launch;
     // 2 = the values too (the caller promises that nothing queued before the product writes them)
