@@ -82,6 +82,21 @@ int rsg_dist_create(rsg_handle_t h, char precision, int m, int n_ext, int nnz, i
         f.counter = h->scratch_i + 62;
         f.nsend = nsend; f.npeers = npeers; f.ctas = npeers > 0 ? 1 : 0;
     }
+    if (nsend > 0 && npeers > 0) { // a send list made of a few contiguous runs needs no index load in the push
+        std::vector<int> idx((size_t)nsend);
+        DevGuard g0(h->device);
+        if (cudaMemcpy(idx.data(), send_idx, sizeof(int) * (size_t)nsend, cudaMemcpyDeviceToHost) != cudaSuccess) { (void)cudaGetLastError(); delete d; return RSG_CUDA_ERROR; }
+        int nruns = 1, start[4] = {idx[0], 0, 0, 0}, len[4] = {1, 0, 0, 0};
+        for (int j = 1; j < nsend && nruns <= 4; ++j) {
+            if (idx[(size_t)j] == idx[(size_t)j - 1] + 1) { len[nruns - 1]++; continue; }
+            if (++nruns > 4) break;
+            start[nruns - 1] = idx[(size_t)j]; len[nruns - 1] = 1;
+        }
+        for (int p = 0; p < 2; ++p) {
+            d->fuse[p].nruns = nruns <= 4 ? nruns : 0;
+            for (int r = 0; r < 4; ++r) { d->fuse[p].run_start[r] = start[r]; d->fuse[p].run_len[r] = len[r]; }
+        }
+    }
     // the plan of this block, halo tiles marked, now (so that no step pays for an analysis)
     DevGuard g(h->device);
     const int keep = h->opts[RSG_OPT_SPMV_HALO_START];

@@ -44,6 +44,8 @@ struct HaloFuse {
     const int *send_idx;
     int *counter;
     int nsend, npeers, epoch, ctas;
+    // the send list as at most 4 contiguous runs of x (a slab of a stencil: its first and last plane): no index load
+    int nruns, run_start[4], run_len[4];
 };
 
 // Long rows of a TILE plan (longer than a CTA's staging capacity) are cut into segments, one CTA each, placed in

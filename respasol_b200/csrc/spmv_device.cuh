@@ -149,17 +149,30 @@ __device__ __forceinline__ float ld_x_coherent(const float *p)
 
 // The first `fuse.ctas` CTAs of a product's grid: store this rank's boundary entries of x into the peers' halo slots
 // (plain stores into P2P-mapped memory), then the last of them to finish releases `epoch` to the peers' flags.
-template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_push(const HaloFuse &fuse, const TX *__restrict__ x)
+template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_push(const HaloFuse &fuse, const TX *__restrict__ x, int cta = -1)
 {
     __shared__ int s_last;
     const int tid = threadIdx.x;
-    // four entries per thread, their two dependent loads (index, then x) issued back to back: the push is latency, not bandwidth
+    if (cta < 0) cta = blockIdx.x;
+    // four entries per thread, their loads issued back to back: the push is a latency chain, not bandwidth
     const int stride = fuse.ctas * THREADS;
-    for (int j0 = blockIdx.x * THREADS + tid; j0 < fuse.nsend; j0 += 4 * stride) {
+    for (int j0 = cta * THREADS + tid; j0 < fuse.nsend; j0 += 4 * stride) {
         int idx[4];
         TX v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) idx[u] = (j0 + u * stride < fuse.nsend) ? fuse.send_idx[j0 + u * stride] : -1;
+        for (int u = 0; u < 4; ++u) {
+            const int j = j0 + u * stride;
+            idx[u] = -1;
+            if (j < fuse.nsend) {
+                if (fuse.nruns > 0) { // entry j of the concatenated runs
+                    int r = 0, off = j;
+                    while (r + 1 < fuse.nruns && off >= fuse.run_len[r]) { off -= fuse.run_len[r]; ++r; }
+                    idx[u] = fuse.run_start[r] + off;
+                } else {
+                    idx[u] = fuse.send_idx[j];
+                }
+            }
+        }
 #pragma unroll
         for (int u = 0; u < 4; ++u) v[u] = idx[u] >= 0 ? x[idx[u]] : (TX)0;
 #pragma unroll
@@ -173,7 +186,7 @@ template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_pu
             }
         }
     }
-    __threadfence_system();
+    __threadfence_system(); // every thread: its own stores have reached the peers
     __syncthreads();
     if (tid == 0) {
         const int done = atomicAdd(fuse.counter, 1);
@@ -197,7 +210,7 @@ __device__ __forceinline__ void halo_flag_wait(const int *flags, int n, int epoc
         int spins = 0, v;
         for (;;) {
             asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(flags + tid) : "memory");
-            if (v >= epoch) break;
+            if (v - epoch >= 0) break; // (wrap-aware)
             if (++spins >= max_spins) { if (err_flag) atomicExch(err_flag, 1); break; }
             if (spins > 64) __nanosleep(spins > 4096 ? 400 : 40);
         }

@@ -56,6 +56,10 @@ def main():
             ops[i % 2].step()
         torch.cuda.synchronize()
         res = {}
+        scratch = torch.zeros(ops[0].plan.n_ext + 64, dtype=torch.float64, device=dev)
+        lflags = torch.zeros(64, dtype=torch.int32, device=dev)
+        local_slots = h.ptr_array([scratch.data_ptr() if q != rank else 0 for q in range(world)])
+        local_flags = h.ptr_array([lflags[q:].data_ptr() if q != rank else 0 for q in range(world)])
         for mode in args.modes.split(","):
             def one(i, mode=mode):
                 op = ops[i % 2]
@@ -64,7 +68,9 @@ def main():
                     return
                 h.set_option("SPMV_HALO_START", op.plan.halo_base)
                 if mode == "fuse_only":  # push + signal with an epoch the peers have long passed: nobody waits on it
-                    h.spmv_halo_fuse(op.send_idx32, op.slots[0], op.flag_slots[0], 1)
+                    h.spmv_halo_fuse(op.send_idx32, op.slots[0], local_flags, 1)  # (signals go to a dummy: the real flags count)
+                elif mode == "fuse_local":  # the same push, but into a buffer on THIS device: is the NVLink store the slow part?
+                    h.spmv_halo_fuse(op.send_idx32, local_slots, local_flags, 1)
                 elif mode == "wait_only":  # flags already at a later epoch: the polls succeed at once
                     h.spmv_halo_wait(op.flag_views[0], op.n_wait, 1)
                 h.spmv(op.A, op.images[0], op.y)
