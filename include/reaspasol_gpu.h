@@ -71,7 +71,8 @@ typedef enum {
     RSG_OPT_SPMV_LONG_ROW = 2,  /* rows longer than this get a CTA each (0 = default, tile/4) */
     RSG_OPT_SPMV_VARIANT = 3,   /* compiled tile/CTA shape variant index (0 = default) */
     RSG_OPT_SPMV_CACHE_HINT = 4,/* 0: plain ld.global.nc; 1: L1::no_allocate streams; 2: + L2 evict_first streams */
-    RSG_OPT_TRSV_ALGO = 5,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
+    RSG_OPT_TRSV_ALGO = 5,      /* 0 auto (by level width), 1 sync-free flags on every SM, 2 level-scheduled launches,
+                                   3 chain: one CTA walks the levels, a block barrier per level (narrow levels) */
     RSG_OPT_ILU0_ALGO = 6,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_SPMV_X_PERSIST = 7, /* 1: pin x in L2 with an access-policy window on the stream */
     RSG_OPT_SPMV_X_HINT = 8,    /* tile kernel plan: 4 = never size tiles for two lanes per row (A/B); other values unused */

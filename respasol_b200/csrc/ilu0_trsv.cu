@@ -417,6 +417,117 @@ trsv_thin_levels_kernel(int l0, int l1, const int *__restrict__ level_ptr, int b
     }
 }
 
+// ---- chain solve: ONE CTA walks the levels ------------------------------------------------------------------
+// The flag-polling kernel above pays, per level, a store that must reach L2, a poll that must find it and usually a
+// second poll for the dependencies that were not there yet: 1.6 us per level on config 3, on 148 SMs that are idle most
+// of the time.  When levels are narrow (config 3: 323 rows on average, the 2-D 5-point 1000^2: 500) one SM can take a
+// whole level, and then a level boundary is a block barrier (tens of ns) instead of a trip through L2 flags:
+//   * rows are taken in level order, a "chunk" of at most kChainThreads rows at a time (a wide level is several chunks
+//     without a barrier between them, a new level starts with __syncthreads());
+//   * everything a row needs except the solution entries is off the dependency chain: its (row, first entry, end, diagonal)
+//     record is fetched two chunks ahead, its first B entries (column, coefficient), right-hand side and pivot one chunk
+//     ahead, into registers;
+//   * the solution entries are plain loads: inside one CTA a barrier orders them after the stores of the previous level
+//     (no flags, no sentinel, no fill kernel); the fma chain runs in stored order, so the result is bit-identical to the
+//     oracle's and to the polling kernel's.
+static constexpr int kChainThreads = 512;
+// AUTO: average rows per level up to which one SM beats 148 polling ones.  Measured (tools/trsv_ab.py, profiles/r2_trsv_ab.log):
+// 2-D 5-point 200^2 (100 rows per level) 0.72 vs 1.10 ms; config 3 (323 per level) 2.24 vs 1.05 ms, 1000^2 (500) 9.6 vs 5.6 ms --
+// one SM's load pipeline (about 35 GB/s of 32-byte sectors here) saturates long before the level barrier matters.
+static constexpr int kChainMaxWidth = 128;
+
+__global__ void chain_meta_kernel(int n, int base, int upper, const int *__restrict__ rowptr, const int *__restrict__ diag_pos,
+                                  const int *__restrict__ order, int4 *tmeta)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n) return;
+    const int i = order[t], kd = diag_pos[i];
+    tmeta[t] = upper ? make_int4(i, kd + 1, rowptr[i + 1] - base, kd) : make_int4(i, rowptr[i] - base, kd, kd);
+}
+
+template <typename T, bool UPPER, int B>
+__global__ void __launch_bounds__(kChainThreads, 1)
+trsv_chain_kernel(int nchunks, const int2 *__restrict__ chunks, const int4 *__restrict__ tmeta, int base,
+                  const int *__restrict__ colidx, const T *__restrict__ lu, const T *__restrict__ rhs, T *sol)
+{
+    const int tid = threadIdx.x;
+    auto meta_of = [&](int c, int &newlevel) -> int4 {
+        newlevel = 0;
+        if (c >= nchunks) return make_int4(-1, 0, 0, 0);
+        const int2 ch = __ldg(chunks + c);
+        newlevel = (unsigned)ch.x >> 31;
+        const int t = (ch.x & 0x7fffffff) + tid;
+        return t < ch.y ? __ldg(tmeta + t) : make_int4(-1, 0, 0, 0);
+    };
+    int col0[B], col1[B];
+    T a0[B], a1[B];
+    T rhs0 = 0, rhs1 = 0, dg0 = 1, dg1 = 1;
+    int nl0, nl1, nl2;
+    int4 m0 = meta_of(0, nl0), m1 = meta_of(1, nl1), m2;
+    auto load_row = [&](const int4 &m, int (&col)[B], T (&a)[B], T &r, T &dg) {
+        if (m.x < 0) return;
+#pragma unroll
+        for (int u = 0; u < B; ++u)
+            if (m.y + u < m.z) { col[u] = __ldg(colidx + m.y + u) - base; a[u] = __ldg(lu + m.y + u); }
+        r = __ldg(rhs + m.x);
+        if (UPPER) dg = __ldg(lu + m.w);
+    };
+    load_row(m0, col0, a0, rhs0, dg0);
+    for (int c = 0; c < nchunks; ++c) {
+        m2 = meta_of(c + 2, nl2);               // two chunks ahead: the record
+        load_row(m1, col1, a1, rhs1, dg1);      // one chunk ahead: entries, right-hand side, pivot
+        if (m0.x >= 0) {
+            T s = rhs0;
+            const int len = m0.z - m0.y;
+#pragma unroll
+            for (int u = 0; u < B; ++u)
+                if (u < len) s = fma_t<T>(-a0[u], sol[col0[u]], s);
+            for (int k = m0.y + B; k < m0.z; ++k) s = fma_t<T>(-__ldg(lu + k), sol[__ldg(colidx + k) - base], s); // a row longer than B
+            sol[m0.x] = UPPER ? div_t<T>(s, dg0) : s;
+        }
+        if (nl1) __syncthreads(); // the next chunk opens a new level: its rows read what this level wrote
+        m0 = m1; nl0 = nl1; rhs0 = rhs1; dg0 = dg1;
+#pragma unroll
+        for (int u = 0; u < B; ++u) { col0[u] = col1[u]; a0[u] = a1[u]; }
+        m1 = m2; nl1 = nl2;
+    }
+}
+
+template <typename T>
+static int chain_prepare(rsg_context *h, TriPlan *p, int which)
+{
+    if (p->tmeta[which]) return RSG_OK;
+    cudaStream_t st = h->stream;
+    const int n = p->n;
+    const std::vector<int> &lp = p->level_ptr_host[which];
+    std::vector<int2> ch;
+    for (int l = 0; l < p->nlevels[which]; ++l)
+        for (int t = lp[(size_t)l]; t < lp[(size_t)l + 1]; t += kChainThreads)
+            ch.push_back(make_int2((int)((unsigned)t | (t == lp[(size_t)l] ? 0x80000000u : 0u)), std::min(t + kChainThreads, lp[(size_t)l + 1])));
+    p->nchunks[which] = (int)ch.size();
+    RSG_CUDA_TRY(cudaMalloc(&p->tmeta[which], sizeof(int4) * (size_t)(n > 0 ? n : 1)));
+    RSG_CUDA_TRY(cudaMalloc(&p->chunks[which], sizeof(int2) * (ch.size() ? ch.size() : 1)));
+    if (!ch.empty()) RSG_CUDA_TRY(cudaMemcpyAsync(p->chunks[which], ch.data(), sizeof(int2) * ch.size(), cudaMemcpyHostToDevice, st));
+    chain_meta_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, p->base, which, p->rowptr, p->diag_pos, p->order[which], p->tmeta[which]);
+    h->launches++;
+    RSG_CUDA_TRY(cudaStreamSynchronize(st)); // (ch is a host temporary)
+    p->bytes += sizeof(int4) * (size_t)n + sizeof(int2) * ch.size();
+    return RSG_OK;
+}
+
+template <typename T>
+static int trsv_chain(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
+{
+    RSG_TRY(chain_prepare<T>(h, p, 0));
+    RSG_TRY(chain_prepare<T>(h, p, 1));
+    constexpr int B = sizeof(T) == 8 ? 8 : 12;
+    trsv_chain_kernel<T, false, B><<<1, kChainThreads, 0, h->stream>>>(p->nchunks[0], p->chunks[0], p->tmeta[0], p->base, p->colidx, lu, b, z);
+    trsv_chain_kernel<T, true, B><<<1, kChainThreads, 0, h->stream>>>(p->nchunks[1], p->chunks[1], p->tmeta[1], p->base, p->colidx, lu, z, y);
+    h->launches += 2;
+    RSG_CUDA_TRY(cudaGetLastError());
+    return RSG_OK;
+}
+
 // ------------------------------------------------------------------ host side
 template <typename T>
 int ilu0_run(rsg_context *h, TriPlan *p, T *values, int *zero_pivot_row)
@@ -494,7 +605,12 @@ int trsv_run(rsg_context *h, TriPlan *p, const T *lu, const T *b, T *z, T *y)
     RSG_TRY(tri_build_levels(h, p, -1));
     cudaStream_t st = h->stream;
     const int n = p->n;
-    if (h->opts[RSG_OPT_TRSV_ALGO] == 2) {
+    // RSG_OPT_TRSV_ALGO: 0 = by level width (narrow levels: one CTA walks them; wide levels: flag polling on every SM),
+    // 1 = flag polling, 2 = one launch per fat level, 3 = chain
+    const int talgo = h->opts[RSG_OPT_TRSV_ALGO];
+    const long long avg_width = n / std::max(1, std::min(p->nlevels[0], p->nlevels[1]));
+    if (talgo == 3 || (talgo == 0 && avg_width <= kChainMaxWidth)) return trsv_chain<T>(h, p, lu, b, z, y);
+    if (talgo == 2) {
         RSG_TRY((trsv_levels_launches<T, false>(h, p, lu, b, z)));
         RSG_TRY((trsv_levels_launches<T, true>(h, p, lu, z, y)));
         RSG_CUDA_TRY(cudaGetLastError());

@@ -163,8 +163,18 @@ int ensure_cub_tmp(rsg_context *h, size_t bytes)
     return RSG_OK;
 }
 
+void tri_free_chain(TriPlan &p)
+{
+    for (int w = 0; w < 2; ++w) {
+        if (p.tmeta[w]) cudaFree(p.tmeta[w]);
+        if (p.chunks[w]) cudaFree(p.chunks[w]);
+        p.tmeta[w] = nullptr; p.chunks[w] = nullptr; p.nchunks[w] = 0;
+    }
+}
+
 void tri_free_plan(TriPlan &p)
 {
+    tri_free_chain(p);
     if (p.slab) cudaFree(p.slab);
     p = TriPlan();
 }
@@ -210,6 +220,7 @@ int tri_get_plan(rsg_context *h, int n, int nnz_hint, int base, const int *rowpt
             if (!force_rebuild) { *out = &q; h->last_tri = (int)i; return RSG_OK; }
             // re-analysis of the same arrays: keep the slab (and its epoch), rebuild the contents
             p.slab = q.slab; p.slab_n = q.slab_n; p.epoch = q.epoch;
+            tri_free_chain(q);
             h->tri_plans.erase(h->tri_plans.begin() + (long)i);
             break;
         }

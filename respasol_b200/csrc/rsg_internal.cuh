@@ -125,6 +125,11 @@ struct TriPlan {
     int *ctl = nullptr;            // 16 ints: [0] ticket, [1] error flag, [2] min zero-pivot row; [4..7] second kernel
     int *sort_keys = nullptr;      // radix-sort scratch (n ints each)
     int *sort_vals = nullptr;
+    // chain solves (ilu0_trsv.cu: trsv_chain_kernel): per position of the level order (row, first entry, end entry, diagonal
+    // position), and the (first position | new-level flag << 31, end position) chunks of at most kChainThreads rows
+    int4 *tmeta[2] = {nullptr, nullptr};
+    int2 *chunks[2] = {nullptr, nullptr};
+    int nchunks[2] = {0, 0};
     int *slab = nullptr;           // ONE allocation holding every array above (re-used when the analysis is re-run)
     int slab_n = 0;
     size_t bytes = 0;

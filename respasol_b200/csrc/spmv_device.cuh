@@ -246,14 +246,26 @@ __device__ __forceinline__ TX cta_row_sum(int k0, int k1, const int *__restrict_
         if (qf0 < qf1) {
             ks = qf0 << 2; ke = qf1 << 2;
             TX acc2 = 0;
-            for (int q = qf0 + tid; q < qf1; q += THREADS) {
-                int4 c = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
-                TV v[4];
-                ld_values4<HINT>(values + (q << 2), pol, v);
-                acc += (TX)v[0] * ld_xg<COH>(x + (c.x - base));
-                acc2 += (TX)v[1] * ld_xg<COH>(x + (c.y - base));
-                acc += (TX)v[2] * ld_xg<COH>(x + (c.z - base));
-                acc2 += (TX)v[3] * ld_xg<COH>(x + (c.w - base));
+            // two quads per thread and iteration, every load of both issued before any is used: a long row's segment is a
+            // chain of (index, value) -> x gather -> multiply-add per quad, and with one quad in flight per thread a 2048-entry
+            // segment took four dependent round trips (profiles/r2_tile_c4_d_ncu_full.txt: half of the stall samples of config 4)
+            for (int q = qf0 + tid; q < qf1; q += 2 * THREADS) {
+                const int qb = q + THREADS;
+                const bool hb = qb < qf1;
+                const int4 ca = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (q << 2)), pol);
+                int4 cb = ca;
+                TV va[4], vb[4] = {0, 0, 0, 0};
+                ld_values4<HINT>(values + (q << 2), pol, va);
+                if (hb) {
+                    cb = ld_stream<HINT>(reinterpret_cast<const int4 *>(colidx + (qb << 2)), pol);
+                    ld_values4<HINT>(values + (qb << 2), pol, vb);
+                }
+                const TX xa0 = ld_xg<COH>(x + (ca.x - base)), xa1 = ld_xg<COH>(x + (ca.y - base));
+                const TX xa2 = ld_xg<COH>(x + (ca.z - base)), xa3 = ld_xg<COH>(x + (ca.w - base));
+                const TX xb0 = ld_xg<COH>(x + (cb.x - base)), xb1 = ld_xg<COH>(x + (cb.y - base));
+                const TX xb2 = ld_xg<COH>(x + (cb.z - base)), xb3 = ld_xg<COH>(x + (cb.w - base));
+                acc += (TX)va[0] * xa0; acc2 += (TX)va[1] * xa1; acc += (TX)va[2] * xa2; acc2 += (TX)va[3] * xa3;
+                acc += (TX)vb[0] * xb0; acc2 += (TX)vb[1] * xb1; acc += (TX)vb[2] * xb2; acc2 += (TX)vb[3] * xb3; // (vb = 0 without a second quad)
             }
             acc += acc2;
             // ragged ends

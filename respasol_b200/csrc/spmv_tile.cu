@@ -128,17 +128,22 @@ template <typename TV, typename TX, int THREADS, int CAPE, int ROWS, int MINB, b
 __global__ void __launch_bounds__(THREADS, MINB)
 spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ colidx, const TV *__restrict__ values,
                  const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta, const int4 *__restrict__ desc,
-                 int nnz_end, int ntiles, int reduce_opt, const int *wait_flags, int wait_n, int wait_epoch, int *err_flag,
-                 int max_spins, const HaloFuse fuse, const LongSplit ls)
+                 int nnz_end, int ntiles, int reduce_opt, int early_values, const int *wait_flags, int wait_n, int wait_epoch,
+                 int *err_flag, int max_spins, const HaloFuse fuse, const LongSplit ls)
 {
     typedef PipeStage<TV, CAPE, ROWS> Stage;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) uint64_t s_full;
     __shared__ __align__(8) uint64_t s_aux;
     const int tid = threadIdx.x;
+    // programmatic dependent launch, as in the window kernel: the next kernel of the stream may start once every CTA of
+    // this grid is here; this grid reads only pattern data (descriptor, row pointers, colidx -- the plan is keyed on the
+    // pattern) and, if promised static, the values before grid_dependency_wait()
+    grid_launch_dependents();
     if (COH && (int)blockIdx.x < fuse.ctas) {
         // ---- fused exchange: these CTAs are dispatched first; they publish this rank's boundary entries of x
         // to the peers (plain stores into P2P-mapped memory over NVLink) while the tiles behind them multiply
+        grid_dependency_wait();
         halo_fuse_push<TX, THREADS>(fuse, x);
         return;
     }
@@ -146,6 +151,7 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
     if (seg_id < ls.nseg) {
         // ---- one segment of a long row, straight from global memory with 128-bit loads; the last segment of the
         // row to arrive adds the partial sums in segment order and stores y
+        grid_dependency_wait();
         if (COH && wait_n > 0) { // a dense row may reach into the halo: its segments wait like a marked tile
             halo_flag_wait(wait_flags, wait_n, wait_epoch, err_flag, max_spins);
             __syncthreads();
@@ -191,10 +197,13 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
         mbar_expect_tx(&s_full, nrp * 4u + nq * (uint32_t)(sizeof(TV) + sizeof(int)));
         bulk_g2s(smem_raw + Stage::rp_off, rp0 + ra, nrp * 4u, &s_full, spol);
         if (nq) {
-            bulk_g2s(smem_raw + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full, spol);
             bulk_g2s(smem_raw + Stage::col_off, colidx + sb, nq * 4u, &s_full, spol);
+            if (early_values) bulk_g2s(smem_raw + Stage::val_off, values + sb, nq * (uint32_t)sizeof(TV), &s_full, spol);
         }
     }
+    grid_dependency_wait(); // x, y and (unless promised static) the values: what earlier work of the stream may have written
+    if (tid == 0 && mt.nr > 0 && qe > sb && !early_values)
+        bulk_g2s(smem_raw + Stage::val_off, values + sb, (uint32_t)(qe - sb) * (uint32_t)sizeof(TV), &s_full, spol);
     if (must_wait) {
         // this tile gathers x entries that peers write over NVLink: wait for their arrival flags
         // (while the bulk copies of the tile are in flight); every other tile never looks at them
@@ -291,7 +300,7 @@ static const int kNumTileVariants = (int)(sizeof(kTileVariants) / sizeof(kTileVa
 int tile_num_variants() { return kNumTileVariants; }
 
 static constexpr int kMaxLongRows = 4096;  // rows split into segments per plan
-static constexpr int kSegEntries = 2048;   // entries per segment CTA
+static constexpr int kSegEntries = 1024;   // entries per segment CTA (128 threads x 2 quads: one pass, both quads' loads in flight together)
 static constexpr int kMaxSegments = 1 << 20;
 
 // LongSplit of a TILE plan.  strict: RSG_UNSUPPORTED when there are too many long rows (the AUTO caller then
@@ -418,9 +427,24 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(1024, (fuse.nsend + 4 * THREADS - 1) / (4 * THREADS)));
     LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg};
     const int ropt = h->opts[RSG_OPT_SPMV_REDUCE] | (p->lanes_hint == 2 ? 1 << 16 : 0);
-    (multi ? kern_coh : kern)<<<p->nblk + fuse.ctas + ls.nseg, THREADS, smem, h->stream>>>(
-        p->base, p->rp0, p->colidx, values, x, y, alpha, beta, p->pdesc, p->first + p->nnz, p->nblk, ropt, h->wait_flags,
-        h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse, ls);
+    int pdl = h->opts[RSG_OPT_SPMV_PDL]; // see spmv_window.cu / the header
+    if (pdl != 1) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(h->stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { (void)cudaGetLastError(); pdl = 1; }
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(p->nblk + fuse.ctas + ls.nseg));
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = h->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl != 1 ? 1 : 0;
+    RSG_CUDA_TRY(cudaLaunchKernelEx(&cfg, multi ? kern_coh : kern, p->base, (const int *)p->rp0, p->colidx, values, x, y, alpha, beta,
+                                    (const int4 *)p->pdesc, p->first + p->nnz, p->nblk, ropt, pdl == 2 ? 1 : 0, h->wait_flags,
+                                    h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse, ls));
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;
     h->launches++;

@@ -72,7 +72,7 @@ def test_levels_bit_exact(handle, name):
 
 @pytest.mark.parametrize("name", sorted(MATS))
 @pytest.mark.parametrize("dtype", [np.float64, np.float32])
-@pytest.mark.parametrize("trsv_algo", [0, 2])
+@pytest.mark.parametrize("trsv_algo", [0, 1, 2, 3])
 def test_ilu0_and_solves(handle, name, dtype, trsv_algo):
     a = MATS[name]()
     prec = "d" if dtype == np.float64 else "s"
@@ -225,6 +225,7 @@ def test_hung_solve_reports_dependency_timeout(handle):
     sentinel = torch.tensor([0xFFF8DEADBEEF0001 - (1 << 64)], dtype=torch.int64, device="cuda").view(torch.float64)
     b[0:1] = sentinel
     handle.set_option("WAIT_SPINS", 2000)
+    handle.set_option("TRSV_ALGO", 1)  # the flag-polling kernel (the chain kernel has no flags: it would just propagate the NaN)
     try:
         handle.sptrsv_lu(A, A.values, b)
         with pytest.raises(RsgError) as ei:
@@ -237,6 +238,7 @@ def test_hung_solve_reports_dependency_timeout(handle):
         assert bool(torch.isfinite(y).all())
     finally:
         handle.set_option("WAIT_SPINS", 0)
+        handle.set_option("TRSV_ALGO", 0)
 
 
 def test_unsorted_rows_are_refused(handle):
