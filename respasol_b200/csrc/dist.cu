@@ -35,6 +35,7 @@ struct rsg_dist {
     HaloFuse fuse[2];
     const int *wait_flags[2] = {nullptr, nullptr};
     int nwait = 0, epoch = 0;
+    long long stored = 0; // entries of the block (from its plan)
 };
 
 namespace {
@@ -44,6 +45,8 @@ struct DevGuard {
     explicit DevGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
     ~DevGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
+
+constexpr long long kDistPdlMinEntries = 12000000; // per-rank entries below which a fused-exchange step is launched plainly
 
 inline int halo_base_of(int n_local) { return (n_local + 31) / 32 * 32; } // the halo starts on its own 128/256-byte line
 
@@ -106,6 +109,7 @@ int rsg_dist_create(rsg_handle_t h, char precision, int m, int n_ext, int nnz, i
     const int rc = m > 0 ? spmv_get_plan(h, m, n_ext, nnz, base, rowptr, colidx, false, &pl, pkey) : RSG_OK;
     h->opts[RSG_OPT_SPMV_HALO_START] = keep;
     if (rc != RSG_OK) { delete d; return rc; }
+    d->stored = pl ? pl->nnz : 0;
     *out = d;
     return RSG_OK;
 }
@@ -131,8 +135,13 @@ int rsg_dist_step(rsg_dist_t d, void *y)
         h->fuse.epoch = d->epoch;
     }
     if (d->nwait > 0) { h->wait_flags = d->wait_flags[p]; h->wait_n = d->nwait; h->wait_epoch = d->epoch; }
-    const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
+    const int keep = h->opts[RSG_OPT_SPMV_HALO_START], keep_pdl = h->opts[RSG_OPT_SPMV_PDL];
     h->opts[RSG_OPT_SPMV_HALO_START] = d->halo_start; // part of the plan's key
+    // A step cannot be shorter than push + signal + the neighbours' halo tiles (the push of step e+1 follows the end of step e,
+    // which follows the arrival of the neighbours' push e): about 15 us while a dependent-launched product saturates the
+    // memory system (every hop of the push queues behind its burst), about 1 us more than the product itself with plain
+    // launches (profiles/r2_dist_probe.jsonl).  Short per-rank products therefore keep plain launches.
+    if (d->fuse[p].npeers > 0 && d->stored < kDistPdlMinEntries && keep_pdl != 1) h->opts[RSG_OPT_SPMV_PDL] = 1;
     int rc;
     if (d->precision == 'd')
         rc = spmv_run<double, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const double *>(d->values), 1.0,
@@ -144,6 +153,7 @@ int rsg_dist_step(rsg_dist_t d, void *y)
         rc = spmv_run<float, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const float *>(d->values), 1.0,
                                      static_cast<const double *>(d->x_image[p]), 0.0, static_cast<double *>(y));
     h->opts[RSG_OPT_SPMV_HALO_START] = keep;
+    h->opts[RSG_OPT_SPMV_PDL] = keep_pdl;
     h->wait_flags = nullptr;
     h->fuse.ctas = 0;
     return rc;
