@@ -420,6 +420,37 @@ __device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_
                                                   TX alpha, TX beta)
 {
     const TX *xb = x - base;
+    if (nrows > THREADS) {
+        // more rows than threads (short rows: config 4): a thread's two rows go TOGETHER when both fit one batch -- their gathers
+        // are issued back to back, one round trip instead of two (each row is still summed left to right)
+        asm volatile("" : "+l"(xb));
+        for (int i = threadIdx.x; i < nrows; i += 2 * THREADS) {
+            const int i2 = i + THREADS;
+            const int k0 = s_rp[i] - sb, e0 = s_rp[i + 1] - sb;
+            const bool two = i2 < nrows;
+            const int k1 = two ? s_rp[i2] - sb : 0, e1 = two ? s_rp[i2 + 1] - sb : 0;
+            if (e0 - k0 <= B && e1 - k1 <= B) {
+                TX xv0[B], xv1[B];
+#pragma unroll
+                for (int u = 0; u < B; ++u) xv0[u] = (k0 + u < e0) ? ld_xg<COH>(xb + s_col[k0 + u]) : (TX)0;
+#pragma unroll
+                for (int u = 0; u < B; ++u) xv1[u] = (k1 + u < e1) ? ld_xg<COH>(xb + s_col[k1 + u]) : (TX)0;
+                TX s0 = 0, s1 = 0;
+#pragma unroll
+                for (int u = 0; u < B; ++u)
+                    if (k0 + u < e0) s0 += (TX)s_val[k0 + u] * xv0[u];
+#pragma unroll
+                for (int u = 0; u < B; ++u)
+                    if (k1 + u < e1) s1 += (TX)s_val[k1 + u] * xv1[u];
+                store_y(y, row_glob + i, s0, alpha, beta);
+                if (two) store_y(y, row_glob + i2, s1, alpha, beta);
+            } else {
+                store_y(y, row_glob + i, row_dot_lean2<TV, TX, 1, B, COH>(s_val, s_col, k0, e0, xb), alpha, beta);
+                if (two) store_y(y, row_glob + i2, row_dot_lean2<TV, TX, 1, B, COH>(s_val, s_col, k1, e1, xb), alpha, beta);
+            }
+        }
+        return;
+    }
     for (int i = threadIdx.x; i < nrows; i += THREADS) {
         const TX s = row_dot_lean2<TV, TX, 1, B, COH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
         store_y(y, row_glob + i, s, alpha, beta);

@@ -295,6 +295,8 @@ static const TileVariant kTileVariants[] = { // threads, entries per CTA, rows p
     {128, 1152, 256},  // 5: short rows (gather-latency bound): small stages, 56-60 resident warps per SM
     {128, 2304, 512},  // 6: shape of 0 WITHOUT the residency hint (round 1's build; A/B of the register cap)
     {128, 4352, 512},  // 7: shape of 1 without it
+    {128, 768, 128},   // 8: short rows, one row per thread: 16 CTAs of 10 KB per SM, one round of gathers per CTA
+    {64, 512, 64},     // 9: the same with 64-thread CTAs
 };
 static const int kNumTileVariants = (int)(sizeof(kTileVariants) / sizeof(kTileVariants[0]));
 int tile_num_variants() { return kNumTileVariants; }
@@ -463,6 +465,8 @@ int tile_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, c
     case 5: return tile_launch_one<TV, TX, 128, 1152, 256, true, true>(h, p, values, alpha, x, beta, y);
     case 6: return tile_launch_one<TV, TX, 128, 2304, 512, false, false>(h, p, values, alpha, x, beta, y);
     case 7: return tile_launch_one<TV, TX, 128, 4352, 512, false, false>(h, p, values, alpha, x, beta, y);
+    case 8: return tile_launch_one<TV, TX, 128, 768, 128, true, false>(h, p, values, alpha, x, beta, y);
+    case 9: return tile_launch_one<TV, TX, 64, 512, 64, true, false>(h, p, values, alpha, x, beta, y);
     default: return tile_launch_one<TV, TX, 128, 2304, 512, true, true>(h, p, values, alpha, x, beta, y);
     }
 }

@@ -218,7 +218,7 @@ def test_window_declines_scattered_patterns(handle):
     handle.set_option("SPMV_ALGO", 0)
 
 
-@pytest.mark.parametrize("variant", list(range(8)))
+@pytest.mark.parametrize("variant", list(range(10)))
 @pytest.mark.parametrize("reduce", [0, 1, 4, 32])
 @pytest.mark.parametrize("rpt", [0, 3])
 def test_tile_variants(handle, variant, reduce, rpt):
