@@ -254,6 +254,21 @@ int rsg_dist_step(rsg_dist_t dist, void *y);
 void *rsg_dist_x(rsg_dist_t dist); /* DEVICE pointer of the x image the NEXT step reads (write the local entries there) */
 int rsg_dist_destroy(rsg_dist_t dist);
 
+/* Chained products x_{k+1} = alpha * A * x_k on one rank's block ("repeated products, x_{k+1} <- y_k ... the SpMV
+ * epilogue stores its y rows straight into the peers' x buffers").  THREE x images rotate: step e (1, 2, ...) reads image e % 3
+ * and writes its rows into the local part of image (e + 1) % 3; the tiles that own rows a neighbour reads also store them into
+ * that neighbour's halo slots of image (e + 1) % 3 and the last of them releases e to the neighbour's flag of that image; step
+ * e + 1 acquires flags >= e before its halo tiles copy x.  The exchange of a step has the whole product to complete in instead
+ * of sitting between two products.  Arguments as rsg_dist_create with 3 images (peer_slots / peer_flags: 3 * npeers pointers,
+ * image-major; wait_flags: 3).  Before step 1 the caller fills image 1 completely, local entries AND halo (rsg_dist_x), and
+ * zeroes the flags.  Needs the window kernel and a rank somebody reads from: RSG_UNSUPPORTED otherwise. */
+int rsg_dist_create_chain(rsg_handle_t handle, char precision, int m, int n_ext, int nnz, int base, const int *rowptr,
+                          const int *colidx, const void *values, void *const *x_images, int halo_start, int nsend,
+                          const int *send_idx, int npeers, void *const *peer_slots, int *const *peer_flags, const int *peer_lo,
+                          const int *peer_hi, const int *const *wait_flags, int nwait, rsg_dist_t *dist);
+int rsg_dist_step_chain(rsg_dist_t dist, double alpha); /* one launch: x <- alpha * A * x, boundary rows pushed by their tiles */
+int rsg_dist_chain_reset(rsg_dist_t dist);              /* the next step is step 1 again (image 1 refilled, flags zeroed) */
+
 /* A whole square CSR matrix (HOST arrays, values fp64 like the reference's struct CSR) over ngpu devices of this process:
  * row blocks (row_starts: ngpu+1 cuts, or NULL for the nnz-balanced cuts of rsg_get_row_partition), halo relabelling,
  * peer access, one handle and one rsg_dist per device, one host thread per device issuing its steps.  devices: ngpu
@@ -265,6 +280,10 @@ int rsg_spmv_multi_set_x(rsg_multi_t multi, const void *x_host);            /* n
 int rsg_spmv_multi_step(rsg_multi_t multi, int nsteps);                     /* nsteps products, asynchronous */
 int rsg_spmv_multi_time(rsg_multi_t multi, int nsteps, double *us_per_step); /* timed on the devices, slowest device */
 int rsg_spmv_multi_get_y(rsg_multi_t multi, void *y_host);                  /* waits, gathers the m entries of y */
+/* chained products x <- alpha * A * x, nsteps times; x_host != NULL (re)starts the chain from that vector, NULL continues it;
+ * us_per_step (may be NULL): device time of the slowest rank / nsteps */
+int rsg_spmv_multi_chain(rsg_multi_t multi, const void *x_host, int nsteps, double alpha, double *us_per_step);
+int rsg_spmv_multi_get_x(rsg_multi_t multi, void *x_host);                  /* waits, gathers the chain's current x */
 /* what: 0 ranks, 1 halo bytes all ranks receive per step, 2 rsg_spmv_algo of rank 0's last product, 3 halo slot width;
  * row_starts (may be NULL): ngpu+1 ints */
 int rsg_spmv_multi_info(rsg_multi_t multi, int what, long long *value, int *row_starts);

@@ -80,6 +80,9 @@ GPU_SYMBOLS = {
     "rsg_spmv_halo_fuse_ranges": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _I]),
     "rsg_dist_create": (_I, [_P, C.c_char, _I, _I, _I, _I, _P, _P, _P, _P, _I, _I, _P, _I, _P, _P, _P, _P, _P, _I, C.POINTER(_P)]),
     "rsg_dist_step": (_I, [_P, _P]),
+    "rsg_dist_create_chain": (_I, [_P, C.c_char, _I, _I, _I, _I, _P, _P, _P, _P, _I, _I, _P, _I, _P, _P, _P, _P, _P, _I, C.POINTER(_P)]),
+    "rsg_dist_step_chain": (_I, [_P, _D]),
+    "rsg_dist_chain_reset": (_I, [_P]),
     "rsg_dist_x": (_P, [_P]),
     "rsg_dist_destroy": (_I, [_P]),
     "rsg_spmv_multi_create": (_I, [_I, _P, C.c_char, _I, _I, _I, _I, _P, _P, _P, _P, C.POINTER(_P)]),
@@ -87,6 +90,8 @@ GPU_SYMBOLS = {
     "rsg_spmv_multi_step": (_I, [_P, _I]),
     "rsg_spmv_multi_time": (_I, [_P, _I, C.POINTER(_D)]),
     "rsg_spmv_multi_get_y": (_I, [_P, _P]),
+    "rsg_spmv_multi_chain": (_I, [_P, _P, _I, _D, C.POINTER(_D)]),
+    "rsg_spmv_multi_get_x": (_I, [_P, _P]),
     "rsg_spmv_multi_info": (_I, [_P, _I, _LLP, _P]),
     "rsg_spmv_multi_destroy": (_I, [_P]),
 }

@@ -36,6 +36,13 @@ struct rsg_dist {
     const int *wait_flags[2] = {nullptr, nullptr};
     int nwait = 0, epoch = 0;
     long long stored = 0; // entries of the block (from its plan)
+    // chained products (rsg_dist_create_chain): three x images, step e reads image e % 3 and writes image (e + 1) % 3
+    bool chained = false;
+    void *x3[3] = {nullptr, nullptr, nullptr};
+    ChainPush cp[3];                 // cp[i]: the push INTO the peers' image i
+    const int *wflags3[3] = {nullptr, nullptr, nullptr};
+    int *send_pos = nullptr;         // device, m ints (owned)
+    int *chain_counter = nullptr;    // device (owned, with send_pos)
 };
 
 namespace {
@@ -117,11 +124,16 @@ int rsg_dist_create(rsg_handle_t h, char precision, int m, int n_ext, int nnz, i
 int rsg_dist_destroy(rsg_dist_t d)
 {
     if (!d) return RSG_BAD_ARG;
+    if (d->send_pos) { DevGuard g(d->h->device); cudaFree(d->send_pos); }
     delete d;
     return RSG_OK;
 }
 
-void *rsg_dist_x(rsg_dist_t d) { return d ? d->x_image[d->epoch & 1] : nullptr; } // the image the NEXT step reads
+void *rsg_dist_x(rsg_dist_t d) // the image the NEXT step reads
+{
+    if (!d) return nullptr;
+    return d->chained ? d->x3[(d->epoch + 1) % 3] : d->x_image[d->epoch & 1];
+}
 
 int rsg_dist_step(rsg_dist_t d, void *y)
 {
@@ -159,6 +171,118 @@ int rsg_dist_step(rsg_dist_t d, void *y)
     return rc;
 }
 
+/* Chained products x_{k+1} = alpha * A * x_k on one rank's block (SURVEY.md 8e's use case: "repeated products, x_{k+1} <- y_k").
+ * Three x images of the [local | halo] layout rotate: step e reads image e % 3 and writes its rows of the product into the local
+ * part of image (e + 1) % 3; the tiles that own rows a neighbour reads also store them into that neighbour's halo slots of
+ * image (e + 1) % 3 and, when the last of them is done, release e to the neighbour's flag of that image.  Step e + 1 acquires
+ * flags >= e before its halo tiles copy x.  The exchange of a step thus has the whole product to complete in, instead of
+ * sitting between two products.  peer_slots / peer_flags: 3 * npeers pointers, image-major; wait_flags: 3 pointers.
+ * Before the first step the caller fills image 1 completely (local entries AND halo; rsg_dist_x gives the pointer).
+ * Needs the window kernel (RSG_UNSUPPORTED for patterns it declines). */
+int rsg_dist_create_chain(rsg_handle_t h, char precision, int m, int n_ext, int nnz, int base, const int *rowptr, const int *colidx,
+                          const void *values, void *const *x_images, int halo_start, int nsend, const int *send_idx, int npeers,
+                          void *const *peer_slots, int *const *peer_flags, const int *peer_lo, const int *peer_hi,
+                          const int *const *wait_flags, int nwait, rsg_dist_t *out)
+{
+    if (!h || !out || m <= 0 || n_ext < m || !rowptr || !x_images || !x_images[0] || !x_images[1] || !x_images[2] || npeers < 0 ||
+        npeers > RSG_MAX_PEERS || nwait < 0 || nwait > RSG_MAX_PEERS || (precision != 'd' && precision != 's' && precision != 'm') ||
+        (npeers > 0 && (!peer_slots || !peer_flags)) || (nwait > 0 && (!wait_flags || !wait_flags[0] || !wait_flags[1] || !wait_flags[2])) ||
+        (nsend > 0 && !send_idx))
+        return RSG_BAD_ARG;
+    *out = nullptr;
+    rsg_dist *d = new (std::nothrow) rsg_dist();
+    if (!d) return RSG_ALLOC_FAILED;
+    d->h = h; d->precision = precision; d->m = m; d->n_ext = n_ext; d->nnz = nnz; d->base = base; d->halo_start = halo_start;
+    d->rowptr = rowptr; d->colidx = colidx; d->values = values;
+    d->nwait = nwait; d->chained = true;
+    if (npeers > 0 && nsend == 0) { delete d; return RSG_UNSUPPORTED; } // a rank nobody reads from has no producer tile to signal with: use rsg_dist_create
+    DevGuard g(h->device);
+    // send_pos[row] = position of the row in the send list (-1: nobody reads it)
+    std::vector<int> idx((size_t)(nsend > 0 ? nsend : 1)), pos((size_t)m + 1, -1);
+    if (nsend > 0 && cudaMemcpy(idx.data(), send_idx, sizeof(int) * (size_t)nsend, cudaMemcpyDeviceToHost) != cudaSuccess) { (void)cudaGetLastError(); delete d; return RSG_CUDA_ERROR; }
+    for (int j = 0; j < nsend; ++j) {
+        if (idx[(size_t)j] < 0 || idx[(size_t)j] >= m) { delete d; return RSG_BAD_ARG; }
+        pos[(size_t)idx[(size_t)j]] = j;
+    }
+    pos[(size_t)m] = 0; // slot m = the counter of finished producer tiles
+    if (cudaMalloc(&d->send_pos, sizeof(int) * ((size_t)m + 1)) != cudaSuccess ||
+        cudaMemcpy(d->send_pos, pos.data(), sizeof(int) * ((size_t)m + 1), cudaMemcpyHostToDevice) != cudaSuccess) {
+        (void)cudaGetLastError();
+        if (d->send_pos) cudaFree(d->send_pos);
+        delete d;
+        return RSG_ALLOC_FAILED;
+    }
+    d->chain_counter = d->send_pos + m;
+    for (int i = 0; i < 3; ++i) {
+        d->x3[i] = x_images[i];
+        d->wflags3[i] = nwait > 0 ? wait_flags[i] : nullptr;
+        ChainPush &c = d->cp[i];
+        std::memset(&c, 0, sizeof(c));
+        for (int q = 0; q < npeers; ++q) {
+            c.dst[q] = peer_slots[i * npeers + q];
+            c.flag[q] = peer_flags[i * npeers + q];
+            c.lo[q] = peer_lo ? peer_lo[q] : 0;
+            c.hi[q] = peer_hi ? peer_hi[q] : nsend;
+        }
+        c.send_pos = d->send_pos;
+        c.counter = d->chain_counter;
+        c.npeers = npeers;
+    }
+    const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
+    h->opts[RSG_OPT_SPMV_HALO_START] = halo_start;
+    h->plan_send_pos = npeers > 0 ? d->send_pos : nullptr;
+    SpmvPlan *pl = nullptr;
+    const int pkey = precision == 'd' ? 0x88 : precision == 's' ? 0x44 : 0x84;
+    int rc = spmv_get_plan(h, m, n_ext, nnz, base, rowptr, colidx, false, &pl, pkey);
+    h->opts[RSG_OPT_SPMV_HALO_START] = keep;
+    h->plan_send_pos = nullptr;
+    if (rc == RSG_OK && npeers > 0 && (pl->algo != RSG_SPMV_WINDOW || (nsend > 0 && pl->wprod <= 0))) rc = RSG_UNSUPPORTED;
+    if (rc != RSG_OK) { cudaFree(d->send_pos); delete d; return rc; }
+    d->stored = pl->nnz;
+    *out = d;
+    return RSG_OK;
+}
+
+/* restart the chain (after the caller has refilled image 1 and zeroed the flags): the next step is step 1 */
+int rsg_dist_chain_reset(rsg_dist_t d)
+{
+    if (!d || !d->chained) return RSG_BAD_ARG;
+    d->epoch = 0;
+    return RSG_OK;
+}
+
+int rsg_dist_step_chain(rsg_dist_t d, double alpha)
+{
+    if (!d || !d->chained) return RSG_BAD_ARG;
+    rsg_context *h = d->h;
+    DevGuard g(h->device);
+    const int e = ++d->epoch;             // this step
+    const int src = e % 3, dstimg = (e + 1) % 3;
+    if (d->cp[dstimg].npeers > 0) {
+        h->chain = d->cp[dstimg];
+        h->chain.epoch = e;
+    }
+    if (d->nwait > 0) { h->wait_flags = d->wflags3[src]; h->wait_n = d->nwait; h->wait_epoch = e - 1; }
+    const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
+    h->opts[RSG_OPT_SPMV_HALO_START] = d->halo_start;
+    h->plan_send_pos = d->cp[dstimg].npeers > 0 ? d->send_pos : nullptr; // part of the plan's key
+    int rc;
+    if (d->precision == 'd')
+        rc = spmv_run<double, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const double *>(d->values), alpha,
+                                      static_cast<const double *>(d->x3[src]), 0.0, static_cast<double *>(d->x3[dstimg]));
+    else if (d->precision == 's')
+        rc = spmv_run<float, float>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const float *>(d->values), (float)alpha,
+                                    static_cast<const float *>(d->x3[src]), 0.0f, static_cast<float *>(d->x3[dstimg]));
+    else
+        rc = spmv_run<float, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const float *>(d->values), alpha,
+                                     static_cast<const double *>(d->x3[src]), 0.0, static_cast<double *>(d->x3[dstimg]));
+    h->opts[RSG_OPT_SPMV_HALO_START] = keep;
+    h->plan_send_pos = nullptr;
+    h->wait_flags = nullptr;
+    h->chain.npeers = 0;
+    return rc;
+}
+
 } // extern "C"
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -172,7 +296,8 @@ struct rsg_multi {
     int width = 1;
     size_t stride = 0; // elements per x image
     std::vector<rsg_context *> h;
-    std::vector<rsg_dist *> d;
+    std::vector<rsg_dist *> d, dc; // separate products / chained products (dc[r] NULL when the pattern has no chained form)
+    std::vector<std::vector<int>> halo_src; // per rank: global column behind every halo slot entry (-1 unused)
     std::vector<cudaStream_t> stream;
     std::vector<cudaEvent_t> ev0, ev1;
     // per device allocations
@@ -191,6 +316,7 @@ void multi_free(rsg_multi *M)
         DevGuard g(M->dev[r]);
         if ((size_t)r < M->stream.size() && M->stream[r]) cudaStreamSynchronize(M->stream[r]);
         if ((size_t)r < M->d.size() && M->d[r]) rsg_dist_destroy(M->d[r]);
+        if ((size_t)r < M->dc.size() && M->dc[r]) rsg_dist_destroy(M->dc[r]);
         if ((size_t)r < M->h.size() && M->h[r]) rsg_destroy(M->h[r]);
         if ((size_t)r < M->rowptr.size()) cudaFree(M->rowptr[r]);
         if ((size_t)r < M->colidx.size()) cudaFree(M->colidx[r]);
@@ -306,7 +432,7 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
         for (int o = 0; o < P; ++o) if (is[(size_t)o]) nb[(size_t)q].push_back(o);
     }
     // ---- devices: peer access, handles, arrays
-    M->h.assign((size_t)P, nullptr); M->d.assign((size_t)P, nullptr); M->stream.assign((size_t)P, nullptr);
+    M->h.assign((size_t)P, nullptr); M->d.assign((size_t)P, nullptr); M->dc.assign((size_t)P, nullptr); M->halo_src.assign((size_t)P, std::vector<int>()); M->stream.assign((size_t)P, nullptr);
     M->ev0.assign((size_t)P, nullptr); M->ev1.assign((size_t)P, nullptr);
     M->rowptr.assign((size_t)P, nullptr); M->colidx.assign((size_t)P, nullptr); M->send_idx.assign((size_t)P, nullptr);
     M->flags.assign((size_t)P, nullptr); M->values.assign((size_t)P, nullptr); M->x.assign((size_t)P, nullptr); M->y.assign((size_t)P, nullptr);
@@ -349,14 +475,14 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
         bool ok = cudaMalloc(&M->rowptr[(size_t)r], sizeof(int) * ((size_t)ml + 1)) == cudaSuccess &&
                   cudaMalloc(&M->colidx[(size_t)r], sizeof(int) * (cnt ? cnt : 1)) == cudaSuccess &&
                   cudaMalloc(&M->values[(size_t)r], M->vs * (cnt ? cnt : 1)) == cudaSuccess &&
-                  cudaMalloc(&M->x[(size_t)r], M->xs * 2 * stride) == cudaSuccess &&
+                  cudaMalloc(&M->x[(size_t)r], M->xs * 3 * stride) == cudaSuccess &&
                   cudaMalloc(&M->y[(size_t)r], M->xs * (size_t)(ml ? ml : 1)) == cudaSuccess &&
-                  cudaMalloc(&M->flags[(size_t)r], sizeof(int) * 64) == cudaSuccess &&
+                  cudaMalloc(&M->flags[(size_t)r], sizeof(int) * 192) == cudaSuccess &&
                   cudaMalloc(&M->send_idx[(size_t)r], sizeof(int) * (send[(size_t)r].size() ? send[(size_t)r].size() : 1)) == cudaSuccess;
         if (!ok) { (void)cudaGetLastError(); rc = RSG_ALLOC_FAILED; break; }
         ok = cudaMemcpy(M->rowptr[(size_t)r], rp.data(), sizeof(int) * ((size_t)ml + 1), cudaMemcpyHostToDevice) == cudaSuccess &&
              (cnt == 0 || cudaMemcpy(M->colidx[(size_t)r], ci.data(), sizeof(int) * cnt, cudaMemcpyHostToDevice) == cudaSuccess) &&
-             cudaMemset(M->x[(size_t)r], 0, M->xs * 2 * stride) == cudaSuccess && cudaMemset(M->flags[(size_t)r], 0, sizeof(int) * 64) == cudaSuccess &&
+             cudaMemset(M->x[(size_t)r], 0, M->xs * 3 * stride) == cudaSuccess && cudaMemset(M->flags[(size_t)r], 0, sizeof(int) * 192) == cudaSuccess &&
              (send[(size_t)r].empty() || cudaMemcpy(M->send_idx[(size_t)r], send[(size_t)r].data(), sizeof(int) * send[(size_t)r].size(), cudaMemcpyHostToDevice) == cudaSuccess);
         if (ok && cnt) {
             if (M->vs == 8) ok = cudaMemcpy(M->values[(size_t)r], values + k0, 8 * cnt, cudaMemcpyHostToDevice) == cudaSuccess;
@@ -370,8 +496,8 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
     }
     // ---- per rank: the peers' slots / flags, the send-list range each peer reads, the dist context
     for (int r = 0; r < P && rc == RSG_OK; ++r) {
-        std::vector<void *> slots((size_t)(2 * P), nullptr);
-        std::vector<int *> pflags((size_t)(2 * P), nullptr);
+        std::vector<void *> slots((size_t)(2 * P), nullptr), slots3((size_t)(3 * P), nullptr);
+        std::vector<int *> pflags((size_t)(2 * P), nullptr), pflags3((size_t)(3 * P), nullptr);
         std::vector<int> plo((size_t)P, 0), phi((size_t)P, 0);
         const std::vector<int> &s = send[(size_t)r];
         for (int q = 0; q < P; ++q) {
@@ -393,6 +519,12 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
                 if (it != nb[(size_t)q].end())
                     pflags[(size_t)(p * P + q)] = M->flags[(size_t)q] + 32 * p + (int)(it - nb[(size_t)q].begin());
             }
+            for (int p = 0; p < 3; ++p) { // chained products: three images, their flags behind the two-image ones
+                if (q_reads_r)
+                    slots3[(size_t)(p * P + q)] = static_cast<char *>(M->x[(size_t)q]) + M->xs * ((size_t)p * stride + (size_t)M->hbase[(size_t)q] + (size_t)r * (size_t)width);
+                if (it != nb[(size_t)q].end())
+                    pflags3[(size_t)(p * P + q)] = M->flags[(size_t)q] + 64 + 32 * p + (int)(it - nb[(size_t)q].begin());
+            }
         }
         void *ximg[2] = {M->x[(size_t)r], static_cast<char *>(M->x[(size_t)r]) + M->xs * stride};
         const int *wf[2] = {M->flags[(size_t)r], M->flags[(size_t)r] + 32};
@@ -401,6 +533,26 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
         rc = rsg_dist_create(M->h[(size_t)r], precision, ml, M->hbase[(size_t)r] + P * width, 0, 0, M->rowptr[(size_t)r], M->colidx[(size_t)r],
                              M->values[(size_t)r], ximg, P > 1 ? M->hbase[(size_t)r] : 0, (int)s.size(), M->send_idx[(size_t)r], P > 1 ? P : 0,
                              slots.data(), pflags.data(), plo.data(), phi.data(), wf, P > 1 ? (int)nb[(size_t)r].size() : 0, &M->d[(size_t)r]);
+        if (rc != RSG_OK) break;
+        void *ximg3[3] = {M->x[(size_t)r], static_cast<char *>(M->x[(size_t)r]) + M->xs * stride, static_cast<char *>(M->x[(size_t)r]) + M->xs * 2 * stride};
+        const int *wf3[3] = {M->flags[(size_t)r] + 64, M->flags[(size_t)r] + 96, M->flags[(size_t)r] + 128};
+        const int rcc = rsg_dist_create_chain(M->h[(size_t)r], precision, ml, M->hbase[(size_t)r] + P * width, 0, 0, M->rowptr[(size_t)r],
+                                              M->colidx[(size_t)r], M->values[(size_t)r], ximg3, P > 1 ? M->hbase[(size_t)r] : 0, (int)s.size(),
+                                              M->send_idx[(size_t)r], P > 1 ? P : 0, slots3.data(), pflags3.data(), plo.data(), phi.data(), wf3,
+                                              P > 1 ? (int)nb[(size_t)r].size() : 0, &M->dc[(size_t)r]);
+        if (rcc != RSG_OK && rcc != RSG_UNSUPPORTED) rc = rcc; // (unsupported: rsg_spmv_multi_chain will say so)
+        // the global column behind every entry of this rank's halo (for the initial fill of a chain)
+        std::vector<int> &hs = M->halo_src[(size_t)r];
+        hs.assign((size_t)P * (size_t)width, -1);
+        for (int o = 0; o < P; ++o) {
+            if (o == r) continue;
+            const std::vector<int> &so = send[(size_t)o];
+            for (int c : need[(size_t)r])
+                if (c >= rs[(size_t)o] && c < rs[(size_t)o + 1]) {
+                    const int pos = (int)(std::lower_bound(so.begin(), so.end(), c - rs[(size_t)o]) - so.begin());
+                    hs[(size_t)o * (size_t)width + (size_t)pos] = c;
+                }
+        }
     }
     cudaSetDevice(prev);
     if (rc != RSG_OK) { multi_free(M); return rc; }
@@ -472,6 +624,64 @@ int rsg_spmv_multi_get_y(rsg_multi_t M, void *y_host)
     return for_each_rank(M, [&](int r) -> int {
         const size_t nl = (size_t)M->n_local[(size_t)r];
         if (nl) RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(y_host) + M->xs * (size_t)M->row_start[(size_t)r], M->y[(size_t)r], M->xs * nl,
+                                             cudaMemcpyDeviceToHost, M->stream[(size_t)r]));
+        return check_err_flag(M->h[(size_t)r]);
+    });
+}
+
+/* Chained products x <- alpha * A * x, nsteps times, starting from x_host (n entries): x_host == NULL continues the chain.
+ * us_per_step (may be NULL): device time of the slowest rank / nsteps.  RSG_UNSUPPORTED when some block has no chained form. */
+int rsg_spmv_multi_chain(rsg_multi_t M, const void *x_host, int nsteps, double alpha, double *us_per_step)
+{
+    if (!M || nsteps < 0) return RSG_BAD_ARG;
+    for (int r = 0; r < M->P; ++r) if (!M->dc[(size_t)r]) return RSG_UNSUPPORTED;
+    if (x_host) { // image 1 of every rank, local entries AND halo, from the global vector; flags and step counters back to zero
+        RSG_TRY(for_each_rank(M, [&](int r) -> int {
+            cudaStream_t st = M->stream[(size_t)r];
+            RSG_CUDA_TRY(cudaStreamSynchronize(st));
+            const size_t nl = (size_t)M->n_local[(size_t)r];
+            char *img1 = static_cast<char *>(M->x[(size_t)r]) + M->xs * M->stride;
+            const char *src = static_cast<const char *>(x_host);
+            RSG_CUDA_TRY(cudaMemcpyAsync(img1, src + M->xs * (size_t)M->row_start[(size_t)r], M->xs * nl, cudaMemcpyHostToDevice, st));
+            const std::vector<int> &hs = M->halo_src[(size_t)r];
+            std::vector<char> halo(hs.size() * M->xs, 0);
+            for (size_t j = 0; j < hs.size(); ++j)
+                if (hs[j] >= 0) std::memcpy(halo.data() + j * M->xs, src + M->xs * (size_t)hs[j], M->xs);
+            if (!hs.empty()) RSG_CUDA_TRY(cudaMemcpyAsync(img1 + M->xs * (size_t)M->hbase[(size_t)r], halo.data(), halo.size(), cudaMemcpyHostToDevice, st));
+            RSG_CUDA_TRY(cudaMemsetAsync(M->flags[(size_t)r] + 64, 0, sizeof(int) * 96, st));
+            RSG_CUDA_TRY(cudaStreamSynchronize(st)); // (halo is a host temporary)
+            return rsg_dist_chain_reset(M->dc[(size_t)r]);
+        }));
+    }
+    std::vector<float> ms((size_t)M->P, 0.f);
+    RSG_TRY(for_each_rank(M, [&](int r) -> int {
+        cudaStream_t st = M->stream[(size_t)r];
+        if (us_per_step) RSG_CUDA_TRY(cudaEventRecord(M->ev0[(size_t)r], st));
+        for (int s = 0; s < nsteps; ++s) RSG_TRY(rsg_dist_step_chain(M->dc[(size_t)r], alpha));
+        if (us_per_step) {
+            RSG_CUDA_TRY(cudaEventRecord(M->ev1[(size_t)r], st));
+            RSG_CUDA_TRY(cudaStreamSynchronize(st));
+            RSG_CUDA_TRY(cudaEventElapsedTime(&ms[(size_t)r], M->ev0[(size_t)r], M->ev1[(size_t)r]));
+            return check_err_flag(M->h[(size_t)r]);
+        }
+        return RSG_OK;
+    }));
+    if (us_per_step) {
+        float worst = 0.f;
+        for (float v : ms) worst = std::max(worst, v);
+        *us_per_step = nsteps > 0 ? (double)worst * 1e3 / nsteps : 0.0;
+    }
+    return RSG_OK;
+}
+
+/* waits for every device, then gathers the current x of the chain (n entries) to the host */
+int rsg_spmv_multi_get_x(rsg_multi_t M, void *x_host)
+{
+    if (!M || (M->n > 0 && !x_host)) return RSG_BAD_ARG;
+    for (int r = 0; r < M->P; ++r) if (!M->dc[(size_t)r]) return RSG_UNSUPPORTED;
+    return for_each_rank(M, [&](int r) -> int {
+        const size_t nl = (size_t)M->n_local[(size_t)r];
+        if (nl) RSG_CUDA_TRY(cudaMemcpyAsync(static_cast<char *>(x_host) + M->xs * (size_t)M->row_start[(size_t)r], rsg_dist_x(M->dc[(size_t)r]), M->xs * nl,
                                              cudaMemcpyDeviceToHost, M->stream[(size_t)r]));
         return check_err_flag(M->h[(size_t)r]);
     });

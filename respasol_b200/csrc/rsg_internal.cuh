@@ -48,6 +48,18 @@ struct HaloFuse {
     int nruns, run_start[4], run_len[4];
 };
 
+// Chained products x_{k+1} = alpha * A * x_k ("the SpMV epilogue stores its y rows straight into the peers' x
+// buffers"): tiles that own rows a neighbour reads store those rows of y into the neighbours' halo slots of the NEXT x
+// image as soon as they are computed, and the last of them to finish releases the step number to the neighbours' flags.
+struct ChainPush {
+    void *dst[RSG_MAX_PEERS];
+    int *flag[RSG_MAX_PEERS];
+    int lo[RSG_MAX_PEERS], hi[RSG_MAX_PEERS]; // peer q reads positions [lo[q], hi[q]) of the send list
+    const int *send_pos;                      // per local row: its position in the send list, or -1
+    int *counter;                             // producer tiles finished (reset by the last one)
+    int npeers, nprod, epoch;
+};
+
 // Long rows of a TILE plan (longer than a CTA's staging capacity) are cut into segments, one CTA each, placed in
 // the grid ahead of the tiles: partial sums meet in `part`, the last segment of a row to arrive adds them in
 // segment order (deterministic) and stores y.  The tiles skip those rows.
@@ -92,6 +104,7 @@ struct SpmvPlan {
     int4 *wdesc = nullptr;
     uint16_t *widx = nullptr;
     int wsmem = 0, wthreads = 0, whalo = 0, first8 = 0;
+    int wprod = 0;             // window plan built for chained products: tiles that own rows a neighbour reads
     int vbytes = 0, xbytes = 0; // stored-value / vector element sizes the plan was shaped for
     int lanes_hint = 0;        // tile kernel: 2 = the stage holds about half as many rows as the CTA has threads -> two lanes per row
     // merge-path kernel
@@ -174,6 +187,8 @@ struct rsg_context {
     int *pinned_i = nullptr;  // small pinned host mirror, 64 ints
     const int *wait_flags = nullptr;   // one-shot halo wait for the next SpMV (rsg_spmv_halo_wait)
     int wait_n = 0, wait_epoch = 0;
+    rsg::ChainPush chain = {};         // one-shot epilogue push for the next SpMV (rsg_dist_step_chain); npeers == 0: none
+    const int *plan_send_pos = nullptr; // read when a window plan is built: marks producer tiles, orders boundary tiles first
     rsg::HaloFuse fuse = {};           // one-shot fused push for the next SpMV (rsg_spmv_halo_fuse); ctas == 0: none
     const void *persist_ptr = nullptr; // x currently covered by the L2 access-policy window
     size_t persist_bytes = 0;

@@ -98,7 +98,7 @@ template <typename TV, typename TX, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
                    int reduce_opt, int early_values, const int *wait_flags, int wait_n, int wait_epoch, int *err_flag, int max_spins,
-                   const HaloFuse fuse)
+                   const HaloFuse fuse, const ChainPush chain)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(16) int4 s_desc[kWinRecInt4];
@@ -196,6 +196,34 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     case 16: win_rows<TV, TX, THREADS, 16>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
     default: win_rows<TV, TX, THREADS, 32>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
     }
+    if (chain.npeers > 0 && (flags & 4)) {
+        // chained products: this tile owns rows a neighbour reads -- their y goes straight into the neighbours' halo slots of
+        // the next x image; the last producer tile to finish releases the step number to the neighbours' flags
+        __shared__ int s_last;
+        __syncthreads(); // the rows above were stored by other threads of this CTA
+        for (int i = tid; i < nr; i += THREADS) {
+            const int pos = chain.send_pos[r0 + i];
+            if (pos < 0) continue;
+            const TX v = y[r0 + i];
+#pragma unroll 1
+            for (int q = 0; q < chain.npeers; ++q) {
+                TX *dq = static_cast<TX *>(chain.dst[q]);
+                if (dq && pos >= chain.lo[q] && pos < chain.hi[q]) dq[pos] = v;
+            }
+        }
+        __threadfence_system();
+        __syncthreads();
+        if (tid == 0) {
+            const int done = atomicAdd(chain.counter, 1);
+            s_last = (done == chain.nprod - 1);
+            if (s_last) *chain.counter = 0;
+        }
+        __syncthreads();
+        if (s_last && tid < chain.npeers && chain.flag[tid]) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(chain.flag[tid]), "r"(chain.epoch) : "memory");
+        }
+    }
 }
 
 // -------------------------------------------------------------------------------- plan: tile cuts
@@ -241,17 +269,22 @@ __device__ __forceinline__ bool win_any_set(const unsigned *bm, int lo, int hi, 
 // expressed (column out of range, window too wide or too large), out[2] = tiles that read columns >= halo_start.
 __global__ void __launch_bounds__(kWinBuildThreads)
 win_build_kernel(int n, int base, const int *__restrict__ colidx, const int2 *__restrict__ part, int first8, int vbytes, int xbytes,
-                 int smem_cap, int gap0, int halo_start, int4 *wdesc, uint16_t *widx, int *out)
+                 int smem_cap, int gap0, int halo_start, const int *__restrict__ send_pos, int4 *wdesc, uint16_t *widx, int *out)
 {
     extern __shared__ unsigned bm[];
-    __shared__ int s_min, s_max, s_fail, s_halo, s_nstart, s_nend, s_xtma, s_tail;
+    __shared__ int s_min, s_max, s_fail, s_halo, s_nstart, s_nend, s_xtma, s_tail, s_prod;
     __shared__ int s_starts[16], s_ends[16], s_off[16], s_len[16];
     constexpr int T = kWinBuildThreads;
     const int tid = threadIdx.x, b = blockIdx.x;
     const int2 p0 = part[b], p1 = part[b + 1];
     const int r0 = p0.x, k0 = p0.y, nr = p1.x - p0.x, nk = p1.y - p0.y;
-    if (tid == 0) { s_min = 0x7fffffff; s_max = -1; s_fail = 0; s_halo = 0; s_nstart = 0; s_nend = 0; s_xtma = 0; s_tail = 0; }
+    if (tid == 0) { s_min = 0x7fffffff; s_max = -1; s_fail = 0; s_halo = 0; s_nstart = 0; s_nend = 0; s_xtma = 0; s_tail = 0; s_prod = 0; }
     __syncthreads();
+    if (send_pos) { // does a neighbour read a row of this tile (chained products)?
+        int prod = 0;
+        for (int i = tid; i < nr; i += T) prod |= send_pos[r0 + i] >= 0;
+        if (prod) s_prod = 1;
+    }
     {
         int lmin = 0x7fffffff, lmax = -1, bad = 0, halo = 0;
         for (int k = k0 + tid; k < k0 + nk; k += T) {
@@ -336,7 +369,8 @@ win_build_kernel(int n, int base, const int *__restrict__ colidx, const int2 *__
     int *rec = reinterpret_cast<int *>(wdesc + (size_t)b * kWinRecInt4);
     if (tid == 0) {
         rec[0] = r0; rec[1] = k0;
-        rec[2] = nr | (ns << 16) | (((s_halo ? 1 : 0) | (s_tail ? 2 : 0)) << 24);
+        rec[2] = nr | (ns << 16) | (((s_halo ? 1 : 0) | (s_tail ? 2 : 0) | (s_prod ? 4 : 0)) << 24);
+        if (s_prod) atomicAdd(out + 3, 1);
         rec[3] = (int)((unsigned)nk | ((unsigned)s_xtma << 16));
         if (s_halo) atomicAdd(out + 2, 1);
     }
@@ -407,7 +441,7 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     int gap0 = h->opts[RSG_OPT_SPMV_WIN_GAP];
     if (gap0 <= 0) gap0 = 3;
     win_build_kernel<<<p.nblk, kWinBuildThreads, bsmem, st>>>(p.n, p.base, p.colidx, part, p.first8, vbytes, xbytes, smem_cap, gap0,
-                                                              h->opts[RSG_OPT_SPMV_HALO_START], p.wdesc, p.widx, out);
+                                                              h->opts[RSG_OPT_SPMV_HALO_START], h->plan_send_pos, p.wdesc, p.widx, out);
     win_rowptr_copy_kernel<<<(p.rp0_len + 255) / 256, 256, 0, st>>>(m, p.rp0_len, p.base, p.rowptr, p.rp0);
     h->launches += 3;
     e = cudaMemcpyAsync(h->pinned_i + 32, out, 4 * sizeof(int), cudaMemcpyDeviceToHost, st);
@@ -419,17 +453,23 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     p.wsmem = (h->pinned_i[32] + 127) & ~127;
     p.whalo = h->pinned_i[34];
     p.wthreads = threads;
-    if (p.whalo > 0 && p.whalo < p.nblk) {
-        // multi-GPU: tiles that read a peer's entries go to the END of the grid (records are self-contained, so the order is
-        // free): by the time they are dispatched the neighbours' pushes have long landed, instead of the first wave
-        // spinning on flags while interior tiles wait for an SM slot.  Stable on both sides; done once, on the host.
+    p.wprod = h->plan_send_pos ? h->pinned_i[35] : 0;
+    const bool chained = h->plan_send_pos != nullptr;
+    if ((p.whalo > 0 && p.whalo < p.nblk) || (chained && p.wprod > 0 && p.wprod < p.nblk)) {
+        // multi-GPU tile order (records are self-contained, so the order is free; done once, on the host, stable on both sides).
+        // Separate products (the push precedes the product): tiles that read a peer's entries go to the END of the grid -- by
+        // the time they are dispatched the neighbours' pushes have landed.  Chained products: boundary tiles (halo readers
+        // and producers) go FIRST -- what they read arrived during the previous product, and what they produce has the rest
+        // of this product to reach the neighbours.
         std::vector<int4> rec((size_t)p.nblk * kWinRecInt4), out_rec((size_t)p.nblk * kWinRecInt4);
         RSG_CUDA_TRY(cudaMemcpy(rec.data(), p.wdesc, sizeof(int4) * rec.size(), cudaMemcpyDeviceToHost));
         size_t at = 0;
         for (int pass = 0; pass < 2; ++pass)
             for (int b = 0; b < p.nblk; ++b) {
-                const bool halo = ((rec[(size_t)b * kWinRecInt4].z >> 24) & 1) != 0;
-                if ((pass == 1) == halo) { std::copy_n(rec.begin() + (size_t)b * kWinRecInt4, kWinRecInt4, out_rec.begin() + at); at += kWinRecInt4; }
+                const int fl = (rec[(size_t)b * kWinRecInt4].z >> 24) & 0xff;
+                const bool boundary = chained ? (fl & 5) != 0 : (fl & 1) != 0;
+                const bool take = chained ? ((pass == 0) == boundary) : ((pass == 1) == boundary);
+                if (take) { std::copy_n(rec.begin() + (size_t)b * kWinRecInt4, kWinRecInt4, out_rec.begin() + at); at += kWinRecInt4; }
             }
         RSG_CUDA_TRY(cudaMemcpy(p.wdesc, out_rec.data(), sizeof(int4) * out_rec.size(), cudaMemcpyHostToDevice));
     }
@@ -452,6 +492,9 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
     // entry, so with few threads walking many entries it outlasts the whole product (measured: 32 CTAs x 9 entries per
     // thread, one at a time = 18 us for a 14 us product)
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(1024, (fuse.nsend + 4 * THREADS - 1) / (4 * THREADS)));
+    ChainPush chain = h->chain;
+    if (chain.npeers > 0) chain.nprod = p->wprod;
+    h->chain.npeers = 0; // one-shot
     WinArgs w = {p->wdesc, p->rp0, p->widx, p->first8, p->first + p->nnz, p->n, p->nblk};
     // RSG_OPT_SPMV_PDL: 0 = programmatic dependent launch, plan data only ahead of the dependency; 1 = plain launch;
     // 2 = the values too (the caller promises that nothing queued before the product writes them)
@@ -471,7 +514,7 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
     cfg.attrs = attr;
     cfg.numAttrs = pdl != 1 ? 1 : 0;
     RSG_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, w, values, x, y, alpha, beta, h->opts[RSG_OPT_SPMV_REDUCE], pdl == 2 ? 1 : 0, h->wait_flags,
-                                    h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse));
+                                    h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse, chain));
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;
     h->launches++;

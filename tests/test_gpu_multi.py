@@ -117,3 +117,44 @@ def test_harness_gpus_flag(tmp_path, ngpu):
     assert m and float(m.group(1)) <= 1e-12, r.stdout
     if ngpu > 1:
         assert "gpus=%d" % ngpu in lines[2]
+
+
+@pytest.mark.parametrize("ngpu", [1, 2, 4, 8])
+@pytest.mark.parametrize("precision", ["d", "m"])
+def test_multi_gpu_chained_products(ngpu, precision):
+    """x <- alpha * A * x, K times (rsg_spmv_multi_chain: boundary rows pushed by the tiles that computed them, three x images):
+    the whole vector after K steps against the oracle's chain -- bit-exact in fp64, and again after continuing the chain."""
+    if ndev() < ngpu:
+        pytest.skip("needs %d devices" % ngpu)
+    lib = gpu_lib()
+    for a, alpha in ((host.gen_stencil27(30, 30, 48, seed=2), 1.0 / 52), (host.gen_laplace2d(300), 1.0 / 8), (host.gen_femlike(20, 0.6, 5), 0.25)):
+        M = C.c_void_p()
+        assert lib.rsg_spmv_multi_create(ngpu, None, precision.encode(), a.m, a.n, a.stored, a.base, a.rowptr.ctypes.data, a.colidx.ctypes.data,
+                                         np.ascontiguousarray(a.values, dtype=np.float64).ctypes.data, None, C.byref(M)) == 0
+        try:
+            x0 = orc.dlarnv(a.n) - 0.5
+            ref = x0.copy()
+            got = np.zeros(a.n)
+            us = C.c_double(0)
+            done = 0
+            for steps in (1, 2, 7):  # restart once, then continue the chain twice
+                st = lib.rsg_spmv_multi_chain(M, x0.ctypes.data if done == 0 else None, steps, alpha, C.byref(us))
+                assert st == 0, lib.rsg_status_string(st)
+                for _ in range(steps):
+                    ref = orc.spmv(a, ref, precision, alpha=alpha)
+                done += steps
+                assert lib.rsg_spmv_multi_get_x(M, got.ctypes.data) == 0
+                if precision == "d":
+                    assert np.array_equal(got, ref), (ngpu, done)
+                else:
+                    assert np.abs(got - ref).max() <= 1e-5 * np.abs(ref).max()
+            # a fresh start must not see anything of the old chain
+            st = lib.rsg_spmv_multi_chain(M, x0.ctypes.data, 3, alpha, None)
+            assert st == 0
+            assert lib.rsg_spmv_multi_get_x(M, got.ctypes.data) == 0
+            r3 = x0.copy()
+            for _ in range(3):
+                r3 = orc.spmv(a, r3, precision, alpha=alpha)
+            assert np.array_equal(got, r3) if precision == "d" else np.abs(got - r3).max() <= 1e-5 * np.abs(r3).max()
+        finally:
+            lib.rsg_spmv_multi_destroy(M)
