@@ -37,6 +37,8 @@ GRID = 100          # configs[1]: 27-point stencil on 100^3
 GRID5 = 134         # configs[4]: 27-point stencil on 134^3 = 64 000 000 entries
 REPLICAS = 2
 METRIC = "SpMV achieved HBM GB/s (fp64 CSR, algorithmic bytes / device time)"
+CHAIN_ALPHA = 1.0 / 52   # N > 1: x <- A x / 52 keeps the iterates O(1) (the stencil's rows sum to at most 52 in magnitude)
+CHAIN_PARITY_STEPS = 12
 LAUNCH_NOTE = ("back-to-back products of a static matrix, as in the reference's timed loop (GPU/spmv.cu:174-207); programmatic dependent "
                "launch with the values promised static (RSG_OPT_SPMV_PDL = 2) unless --pdl says otherwise")
 
@@ -55,7 +57,8 @@ def job_config(n_gpus):
         return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 100^3 (1000000 rows, 26463592 entries) -- BASELINE configs[1]",
                 "l2_policy": "inputs larger than L2: %d resident replicas of the matrix and vectors are rotated" % REPLICAS,
                 "parallelism": "single GPU", "launch": LAUNCH_NOTE}
-    return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 134^3 (2406104 rows, 64000000 entries) -- BASELINE configs[4], strong scaling",
+    return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 134^3 (2406104 rows, 64000000 entries) -- BASELINE configs[4], strong scaling; "
+                        "a step = one product of the chain x <- A x / 52 (SURVEY 8e: repeated products, x_{k+1} <- y_k)",
             "l2_policy": "inputs larger than L2 up to N = 4; %d resident replicas of every rank's block are rotated at every N" % REPLICAS,
             "parallelism": "row blocks of whole planes over %d GPUs; x halo pushed over NVLink peer memory by the product's own launch" % n_gpus,
             "launch": LAUNCH_NOTE}
@@ -448,10 +451,15 @@ def run_ours(args):
     sampler.start()
     extra = {}
 
-    def dist_ops(a, starts, xs_local, replicas=REPLICAS, overlap=False):
+    def dist_ops(a, starts, xs_local, replicas=REPLICAS, overlap=False, chain=False):
         """`replicas` row-block operators of this rank's block `a` (rotated by the timed loop)"""
         ops = []
         for _ in range(replicas):
+            if world > 1 and chain:
+                op = RowBlockSpmv(a, starts, "p2p-chain", lambda c: DeviceCSR(c, "d", dev), lambda A, x, y: h.spmv(A, x, y), dev,
+                                  torch.float64, push=P2P_FNS, side=side)
+                ops.append(op)
+                continue
             if world > 1:
                 op = RowBlockSpmv(a, starts, "p2p" if args.exchange.startswith("p2p") else "halo", lambda c: DeviceCSR(c, "d", dev),
                                   lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
@@ -514,9 +522,13 @@ def run_ours(args):
         a = host.gen_stencil27(GRID5, GRID5, GRID5, cuts[rank], cuts[rank + 1], seed=2)
         starts5 = np.array(cuts, dtype=np.int64) * GRID5 * GRID5
         xg = orc.dlarnv(GRID5 ** 3) - 0.5
-        ops = dist_ops(a, starts5, xg[starts5[rank]:starts5[rank + 1]], overlap=args.overlap)
+        chained = args.mode == "chain" and args.exchange == "p2p"
+        ops = dist_ops(a, starts5, xg[starts5[rank]:starts5[rank + 1]], overlap=args.overlap, chain=chained)
         stored_total = allsum(float(a.stored))
         bytes_total = stored_total * 12 + (GRID5 ** 3 + 1) * 4 + 2 * 8 * GRID5 ** 3
+        if chained:
+            for op in ops:
+                op.set_x_global(xg)
         if args.graph:
             for op in ops:
                 for _ in range(3):  # eager steps first: plans, NCCL channels, allocator all settled
@@ -525,7 +537,10 @@ def run_ours(args):
             extra["cuda_graph"] = "one graph per step (pack + NCCL all-gather + SpMV launches), replayed"
 
         def step(i):
-            ops[i % REPLICAS].step()
+            if chained:
+                ops[i % REPLICAS].step_chain(CHAIN_ALPHA)
+            else:
+                ops[i % REPLICAS].step()
         launches_per_step = len(ops[0].split) if ops[0].split else 1
         launches_per_step += 1 if (ops[0].p2p is not None and len(ops[0].p2p) < 3) else 0
         scaling = "strong"
@@ -575,6 +590,40 @@ def run_ours(args):
             exact = exact and bool(np.array_equal(got, ref))
         extra["parity_full"] = True
         extra["parity_bit_exact"] = exact
+    elif chained:
+        # restart both chains from the same x and walk CHAIN_PARITY_STEPS steps next to the oracle's chain on the FULL matrix
+        a_full = host.gen_stencil27(GRID5, seed=2)
+        ref = xg.copy()
+        nthr = max(1, len(all_host_cpus()) // world)
+        for _ in range(CHAIN_PARITY_STEPS):
+            ref = orc.spmv(a_full, ref, "d", alpha=CHAIN_ALPHA, threads=nthr)
+        del a_full
+        exact = True
+        for op in ops:
+            op.set_x_global(xg)
+            for _ in range(CHAIN_PARITY_STEPS):
+                op.step_chain(CHAIN_ALPHA)
+            h.synchronize()
+            got = op.x_local().cpu().numpy()
+            want = ref[starts5[rank]:starts5[rank + 1]]
+            assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max(), "rank %d: the chained configs[4] products differ from the oracle" % rank
+            exact = exact and bool(np.array_equal(got, want))
+        extra["parity_full"] = bool(allmin(1.0) > 0)
+        extra["parity_bit_exact"] = bool(allmin(1.0 if exact else 0.0) > 0)
+        extra["parity"] = ("every entry of x after %d chained products (all %d rows) against the oracle's chain on the global matrix; the "
+                           "halo of every step is what the neighbours' tiles pushed" % (CHAIN_PARITY_STEPS, GRID5 ** 3))
+        # the same matrix with SEPARATE products (static x; the push precedes the product inside its launch): round 1's protocol
+        ops_s = dist_ops(a, starts5, xg[starts5[rank]:starts5[rank + 1]])
+        for i in range(6):
+            ops_s[i % REPLICAS].step()
+        Ks = max(50, min(K, 1000))
+        mss, _, _ = timed_loop(torch, lambda i: ops_s[i % REPLICAS].step(), Ks, barrier)
+        mss = allmax(mss)
+        exs = full_parity(a, xg, ops_s, "the distributed configs[4] product")
+        extra["c5_strong_separate_products_fp64"] = {"us_per_product": mss / Ks * 1e3, "GBps_aggregate": bytes_total / (mss / Ks * 1e-3) * 1e-9,
+                                                      "parity_full": True, "parity_bit_exact": bool(allmin(1.0 if exs else 0.0) > 0),
+                                                      "exchange": ops_s[0].describe()["mode"]}
+        del ops_s
     else:
         exact = full_parity(a, xg, ops, "the distributed configs[4] product")
         extra["parity_full"] = bool(allmin(1.0) > 0)
@@ -880,6 +929,9 @@ def main():
     ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-side", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
     ap.add_argument("--pdl", type=int, default=2, choices=[0, 1, 2], help="RSG_OPT_SPMV_PDL for the timed products (2 = matrix values promised static)")
+    ap.add_argument("--mode", default="chain", choices=["chain", "separate"],
+                    help="N>1: chain = products x <- A x / 52 whose boundary rows are pushed by the tiles that compute them (default); "
+                         "separate = independent products of a static x, the push at the head of each launch (round 1's protocol)")
     ap.add_argument("--cpu-leg", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.cpu_leg:

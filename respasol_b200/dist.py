@@ -132,7 +132,8 @@ class RowBlockSpmv:
         self.split = None
         self.p2p = None
         self.side = side  # p2p: the stream the push kernels run on (the caller binds its push handle to it)
-        if mode == "p2p":
+        self.chain = mode == "p2p-chain"
+        if mode in ("p2p", "p2p-chain"):
             mode, self.p2p = "halo", push  # (rsg_halo_push, rsg_spmv_halo_wait or None) of the library's handle
             if push[1] is not None:
                 view = None  # the boundary tiles wait inside the kernel: nothing to split
@@ -194,11 +195,12 @@ class RowBlockSpmv:
         n_ext_all = [None] * self.P
         dist.all_gather_object(n_ext_all, int(plan.n_ext), group=self.group)
         stride = (max(n_ext_all) + 31) // 32 * 32
-        buf = symm_mem.empty(2 * stride, dtype=dtype, device=device)
+        nimg = 3 if self.chain else 2
+        buf = symm_mem.empty(nimg * stride, dtype=dtype, device=device)
         buf.zero_()
         self.symm = symm_mem.rendezvous(buf, group)
         self.symm_buf = buf
-        self.images = [buf[p * stride:p * stride + plan.n_ext] for p in range(2)]
+        self.images = [buf[p * stride:p * stride + plan.n_ext] for p in range(nimg)]
         self.x_ext = self.images[0]
         esz = buf.element_size()
         offs = p2p_slot_offsets(self.row_starts, plan.width, self.rank, stride)
@@ -207,7 +209,7 @@ class RowBlockSpmv:
         # arrival flags: image p, one int per NEIGHBOUR (slot = the sender's position in the receiver's list).
         # A rank signals all its neighbours, data or not, and awaits all of them, so it can never run more
         # than one step ahead of a rank it exchanges entries with -- the two images are enough
-        fl = symm_mem.empty(2 * 32, dtype=torch.int32, device=device)
+        fl = symm_mem.empty(nimg * 32, dtype=torch.int32, device=device)
         fl.zero_()
         self.symm_flags = symm_mem.rendezvous(fl, group)
         self.flags = fl
@@ -228,6 +230,24 @@ class RowBlockSpmv:
         self.flag_views = [self.flags[32 * p:] for p in range(2)]
         self.send_idx32 = torch.from_numpy(plan.my_send.astype(np.int32)).to(device)
         self.cdist = None
+        self.cchain = None
+        if self.chain:
+            # chained products: three images; the library's rsg_dist_create_chain binds everything, a step is one call
+            hnd = self.p2p[2].__self__
+            offs3 = [[int(p * stride + halo_base(np.diff(self.row_starts)[q]) + self.rank * plan.width) for q in range(self.P)] for p in range(3)]
+            raw_slots = [[(ptrs[q] + offs3[p][q] * esz) if q in plan.readers else 0 for q in range(self.P)] for p in range(3)]
+            raw_flags = [[(fptrs[q] + 4 * (32 * p + nb[q].index(self.rank))) if q in nb[self.rank] else 0
+                          for q in range(self.P)] for p in range(3)]
+            self.flag_views = [self.flags[32 * p:] for p in range(3)]
+            self.send_idx32 = torch.from_numpy(plan.my_send.astype(np.int32)).to(device)
+            self.cchain = hnd.dist_create_chain(self.A, [im.data_ptr() for im in self.images], plan.halo_base, self.send_idx32,
+                                                raw_slots, raw_flags, [r[0] for r in plan.send_range], [r[1] for r in plan.send_range],
+                                                [v.data_ptr() for v in self.flag_views], self.n_wait)
+            self.chain_hnd = hnd
+            self.chain_steps = 0
+            torch.cuda.synchronize(device)
+            self.symm.barrier(channel=0)
+            return
         owner = getattr(self.p2p[0], "__self__", None)
         if len(self.p2p) > 2 and owner is not None and hasattr(self.p2p[2].__self__, "dist_create"):
             # fused mode: everything a step needs is bound once inside the library (rsg_dist_create); a step is ONE call
@@ -242,9 +262,42 @@ class RowBlockSpmv:
         torch.cuda.synchronize(device)
         self.symm.barrier(channel=0)
 
+    # ---- chained products (mode "p2p-chain")
+    def set_x_global(self, x_global):
+        """(re)start the chain from the GLOBAL vector (numpy): image 1 gets this rank's slice and the halo entries it reads"""
+        assert self.cchain is not None
+        dev = self.x_ext.device
+        torch.cuda.synchronize(dev)
+        self.symm.barrier(channel=0)  # nobody is still pushing into anybody's images
+        plan, rs = self.plan, self.row_starts
+        img = self.images[1]
+        img[:self.n_local].copy_(torch.from_numpy(np.ascontiguousarray(x_global[rs[self.rank]:rs[self.rank + 1]])).to(dev))
+        for o in range(self.P):
+            if o != self.rank and len(plan.send_idx[o]):
+                vals = np.ascontiguousarray(x_global[plan.send_idx[o] + rs[o]])
+                img[plan.halo_base + o * plan.width:plan.halo_base + o * plan.width + len(vals)].copy_(torch.from_numpy(vals).to(dev))
+        self.flags.zero_()
+        self.chain_hnd.dist_chain_reset(self.cchain)
+        self.chain_steps = 0
+        torch.cuda.synchronize(dev)
+        self.symm.barrier(channel=0)
+
+    def step_chain(self, alpha):
+        """x <- alpha * A * x: one library call, one launch (boundary rows pushed by the tiles that computed them)"""
+        self.chain_hnd.dist_step_chain(self.cchain, alpha)
+        self.chain_steps += 1
+
+    def x_local(self):
+        """this rank's slice of the chain's current x"""
+        return self.images[(self.chain_steps + 1) % 3][:self.n_local]
+
     def describe(self):
         """what the exchange step of this operator is, for the bench line"""
-        if self.p2p is not None:
+        if getattr(self, "cchain", None) is not None:
+            mode = ("chained products x <- alpha A x (rsg_dist_step_chain): the tiles that own rows a neighbour reads store them straight "
+                    "into the neighbour's halo slots of the next x image over NVLink and the last of them signals; the next product's "
+                    "halo tiles acquire the flags before they copy x; three x images rotate; ONE launch per step, no separate exchange")
+        elif self.p2p is not None:
             how = ("FUSED into the SpMV launch (rsg_dist_step: the product's first CTAs push this rank's boundary entries into the "
                    "readers' halo slots and signal, its halo tiles await the neighbours' flags before they copy x)"
                    if len(self.p2p) > 2 else "rsg_halo_push on a side stream, arrival flags awaited inside the product's halo tiles"

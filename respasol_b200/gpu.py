@@ -208,6 +208,28 @@ class Handle:
                                         slots, flags, lo, hi, wf, int(nwait), C.byref(d)), "rsg_dist_create")
         return d
 
+    def dist_create_chain(self, A, x_images, halo_start, send_idx, peer_slots, peer_flags, peer_lo, peer_hi, wait_flags, nwait):
+        """rsg_dist_create_chain: as dist_create with THREE images (chained products x <- alpha A x)."""
+        self._claim(A)
+        npeers = len(peer_slots[0])
+        assert len(peer_slots) == 3 and len(peer_flags) == 3 and len(x_images) == 3 and len(wait_flags) == 3
+        slots = self.ptr_array([p for img in peer_slots for p in img])
+        flags = self.ptr_array([p for img in peer_flags for p in img])
+        lo = (C.c_int * npeers)(*[int(v) for v in peer_lo])
+        hi = (C.c_int * npeers)(*[int(v) for v in peer_hi])
+        d = C.c_void_p()
+        _check(self.lib.rsg_dist_create_chain(self.h, A.precision.encode(), A.m, A.n, A.stored, A.base, self._p(A.rowptr), self._p(A.colidx),
+                                              self._p(A.values), self.ptr_array(x_images), int(halo_start), int(send_idx.numel()),
+                                              self._p(send_idx), npeers, slots, flags, lo, hi, self.ptr_array(wait_flags), int(nwait),
+                                              C.byref(d)), "rsg_dist_create_chain")
+        return d
+
+    def dist_step_chain(self, d, alpha):
+        _check(self.lib.rsg_dist_step_chain(d, float(alpha)), "rsg_dist_step_chain")
+
+    def dist_chain_reset(self, d):
+        _check(self.lib.rsg_dist_chain_reset(d), "rsg_dist_chain_reset")
+
     def dist_step(self, d, y):
         _check(self.lib.rsg_dist_step(d, self._p(y)), "rsg_dist_step")
 
