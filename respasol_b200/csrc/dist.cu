@@ -39,10 +39,10 @@ struct rsg_dist {
     // chained products (rsg_dist_create_chain): three x images, step e reads image e % 3 and writes image (e + 1) % 3
     bool chained = false;
     void *x3[3] = {nullptr, nullptr, nullptr};
-    HaloFuse cf[3];                  // cf[i]: the push INTO the peers' image i
+    ChainPush cp[3];                 // cp[i]: the push INTO the peers' image i
     const int *wflags3[3] = {nullptr, nullptr, nullptr};
     int *send_pos = nullptr;         // device, m ints (owned)
-    int *chain_counter = nullptr;    // device (owned, with send_pos): [0] producer tiles done, [1] push CTAs done
+    int *chain_counter = nullptr;    // device (owned, with send_pos)
 };
 
 namespace {
@@ -204,10 +204,9 @@ int rsg_dist_create_chain(rsg_handle_t h, char precision, int m, int n_ext, int 
         if (idx[(size_t)j] < 0 || idx[(size_t)j] >= m) { delete d; return RSG_BAD_ARG; }
         pos[(size_t)idx[(size_t)j]] = j;
     }
-    pos[(size_t)m] = 0; // slots m, m+1 = the counters of finished producer tiles / push CTAs
-    pos.push_back(0);
-    if (cudaMalloc(&d->send_pos, sizeof(int) * ((size_t)m + 2)) != cudaSuccess ||
-        cudaMemcpy(d->send_pos, pos.data(), sizeof(int) * ((size_t)m + 2), cudaMemcpyHostToDevice) != cudaSuccess) {
+    pos[(size_t)m] = 0; // slot m = the counter of finished producer tiles
+    if (cudaMalloc(&d->send_pos, sizeof(int) * ((size_t)m + 1)) != cudaSuccess ||
+        cudaMemcpy(d->send_pos, pos.data(), sizeof(int) * ((size_t)m + 1), cudaMemcpyHostToDevice) != cudaSuccess) {
         (void)cudaGetLastError();
         if (d->send_pos) cudaFree(d->send_pos);
         delete d;
@@ -217,7 +216,7 @@ int rsg_dist_create_chain(rsg_handle_t h, char precision, int m, int n_ext, int 
     for (int i = 0; i < 3; ++i) {
         d->x3[i] = x_images[i];
         d->wflags3[i] = nwait > 0 ? wait_flags[i] : nullptr;
-        HaloFuse &c = d->cf[i];
+        ChainPush &c = d->cp[i];
         std::memset(&c, 0, sizeof(c));
         for (int q = 0; q < npeers; ++q) {
             c.dst[q] = peer_slots[i * npeers + q];
@@ -225,21 +224,9 @@ int rsg_dist_create_chain(rsg_handle_t h, char precision, int m, int n_ext, int 
             c.lo[q] = peer_lo ? peer_lo[q] : 0;
             c.hi[q] = peer_hi ? peer_hi[q] : nsend;
         }
-        c.send_idx = send_idx;
-        c.counter = d->chain_counter + 1;
-        c.nsend = nsend; c.npeers = npeers; c.ctas = npeers > 0 ? 1 : 0;
-    }
-    if (nsend > 0 && npeers > 0) { // contiguous runs of the send list (no index load in the push)
-        int nruns = 1, start[4] = {idx[0], 0, 0, 0}, len[4] = {1, 0, 0, 0};
-        for (int j = 1; j < nsend && nruns <= 4; ++j) {
-            if (idx[(size_t)j] == idx[(size_t)j - 1] + 1) { len[nruns - 1]++; continue; }
-            if (++nruns > 4) break;
-            start[nruns - 1] = idx[(size_t)j]; len[nruns - 1] = 1;
-        }
-        for (int i = 0; i < 3; ++i) {
-            d->cf[i].nruns = nruns <= 4 ? nruns : 0;
-            for (int r = 0; r < 4; ++r) { d->cf[i].run_start[r] = start[r]; d->cf[i].run_len[r] = len[r]; }
-        }
+        c.send_pos = d->send_pos;
+        c.counter = d->chain_counter;
+        c.npeers = npeers;
     }
     const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
     h->opts[RSG_OPT_SPMV_HALO_START] = halo_start;
@@ -271,17 +258,14 @@ int rsg_dist_step_chain(rsg_dist_t d, double alpha)
     DevGuard g(h->device);
     const int e = ++d->epoch;             // this step
     const int src = e % 3, dstimg = (e + 1) % 3;
-    if (d->cf[dstimg].npeers > 0) {
-        h->fuse = d->cf[dstimg];
-        h->fuse.epoch = e;
-        h->chain.prod_counter = d->chain_counter;
-        h->chain.nprod = 1; // (the launch takes the count from the plan)
-        h->chain.fuse_at = 0;
+    if (d->cp[dstimg].npeers > 0) {
+        h->chain = d->cp[dstimg];
+        h->chain.epoch = e;
     }
     if (d->nwait > 0) { h->wait_flags = d->wflags3[src]; h->wait_n = d->nwait; h->wait_epoch = e - 1; }
     const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
     h->opts[RSG_OPT_SPMV_HALO_START] = d->halo_start;
-    h->plan_send_pos = d->cf[dstimg].npeers > 0 ? d->send_pos : nullptr; // part of the plan's key
+    h->plan_send_pos = d->cp[dstimg].npeers > 0 ? d->send_pos : nullptr; // part of the plan's key
     int rc;
     if (d->precision == 'd')
         rc = spmv_run<double, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const double *>(d->values), alpha,
@@ -295,8 +279,7 @@ int rsg_dist_step_chain(rsg_dist_t d, double alpha)
     h->opts[RSG_OPT_SPMV_HALO_START] = keep;
     h->plan_send_pos = nullptr;
     h->wait_flags = nullptr;
-    h->fuse.ctas = 0;
-    h->chain.nprod = 0;
+    h->chain.npeers = 0;
     return rc;
 }
 

@@ -49,14 +49,15 @@ struct HaloFuse {
 };
 
 // Chained products x_{k+1} = alpha * A * x_k ("the SpMV epilogue stores its y rows straight into the peers' x
-// buffers").  Tiles that own rows a neighbour reads ("producers", first in the grid) count themselves done on `prod_counter`;
-// the push CTAs of HaloFuse sit `fuse_at` tiles into the grid, wait for that counter, then store those rows of y (= the next
-// x image) into the neighbours' halo slots and signal -- the whole latency chain of the exchange runs beside the interior
-// tiles of the SAME product, off every critical path.
+// buffers"): tiles that own rows a neighbour reads store those rows of y into the neighbours' halo slots of the NEXT x
+// image as soon as they are computed, and the last of them to finish releases the step number to the neighbours' flags.
 struct ChainPush {
-    int *prod_counter; // producer tiles finished (reset by the last push CTA)
-    int nprod;         // producer tiles of the plan (0: not a chained launch)
-    int fuse_at;       // tile index in front of which the push CTAs are inserted
+    void *dst[RSG_MAX_PEERS];
+    int *flag[RSG_MAX_PEERS];
+    int lo[RSG_MAX_PEERS], hi[RSG_MAX_PEERS]; // peer q reads positions [lo[q], hi[q]) of the send list
+    const int *send_pos;                      // per local row: its position in the send list, or -1
+    int *counter;                             // producer tiles finished (reset by the last one)
+    int npeers, nprod, epoch;
 };
 
 // Long rows of a TILE plan (longer than a CTA's staging capacity) are cut into segments, one CTA each, placed in

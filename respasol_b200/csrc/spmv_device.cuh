@@ -149,8 +149,7 @@ __device__ __forceinline__ float ld_x_coherent(const float *p)
 
 // The first `fuse.ctas` CTAs of a product's grid: store this rank's boundary entries of x into the peers' halo slots
 // (plain stores into P2P-mapped memory), then the last of them to finish releases `epoch` to the peers' flags.
-// (returns true in the CTA that arrived last and released the flags)
-template <typename TX, int THREADS> __device__ __forceinline__ bool halo_fuse_push(const HaloFuse &fuse, const TX *x, int cta = -1)
+template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_push(const HaloFuse &fuse, const TX *__restrict__ x, int cta = -1)
 {
     __shared__ int s_last;
     const int tid = threadIdx.x;
@@ -199,7 +198,6 @@ template <typename TX, int THREADS> __device__ __forceinline__ bool halo_fuse_pu
         __threadfence_system();
         asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(fuse.flag[tid]), "r"(fuse.epoch) : "memory");
     }
-    return s_last != 0;
 }
 
 // Threads tid < n each await flags[tid] >= epoch (acquire, system scope).  A wait that gives up (max_spins polls with

@@ -110,31 +110,12 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     // 16-bit columns -- and the values when the caller promised them static), so descriptor latency, the launch gap and
     // the ramp of a product hide behind the tail of the one before it.
     grid_launch_dependents();
-    const bool chained = chain.nprod > 0;
-    const int fuse_lo = chained ? chain.fuse_at : 0; // separate products: the push CTAs come first; chained: a wave into the grid
-    if ((int)blockIdx.x >= fuse_lo && (int)blockIdx.x < fuse_lo + fuse.ctas) {
-        if (!chained) { // fused exchange: publish this rank's boundary entries of x to the peers
-            grid_dependency_wait(); // x is what the work before this launch produced
-            halo_fuse_push<TX, THREADS>(fuse, x, (int)blockIdx.x - fuse_lo);
-            return;
-        }
-        // chained products: the boundary rows of THIS product (y = the next x image) go to the neighbours once every producer
-        // tile has counted itself done; the producers precede these CTAs in the grid, so they are resident or finished
-        if (tid == 0) {
-            int v, spins = 0;
-            for (;;) {
-                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(chain.prod_counter) : "memory");
-                if (v >= chain.nprod) break;
-                if (++spins >= max_spins) { if (err_flag) atomicExch(err_flag, 1); break; }
-                __nanosleep(100);
-            }
-        }
-        __syncthreads();
-        const bool last = halo_fuse_push<TX, THREADS>(fuse, y, (int)blockIdx.x - fuse_lo);
-        if (last && tid == 0) *chain.prod_counter = 0; // (the next launch of the stream starts from zero)
+    if ((int)blockIdx.x < fuse.ctas) { // fused exchange: publish this rank's boundary entries of x to the peers
+        grid_dependency_wait(); // x is what the work before this launch produced
+        halo_fuse_push<TX, THREADS>(fuse, x);
         return;
     }
-    const int tile = (int)blockIdx.x - ((int)blockIdx.x >= fuse_lo ? fuse.ctas : 0);
+    const int tile = (int)blockIdx.x - fuse.ctas;
     int4 d = make_int4(0, 0, 0, 0);
     if (tid < kWinRecInt4) { // the 128-byte record: one request
         d = __ldg(w.desc + (size_t)tile * kWinRecInt4 + tid);
@@ -215,9 +196,33 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     case 16: win_rows<TV, TX, THREADS, 16>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
     default: win_rows<TV, TX, THREADS, 32>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
     }
-    if (chained && (flags & 4)) { // this tile owns rows a neighbour reads: count it done (release: its rows of y are visible)
+    if (chain.npeers > 0 && (flags & 4)) {
+        // chained products: this tile owns rows a neighbour reads -- their y goes straight into the neighbours' halo slots of
+        // the next x image; the last producer tile to finish releases the step number to the neighbours' flags
+        __shared__ int s_last;
+        __syncthreads(); // the rows above were stored by other threads of this CTA
+        for (int i = tid; i < nr; i += THREADS) {
+            const int pos = chain.send_pos[r0 + i];
+            if (pos < 0) continue;
+            const TX v = y[r0 + i];
+#pragma unroll 1
+            for (int q = 0; q < chain.npeers; ++q) {
+                TX *dq = static_cast<TX *>(chain.dst[q]);
+                if (dq && pos >= chain.lo[q] && pos < chain.hi[q]) dq[pos] = v;
+            }
+        }
+        __threadfence_system();
         __syncthreads();
-        if (tid == 0) asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(chain.prod_counter), "r"(1) : "memory");
+        if (tid == 0) {
+            const int done = atomicAdd(chain.counter, 1);
+            s_last = (done == chain.nprod - 1);
+            if (s_last) *chain.counter = 0;
+        }
+        __syncthreads();
+        if (s_last && tid < chain.npeers && chain.flag[tid]) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(chain.flag[tid]), "r"(chain.epoch) : "memory");
+        }
     }
 }
 
@@ -488,13 +493,8 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
     // thread, one at a time = 18 us for a 14 us product)
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(1024, (fuse.nsend + 4 * THREADS - 1) / (4 * THREADS)));
     ChainPush chain = h->chain;
-    if (chain.nprod != 0) {
-        // the push CTAs wait for tiles ahead of them in the grid: keep them far fewer than the resident CTA slots
-        chain.nprod = p->wprod;
-        chain.fuse_at = std::min(p->nblk, p->wprod + h->sm_count * 6);
-        fuse.ctas = std::max(1, std::min(fuse.ctas, h->sm_count * 2));
-    }
-    h->chain.nprod = 0; // one-shot
+    if (chain.npeers > 0) chain.nprod = p->wprod;
+    h->chain.npeers = 0; // one-shot
     WinArgs w = {p->wdesc, p->rp0, p->widx, p->first8, p->first + p->nnz, p->n, p->nblk};
     // RSG_OPT_SPMV_PDL: 0 = programmatic dependent launch, plan data only ahead of the dependency; 1 = plain launch;
     // 2 = the values too (the caller promises that nothing queued before the product writes them)

@@ -26,7 +26,6 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--combos", default="")
     ap.add_argument("--modes", default="full,plain,fuse_only,wait_only")
-    ap.add_argument("--chain", action="store_true")
     args = ap.parse_args()
     world, rank, lr = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
@@ -94,31 +93,6 @@ def main():
             res[mode] = round(best, 2)
             torch.cuda.synchronize()
             dist.barrier()
-        if args.chain:  # chained products x <- A x / 52 on the same blocks
-            cops = []
-            for _ in range(2):
-                op = RowBlockSpmv(a, starts, "p2p-chain", lambda c: DeviceCSR(c, "d", dev), lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
-                                  push=(hp.halo_push, h.spmv_halo_wait, h.spmv_halo_fuse))
-                op.set_x_global(xg)
-                cops.append(op)
-            for i in range(10):
-                cops[i % 2].step_chain(1.0 / 52)
-            bestc = None
-            for _ in range(3):
-                dist.barrier()
-                torch.cuda.synchronize()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                for i in range(args.steps):
-                    cops[i % 2].step_chain(1.0 / 52)
-                e1.record()
-                torch.cuda.synchronize()
-                t = torch.tensor([e0.elapsed_time(e1) / args.steps * 1e3], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                bestc = float(t.item()) if bestc is None else min(bestc, float(t.item()))
-            h.synchronize()
-            res["chain"] = round(bestc, 2)
-            del cops
         best = res.get("full", 0.0)
         for i in range(4):  # leave the operators in a consistent state for the parity check
             ops[i % 2].step()
