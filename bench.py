@@ -57,8 +57,7 @@ def job_config(n_gpus):
         return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 100^3 (1000000 rows, 26463592 entries) -- BASELINE configs[1]",
                 "l2_policy": "inputs larger than L2: %d resident replicas of the matrix and vectors are rotated" % REPLICAS,
                 "parallelism": "single GPU", "launch": LAUNCH_NOTE}
-    return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 134^3 (2406104 rows, 64000000 entries) -- BASELINE configs[4], strong scaling; "
-                        "a step = one product of the chain x <- A x / 52 (SURVEY 8e: repeated products, x_{k+1} <- y_k)",
+    return {"workload": "CSR SpMV fp64, 3-D 27-point stencil 134^3 (2406104 rows, 64000000 entries) -- BASELINE configs[4], strong scaling",
             "l2_policy": "inputs larger than L2 up to N = 4; %d resident replicas of every rank's block are rotated at every N" % REPLICAS,
             "parallelism": "row blocks of whole planes over %d GPUs; x halo pushed over NVLink peer memory by the product's own launch" % n_gpus,
             "launch": LAUNCH_NOTE}
@@ -929,9 +928,10 @@ def main():
     ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-side", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
     ap.add_argument("--pdl", type=int, default=2, choices=[0, 1, 2], help="RSG_OPT_SPMV_PDL for the timed products (2 = matrix values promised static)")
-    ap.add_argument("--mode", default="chain", choices=["chain", "separate"],
-                    help="N>1: chain = products x <- A x / 52 whose boundary rows are pushed by the tiles that compute them (default); "
-                         "separate = independent products of a static x, the push at the head of each launch (round 1's protocol)")
+    ap.add_argument("--mode", default="separate", choices=["chain", "separate"],
+                    help="N>1: separate = independent products of a static x, the push at the head of each launch (default; round 1's "
+                         "protocol); chain = products x <- A x / 52 whose boundary rows are pushed by the tiles that compute them "
+                         "(measured no faster: DESIGN.md 6)")
     ap.add_argument("--cpu-leg", default=None, help=argparse.SUPPRESS)
     args = ap.parse_args()
     if args.cpu_leg:
