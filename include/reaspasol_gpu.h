@@ -53,7 +53,8 @@ typedef enum {
     RSG_ZERO_PIVOT_NUMERIC = 6,    /* U(j,j) == 0     -- ilu0.cu:278-282 */
     RSG_DEPENDENCY_TIMEOUT = 7,    /* watchdog in a dependency-flag wait fired (malformed input) */
     RSG_UNSUPPORTED = 8,
-    RSG_BREAKDOWN = 9              /* Krylov recurrence broke down (a scalar became 0, inf or NaN) */
+    RSG_BREAKDOWN = 9,             /* Krylov recurrence broke down (a scalar became 0, inf or NaN) */
+    RSG_SIZE_LIMIT = 10            /* the matrix is larger than the fixed scratch of an allocation-free entry point */
 } rsg_status;
 
 /* ---- handle ---------------------------------------------------------------------------- */
@@ -153,6 +154,23 @@ int spmv_csr_s(rsg_handle_t handle, int m, int n, int nnz, int base,
 int spmv_csr_mixed(rsg_handle_t handle, int m, int n, int nnz, int base,
                    const int *rowptr, const int *colidx, const float *values,
                    double alpha, const double *x, double beta, double *y);
+
+/* Allocation-free fp64 SpMV: y = alpha*A*x + beta*y.  NO counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Takes no handle, runs on the CURRENT device, on `cuda_stream` (cudaStream_t; NULL = default stream), and calls no
+ * cudaMalloc / cudaFree / allocating routine: the tile kernel's plan (tile descriptors + padded row pointers) is rebuilt on
+ * every call in a file-scope device array of RSG_NOALLOC_SCRATCH_BYTES (about 5 MB) that every GPU loading the library holds
+ * until exit.  Limits: m <= RSG_NOALLOC_MAX_ROWS and at most RSG_NOALLOC_MAX_TILES tiles (tiles = ceil((4*m + nnz) / t),
+ * 512 <= t <= 2048 chosen from nnz/m; 4*m + nnz <= 33 554 432 always fits) -- beyond that RSG_SIZE_LIMIT, nothing launched.
+ * Contract: `nnz` is EXACT here (= rowptr[m] - rowptr[0]; nothing is read back to check it) and rowptr[0] == base; colidx and
+ * values 16-byte aligned (RSG_BAD_ARG otherwise); asynchronous, four kernel launches.  All calls share the one array: calls
+ * on one stream are ordered, calls that OVERLAP on a GPU (two streams, two host threads) race on it and give wrong results.
+ * Results agree with spmv_csr_d within its tolerance (1e-12 * max|y|; the summation order inside a row may differ). */
+#define RSG_NOALLOC_MAX_ROWS (1 << 20)
+#define RSG_NOALLOC_MAX_TILES (1 << 16)
+#define RSG_NOALLOC_SCRATCH_BYTES 5243392
+int spmv_csr_d_noalloc(int m, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                       double alpha, const double *x, double beta, double *y, void *cuda_stream);
 
 /* ---- transpose / CSC path ------------------------------------------------- */
 /* CSR -> CSC on the device: what the reference obtains by asking its loader for the transposed matrix

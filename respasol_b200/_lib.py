@@ -49,6 +49,7 @@ GPU_SYMBOLS = {
     "spmv_csr_d": (_I, _CSR_ARGS + [_P, _D, _P, _D, _P]),
     "spmv_csr_s": (_I, _CSR_ARGS + [_P, _F, _P, _F, _P]),
     "spmv_csr_mixed": (_I, _CSR_ARGS + [_P, _D, _P, _D, _P]),
+    "spmv_csr_d_noalloc": (_I, [_I, _I, _I, _I, _P, _P, _P, _D, _P, _D, _P, _P]),  # no handle; last = cudaStream_t
     "rsg_csr2csc_d": (_I, _CSR_ARGS + [_P, _P, _P, _P]),
     "rsg_csr2csc_s": (_I, _CSR_ARGS + [_P, _P, _P, _P]),
     "spmv_csr_t_d": (_I, _CSR_ARGS + [_P, _D, _P, _D, _P]),

@@ -66,6 +66,7 @@ const char *rsg_status_string(int status)
     case RSG_DEPENDENCY_TIMEOUT: return "dependency wait timed out";
     case RSG_UNSUPPORTED: return "unsupported";
     case RSG_BREAKDOWN: return "Krylov recurrence broke down";
+    case RSG_SIZE_LIMIT: return "matrix larger than the fixed scratch of the allocation-free entry point";
     default: return "unknown status";
     }
 }

@@ -15,6 +15,8 @@
 // the enum values now select this kernel.)
 #include "spmv_device.cuh"
 
+#include <cstring>
+
 namespace rsg {
 
 template <typename TV, int CAPE, int ROWS> struct PipeStage {
@@ -476,3 +478,98 @@ template int tile_launch<float, float>(rsg_context *, const SpmvPlan *, const fl
 template int tile_launch<float, double>(rsg_context *, const SpmvPlan *, const float *, double, const double *, double, double *);
 
 } // namespace rsg
+
+// ------------------------------------------------------------------ allocation-free SpMV (spmv_csr_d_noalloc)
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (stream capture, tight serving loops, harnesses that forbid it).  The product is the tile kernel above (shape 0, fp64);
+// its plan -- the per-tile descriptors and the zero-based padded row pointers, which the other entry points keep in
+// cudaMalloc'ed memory inside the handle -- lives in ONE file-scope device array of fixed size, rebuilt by three small
+// kernels on every call (the array belongs to no matrix).  Every GPU that loads the library holds the array until exit.
+// Calls that overlap on one GPU (two streams, two threads) race on it; calls on one stream are ordered and safe.
+namespace rsg {
+
+constexpr int kNoallocMaxRows = RSG_NOALLOC_MAX_ROWS;   // 1 << 20
+constexpr int kNoallocMaxTiles = RSG_NOALLOC_MAX_TILES; // 1 << 16
+constexpr size_t kNoallocDescBytes = sizeof(int4) * ((size_t)kNoallocMaxTiles + 1 + 15);       // 256-byte multiple
+constexpr size_t kNoallocRpBytes = (sizeof(int) * ((((size_t)kNoallocMaxRows + 1 + 3) & ~(size_t)3) + 4) + 255) & ~(size_t)255;
+constexpr size_t kNoallocBytes = kNoallocDescBytes + kNoallocRpBytes;
+static_assert(kNoallocDescBytes % 256 == 0 && kNoallocBytes % 256 == 0, "scratch sections stay 256-byte aligned");
+static_assert(kNoallocBytes == RSG_NOALLOC_SCRATCH_BYTES, "the header states the size");
+
+// [ tile descriptors | row pointers ]: 1 MB + 4 MB.  In HOST code this name is only a stand-in for the symbol: the device
+// address comes from cudaGetSymbolAddress (noalloc_scratch_ptr), once per device.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocBytes];
+
+static unsigned char *g_noalloc_ptr[64]; // device address of the array on each device (index = device ordinal & 63)
+static std::atomic<unsigned long long> g_noalloc_ready{0};
+
+static int noalloc_scratch_ptr(int device, unsigned char **out)
+{
+    const unsigned long long bit = 1ull << (device & 63);
+    if (!(g_noalloc_ready.load(std::memory_order_acquire) & bit)) {
+        // set-up, with `device` current: the symbol's address on THIS device and the kernel's shared-memory opt-in
+        void *ptr = nullptr;
+        RSG_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        if (!ptr) return RSG_CUDA_ERROR;
+        auto kern = spmv_tile_kernel<double, double, 128, 2304, 512, TileResidency<double, 128, 2304, 512>::value, false>;
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PipeStage<double, 2304, 512>::bytes));
+        g_noalloc_ptr[device & 63] = static_cast<unsigned char *>(ptr);
+        g_noalloc_ready.fetch_or(bit, std::memory_order_release);
+    }
+    *out = g_noalloc_ptr[device & 63];
+    return RSG_OK;
+}
+
+} // namespace rsg
+
+extern "C" int spmv_csr_d_noalloc(int m, int n, int nnz, int base, const int *rowptr, const int *colidx, const double *values,
+                                  double alpha, const double *x, double beta, double *y, void *cuda_stream)
+{
+    using namespace rsg;
+    if (m < 0 || n < 0 || nnz < 0 || (base != 0 && base != 1) || !rowptr || (m > 0 && !y) || (nnz > 0 && (!colidx || !values || !x)))
+        return RSG_BAD_ARG;
+    if ((((uintptr_t)colidx) & 15) != 0 || (((uintptr_t)values) & 15) != 0) return RSG_BAD_ARG; // the bulk copies need 16-byte aligned arrays
+    if (m > kNoallocMaxRows) return RSG_SIZE_LIMIT;
+    if (m == 0) return RSG_OK;
+    // the tile size of pipe_build_plan for shape 0 under default options (nnz is trusted here: no device read-back)
+    constexpr int THREADS = 128, CAPE = 2304, ROWS = 512;
+    const int tmax = CAPE * 8 / 9;
+    const int w = (tmax + ROWS - 1) / ROWS;
+    const double avg = (double)nnz / m;
+    int lanes = 1;
+    if (avg >= 12.0) {
+        const double rows_fit = tmax / (avg + w);
+        if (THREADS / rows_fit >= 1.5 && THREADS / rows_fit < 3.0) lanes = 2;
+    }
+    const long long want = (long long)((avg + w) * (THREADS / lanes) + 0.5);
+    const int tile = (int)std::min<long long>(tmax, std::max<long long>(want, 512));
+    const long long items = (long long)w * m + nnz;
+    const long long ntiles_ll = std::max<long long>(1, (items + tile - 1) / tile);
+    if (ntiles_ll > kNoallocMaxTiles) return RSG_SIZE_LIMIT;
+    const int ntiles = (int)ntiles_ll;
+    const int rp0_len = ((m + 1 + 3) & ~3) + 4;
+
+    int device = 0;
+    RSG_CUDA_TRY(cudaGetDevice(&device));
+    unsigned char *scratch = nullptr;
+    RSG_TRY(noalloc_scratch_ptr(device, &scratch));
+    int4 *desc = reinterpret_cast<int4 *>(scratch);
+    int *rp0 = reinterpret_cast<int *>(scratch + kNoallocDescBytes);
+    cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+    // every word the product reads is rewritten here (descriptors 0..ntiles incl. .z/.w, row pointers 0..rp0_len-1):
+    // nothing of the previous call's contents survives into this one
+    pipe_partition_kernel<<<(ntiles + 1 + 255) / 256, 256, 0, st>>>(m, base, rowptr, tile, w, ntiles, desc);
+    pipe_maxlen_kernel<<<(ntiles * 32 + 255) / 256, 256, 0, st>>>(ntiles, base, 0, rowptr, desc);
+    pipe_rowptr_copy_kernel<<<(rp0_len + 255) / 256, 256, 0, st>>>(m, rp0_len, base, rowptr, rp0);
+    HaloFuse fuse;
+    std::memset(&fuse, 0, sizeof(fuse));
+    LongSplit ls = {nullptr, nullptr, nullptr, nullptr, 0}; // rows longer than a stage are reduced CTA-per-row inside their tile
+    const int ropt = lanes == 2 ? 1 << 16 : 0;
+    constexpr int MINB = TileResidency<double, THREADS, CAPE, ROWS>::value;
+    spmv_tile_kernel<double, double, THREADS, CAPE, ROWS, MINB, false>
+        <<<ntiles, THREADS, PipeStage<double, CAPE, ROWS>::bytes, st>>>(base, (const int *)rp0, colidx, values, x, y, alpha, beta,
+                                                                          (const int4 *)desc, nnz, ntiles, ropt, 0, nullptr, 0, 0,
+                                                                          nullptr, 0, fuse, ls);
+    RSG_CUDA_TRY(cudaGetLastError());
+    return RSG_OK;
+}
