@@ -462,7 +462,8 @@ def run_ours(args):
             if world > 1:
                 op = RowBlockSpmv(a, starts, "p2p" if args.exchange.startswith("p2p") else "halo", lambda c: DeviceCSR(c, "d", dev),
                                   lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
-                                  view=(lambda A, r0, r1: A.view_rows(r0, r1)) if overlap else None, push=P2P_FNS, side=side)
+                                  view=(lambda A, r0, r1: A.view_rows(r0, r1)) if overlap else None, push=P2P_FNS, side=side,
+                                  proto=args.proto)
                 if op.p2p is not None and op.p2p[1] is not None:
                     h.set_option("SPMV_HALO_START", op.plan.halo_base)  # marks the tiles that must wait for the peers
             else:
@@ -928,6 +929,9 @@ def main():
     ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-side", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
     ap.add_argument("--pdl", type=int, default=2, choices=[0, 1, 2], help="RSG_OPT_SPMV_PDL for the timed products (2 = matrix values promised static)")
+    ap.add_argument("--proto", default="packets", choices=["pull", "packets", "packets-fused", "flags"],
+                    help="N>1, fused exchange: pull = the product's first CTAs fetch the halo (no remote store in the product); "
+                         "packets = {value, step} packets pushed and unpacked by the halo tiles; flags = push + fence + arrival flags")
     ap.add_argument("--mode", default="separate", choices=["chain", "separate"],
                     help="N>1: separate = independent products of a static x, the push at the head of each launch (default; round 1's "
                          "protocol); chain = products x <- A x / 52 whose boundary rows are pushed by the tiles that compute them "

@@ -108,6 +108,12 @@ typedef enum {
                                    16-bit columns) before they wait for it; 2 = the matrix VALUES too -- the caller promises that
                                    nothing queued ahead of the product writes them (a solver loop on a fixed matrix, the harness's
                                    50 timed products, spmv.cu:174-207); 1 = plain launches */
+    RSG_OPT_SPMV_HALO_PLACE = 25, /* multi-GPU window plans: share of the grid (percent) that is interior tiles before the first tile
+                                   that reads a peer's entries; from there the two kinds alternate, the last wave is interior again.
+                                   0 = default (packet exchange: 35; arrival flags: 100 = all such tiles at the end).  Read when the
+                                   plan is built and by rsg_dist_enable_packets; not part of the plan's key */
+    RSG_OPT_SPMV_HALO_END = 26,  /* the same plans: share of the grid (percent) by which the last such tile has been placed (0 = default:
+                                   all but the last wave) */
     RSG_OPT_COUNT_
 } rsg_option;
 
@@ -139,6 +145,11 @@ typedef enum {
  * rowptr/colidx plus m, n, nnz and base.  When a matrix is freed and another one may be allocated
  * at the same addresses, call rsg_forget_matrix (or re-run the analysis, which always rebuilds). */
 int rsg_forget_matrix(rsg_handle_t handle, const int *rowptr);
+/* Debug aid (tools/dist_trace.py): while buf != NULL the window kernel writes four %globaltimer values (ns) per CTA of every
+ * product into the DEVICE array buf (2 * 4 * capacity_ctas words: two halves used in turn by consecutive products) at
+ * [half][4 * blockIdx]: entry, launch dependency resolved, tile staged in shared memory, done (bit 63 of the last word: the
+ * tile reads a peer's entries).  Products with more CTAs than capacity_ctas are not traced. */
+int rsg_debug_trace(rsg_handle_t handle, unsigned long long *buf, int capacity_ctas);
 int rsg_set_option(rsg_handle_t handle, int option, int value);
 int rsg_get_info(rsg_handle_t handle, int info, long long *value);
 
@@ -269,6 +280,35 @@ int rsg_dist_create(rsg_handle_t handle, char precision, int m, int n_ext, int n
  * (image of this step) into the peers' slots and release the step number to their flags, its halo tiles (and always its
  * last tile) acquire the neighbours' flags before they read x.  Asynchronous. */
 int rsg_dist_step(rsg_dist_t dist, void *y);
+/* Packet exchange for a context made by rsg_dist_create (window-kernel blocks; RSG_UNSUPPORTED otherwise): every boundary
+ * entry travels as {value, step number} in ONE 16-byte store (fp32 x: 8 bytes) and the halo tiles unpack their x window out of
+ * the packets, polling the step number inside each entry -- no fence + counter + flag hop between the data and its consumer,
+ * which is what bounds a product of a few microseconds (8 GPUs on config 5).  local_packets: this rank's 2 packet buffers
+ * (image 0, 1), (n_ext - halo_start) packets each, ZERO-filled by the caller, peer-mapped; peer_packets: 2*npeers DEVICE
+ * pointers, image-major like peer_slots: where entry 0 of this rank's send list lands in peer q's buffer.  ONLY for
+ * exchange patterns in which every rank also reads from every rank it sends to (stencils, structurally symmetric matrices):
+ * that mutual dependency keeps a rank from running two steps ahead of a reader -- the job the arrival flags did, which are
+ * no longer touched.  Every rank must have returned from this call before any rank steps; local_packets == NULL switches
+ * back to the flags (a caller whose ranks did not all get RSG_OK).  side_stream != 0: the packets are pushed by a small kernel
+ * of their own on a high-priority stream of the context, ordered after everything queued on the handle's stream when
+ * rsg_dist_step is called (an event), instead of by the product's first CTAs: the product then issues no remote store, so its
+ * completion -- the next launch's dependency -- does not wait for a flush through NVLink (measured: 2-4.5 us).  rsg_spmv_multi_create does all
+ * of this by itself when the pattern allows (RSG_DIST_EXCHANGE=flags | packets | packets-fused | pull in the environment). */
+int rsg_dist_enable_packets(rsg_dist_t dist, void *const *local_packets, void *const *peer_packets, int side_stream);
+/* Pull exchange for a context made by rsg_dist_create (any exchange pattern; window and tile kernels): the product's first CTAs
+ * FETCH this rank's halo instead of pushing its boundary -- they poll the neighbours' "x of step e is final" counters over
+ * NVLink, load the entries from the owners' x images, store them into this rank's own image and raise a LOCAL flag the halo
+ * tiles wait for.  The product then contains no remote store: nothing to flush through NVLink when its grid completes (measured:
+ * that flush delays the next launch by 2-4 us) and no fence behind remote stores (6-10 us under load).  pull_col / pull_idx:
+ * DEVICE arrays of npull entries grouped by owner (halo column the entry goes to; its index in the owner's x); owner q's
+ * entries are [owner_lo[q], owner_hi[q]); peer_x: 2*npeers DEVICE pointers, image-major: peer q's x image p (NULL: nothing
+ * fetched from q); peer_ready: npeers DEVICE pointers to the neighbours' counters (NULL: not a neighbour); my_ready: this
+ * rank's counter; local_flags: 2 ints (image 0, 1).  Counters and flags zeroed by the caller; every rank enables before any
+ * rank steps.  Measured slower than the packets here (two NVLink round trips under load before the halo tiles may start); kept for patterns that
+ * are not mutual.  rsg_spmv_multi_create: RSG_DIST_EXCHANGE=pull in the environment. */
+int rsg_dist_enable_pull(rsg_dist_t dist, int npull, const int *pull_col, const int *pull_idx, int npeers,
+                         const void *const *peer_x, const int *const *peer_ready, const int *owner_lo, const int *owner_hi,
+                         int *my_ready, int *local_flags);
 void *rsg_dist_x(rsg_dist_t dist); /* DEVICE pointer of the x image the NEXT step reads (write the local entries there) */
 int rsg_dist_destroy(rsg_dist_t dist);
 

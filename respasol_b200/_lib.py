@@ -43,6 +43,7 @@ GPU_SYMBOLS = {
     "rsg_status_string": (C.c_char_p, [_I]),
     "rsg_version": (_I, []),
     "rsg_forget_matrix": (_I, [_P, _P]),
+    "rsg_debug_trace": (_I, [_P, _P, _I]),
     "rsg_set_option": (_I, [_P, _I, _I]),
     "rsg_get_info": (_I, [_P, _I, _LLP]),
     "rsg_spmv_analysis": (_I, _CSR_ARGS),
@@ -81,6 +82,8 @@ GPU_SYMBOLS = {
     "rsg_spmv_halo_fuse_ranges": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _I]),
     "rsg_dist_create": (_I, [_P, C.c_char, _I, _I, _I, _I, _P, _P, _P, _P, _I, _I, _P, _I, _P, _P, _P, _P, _P, _I, C.POINTER(_P)]),
     "rsg_dist_step": (_I, [_P, _P]),
+    "rsg_dist_enable_packets": (_I, [_P, _P, _P, _I]),
+    "rsg_dist_enable_pull": (_I, [_P, _I, _P, _P, _I, _P, _P, _P, _P, _P, _P]),
     "rsg_dist_create_chain": (_I, [_P, C.c_char, _I, _I, _I, _I, _P, _P, _P, _P, _I, _I, _P, _I, _P, _P, _P, _P, _P, _I, C.POINTER(_P)]),
     "rsg_dist_step_chain": (_I, [_P, _D]),
     "rsg_dist_chain_reset": (_I, [_P]),

@@ -71,6 +71,16 @@ const char *rsg_status_string(int status)
     }
 }
 
+/* debug: the window kernel writes 4 x %globaltimer (ns) per CTA into buf (entry, dependency resolved, data staged, done; bit 63
+ * of the last word = the tile reads a peer's entries); buf == NULL switches it off */
+int rsg_debug_trace(rsg_handle_t h, unsigned long long *buf, int capacity_ctas)
+{
+    if (!h || capacity_ctas < 0) return RSG_BAD_ARG;
+    h->trace = buf;
+    h->trace_ctas = buf ? capacity_ctas : 0;
+    return RSG_OK;
+}
+
 int rsg_create(rsg_handle_t *handle, int device)
 {
     if (!handle) return RSG_BAD_ARG;

@@ -16,8 +16,9 @@
 // its boundary entries of image p into the readers' image-p halo slots and releases e to their flags; tiles that read
 // halo columns (and, always, the last tile) acquire flags[p][i] >= e from every neighbour.  A rank therefore never runs
 // more than one step ahead of a neighbour, which is what makes two images enough.
-#include "rsg_internal.cuh"
+#include "spmv_device.cuh"
 
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <new>
@@ -41,6 +42,17 @@ struct rsg_dist {
     void *x3[3] = {nullptr, nullptr, nullptr};
     ChainPush cp[3];                 // cp[i]: the push INTO the peers' image i
     const int *wflags3[3] = {nullptr, nullptr, nullptr};
+    // packet exchange (rsg_dist_enable_packets): this rank's two packet buffers; fuse[p].dst then point at the peers' ones
+    bool packets = false;
+    const void *pk_local[2] = {nullptr, nullptr};
+    bool pk_side = false;            // the packets are pushed by a small kernel of their own on `side` (no remote store in the product)
+    cudaStream_t side = nullptr;
+    cudaEvent_t x_ready = nullptr;
+    void *slot_dst[2][RSG_MAX_PEERS] = {}; // the peers' plain halo slots (restored when the packets are switched off)
+    // pull exchange (rsg_dist_enable_pull): the product's first CTAs fetch the halo; no remote write in the product
+    bool pull = false;
+    HaloFuse pullf[2];
+    const int *local_flag[2] = {nullptr, nullptr};
     int *send_pos = nullptr;         // device, m ints (owned)
     int *chain_counter = nullptr;    // device (owned, with send_pos)
 };
@@ -54,6 +66,30 @@ struct DevGuard {
 };
 
 constexpr long long kDistPdlMinEntries = 12000000; // per-rank entries below which a fused-exchange step is launched plainly
+
+// every halo column this block reads: its packet (both images) -> "pending" (epoch field all ones); packets of columns
+// nobody reads keep epoch 0 = "padding of an x window, take it as it is"
+__global__ void packet_mark_kernel(long long cnt, const int *__restrict__ colidx, int base, int halo_start, void *pk0, void *pk1, int wide)
+{
+    const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= cnt) return;
+    const int c = colidx[k] - base;
+    if (c < halo_start) return;
+    const int j = c - halo_start;
+    if (wide) {
+        static_cast<uint4 *>(pk0)[j] = make_uint4(0u, 0xffffffffu, 0u, 0xffffffffu);
+        static_cast<uint4 *>(pk1)[j] = make_uint4(0u, 0xffffffffu, 0u, 0xffffffffu);
+    } else {
+        static_cast<uint2 *>(pk0)[j] = make_uint2(0u, 0xffffffffu);
+        static_cast<uint2 *>(pk1)[j] = make_uint2(0u, 0xffffffffu);
+    }
+}
+
+// the boundary entries of x as {value, step} packets into the peers' packet buffers (rsg_dist_enable_packets, side-stream form)
+template <typename TX> __global__ void __launch_bounds__(128) packet_push_kernel(const HaloFuse fuse, const TX *__restrict__ x)
+{
+    halo_fuse_push<TX, 128>(fuse, x);
+}
 
 inline int halo_base_of(int n_local) { return (n_local + 31) / 32 * 32; } // the halo starts on its own 128/256-byte line
 
@@ -121,10 +157,149 @@ int rsg_dist_create(rsg_handle_t h, char precision, int m, int n_ext, int nnz, i
     return RSG_OK;
 }
 
+} // extern "C"
+
+// the (cached) SpMV plan of a dist context's block
+static int dist_plan(rsg_dist *d, SpmvPlan **pl)
+{
+    rsg_context *h = d->h;
+    *pl = nullptr;
+    if (d->m <= 0) return RSG_OK;
+    const int keep = h->opts[RSG_OPT_SPMV_HALO_START];
+    h->opts[RSG_OPT_SPMV_HALO_START] = d->halo_start;
+    const int pkey = d->precision == 'd' ? 0x88 : d->precision == 's' ? 0x44 : 0x84;
+    const int rc = spmv_get_plan(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, false, pl, pkey);
+    h->opts[RSG_OPT_SPMV_HALO_START] = keep;
+    return rc;
+}
+
+extern "C" {
+
+/* Packet exchange for a dist context made by rsg_dist_create: every boundary entry travels as {value, step number} in one
+ * 16-byte (fp32 x: 8-byte) store, and the halo tiles of the product unpack their x window out of the packets, polling the step
+ * number inside each entry -- no fence + counter + flag between the data and its consumer (the latency chain that bounds a
+ * short product).  local_packets: this rank's 2 packet buffers (image 0, 1; (n_ext - halo_start) packets each, zero-filled by
+ * the caller, written by the peers); peer_packets: 2 * npeers pointers, image-major like peer_slots: where entry 0 of this rank's
+ * send list lands in peer q's buffer.  ONLY for exchange patterns in which every rank also READS from every rank it sends to
+ * (stencils, symmetric patterns): that mutual dependency is what keeps a rank from running two steps ahead of a reader, the
+ * job the arrival flags did.  Every rank must have returned from this call before any rank steps (the caller's barrier).
+ * RSG_UNSUPPORTED when the block's plan is not the window kernel's. */
+int rsg_dist_enable_packets(rsg_dist_t d, void *const *local_packets, void *const *peer_packets, int side_stream)
+{
+    if (!d || d->chained) return RSG_BAD_ARG;
+    rsg_context *h = d->h;
+    const int npeers = d->fuse[0].npeers;
+    if (!local_packets) { // back to the arrival flags (a caller whose ranks did not all get the window kernel)
+        if (d->packets)
+            for (int p = 0; p < 2; ++p) {
+                for (int q = 0; q < npeers; ++q) d->fuse[p].dst[q] = d->slot_dst[p][q];
+                d->fuse[p].packets = 0;
+            }
+        d->packets = false;
+        DevGuard g0(h->device);
+        SpmvPlan *pl0 = nullptr;
+        RSG_TRY(dist_plan(d, &pl0));
+        if (pl0 && pl0->algo == RSG_SPMV_WINDOW) RSG_TRY(window_place_halo(h, *pl0, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 100));
+        return RSG_OK;
+    }
+    if (d->packets || !local_packets[0] || !local_packets[1] || d->halo_start <= 0) return RSG_BAD_ARG;
+    for (int p = 0; p < 2; ++p)
+        for (int q = 0; q < npeers; ++q)
+            if (d->fuse[p].dst[q] && (!peer_packets || !peer_packets[p * npeers + q])) return RSG_BAD_ARG;
+    DevGuard g(h->device);
+    SpmvPlan *pl = nullptr;
+    RSG_TRY(dist_plan(d, &pl));
+    if (pl && pl->algo != RSG_SPMV_WINDOW) return RSG_UNSUPPORTED;
+    if (pl && pl->nnz > 0) {
+        const long long cnt = pl->nnz;
+        packet_mark_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, h->stream>>>(cnt, d->colidx + pl->first, d->base, d->halo_start,
+                                                                                  local_packets[0], local_packets[1], d->precision == 's' ? 0 : 1);
+        h->launches++;
+        RSG_CUDA_TRY(cudaGetLastError());
+        RSG_CUDA_TRY(cudaStreamSynchronize(h->stream));
+    }
+    // halo tiles no longer wait for a flag that trails the data: they can sit in the middle of the grid, and the last wave
+    // (the critical path into the next launch) is interior tiles
+    if (pl) RSG_TRY(window_place_halo(h, *pl, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 35));
+    for (int p = 0; p < 2; ++p) {
+        d->pk_local[p] = local_packets[p];
+        for (int q = 0; q < npeers; ++q)
+            if ((d->slot_dst[p][q] = d->fuse[p].dst[q]) != nullptr) d->fuse[p].dst[q] = peer_packets[p * npeers + q];
+        d->fuse[p].packets = 1;
+    }
+    d->packets = true;
+    d->pk_side = false;
+    if (side_stream) {
+        // The push as a kernel of its own beside the product: a grid that issued remote stores is complete only once they are
+        // flushed through NVLink, which delays the launch that depends on it by 2-4.5 us (measured, tools/dist_trace.py); on a
+        // side stream that flush is nobody's dependency.  An event record between two products does not cost them their
+        // programmatic overlap (measured: 14.15 us with and without).
+        int lo_prio = 0, hi_prio = 0;
+        cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
+        if (!d->side && cudaStreamCreateWithPriority(&d->side, cudaStreamNonBlocking, hi_prio) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
+        if (!d->x_ready && cudaEventCreateWithFlags(&d->x_ready, cudaEventDisableTiming) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
+        d->pk_side = true;
+    }
+    return RSG_OK;
+}
+
+/* Pull exchange for a context made by rsg_dist_create (any pattern, any kernel): instead of pushing its boundary entries, the
+ * product's first CTAs FETCH this rank's halo -- they poll the neighbours' "x of step e is final" counters over NVLink, load
+ * the entries from the owners' x images and store them into this rank's own image, then raise a local flag the halo tiles
+ * wait for.  The product then holds no remote store: nothing to flush through NVLink when the grid completes (which delays the
+ * next launch by 2-4 us) and no fence behind remote stores (6-10 us while the memory system is saturated).
+ *   npull entries, grouped by owner: pull_col[k] = halo column (in this rank's relabelled numbering) entry k goes to,
+ *   pull_idx[k] = its index in the owner's x (DEVICE arrays, caller-owned); owner q's entries are [owner_lo[q], owner_hi[q]).
+ *   peer_x: 2 * npeers DEVICE pointers, image-major: peer q's x image p (NULL: nothing is fetched from q).
+ *   peer_ready: npeers DEVICE pointers: peer q's counter (NULL: not a neighbour; every neighbour -- source or reader -- is
+ *   awaited, so that no rank overwrites an image a reader has not finished with); my_ready: this rank's own counter;
+ *   local_flags: 2 ints of this rank (image 0, 1).  All zero-initialised by the caller; every rank enables before any steps. */
+int rsg_dist_enable_pull(rsg_dist_t d, int npull, const int *pull_col, const int *pull_idx, int npeers, const void *const *peer_x,
+                         const int *const *peer_ready, const int *owner_lo, const int *owner_hi, int *my_ready, int *local_flags)
+{
+    if (!d || d->chained || d->packets || npull < 0 || npeers < 0 || npeers > RSG_MAX_PEERS || !my_ready || !local_flags ||
+        (npull > 0 && (!pull_col || !pull_idx || !peer_x || !owner_lo || !owner_hi)) || (npeers > 0 && !peer_ready) || d->halo_start <= 0)
+        return RSG_BAD_ARG;
+    rsg_context *h = d->h;
+    DevGuard g(h->device);
+    SpmvPlan *pl = nullptr;
+    RSG_TRY(dist_plan(d, &pl));
+    if (pl && pl->algo != RSG_SPMV_WINDOW && pl->algo != RSG_SPMV_TILE) return RSG_UNSUPPORTED;
+    // the halo tiles wait for a LOCAL flag that trails the fetch by about two NVLink round trips: mid-grid, last wave interior
+    if (pl && pl->algo == RSG_SPMV_WINDOW)
+        RSG_TRY(window_place_halo(h, *pl, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 55));
+    for (int p = 0; p < 2; ++p) {
+        HaloFuse &f = d->pullf[p];
+        std::memset(&f, 0, sizeof(f));
+        for (int q = 0; q < npeers; ++q) {
+            f.dst[q] = peer_x ? const_cast<void *>(peer_x[p * npeers + q]) : nullptr;
+            f.flag[q] = const_cast<int *>(peer_ready[q]);
+            f.lo[q] = owner_lo ? owner_lo[q] : 0;
+            f.hi[q] = owner_hi ? owner_hi[q] : 0;
+        }
+        f.send_idx = pull_idx;
+        f.pull_col = pull_col;
+        f.counter = h->scratch_i + 62;
+        f.nsend = npull; f.npeers = npeers; f.ctas = 1;
+        f.pull = 1;
+        f.local_x = d->x_image[p];
+        f.my_ready = my_ready;
+        f.local_flag = local_flags + p;
+        d->local_flag[p] = local_flags + p;
+    }
+    d->pull = true;
+    return RSG_OK;
+}
+
 int rsg_dist_destroy(rsg_dist_t d)
 {
     if (!d) return RSG_BAD_ARG;
     if (d->send_pos) { DevGuard g(d->h->device); cudaFree(d->send_pos); }
+    if (d->side || d->x_ready) {
+        DevGuard g(d->h->device);
+        if (d->side) { cudaStreamSynchronize(d->side); cudaStreamDestroy(d->side); }
+        if (d->x_ready) cudaEventDestroy(d->x_ready);
+    }
     delete d;
     return RSG_OK;
 }
@@ -142,18 +317,42 @@ int rsg_dist_step(rsg_dist_t d, void *y)
     DevGuard g(h->device);
     const int p = d->epoch & 1; // step e = epoch + 1 uses image (e - 1) & 1
     d->epoch += 1;
-    if (d->fuse[p].npeers > 0) {
+    // timing experiments only (tools/dist_trace.py; the results are wrong): RSG_OPT_SPMV_X_HINT bit 8 = nobody waits for / unpacks
+    // the halo, bit 16 = no push (implies bit 8), bit 32 = never fall back to plain launches, bit 64 = an eighth of the push CTAs
+    int dbg = h->opts[RSG_OPT_SPMV_X_HINT] & (8 | 16 | 32 | 64);
+    if (dbg & 16) dbg |= 8; // (waiting for a push that never comes would hang until the spin limit)
+    if (d->pull) {
+        if (!(dbg & 16)) { h->fuse = d->pullf[p]; h->fuse.epoch = d->epoch; }
+    } else if (d->packets && d->pk_side) {
+        if (d->fuse[p].npeers > 0 && d->fuse[p].nsend > 0 && !(dbg & 16)) {
+            // x of this step = everything queued on the product's stream so far; the push follows it on the side stream
+            RSG_CUDA_TRY(cudaEventRecord(d->x_ready, h->stream));
+            RSG_CUDA_TRY(cudaStreamWaitEvent(d->side, d->x_ready, 0));
+            HaloFuse f = d->fuse[p];
+            f.epoch = d->epoch;
+            f.ctas = std::max(1, std::min(1024, (f.nsend + 4 * 128 - 1) / (4 * 128)));
+            if (dbg & 64) f.ctas = std::max(1, f.ctas / 8); // (experiment: few CTAs, each walking eight batches)
+            if (d->precision == 's') packet_push_kernel<float><<<f.ctas, 128, 0, d->side>>>(f, static_cast<const float *>(d->x_image[p]));
+            else packet_push_kernel<double><<<f.ctas, 128, 0, d->side>>>(f, static_cast<const double *>(d->x_image[p]));
+            h->launches++;
+            RSG_CUDA_TRY(cudaGetLastError());
+        }
+    } else if (d->fuse[p].npeers > 0 && !(dbg & 16)) {
         h->fuse = d->fuse[p];
         h->fuse.epoch = d->epoch;
     }
-    if (d->nwait > 0) { h->wait_flags = d->wait_flags[p]; h->wait_n = d->nwait; h->wait_epoch = d->epoch; }
+    if (dbg & 8) { /* no wait */ }
+    else if (d->pull) { h->wait_flags = d->local_flag[p]; h->wait_n = 1; h->wait_epoch = d->epoch; }
+    else if (d->packets) { h->packets.pkts = d->pk_local[p]; h->packets.halo_start = d->halo_start; h->wait_epoch = d->epoch; }
+    else if (d->nwait > 0) { h->wait_flags = d->wait_flags[p]; h->wait_n = d->nwait; h->wait_epoch = d->epoch; }
     const int keep = h->opts[RSG_OPT_SPMV_HALO_START], keep_pdl = h->opts[RSG_OPT_SPMV_PDL];
     h->opts[RSG_OPT_SPMV_HALO_START] = d->halo_start; // part of the plan's key
     // A step cannot be shorter than push + signal + the neighbours' halo tiles (the push of step e+1 follows the end of step e,
     // which follows the arrival of the neighbours' push e): about 15 us while a dependent-launched product saturates the
     // memory system (every hop of the push queues behind its burst), about 1 us more than the product itself with plain
     // launches (profiles/r2_dist_probe.jsonl).  Short per-rank products therefore keep plain launches.
-    if (d->fuse[p].npeers > 0 && d->stored < kDistPdlMinEntries && keep_pdl != 1) h->opts[RSG_OPT_SPMV_PDL] = 1;
+    // (The packet exchange has no such chain: its products keep the dependent launches.)
+    if (!d->packets && !d->pull && !(dbg & 32) && d->fuse[p].npeers > 0 && d->stored < kDistPdlMinEntries && keep_pdl != 1) h->opts[RSG_OPT_SPMV_PDL] = 1;
     int rc;
     if (d->precision == 'd')
         rc = spmv_run<double, double>(h, d->m, d->n_ext, d->nnz, d->base, d->rowptr, d->colidx, static_cast<const double *>(d->values), 1.0,
@@ -167,6 +366,7 @@ int rsg_dist_step(rsg_dist_t d, void *y)
     h->opts[RSG_OPT_SPMV_HALO_START] = keep;
     h->opts[RSG_OPT_SPMV_PDL] = keep_pdl;
     h->wait_flags = nullptr;
+    h->packets.pkts = nullptr;
     h->fuse.ctas = 0;
     return rc;
 }
@@ -302,7 +502,10 @@ struct rsg_multi {
     std::vector<cudaEvent_t> ev0, ev1;
     // per device allocations
     std::vector<int *> rowptr, colidx, send_idx, flags;
-    std::vector<void *> values, x, y;
+    std::vector<void *> values, x, y, pk; // pk: packet buffers (2 images) when the packet exchange is on
+    bool packets = false;
+    int proto = 0; // 0 arrival flags, 1 packets, 2 pull
+    std::vector<int *> pull_col, pull_idx;
     long long bytes_received_per_step = 0; // sum over ranks of the halo entries they read, in bytes
     long long halo_tiles = 0;
 };
@@ -325,6 +528,9 @@ void multi_free(rsg_multi *M)
         if ((size_t)r < M->values.size()) cudaFree(M->values[r]);
         if ((size_t)r < M->x.size()) cudaFree(M->x[r]);
         if ((size_t)r < M->y.size()) cudaFree(M->y[r]);
+        if ((size_t)r < M->pk.size() && M->pk[r]) cudaFree(M->pk[r]);
+        if ((size_t)r < M->pull_col.size() && M->pull_col[r]) cudaFree(M->pull_col[r]);
+        if ((size_t)r < M->pull_idx.size() && M->pull_idx[r]) cudaFree(M->pull_idx[r]);
         if ((size_t)r < M->ev0.size() && M->ev0[r]) cudaEventDestroy(M->ev0[r]);
         if ((size_t)r < M->ev1.size() && M->ev1[r]) cudaEventDestroy(M->ev1[r]);
         if ((size_t)r < M->stream.size() && M->stream[r]) cudaStreamDestroy(M->stream[r]);
@@ -554,6 +760,85 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
                 }
         }
     }
+    // ---- packet exchange (rsg_dist_enable_packets) when every rank reads from every rank it sends to and every block runs
+    // the window kernel; RSG_DIST_PACKETS=0 in the environment keeps the arrival flags (A/B)
+    // RSG_DIST_EXCHANGE in the environment: "packets" (default; mutual patterns on the window kernel, else the flags stay) |
+    // "packets-fused" | "pull" | "flags" (A/B; the tests run all four)
+    int proto = 1;
+    if (const char *env = getenv("RSG_DIST_EXCHANGE")) proto = !std::strcmp(env, "flags") ? 0 : !std::strcmp(env, "packets") ? 1 : !std::strcmp(env, "packets-fused") ? 3 : 2;
+    if (P > 1 && rc == RSG_OK && proto == 2) {
+        // ---- pull exchange (rsg_dist_enable_pull): per rank, the entries it reads, grouped by owner
+        M->pull_col.assign((size_t)P, nullptr); M->pull_idx.assign((size_t)P, nullptr);
+        for (int r = 0; r < P && rc == RSG_OK; ++r) {
+            cudaSetDevice(M->dev[(size_t)r]);
+            std::vector<int> col, idx, lo((size_t)P, 0), hi((size_t)P, 0);
+            for (int o = 0; o < P; ++o) {
+                lo[(size_t)o] = (int)col.size();
+                if (o != r) {
+                    const std::vector<int> &so = send[(size_t)o];
+                    for (int c : need[(size_t)r])
+                        if (c >= rs[(size_t)o] && c < rs[(size_t)o + 1]) {
+                            const int li = c - rs[(size_t)o];
+                            const int pos = (int)(std::lower_bound(so.begin(), so.end(), li) - so.begin());
+                            col.push_back(M->hbase[(size_t)r] + o * width + pos);
+                            idx.push_back(li);
+                        }
+                }
+                hi[(size_t)o] = (int)col.size();
+            }
+            const size_t np = col.size();
+            if (cudaMalloc(&M->pull_col[(size_t)r], sizeof(int) * (np ? np : 1)) != cudaSuccess || cudaMalloc(&M->pull_idx[(size_t)r], sizeof(int) * (np ? np : 1)) != cudaSuccess ||
+                (np && (cudaMemcpy(M->pull_col[(size_t)r], col.data(), sizeof(int) * np, cudaMemcpyHostToDevice) != cudaSuccess ||
+                        cudaMemcpy(M->pull_idx[(size_t)r], idx.data(), sizeof(int) * np, cudaMemcpyHostToDevice) != cudaSuccess))) {
+                (void)cudaGetLastError(); rc = RSG_ALLOC_FAILED; break;
+            }
+            std::vector<const void *> px((size_t)(2 * P), nullptr);
+            std::vector<const int *> pr((size_t)P, nullptr);
+            for (int q = 0; q < P; ++q) {
+                if (q == r) continue;
+                if (std::find(nb[(size_t)r].begin(), nb[(size_t)r].end(), q) != nb[(size_t)r].end()) pr[(size_t)q] = M->flags[(size_t)q] + 160;
+                if (hi[(size_t)q] > lo[(size_t)q])
+                    for (int p = 0; p < 2; ++p) px[(size_t)(p * P + q)] = static_cast<char *>(M->x[(size_t)q]) + M->xs * (size_t)p * stride;
+            }
+            rc = rsg_dist_enable_pull(M->d[(size_t)r], (int)np, M->pull_col[(size_t)r], M->pull_idx[(size_t)r], P, px.data(), pr.data(), lo.data(), hi.data(),
+                                      M->flags[(size_t)r] + 160, M->flags[(size_t)r] + 161);
+            if (rc == RSG_UNSUPPORTED) { rc = RSG_OK; proto = 0; break; } // (a block on a gather kernel: everybody keeps the flags)
+        }
+        if (proto == 2) M->proto = 2;
+        else for (int r = 0; r < P; ++r) if (M->d[(size_t)r]) M->d[(size_t)r]->pull = false;
+    }
+    bool want = P > 1 && rc == RSG_OK && (proto == 1 || proto == 3);
+    for (int q = 0; q < P && want; ++q)
+        for (int o : reads[(size_t)q])
+            if (std::find(reads[(size_t)o].begin(), reads[(size_t)o].end(), q) == reads[(size_t)o].end()) want = false;
+    for (int r = 0; r < P && want; ++r) {
+        if (reads[(size_t)r].empty()) { want = false; break; }
+        cudaSetDevice(M->dev[(size_t)r]);
+        SpmvPlan *pl = nullptr;
+        if (dist_plan(M->d[(size_t)r], &pl) != RSG_OK || !pl || pl->algo != RSG_SPMV_WINDOW) want = false;
+    }
+    if (want) {
+        const size_t pbytes = 2 * M->xs, per_image = (size_t)P * (size_t)width;
+        M->pk.assign((size_t)P, nullptr);
+        for (int r = 0; r < P && rc == RSG_OK; ++r) {
+            cudaSetDevice(M->dev[(size_t)r]);
+            if (cudaMalloc(&M->pk[(size_t)r], 2 * per_image * pbytes) != cudaSuccess || cudaMemset(M->pk[(size_t)r], 0, 2 * per_image * pbytes) != cudaSuccess) {
+                (void)cudaGetLastError(); rc = RSG_ALLOC_FAILED;
+            }
+        }
+        for (int r = 0; r < P && rc == RSG_OK; ++r) {
+            cudaSetDevice(M->dev[(size_t)r]);
+            std::vector<void *> peer((size_t)(2 * P), nullptr);
+            for (int q = 0; q < P; ++q)
+                for (int p = 0; p < 2 && q != r; ++p)
+                    peer[(size_t)(p * P + q)] = static_cast<char *>(M->pk[(size_t)q]) + pbytes * ((size_t)p * per_image + (size_t)r * (size_t)width);
+            void *mine[2] = {M->pk[(size_t)r], static_cast<char *>(M->pk[(size_t)r]) + pbytes * per_image};
+            rc = rsg_dist_enable_packets(M->d[(size_t)r], mine, peer.data(), proto == 1 ? 1 : 0);
+        }
+        for (int r = 0; r < P && rc == RSG_OK; ++r) { cudaSetDevice(M->dev[(size_t)r]); cudaDeviceSynchronize(); }
+        M->packets = rc == RSG_OK;
+        if (M->packets) M->proto = 1;
+    }
     cudaSetDevice(prev);
     if (rc != RSG_OK) { multi_free(M); return rc; }
     *out = M;
@@ -688,7 +973,7 @@ int rsg_spmv_multi_get_x(rsg_multi_t M, void *x_host)
 }
 
 /* what: 0 = ranks, 1 = halo bytes all ranks together receive per step, 2 = SpMV kernel (rsg_spmv_algo) of rank 0,
- * 3 = halo width (entries per rank slot); row_starts (may be NULL): ngpu+1 ints */
+ * 3 = halo width (entries per rank slot), 4 = exchange protocol (0 arrival flags, 1 packets, 2 pull); row_starts (may be NULL): ngpu+1 ints */
 int rsg_spmv_multi_info(rsg_multi_t M, int what, long long *value, int *row_starts)
 {
     if (!M || !value) return RSG_BAD_ARG;
@@ -697,6 +982,7 @@ int rsg_spmv_multi_info(rsg_multi_t M, int what, long long *value, int *row_star
     case 1: *value = M->bytes_received_per_step; break;
     case 2: *value = M->h[0]->last_spmv_algo; break;
     case 3: *value = M->width; break;
+    case 4: *value = M->proto; break;
     default: return RSG_BAD_ARG;
     }
     if (row_starts) for (int g = 0; g <= M->P; ++g) row_starts[g] = M->row_start[(size_t)g];

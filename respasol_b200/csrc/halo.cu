@@ -111,6 +111,8 @@ extern "C" int rsg_spmv_halo_fuse_ranges(rsg_handle_t h, int nsend, const int *s
     f.counter = h->scratch_i + 62;
     f.nsend = nsend; f.npeers = npeers; f.epoch = epoch;
     f.nruns = 0;
+    f.packets = 0;
+    f.pull = 0;
     f.ctas = 1; // sized at launch from the kernel's CTA width
     return RSG_OK;
 }

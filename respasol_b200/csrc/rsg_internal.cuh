@@ -46,6 +46,24 @@ struct HaloFuse {
     int nsend, npeers, epoch, ctas;
     // the send list as at most 4 contiguous runs of x (a slab of a stencil: its first and last plane): no index load
     int nruns, run_start[4], run_len[4];
+    // packets != 0: dst[q] point at the peers' PACKET buffers and every entry travels as {value, epoch} in one store -- no fence,
+    // no counter, no flag (rsg_dist_enable_packets); the readers poll the epoch inside the data
+    int packets;
+    // pull != 0 (rsg_dist_enable_pull): these CTAs FETCH instead -- dst[q] = peer q's x image (read), flag[q] = peer q's "x of
+    // step e is final" counter (read, remote), lo/hi = owner q's range of the pull list, send_idx = index into the owner's x,
+    // pull_col = where the entry goes in this rank's own image.  The product then contains no remote write at all.
+    int pull;
+    const int *pull_col;
+    void *local_x;    // this rank's x image of the step (the halo part is written)
+    int *my_ready;    // this rank's own counter, raised to `epoch` once the launch dependency is resolved
+    int *local_flag;  // raised to `epoch` when the whole halo has been fetched: what the halo tiles wait for
+};
+
+// Receiving side of the packet exchange: pkts[c - halo_start] holds x entry c of this rank's halo as {value, epoch}
+// (16 bytes for fp64 x: {lo, epoch, hi, epoch}; 8 bytes for fp32 x: {bits, epoch}).  pkts == nullptr: off.
+struct PacketRecv {
+    const void *pkts;
+    int halo_start;
 };
 
 // Chained products x_{k+1} = alpha * A * x_k ("the SpMV epilogue stores its y rows straight into the peers' x
@@ -189,6 +207,9 @@ struct rsg_context {
     int wait_n = 0, wait_epoch = 0;
     rsg::ChainPush chain = {};         // one-shot epilogue push for the next SpMV (rsg_dist_step_chain); npeers == 0: none
     const int *plan_send_pos = nullptr; // read when a window plan is built: marks producer tiles, orders boundary tiles first
+    unsigned long long *trace = nullptr; // rsg_debug_trace: per-CTA timestamps of the window kernel (debug; nullptr = off)
+    int trace_ctas = 0, trace_parity = 0;
+    rsg::PacketRecv packets = {nullptr, 0}; // one-shot: the next SpMV's halo tiles read their halo entries out of packets
     rsg::HaloFuse fuse = {};           // one-shot fused push for the next SpMV (rsg_spmv_halo_fuse); ctas == 0: none
     const void *persist_ptr = nullptr; // x currently covered by the L2 access-policy window
     size_t persist_bytes = 0;
@@ -249,6 +270,7 @@ int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split = false);
 
 // spmv_window.cu
 int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool strict);
+int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct); // where the halo tiles sit in the grid (see spmv_window.cu)
 template <typename TV, typename TX>
 int window_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 

@@ -609,6 +609,7 @@ int spmv_run(rsg_context *h, int m, int n, int nnz_hint, int base, const int *ro
     RSG_TRY(set_x_persistence(h, x, sizeof(TX) * (size_t)n));
     const bool vec = (((uintptr_t)colidx | (uintptr_t)values) & 15) == 0;
     if ((h->wait_flags || h->fuse.ctas) && p->algo != RSG_SPMV_TILE && p->algo != RSG_SPMV_WINDOW) { h->wait_flags = nullptr; h->fuse.ctas = 0; h->chain.npeers = 0; return RSG_UNSUPPORTED; }
+    if (h->packets.pkts && p->algo != RSG_SPMV_WINDOW) { h->packets.pkts = nullptr; h->wait_flags = nullptr; h->fuse.ctas = 0; return RSG_UNSUPPORTED; }
     if (h->chain.npeers > 0 && (p->algo != RSG_SPMV_WINDOW || p->wprod <= 0)) { h->wait_flags = nullptr; h->chain.npeers = 0; return RSG_UNSUPPORTED; }
     switch (p->algo) {
     case RSG_SPMV_ROWBLOCK:

@@ -147,6 +147,48 @@ __device__ __forceinline__ float ld_x_coherent(const float *p)
     return r;
 }
 
+// ---- packet exchange (rsg_dist_enable_packets): an x entry and the step number travel in ONE store, so an entry is usable the
+// moment it lands -- no fence, no counter, no flag hop between the data and its consumer (the protocol NCCL calls LL).
+// fp64: 16 bytes {lo, epoch, hi, epoch} (both halves checked: 8-byte atomicity suffices); fp32: 8 bytes {bits, epoch}.
+__device__ __forceinline__ void packet_store(void *base, int j, double v, int epoch)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    uint4 *p = static_cast<uint4 *>(base) + j;
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"((unsigned)b), "r"(epoch), "r"((unsigned)(b >> 32)), "r"(epoch) : "memory");
+}
+__device__ __forceinline__ void packet_store(void *base, int j, float v, int epoch)
+{
+    uint2 *p = static_cast<uint2 *>(base) + j;
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(epoch) : "memory");
+}
+// one poll: true when packet j carries `epoch` (or 0 = a column nobody writes: window padding), value in *v
+__device__ __forceinline__ bool packet_try(const void *base, int j, int epoch, double *v)
+{
+    unsigned a, b, c, d;
+    const uint4 *p = static_cast<const uint4 *>(base) + j;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(p) : "memory");
+    *v = __longlong_as_double((long long)(((unsigned long long)c << 32) | a));
+    return ((int)b == epoch && (int)d == epoch) || (b == 0u && d == 0u);
+}
+__device__ __forceinline__ bool packet_try(const void *base, int j, int epoch, float *v)
+{
+    unsigned a, b;
+    const uint2 *p = static_cast<const uint2 *>(base) + j;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(p) : "memory");
+    *v = __uint_as_float(a);
+    return (int)b == epoch || b == 0u;
+}
+template <typename TX> __device__ __forceinline__ TX packet_wait(const void *base, int j, int epoch, int *err_flag, int max_spins)
+{
+    TX v;
+    int spins = 0;
+    while (!packet_try(base, j, epoch, &v)) {
+        if (++spins >= max_spins) { if (err_flag) atomicExch(err_flag, 1); break; }
+        if (spins > 64) __nanosleep(spins > 4096 ? 400 : 40);
+    }
+    return v;
+}
+
 // The first `fuse.ctas` CTAs of a product's grid: store this rank's boundary entries of x into the peers' halo slots
 // (plain stores into P2P-mapped memory), then the last of them to finish releases `epoch` to the peers' flags.
 template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_push(const HaloFuse &fuse, const TX *__restrict__ x, int cta = -1)
@@ -182,10 +224,13 @@ template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_pu
 #pragma unroll 1
             for (int q = 0; q < fuse.npeers; ++q) {
                 TX *d = static_cast<TX *>(fuse.dst[q]);
-                if (d && j >= fuse.lo[q] && j < fuse.hi[q]) d[j] = v[u]; // each boundary entry only to the peers that read it
+                if (d && j >= fuse.lo[q] && j < fuse.hi[q]) { // each boundary entry only to the peers that read it
+                    if (fuse.packets) packet_store(fuse.dst[q], j, v[u], fuse.epoch); else d[j] = v[u];
+                }
             }
         }
     }
+    if (fuse.packets) return; // the epoch rode with every entry
     __threadfence_system(); // every thread: its own stores have reached the peers
     __syncthreads();
     if (tid == 0) {
@@ -197,6 +242,84 @@ template <typename TX, int THREADS> __device__ __forceinline__ void halo_fuse_pu
     if (s_last && tid < fuse.npeers && fuse.flag[tid]) {
         __threadfence_system();
         asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(fuse.flag[tid]), "r"(fuse.epoch) : "memory");
+    }
+}
+
+template <typename TX> __device__ __forceinline__ TX ld_remote(const TX *p);
+template <> __device__ __forceinline__ double ld_remote<double>(const double *p)
+{
+    double v;
+    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+template <> __device__ __forceinline__ float ld_remote<float>(const float *p)
+{
+    float v;
+    asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Pull exchange (rsg_dist_enable_pull): the first `fuse.ctas` CTAs of a product FETCH this rank's halo.  A remote store has
+// to be flushed through NVLink before the grid that issued it counts as complete (measured: the launch dependency of the
+// next product resolves 2-4.5 us after the last CTA instead of 1.2 us), and a fence behind remote stores costs 6-10 us while
+// the memory system is saturated; a remote LOAD is complete when its data is back.  So: CTA 0 raises this rank's own counter
+// ("my x of this step is final") once the launch dependency is resolved; every fetch CTA polls the neighbours' counters over
+// NVLink, loads its share of the entries from the owners' x and stores them into this rank's own image; the last one raises
+// the local flag the halo tiles wait for.  These CTAs do not wait for this rank's own launch dependency (they write only the
+// halo part of an image the product before does not read), so the fetch runs beside the tail of the previous product.
+template <typename TX, int THREADS>
+__device__ __forceinline__ void halo_pull(const HaloFuse &f, int *err_flag, int max_spins, int cta = -1)
+{
+    const int tid = threadIdx.x;
+    if (cta < 0) cta = blockIdx.x;
+    if (cta == 0) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        if (tid == 0 && f.my_ready) asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(f.my_ready), "r"(f.epoch) : "memory");
+    }
+    if (tid < f.npeers && f.flag[tid]) { // the neighbour's x of this step is final, and it is done with ours of two steps ago
+        int spins = 0, v;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(f.flag[tid]) : "memory");
+            if (v - f.epoch >= 0) break;
+            if (++spins >= max_spins) { if (err_flag) atomicExch(err_flag, 1); break; }
+            if (spins > 16) __nanosleep(spins > 1024 ? 400 : 100);
+        }
+    }
+    __syncthreads();
+    TX *xl = static_cast<TX *>(f.local_x);
+    const int stride = f.ctas * THREADS;
+    for (int k0 = cta * THREADS + tid; k0 < f.nsend; k0 += 4 * stride) {
+        const TX *src[4];
+        int col[4];
+        TX v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int k = k0 + u * stride;
+            src[u] = nullptr;
+            col[u] = -1;
+            if (k < f.nsend) {
+                col[u] = f.pull_col[k];
+                const int idx = f.send_idx[k];
+#pragma unroll 1
+                for (int q = 0; q < f.npeers; ++q)
+                    if (f.dst[q] && k >= f.lo[q] && k < f.hi[q]) src[u] = static_cast<const TX *>(f.dst[q]) + idx;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = src[u] ? ld_remote<TX>(src[u]) : (TX)0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (src[u]) xl[col[u]] = v[u];
+    }
+    __threadfence(); // device scope: the readers are this product's own halo tiles
+    __syncthreads();
+    if (tid == 0) {
+        const int done = atomicAdd(f.counter, 1);
+        if (done == f.ctas - 1) {
+            *f.counter = 0;
+            __threadfence();
+            asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(f.local_flag), "r"(f.epoch) : "memory");
+        }
     }
 }
 

@@ -141,10 +141,11 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
     // programmatic dependent launch, as in the window kernel: the next kernel of the stream may start once every CTA of
     // this grid is here; this grid reads only pattern data (descriptor, row pointers, colidx -- the plan is keyed on the
     // pattern) and, if promised static, the values before grid_dependency_wait()
-    grid_launch_dependents();
+    if (!(COH && fuse.pull) || (int)blockIdx.x < fuse.ctas) grid_launch_dependents(); // (pull exchange: see spmv_window.cu)
     if (COH && (int)blockIdx.x < fuse.ctas) {
         // ---- fused exchange: these CTAs are dispatched first; they publish this rank's boundary entries of x
         // to the peers (plain stores into P2P-mapped memory over NVLink) while the tiles behind them multiply
+        if (fuse.pull) { halo_pull<TX, THREADS>(fuse, err_flag, max_spins); return; }
         grid_dependency_wait();
         halo_fuse_push<TX, THREADS>(fuse, x);
         return;
@@ -154,6 +155,7 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
         // ---- one segment of a long row, straight from global memory with 128-bit loads; the last segment of the
         // row to arrive adds the partial sums in segment order and stores y
         grid_dependency_wait();
+        if (COH && fuse.pull) grid_launch_dependents();
         if (COH && wait_n > 0) { // a dense row may reach into the halo: its segments wait like a marked tile
             halo_flag_wait(wait_flags, wait_n, wait_epoch, err_flag, max_spins);
             __syncthreads();
@@ -204,6 +206,7 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
         }
     }
     grid_dependency_wait(); // x, y and (unless promised static) the values: what earlier work of the stream may have written
+    if (COH && fuse.pull) grid_launch_dependents();
     if (tid == 0 && mt.nr > 0 && qe > sb && !early_values)
         bulk_g2s(smem_raw + Stage::val_off, values + sb, (uint32_t)(qe - sb) * (uint32_t)sizeof(TV), &s_full, spol);
     if (must_wait) {

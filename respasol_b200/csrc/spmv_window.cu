@@ -48,7 +48,15 @@ struct WinArgs {
     const int *rp0;         // zero-based padded row pointers (absolute entry offsets)
     const uint16_t *widx;   // window-local column of entry k at widx[k - first8]
     int first8, nnz_end, n, ntiles;
+    unsigned long long *trace; // debug (rsg_debug_trace): 4 x %globaltimer per CTA -- entry, dependency resolved, data staged, done
 };
+
+__device__ __forceinline__ unsigned long long global_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 // -------------------------------------------------------------------------------- row reductions
 template <typename TV, typename TX>
@@ -94,11 +102,13 @@ __device__ __forceinline__ void win_rows(const TV *s_val, const uint16_t *s_idx,
 }
 
 // -------------------------------------------------------------------------------- the kernel
-template <typename TV, typename TX, int THREADS, int MINB>
+// PK: the instantiation whose halo tiles unpack {value, step} packets (rsg_dist_enable_packets); its eight-packets-in-flight loop
+// costs registers the single-GPU product must not pay (53 -> 86 would drop a resident CTA per SM), hence a separate one.
+template <typename TV, typename TX, int THREADS, int MINB, bool PK>
 __global__ void __launch_bounds__(THREADS, MINB)
 spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__restrict__ x, TX *__restrict__ y, TX alpha, TX beta,
                    int reduce_opt, int early_values, const int *wait_flags, int wait_n, int wait_epoch, int *err_flag, int max_spins,
-                   const HaloFuse fuse, const ChainPush chain)
+                   const HaloFuse fuse, const ChainPush chain, const PacketRecv pk)
 {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ __align__(16) int4 s_desc[kWinRecInt4];
@@ -109,10 +119,21 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     // everything up to grid_dependency_wait() below reads plan-owned, immutable data only (tile record, row pointers,
     // 16-bit columns -- and the values when the caller promised them static), so descriptor latency, the launch gap and
     // the ramp of a product hide behind the tail of the one before it.
-    grid_launch_dependents();
-    if ((int)blockIdx.x < fuse.ctas) { // fused exchange: publish this rank's boundary entries of x to the peers
+    // (pull exchange: the tiles trigger only once their own dependency is resolved -- the next product's fetch CTAs write the
+    // halo of the image the product BEFORE this one reads, so they must not start while that one may still be running)
+    if (!fuse.pull || (int)blockIdx.x < fuse.ctas) grid_launch_dependents();
+    unsigned long long *tr = w.trace ? w.trace + 4 * (size_t)blockIdx.x : nullptr;
+    if (tr && tid == 0) tr[0] = global_ns();
+    if ((int)blockIdx.x < fuse.ctas) { // fused exchange: publish this rank's boundary entries of x to the peers, or fetch theirs
+        if (fuse.pull) {
+            halo_pull<TX, THREADS>(fuse, err_flag, max_spins);
+            if (tr && tid == 0) tr[1] = tr[2] = tr[3] = global_ns();
+            return;
+        }
         grid_dependency_wait(); // x is what the work before this launch produced
+        if (tr && tid == 0) tr[1] = global_ns();
         halo_fuse_push<TX, THREADS>(fuse, x);
+        if (tr && tid == 0) tr[2] = tr[3] = global_ns();
         return;
     }
     const int tile = (int)blockIdx.x - fuse.ctas;
@@ -128,6 +149,9 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     const int nr = hd.z & 0xffff, nseg = (hd.z >> 16) & 0xff, flags = (hd.z >> 24) & 0xff;
     const int nk = hd.w & 0xffff, xtma = (int)((unsigned)hd.w >> 16);
     const bool must_wait = wait_n > 0 && ((flags & 1) || tile == w.ntiles - 1);
+    // packet exchange: the halo entries of this tile's x window are unpacked out of {value, epoch} packets by the CTA's
+    // threads (each polls the entries it copies); only the local part of the window is bulk-copied
+    const bool pk_tile = PK && pk.pkts != nullptr && (flags & 1);
     if (nr == 0 && !must_wait) return;
     const WinLayout L = win_layout(k0, nk, nr, xtma, (int)sizeof(TV), (int)sizeof(TX));
     TV *s_val = reinterpret_cast<TV *>(smem);
@@ -140,7 +164,15 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     const uint32_t nrp = (uint32_t)((rp_shift + nr + 1 + 3) & ~3);
     if (tid == 0 && nr > 0) {
         const uint64_t spol = make_evict_first_policy();
-        mbar_expect_tx(&s_bar, nrp * 4u + nstage * (uint32_t)(sizeof(TV) + 2) + (uint32_t)xtma * (uint32_t)sizeof(TX));
+        int xcopied = xtma;
+        if (pk_tile) { // what the bulk copies will NOT bring: the part of every segment at or beyond halo_start
+            for (int j = 0; j < nseg; ++j) {
+                const int4 q = s_desc[1 + (j >> 1)];
+                const int st = (j & 1) ? q.z : q.x, len = (int)((unsigned)((j & 1) ? q.w : q.y) & 0xffffu);
+                xcopied -= max(0, st + len - max(st, pk.halo_start));
+            }
+        }
+        mbar_expect_tx(&s_bar, nrp * 4u + nstage * (uint32_t)(sizeof(TV) + 2) + (uint32_t)xcopied * (uint32_t)sizeof(TX));
         bulk_g2s(smem + L.o_rp, w.rp0 + ra, nrp * 4u, &s_bar, spol);
         if (nstage) {
             bulk_g2s(s_idx, w.widx + (sb - w.first8), nstage * 2u, &s_bar, spol);
@@ -148,6 +180,8 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
         }
     }
     grid_dependency_wait(); // from here on: x, y and (unless promised static) the values -- what earlier work may have written
+    if (fuse.pull) grid_launch_dependents();
+    if (tr && tid == 0) tr[1] = global_ns();
     if (tid == 0 && nr > 0 && nstage && !early_values)
         bulk_g2s(s_val, values + sb, nstage * (uint32_t)sizeof(TV), &s_bar, make_evict_first_policy());
     if (must_wait) {
@@ -159,11 +193,42 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     }
     if (tid >= 1 && tid < kWinRecInt4) { // seven threads issue two x segments each
         const uint64_t xpol = make_evict_last_policy();
-        const unsigned l0 = (unsigned)d.y & 0xffffu, l1 = (unsigned)d.w & 0xffffu;
+        unsigned l0 = (unsigned)d.y & 0xffffu, l1 = (unsigned)d.w & 0xffffu;
+        if (pk_tile) { // halo_start is a multiple of 32 entries: the cut keeps every copy a multiple of 16 bytes
+            l0 = (unsigned)max(0, min((int)l0, pk.halo_start - d.x));
+            l1 = (unsigned)max(0, min((int)l1, pk.halo_start - d.z));
+        }
         if (l0) bulk_g2s(s_x + ((unsigned)d.y >> 16), x + d.x, l0 * (uint32_t)sizeof(TX), &s_bar, xpol);
         if (l1) bulk_g2s(s_x + ((unsigned)d.w >> 16), x + d.z, l1 * (uint32_t)sizeof(TX), &s_bar, xpol);
     }
     bool wrote = false;
+    if (pk_tile) {
+        // four packets per thread in flight at once (a poll is a round trip to L2); stragglers are re-polled one by one.
+        // (All segments as one index space, eight in flight, measured slower: 18.7 vs 16.0 us per step at 8 M entries per rank.)
+        for (int j = 0; j < nseg; ++j) {
+            const int4 q = s_desc[1 + (j >> 1)];
+            const int st = (j & 1) ? q.z : q.x;
+            const unsigned lo = (unsigned)((j & 1) ? q.w : q.y);
+            const int len = (int)(lo & 0xffffu), off = (int)(lo >> 16);
+            for (int c0 = max(st, pk.halo_start) + tid; c0 < st + len; c0 += 4 * THREADS) {
+                TX v[4];
+                bool ok[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int c = c0 + u * THREADS;
+                    ok[u] = c >= st + len || packet_try(pk.pkts, c - pk.halo_start, wait_epoch, &v[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int c = c0 + u * THREADS;
+                    if (c >= st + len) continue;
+                    if (!ok[u]) v[u] = packet_wait<TX>(pk.pkts, c - pk.halo_start, wait_epoch, err_flag, max_spins);
+                    s_x[off + (c - st)] = v[u];
+                }
+            }
+        }
+        wrote = true;
+    }
     if (qe < k1) { // last tile of a matrix whose entry count is not a multiple of 8: < 8 entries by plain loads
         const int k = qe + tid;
         if (tid < 8 && k < k1) { s_val[k - sb] = values[k]; s_idx[k - sb] = w.widx[k - w.first8]; }
@@ -174,11 +239,15 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
         const int4 q = s_desc[1 + (j >> 1)];
         const unsigned lo = (unsigned)((j & 1) ? q.w : q.y);
         const int n4 = w.n & ~3;
-        if (tid < w.n - n4) s_x[(lo >> 16) + (lo & 0xffffu) + tid] = x[n4 + tid];
+        if (tid < w.n - n4)
+            s_x[(lo >> 16) + (lo & 0xffffu) + tid] = (pk_tile && n4 + tid >= pk.halo_start)
+                                                         ? packet_wait<TX>(pk.pkts, n4 + tid - pk.halo_start, wait_epoch, err_flag, max_spins)
+                                                         : x[n4 + tid];
         wrote = true;
     }
     if (wrote) __syncthreads();
     mbar_wait(&s_bar, 0);
+    if (tr && tid == 0) tr[2] = global_ns();
     const int *rp = reinterpret_cast<const int *>(smem + L.o_rp) + rp_shift;
     int g = reduce_opt & 0xff;
     if (g == 0) { // lanes per row from the tile's row lengths
@@ -196,6 +265,7 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     case 16: win_rows<TV, TX, THREADS, 16>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
     default: win_rows<TV, TX, THREADS, 32>(s_val, s_idx, s_x, rp, sb, nr, r0, y, alpha, beta); break;
     }
+    if (tr && tid == 0) tr[3] = global_ns() | ((unsigned long long)(flags & 1) << 63);
     if (chain.npeers > 0 && (flags & 4)) {
         // chained products: this tile owns rows a neighbour reads -- their y goes straight into the neighbours' halo slots of
         // the next x image; the last producer tile to finish releases the step number to the neighbours' flags
@@ -455,7 +525,9 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     p.wthreads = threads;
     p.wprod = h->plan_send_pos ? h->pinned_i[35] : 0;
     const bool chained = h->plan_send_pos != nullptr;
-    if ((p.whalo > 0 && p.whalo < p.nblk) || (chained && p.wprod > 0 && p.wprod < p.nblk)) {
+    if (!chained && p.whalo > 0 && p.whalo < p.nblk) {
+        RSG_TRY(window_place_halo(h, p, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 100));
+    } else if (chained && p.wprod > 0 && p.wprod < p.nblk) {
         // multi-GPU tile order (records are self-contained, so the order is free; done once, on the host, stable on both sides).
         // Separate products (the push precedes the product): tiles that read a peer's entries go to the END of the grid -- by
         // the time they are dispatched the neighbours' pushes have landed.  Chained products: boundary tiles (halo readers
@@ -477,15 +549,62 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     return RSG_OK;
 }
 
+// Where the tiles that read a peer's entries sit in the grid (records are self-contained, so the order is free; host side,
+// once).  They must not come first (their data is still on its way when the product starts: they would hold SM slots idle),
+// and they should not be the very last either: a tile that polls for its halo lives longer than an interior tile, and the
+// last tiles of a grid are the critical path into the next launch.  start_pct = share of the grid that is interior tiles
+// before the first halo tile; from there halo and interior tiles alternate evenly, and the last wave is interior again.
+// start_pct >= 100: all halo tiles at the end (the order the arrival-flag exchange was measured with).
+int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct)
+{
+    if (p.whalo <= 0 || p.whalo >= p.nblk) return RSG_OK;
+    std::vector<int4> rec((size_t)p.nblk * kWinRecInt4), out((size_t)p.nblk * kWinRecInt4);
+    RSG_CUDA_TRY(cudaMemcpy(rec.data(), p.wdesc, sizeof(int4) * rec.size(), cudaMemcpyDeviceToHost));
+    std::vector<int> in, ha;
+    for (int b = 0; b < p.nblk; ++b) {
+        const int fl = (rec[(size_t)b * kWinRecInt4].z >> 24) & 0xff;
+        ((fl & 1) ? ha : in).push_back(b);
+    }
+    std::sort(in.begin(), in.end(), [&](int a, int b) { return rec[(size_t)a * kWinRecInt4].x < rec[(size_t)b * kWinRecInt4].x; }); // by first row
+    std::sort(ha.begin(), ha.end(), [&](int a, int b) { return rec[(size_t)a * kWinRecInt4].x < rec[(size_t)b * kWinRecInt4].x; });
+    std::vector<int> order;
+    order.reserve((size_t)p.nblk);
+    const int ni = (int)in.size(), nh = (int)ha.size();
+    if (start_pct >= 100) {
+        order = in;
+        order.insert(order.end(), ha.begin(), ha.end());
+    } else {
+        int tail = std::min(ni / 4, 6 * h->sm_count);
+        const int end_pct = h->opts[RSG_OPT_SPMV_HALO_END];
+        if (end_pct > 0 && end_pct < 100) tail = std::min(ni, std::max(tail, (int)((long long)p.nblk * (100 - end_pct) / 100)));
+        const int head = std::min(ni - tail, (int)((long long)p.nblk * std::max(start_pct, 0) / 100));
+        const int mid = ni - tail - head; // interior tiles that alternate with the halo tiles
+        for (int i = 0; i < head; ++i) order.push_back(in[(size_t)i]);
+        int ii = 0, hh = 0;
+        while (ii < mid || hh < nh) { // even merge: after k of the (mid + nh) slots, about k * nh / (mid + nh) halo tiles are out
+            const long long k = ii + hh + 1;
+            if (hh < nh && (ii >= mid || (long long)hh * (mid + nh) < k * nh)) order.push_back(ha[(size_t)hh++]);
+            else order.push_back(in[(size_t)(head + ii++)]);
+        }
+        for (int i = head + mid; i < ni; ++i) order.push_back(in[(size_t)i]);
+    }
+    for (int b = 0; b < p.nblk; ++b) std::copy_n(rec.begin() + (size_t)order[(size_t)b] * kWinRecInt4, kWinRecInt4, out.begin() + (size_t)b * kWinRecInt4);
+    RSG_CUDA_TRY(cudaMemcpy(p.wdesc, out.data(), sizeof(int4) * out.size(), cudaMemcpyHostToDevice));
+    return RSG_OK;
+}
+
 template <typename TV, typename TX, int THREADS>
 static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y)
 {
     constexpr int MINB = THREADS >= 256 ? 2 : 4;
-    auto kern = spmv_window_kernel<TV, TX, THREADS, MINB>;
+    auto kern_plain = spmv_window_kernel<TV, TX, THREADS, MINB, false>;
+    auto kern_pk = spmv_window_kernel<TV, TX, THREADS, MINB, true>;
     static PerDeviceOnce configured; // function attributes are per device (and per instantiation)
     if (configured.need(h->device)) {
-        RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, std::min(h->max_smem_optin - 1024, 200 * 1024)));
-        RSG_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern_plain, cudaFuncAttributeMaxDynamicSharedMemorySize, std::min(h->max_smem_optin - 1024, 200 * 1024)));
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern_plain, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern_pk, cudaFuncAttributeMaxDynamicSharedMemorySize, std::min(h->max_smem_optin - 1024, 200 * 1024)));
+        RSG_CUDA_TRY(cudaFuncSetAttribute(kern_pk, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     }
     HaloFuse fuse = h->fuse;
     // four boundary entries per thread, issued together: the push is a chain of two dependent loads and a remote store per
@@ -495,7 +614,14 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
     ChainPush chain = h->chain;
     if (chain.npeers > 0) chain.nprod = p->wprod;
     h->chain.npeers = 0; // one-shot
-    WinArgs w = {p->wdesc, p->rp0, p->widx, p->first8, p->first + p->nnz, p->n, p->nblk};
+    const PacketRecv pk = h->packets;
+    h->packets.pkts = nullptr; // one-shot
+    WinArgs w = {p->wdesc, p->rp0, p->widx, p->first8, p->first + p->nnz, p->n, p->nblk,
+                 nullptr};
+    if (h->trace && h->trace_ctas >= p->nblk + fuse.ctas) { // two halves, used in turn: consecutive launches overlap
+        w.trace = h->trace + (size_t)(h->trace_parity & 1) * 4 * (size_t)h->trace_ctas;
+        h->trace_parity ^= 1;
+    }
     // RSG_OPT_SPMV_PDL: 0 = programmatic dependent launch, plan data only ahead of the dependency; 1 = plain launch;
     // 2 = the values too (the caller promises that nothing queued before the product writes them)
     int pdl = h->opts[RSG_OPT_SPMV_PDL];
@@ -513,8 +639,8 @@ static int window_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl != 1 ? 1 : 0;
-    RSG_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, w, values, x, y, alpha, beta, h->opts[RSG_OPT_SPMV_REDUCE], pdl == 2 ? 1 : 0, h->wait_flags,
-                                    h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse, chain));
+    RSG_CUDA_TRY(cudaLaunchKernelEx(&cfg, pk.pkts ? kern_pk : kern_plain, w, values, x, y, alpha, beta, h->opts[RSG_OPT_SPMV_REDUCE], pdl == 2 ? 1 : 0, h->wait_flags,
+                                    h->wait_flags ? h->wait_n : 0, h->wait_epoch, h->err_flag, wait_spins(h), fuse, chain, pk));
     h->wait_flags = nullptr; // one-shot
     h->fuse.ctas = 0;
     h->launches++;

@@ -105,6 +105,8 @@ class HaloPlan:
         # A rank signals and awaits exactly its neighbours -- enough to keep it within one step of each of them.
         reads = [[o for o in range(P) if o != q and np.any((nb >= rs[o]) & (nb < rs[o + 1]))] for q, nb in enumerate(needs_by_rank)]
         self.neighbours = [sorted(set(reads[q]) | {o for o in range(P) if q in reads[o]}) for q in range(P)]
+        # every rank reads from every rank it sends to (and reads from somebody): what the packet exchange needs
+        self.symmetric = all(len(reads[q]) > 0 and all(q in reads[o] for o in reads[q]) for q in range(P))
         self.interior = self._interior_run(a, off)
         return self
 
@@ -127,8 +129,14 @@ class RowBlockSpmv:
     """y_local = A_local * x, x distributed by rows.  `upload(csr)` and `spmv(A, x_ext, y)` are injected so
     the same exchange logic runs on the GPU (libreaspasol_gpu through Handle) and in the gloo CPU tests."""
 
-    def __init__(self, local: CSR, row_starts, mode, upload, spmv, device, dtype, group=None, view=None, push=None, side=None):
+    def __init__(self, local: CSR, row_starts, mode, upload, spmv, device, dtype, group=None, view=None, push=None, side=None,
+                 packets=False, proto=None):
         self.group = group
+        # exchange protocol of the rsg_dist mode: "packets" ({value, step} packets pushed by a small kernel on a side stream and
+        # unpacked by the halo tiles; symmetric patterns on the window kernel, otherwise the flags stay), "packets-fused" (the
+        # product's first CTAs push them), "pull" (the product's first CTAs fetch the halo), "flags" (push + fence + arrival flags)
+        self.proto = proto if proto is not None else "packets"
+        self.use_packets = self.proto in ("packets", "packets-fused")
         self.split = None
         self.p2p = None
         self.side = side  # p2p: the stream the push kernels run on (the caller binds its push handle to it)
@@ -209,7 +217,7 @@ class RowBlockSpmv:
         # arrival flags: image p, one int per NEIGHBOUR (slot = the sender's position in the receiver's list).
         # A rank signals all its neighbours, data or not, and awaits all of them, so it can never run more
         # than one step ahead of a rank it exchanges entries with -- the two images are enough
-        fl = symm_mem.empty(nimg * 32, dtype=torch.int32, device=device)
+        fl = symm_mem.empty(nimg * 32 + 32, dtype=torch.int32, device=device)  # (+32: pull exchange: ready counter, 2 local flags)
         fl.zero_()
         self.symm_flags = symm_mem.rendezvous(fl, group)
         self.flags = fl
@@ -259,6 +267,52 @@ class RowBlockSpmv:
                                          raw_slots, raw_flags, [r[0] for r in plan.send_range], [r[1] for r in plan.send_range],
                                          [v.data_ptr() for v in self.flag_views], self.n_wait)
             self.cdist_step = hnd.dist_step
+            self.pull = False
+            if self.proto == "pull":
+                # pull exchange (rsg_dist_enable_pull): entries this rank reads, grouped by owner
+                rs = self.row_starts
+                cols, idxs, lo, hi = [], [], [], []
+                n = 0
+                for o in range(self.P):
+                    lo.append(n)
+                    if o != self.rank:
+                        mine = plan.need[(plan.need >= rs[o]) & (plan.need < rs[o + 1])] - rs[o]
+                        pos = np.searchsorted(plan.send_idx[o], mine)
+                        cols.append(plan.halo_base + o * plan.width + pos)
+                        idxs.append(mine)
+                        n += len(mine)
+                    hi.append(n)
+                self.pull_col = torch.from_numpy(np.concatenate(cols).astype(np.int32) if cols else np.zeros(0, np.int32)).to(device)
+                self.pull_idx = torch.from_numpy(np.concatenate(idxs).astype(np.int32) if idxs else np.zeros(0, np.int32)).to(device)
+                base = nimg * 32
+                peer_x = [[(ptrs[q] + p * stride * esz) if hi[q] > lo[q] else 0 for q in range(self.P)] for p in range(2)]
+                peer_ready = [(fptrs[q] + 4 * base) if q in nb[self.rank] else 0 for q in range(self.P)]
+                ok = hnd.dist_enable_pull(self.cdist, self.pull_col, self.pull_idx, peer_x, peer_ready, lo, hi,
+                                          self.flags[base:].data_ptr(), self.flags[base + 1:].data_ptr())
+                agree = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+                dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=self.group)
+                assert int(agree.item()) == 1 or not ok, "pull exchange enabled on some ranks only"
+                self.pull = bool(ok)
+            # packet exchange (rsg_dist_enable_packets): {value, step} packets instead of data + fence + counter + flag
+            self.packets = False
+            if self.use_packets and plan.symmetric:
+                per_image = self.P * plan.width
+                pk = symm_mem.empty(2 * per_image * 2, dtype=dtype, device=device)  # a packet = 2 elements
+                pk.zero_()
+                self.symm_pk = symm_mem.rendezvous(pk, group)
+                self.pk = pk
+                pptrs = list(self.symm_pk.buffer_ptrs)
+                pb = 2 * esz
+                raw_pk = [[(pptrs[q] + pb * (p * per_image + self.rank * plan.width)) if q in plan.readers else 0
+                           for q in range(self.P)] for p in range(2)]
+                mine = [pk.data_ptr() + pb * p * per_image for p in range(2)]
+                ok = hnd.dist_enable_packets(self.cdist, mine, raw_pk, side_stream=self.proto == "packets")
+                agree = torch.tensor([1 if ok else 0], dtype=torch.int32, device=device)
+                dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=self.group)
+                if int(agree.item()) == 1:
+                    self.packets = True
+                elif ok:  # some rank's block is not a window plan: everybody back to the flags
+                    hnd.dist_enable_packets(self.cdist, None, None)
         torch.cuda.synchronize(device)
         self.symm.barrier(channel=0)
 
@@ -298,7 +352,15 @@ class RowBlockSpmv:
                     "into the neighbour's halo slots of the next x image over NVLink and the last of them signals; the next product's "
                     "halo tiles acquire the flags before they copy x; three x images rotate; ONE launch per step, no separate exchange")
         elif self.p2p is not None:
-            how = ("FUSED into the SpMV launch (rsg_dist_step: the product's first CTAs push this rank's boundary entries into the "
+            how = ("FETCHED by the SpMV launch itself (rsg_dist_step after rsg_dist_enable_pull: the product's first CTAs poll the "
+                   "neighbours' step counters over NVLink, load this rank's halo entries from the owners' x and raise a local flag the "
+                   "halo tiles wait for; the product contains no remote store)" if getattr(self, "pull", False) else
+                   "as {value, step} PACKETS (rsg_dist_step after rsg_dist_enable_packets: one call = a small push kernel on a side stream "
+                   "that stores every boundary entry with the step number in one 16-byte store into the readers' packet buffers, and "
+                   "the product, whose halo tiles unpack their x window out of the packets, polling the step number inside each "
+                   "entry -- no fence, counter or flag, no remote store inside the product)" if getattr(self, "packets", False) and self.proto == "packets" else
+                   "FUSED into the SpMV launch as {value, step} PACKETS (the product's first CTAs push them)" if getattr(self, "packets", False) else
+                   "FUSED into the SpMV launch (rsg_dist_step: the product's first CTAs push this rank's boundary entries into the "
                    "readers' halo slots and signal, its halo tiles await the neighbours' flags before they copy x)"
                    if len(self.p2p) > 2 else "rsg_halo_push on a side stream, arrival flags awaited inside the product's halo tiles"
                    if self.p2p[1] else "rsg_halo_push + symmetric-memory barrier")
@@ -310,7 +372,7 @@ class RowBlockSpmv:
         if self.split:
             mode += "; exchange on a side stream overlapped with the %d interior rows, boundary rows follow" % self.interior_rows
         return {"mode": mode, "bytes_received_per_rank_per_step": int(self.exchange_bytes),
-                "neighbours": int(getattr(self, "n_wait", 0))}
+                "neighbours": int(getattr(self, "n_wait", 0)), "protocol": "pull" if getattr(self, "pull", False) else "packets" if getattr(self, "packets", False) else "flags"}
 
     def set_x(self, x_local):
         """x_local: this rank's slice of x (device tensor)."""

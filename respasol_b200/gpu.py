@@ -16,7 +16,7 @@ OPT = dict(SPMV_ALGO=0, SPMV_REDUCE=1, SPMV_LONG_ROW=2, SPMV_VARIANT=3, SPMV_CAC
            TRSV_ALGO=5, ILU0_ALGO=6, SPMV_X_PERSIST=7, SPMV_X_HINT=8,
            SPMV_ROWS_PER_THREAD=9, SPMV_CTAS_PER_SM=10, TRSV_BATCH=11, TRSV_GATE=12,
            TRI_CTAS_PER_SM=13, TRSV_BLOCK=14, SPMV_HALO_START=15, HOST_CHUNKS=16, HOST_Y_DIRECT=17, HOST_GRAPH=18, TRANSPOSE_STATIC=19,
-           SPMV_WIN_BYTES=20, SPMV_WIN_STREAM_PCT=21, SPMV_WIN_GAP=22, WAIT_SPINS=23, SPMV_PDL=24)
+           SPMV_WIN_BYTES=20, SPMV_WIN_STREAM_PCT=21, SPMV_WIN_GAP=22, WAIT_SPINS=23, SPMV_PDL=24, SPMV_HALO_PLACE=25, SPMV_HALO_END=26)
 ALGO = dict(auto=0, rowblock=1, merge=2, vector=3, scalar=4, stream=5, pipe=6, tile=7, window=8)
 INFO = dict(KERNEL_LAUNCHES=0, SPMV_ALGO_USED=1, SPMV_ROW_BLOCKS=2, SPMV_MAX_ROW=3, LEVELS_L=4, LEVELS_U=5,
             SM_COUNT=6, WORKSPACE_BYTES=7)
@@ -232,6 +232,30 @@ class Handle:
 
     def dist_step(self, d, y):
         _check(self.lib.rsg_dist_step(d, self._p(y)), "rsg_dist_step")
+
+    def dist_enable_packets(self, d, local_packets, peer_packets, side_stream=True):
+        """rsg_dist_enable_packets: local_packets = the 2 images' device addresses, peer_packets = [image][peer] (0 = NULL).
+        Returns False when the block's plan is not the window kernel's (the flags stay)."""
+        if local_packets is None:  # back to the arrival flags
+            _check(self.lib.rsg_dist_enable_packets(d, None, None, 0), "rsg_dist_enable_packets")
+            return False
+        mine = self.ptr_array(local_packets)
+        peers = self.ptr_array([p for img in peer_packets for p in img])
+        rc = _check(self.lib.rsg_dist_enable_packets(d, mine, peers, 1 if side_stream else 0), "rsg_dist_enable_packets", allow=(8,))
+        return rc == OK
+
+    def dist_enable_pull(self, d, pull_col, pull_idx, peer_x, peer_ready, owner_lo, owner_hi, my_ready, local_flags):
+        """rsg_dist_enable_pull: peer_x = [image][peer] device addresses (0 = NULL), peer_ready = [peer]; my_ready / local_flags
+        device addresses.  Returns False when the block runs a gather kernel (the flags stay)."""
+        npeers = len(peer_ready)
+        px = self.ptr_array([p for img in peer_x for p in img])
+        pr = self.ptr_array(peer_ready)
+        lo = (C.c_int * npeers)(*[int(v) for v in owner_lo])
+        hi = (C.c_int * npeers)(*[int(v) for v in owner_hi])
+        rc = _check(self.lib.rsg_dist_enable_pull(d, int(pull_col.numel()), self._p(pull_col), self._p(pull_idx), npeers, px, pr, lo, hi,
+                                                  C.c_void_p(int(my_ready)), C.c_void_p(int(local_flags))),
+                    "rsg_dist_enable_pull", allow=(8,))
+        return rc == OK
 
     def dist_destroy(self, d):
         _check(self.lib.rsg_dist_destroy(d), "rsg_dist_destroy")

@@ -72,8 +72,9 @@ def test_multi_gpu_product_matches_the_oracle(ngpu, precision):
             assert np.abs(y.astype(np.float64) - ref.astype(np.float64)).max() <= (5e-5 if precision == "s" else 1e-12) * np.abs(ref).max()
 
 
+@pytest.mark.parametrize("proto", ["pull", "packets", "flags"])
 @pytest.mark.parametrize("ngpu", [2, 4])
-def test_multi_gpu_one_directional_pattern_and_changing_x(ngpu):
+def test_multi_gpu_one_directional_pattern_and_changing_x(ngpu, proto, monkeypatch):
     """An upwind (lower-bidiagonal-by-planes) pattern: rank r reads only from rank r-1, so rank 0 feeds a neighbour but
     reads nothing -- it must still not run ahead (its last tile awaits the flags).  x changes between steps, so a stale
     or early halo would show."""
@@ -86,10 +87,14 @@ def test_multi_gpu_one_directional_pattern_and_changing_x(ngpu):
     rp[1:] = np.cumsum(lens)
     ci = np.concatenate([[r] if r < band else [r - band, r] for r in range(n)]).astype(np.int32)
     a = host.CSR(n, n, int(rp[-1]), rp, ci, np.random.default_rng(1).uniform(0.5, 1.5, int(rp[-1])), 0)
+    monkeypatch.setenv("RSG_DIST_EXCHANGE", proto)
     lib = gpu_lib()
     M = C.c_void_p()
     assert lib.rsg_spmv_multi_create(ngpu, None, b"d", n, n, a.stored, 0, rp.ctypes.data, ci.ctypes.data, a.values.ctypes.data, None, C.byref(M)) == 0
     try:
+        v = C.c_longlong(-1)
+        # packets need a mutual pattern (the arrival flags stay); pull and flags take any
+        assert lib.rsg_spmv_multi_info(M, 4, C.byref(v), None) == 0 and v.value == {"pull": 2, "packets": 0, "flags": 0}[proto]  # (packets: not mutual)
         y = np.zeros(n)
         for it in range(6):
             x = orc.dlarnv(n) + it
@@ -99,6 +104,46 @@ def test_multi_gpu_one_directional_pattern_and_changing_x(ngpu):
             assert np.array_equal(y, orc.spmv(a, x, "d")), it
     finally:
         lib.rsg_spmv_multi_destroy(M)
+
+
+@pytest.mark.parametrize("proto", ["pull", "packets", "packets-fused", "flags"])
+@pytest.mark.parametrize("ngpu", [2, 4, 8])
+def test_multi_gpu_exchange_protocols_changing_x(ngpu, proto, monkeypatch):
+    """The three exchange protocols of rsg_spmv_multi_* on symmetric patterns: pull (the product's first CTAs fetch the halo --
+    rsg_dist_enable_pull, the default), {value, step} packets unpacked by the halo tiles (rsg_dist_enable_packets) and push +
+    arrival flags.  x changes every step and many steps run back to back, so a stale entry (the image of two steps ago), a
+    torn packet or an early read would show; fp64 bit-exact."""
+    if ndev() < ngpu:
+        pytest.skip("needs %d devices" % ngpu)
+    monkeypatch.setenv("RSG_DIST_EXCHANGE", proto)
+    packets = {"flags": 0, "packets": 1, "packets-fused": 1, "pull": 2}[proto]
+    lib = gpu_lib()
+    for a, prec in ((host.gen_stencil27(30, 30, 48, seed=2), "d"), (host.gen_laplace2d(301), "d"), (host.gen_stencil27(20, 20, 40, seed=5), "s")):
+        M = C.c_void_p()
+        assert lib.rsg_spmv_multi_create(ngpu, None, prec.encode(), a.m, a.n, a.stored, a.base, a.rowptr.ctypes.data, a.colidx.ctypes.data,
+                                         np.ascontiguousarray(a.values, dtype=np.float64).ctypes.data, None, C.byref(M)) == 0
+        try:
+            v = C.c_longlong(-1)
+            assert lib.rsg_spmv_multi_info(M, 4, C.byref(v), None) == 0 and v.value == packets
+            xt = np.float64 if prec == "d" else np.float32
+            y = np.zeros(a.m, dtype=xt)
+            for it in range(5):
+                x = np.ascontiguousarray(orc.dlarnv(a.n) - 0.5 + 0.25 * it, dtype=xt)
+                assert lib.rsg_spmv_multi_set_x(M, x.ctypes.data) == 0
+                assert lib.rsg_spmv_multi_step(M, 1 + 2 * it) == 0   # odd and even step counts: both images, epochs far apart
+                assert lib.rsg_spmv_multi_get_y(M, y.ctypes.data) == 0
+                ref = orc.spmv(a, x.astype(np.float64), prec)
+                if prec == "d":
+                    assert np.array_equal(y, ref), (it, packets)
+                else:
+                    assert np.abs(y.astype(np.float64) - ref.astype(np.float64)).max() <= 5e-5 * np.abs(ref).max()
+            us = C.c_double(0)
+            assert lib.rsg_spmv_multi_time(M, 50, C.byref(us)) == 0 and us.value > 0
+            assert lib.rsg_spmv_multi_get_y(M, y.ctypes.data) == 0
+            if prec == "d":
+                assert np.array_equal(y, ref)
+        finally:
+            assert lib.rsg_spmv_multi_destroy(M) == 0
 
 
 @pytest.mark.parametrize("ngpu", [1, 2])

@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--combos", default="")
     ap.add_argument("--modes", default="full,plain,fuse_only,wait_only")
+    ap.add_argument("--proto", default="packets", choices=["pull", "packets", "packets-fused", "flags"])
+    ap.add_argument("--packets", type=int, default=1, help="1: {value, step} packet exchange (rsg_dist_enable_packets); 0: arrival flags")
     args = ap.parse_args()
     world, rank, lr = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
@@ -49,7 +51,7 @@ def main():
         ops = []
         for _ in range(2):
             op = RowBlockSpmv(a, starts, "p2p", lambda c: DeviceCSR(c, "d", dev), lambda A, x, y: h.spmv(A, x, y), dev, torch.float64,
-                              push=(hp.halo_push, h.spmv_halo_wait, h.spmv_halo_fuse))
+                              push=(hp.halo_push, h.spmv_halo_wait, h.spmv_halo_fuse), proto=args.proto)
             op.set_x(torch.from_numpy(np.ascontiguousarray(xg[starts[rank]:starts[rank + 1]])).to(dev))
             ops.append(op)
         for i in range(10):
@@ -101,7 +103,7 @@ def main():
         ok = bool(np.array_equal(ops[0].y.cpu().numpy(), ref))
         if rank == 0:
             print(json.dumps({"world": world, "planes": args.planes, "opts": spec, "us_per_step": round(best, 2), "rows": a.m, "stored": a.stored,
-                              "tiles": h.info("SPMV_ROW_BLOCKS"), "algo": h.info("SPMV_ALGO_USED"), "bit_exact": ok, "modes": res}), flush=True)
+                              "tiles": h.info("SPMV_ROW_BLOCKS"), "algo": h.info("SPMV_ALGO_USED"), "bit_exact": ok, "proto": ops[0].describe()["protocol"], "modes": res}), flush=True)
         del ops
         dist.barrier()
     dist.barrier()
