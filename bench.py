@@ -929,7 +929,7 @@ def main():
     ap.add_argument("--overlap", action="store_true", help="N>1: exchange on a side stream while the interior rows are multiplied")
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "p2p-side", "p2p-barrier", "nccl"], help="N>1: x-halo exchange: peer-memory push or NCCL all-gather")
     ap.add_argument("--pdl", type=int, default=2, choices=[0, 1, 2], help="RSG_OPT_SPMV_PDL for the timed products (2 = matrix values promised static)")
-    ap.add_argument("--proto", default="packets", choices=["pull", "packets", "packets-fused", "flags"],
+    ap.add_argument("--proto", default="auto", choices=["auto", "pull", "packets", "packets-fused", "flags"],
                     help="N>1, fused exchange: pull = the product's first CTAs fetch the halo (no remote store in the product); "
                          "packets = {value, step} packets pushed and unpacked by the halo tiles; flags = push + fence + arrival flags")
     ap.add_argument("--mode", default="separate", choices=["chain", "separate"],

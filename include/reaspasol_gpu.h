@@ -110,7 +110,7 @@ typedef enum {
                                    50 timed products, spmv.cu:174-207); 1 = plain launches */
     RSG_OPT_SPMV_HALO_PLACE = 25, /* multi-GPU window plans: share of the grid (percent) that is interior tiles before the first tile
                                    that reads a peer's entries; from there the two kinds alternate, the last wave is interior again.
-                                   0 = default (packet exchange: 35; arrival flags: 100 = all such tiles at the end).  Read when the
+                                   0 = default (packet exchange: 20, ending at 60; arrival flags: 100 = all such tiles at the end).  Read when the
                                    plan is built and by rsg_dist_enable_packets; not part of the plan's key */
     RSG_OPT_SPMV_HALO_END = 26,  /* the same plans: share of the grid (percent) by which the last such tile has been placed (0 = default:
                                    all but the last wave) */

@@ -199,7 +199,7 @@ int rsg_dist_enable_packets(rsg_dist_t d, void *const *local_packets, void *cons
         DevGuard g0(h->device);
         SpmvPlan *pl0 = nullptr;
         RSG_TRY(dist_plan(d, &pl0));
-        if (pl0 && pl0->algo == RSG_SPMV_WINDOW) RSG_TRY(window_place_halo(h, *pl0, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 100));
+        if (pl0 && pl0->algo == RSG_SPMV_WINDOW) RSG_TRY(window_place_halo(h, *pl0, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 100, 0));
         return RSG_OK;
     }
     if (d->packets || !local_packets[0] || !local_packets[1] || d->halo_start <= 0) return RSG_BAD_ARG;
@@ -220,7 +220,8 @@ int rsg_dist_enable_packets(rsg_dist_t d, void *const *local_packets, void *cons
     }
     // halo tiles no longer wait for a flag that trails the data: they can sit in the middle of the grid, and the last wave
     // (the critical path into the next launch) is interior tiles
-    if (pl) RSG_TRY(window_place_halo(h, *pl, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 35));
+    // (probe, 8 M entries per rank: 20 % .. 60 % of the grid 15.84-15.87 us, 35 % .. last wave 16.0-16.2, all at the end 20.2)
+    if (pl) RSG_TRY(window_place_halo(h, *pl, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 20, 60));
     for (int p = 0; p < 2; ++p) {
         d->pk_local[p] = local_packets[p];
         for (int q = 0; q < npeers; ++q)
@@ -267,7 +268,7 @@ int rsg_dist_enable_pull(rsg_dist_t d, int npull, const int *pull_col, const int
     if (pl && pl->algo != RSG_SPMV_WINDOW && pl->algo != RSG_SPMV_TILE) return RSG_UNSUPPORTED;
     // the halo tiles wait for a LOCAL flag that trails the fetch by about two NVLink round trips: mid-grid, last wave interior
     if (pl && pl->algo == RSG_SPMV_WINDOW)
-        RSG_TRY(window_place_halo(h, *pl, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 55));
+        RSG_TRY(window_place_halo(h, *pl, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 55, 0));
     for (int p = 0; p < 2; ++p) {
         HaloFuse &f = d->pullf[p];
         std::memset(&f, 0, sizeof(f));
@@ -319,7 +320,7 @@ int rsg_dist_step(rsg_dist_t d, void *y)
     d->epoch += 1;
     // timing experiments only (tools/dist_trace.py; the results are wrong): RSG_OPT_SPMV_X_HINT bit 8 = nobody waits for / unpacks
     // the halo, bit 16 = no push (implies bit 8), bit 32 = never fall back to plain launches, bit 64 = an eighth of the push CTAs
-    int dbg = h->opts[RSG_OPT_SPMV_X_HINT] & (8 | 16 | 32 | 64);
+    int dbg = h->opts[RSG_OPT_SPMV_X_HINT] & (8 | 16 | 32 | 64 | 128);
     if (dbg & 16) dbg |= 8; // (waiting for a push that never comes would hang until the spin limit)
     if (d->pull) {
         if (!(dbg & 16)) { h->fuse = d->pullf[p]; h->fuse.epoch = d->epoch; }
@@ -331,6 +332,7 @@ int rsg_dist_step(rsg_dist_t d, void *y)
             HaloFuse f = d->fuse[p];
             f.epoch = d->epoch;
             f.ctas = std::max(1, std::min(1024, (f.nsend + 4 * 128 - 1) / (4 * 128)));
+            if (dbg & 128) f.ctas = std::max(1, std::min(1024, (f.nsend + 127) / 128)); // (experiment: one entry per thread)
             if (dbg & 64) f.ctas = std::max(1, f.ctas / 8); // (experiment: few CTAs, each walking eight batches)
             if (d->precision == 's') packet_push_kernel<float><<<f.ctas, 128, 0, d->side>>>(f, static_cast<const float *>(d->x_image[p]));
             else packet_push_kernel<double><<<f.ctas, 128, 0, d->side>>>(f, static_cast<const double *>(d->x_image[p]));
@@ -762,9 +764,12 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
     }
     // ---- packet exchange (rsg_dist_enable_packets) when every rank reads from every rank it sends to and every block runs
     // the window kernel; RSG_DIST_PACKETS=0 in the environment keeps the arrival flags (A/B)
-    // RSG_DIST_EXCHANGE in the environment: "packets" (default; mutual patterns on the window kernel, else the flags stay) |
+    // RSG_DIST_EXCHANGE in the environment: "packets" (default for blocks below 12 M entries; mutual patterns on the window kernel,
+    // else the flags stay) | "flags" (default for larger blocks) |
     // "packets-fused" | "pull" | "flags" (A/B; the tests run all four)
-    int proto = 1;
+    long long biggest = 0; // entries of the largest block
+    for (int r = 0; r < P; ++r) biggest = std::max(biggest, (long long)rowptr[rs[(size_t)r + 1]] - (long long)rowptr[rs[(size_t)r]]);
+    int proto = biggest < kDistPdlMinEntries ? 1 : 0; // short products: packets; long ones hide the flag chain (dist.py: the same rule)
     if (const char *env = getenv("RSG_DIST_EXCHANGE")) proto = !std::strcmp(env, "flags") ? 0 : !std::strcmp(env, "packets") ? 1 : !std::strcmp(env, "packets-fused") ? 3 : 2;
     if (P > 1 && rc == RSG_OK && proto == 2) {
         // ---- pull exchange (rsg_dist_enable_pull): per rank, the entries it reads, grouped by owner

@@ -270,7 +270,7 @@ int pipe_build_plan(rsg_context *h, SpmvPlan &p, bool strict_split = false);
 
 // spmv_window.cu
 int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool strict);
-int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct); // where the halo tiles sit in the grid (see spmv_window.cu)
+int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct, int end_pct); // where the halo tiles sit in the grid (see spmv_window.cu)
 template <typename TV, typename TX>
 int window_launch(rsg_context *h, const SpmvPlan *p, const TV *values, TX alpha, const TX *x, TX beta, TX *y);
 

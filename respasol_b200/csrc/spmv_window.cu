@@ -203,29 +203,45 @@ spmv_window_kernel(const WinArgs w, const TV *__restrict__ values, const TX *__r
     }
     bool wrote = false;
     if (pk_tile) {
-        // four packets per thread in flight at once (a poll is a round trip to L2); stragglers are re-polled one by one.
-        // (All segments as one index space, eight in flight, measured slower: 18.7 vs 16.0 us per step at 8 M entries per rank.)
-        for (int j = 0; j < nseg; ++j) {
-            const int4 q = s_desc[1 + (j >> 1)];
-            const int st = (j & 1) ? q.z : q.x;
-            const unsigned lo = (unsigned)((j & 1) ? q.w : q.y);
-            const int len = (int)(lo & 0xffffu), off = (int)(lo >> 16);
-            for (int c0 = max(st, pk.halo_start) + tid; c0 < st + len; c0 += 4 * THREADS) {
+        // A poll is a round trip to an L2 that is busy streaming the matrix, so the halo parts of up to FOUR segments are polled
+        // together, one packet of each per thread in flight (a stencil tile has three such segments of about a row each: one
+        // round instead of three); stragglers -- a packet still on its way -- are re-polled one by one.
+        int ha[4] = {0, 0, 0, 0}, hb[4] = {0, 0, 0, 0}, hd[4] = {0, 0, 0, 0}; // [ha, hb) = halo columns, hd = s_x offset of column 0
+        int nh = 0;
+        for (int j = 0; j <= nseg; ++j) {
+            if (j < nseg) {
+                const int4 q = s_desc[1 + (j >> 1)];
+                const int st = (j & 1) ? q.z : q.x;
+                const unsigned lo = (unsigned)((j & 1) ? q.w : q.y);
+                const int a = max(st, pk.halo_start), b = st + (int)(lo & 0xffffu);
+                if (a < b) {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (u == nh) { ha[u] = a; hb[u] = b; hd[u] = (int)(lo >> 16) - st; }
+                    ++nh;
+                }
+                if (nh < 4) continue;
+            }
+            if (nh == 0) continue;
+            int longest = 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) longest = max(longest, hb[u] - ha[u]);
+            for (int base = tid; base < longest; base += THREADS) {
                 TX v[4];
                 bool ok[4];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int c = c0 + u * THREADS;
-                    ok[u] = c >= st + len || packet_try(pk.pkts, c - pk.halo_start, wait_epoch, &v[u]);
-                }
+                for (int u = 0; u < 4; ++u) ok[u] = ha[u] + base >= hb[u] || packet_try(pk.pkts, ha[u] + base - pk.halo_start, wait_epoch, &v[u]);
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const int c = c0 + u * THREADS;
-                    if (c >= st + len) continue;
+                    const int c = ha[u] + base;
+                    if (c >= hb[u]) continue;
                     if (!ok[u]) v[u] = packet_wait<TX>(pk.pkts, c - pk.halo_start, wait_epoch, err_flag, max_spins);
-                    s_x[off + (c - st)] = v[u];
+                    s_x[hd[u] + c] = v[u];
                 }
             }
+            nh = 0;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { ha[u] = 0; hb[u] = 0; }
         }
         wrote = true;
     }
@@ -526,7 +542,7 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
     p.wprod = h->plan_send_pos ? h->pinned_i[35] : 0;
     const bool chained = h->plan_send_pos != nullptr;
     if (!chained && p.whalo > 0 && p.whalo < p.nblk) {
-        RSG_TRY(window_place_halo(h, p, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 100));
+        RSG_TRY(window_place_halo(h, p, h->opts[RSG_OPT_SPMV_HALO_PLACE] > 0 ? h->opts[RSG_OPT_SPMV_HALO_PLACE] : 100, 0));
     } else if (chained && p.wprod > 0 && p.wprod < p.nblk) {
         // multi-GPU tile order (records are self-contained, so the order is free; done once, on the host, stable on both sides).
         // Separate products (the push precedes the product): tiles that read a peer's entries go to the END of the grid -- by
@@ -555,7 +571,7 @@ int window_build_plan(rsg_context *h, SpmvPlan &p, int vbytes, int xbytes, bool 
 // last tiles of a grid are the critical path into the next launch.  start_pct = share of the grid that is interior tiles
 // before the first halo tile; from there halo and interior tiles alternate evenly, and the last wave is interior again.
 // start_pct >= 100: all halo tiles at the end (the order the arrival-flag exchange was measured with).
-int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct)
+int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct, int end_pct)
 {
     if (p.whalo <= 0 || p.whalo >= p.nblk) return RSG_OK;
     std::vector<int4> rec((size_t)p.nblk * kWinRecInt4), out((size_t)p.nblk * kWinRecInt4);
@@ -575,7 +591,7 @@ int window_place_halo(rsg_context *h, SpmvPlan &p, int start_pct)
         order.insert(order.end(), ha.begin(), ha.end());
     } else {
         int tail = std::min(ni / 4, 6 * h->sm_count);
-        const int end_pct = h->opts[RSG_OPT_SPMV_HALO_END];
+        if (h->opts[RSG_OPT_SPMV_HALO_END] > 0) end_pct = h->opts[RSG_OPT_SPMV_HALO_END];
         if (end_pct > 0 && end_pct < 100) tail = std::min(ni, std::max(tail, (int)((long long)p.nblk * (100 - end_pct) / 100)));
         const int head = std::min(ni - tail, (int)((long long)p.nblk * std::max(start_pct, 0) / 100));
         const int mid = ni - tail - head; // interior tiles that alternate with the halo tiles

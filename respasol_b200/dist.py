@@ -31,6 +31,9 @@ HALO_ALIGN = 32  # elements: the halo region starts on its own 128/256-byte line
 #                  mixes entries this GPU owns with entries a peer writes while the product is running
 
 
+PACKETS_BELOW_ENTRIES = 12_000_000  # per-rank entries below which the packet exchange is the default (kDistPdlMinEntries of csrc/dist.cu)
+
+
 def halo_base(n_local):
     return (int(n_local) + HALO_ALIGN - 1) // HALO_ALIGN * HALO_ALIGN
 
@@ -135,7 +138,7 @@ class RowBlockSpmv:
         # exchange protocol of the rsg_dist mode: "packets" ({value, step} packets pushed by a small kernel on a side stream and
         # unpacked by the halo tiles; symmetric patterns on the window kernel, otherwise the flags stay), "packets-fused" (the
         # product's first CTAs push them), "pull" (the product's first CTAs fetch the halo), "flags" (push + fence + arrival flags)
-        self.proto = proto if proto is not None else "packets"
+        self.proto = proto if proto is not None else "auto"
         self.use_packets = self.proto in ("packets", "packets-fused")
         self.split = None
         self.p2p = None
@@ -267,6 +270,14 @@ class RowBlockSpmv:
                                          raw_slots, raw_flags, [r[0] for r in plan.send_range], [r[1] for r in plan.send_range],
                                          [v.data_ptr() for v in self.flag_views], self.n_wait)
             self.cdist_step = hnd.dist_step
+            if self.proto == "auto":
+                # short products (a rank's share of config 5 on 8 GPUs: 14 us) cannot hide the push -> fence -> counter -> flag chain
+                # behind their interior tiles: packets.  Longer ones can, and the flags cost their halo tiles nothing: flags.
+                # (measured on config 5: 8 GPUs 16.4 us with packets / 20.4 with flags; 4 GPUs 28.9 / 27.0-27.6)
+                big = torch.tensor([int(self.A.stored)], dtype=torch.int64, device=device)
+                dist.all_reduce(big, op=dist.ReduceOp.MAX, group=self.group)
+                self.proto = "packets" if int(big.item()) < PACKETS_BELOW_ENTRIES else "flags"
+                self.use_packets = self.proto == "packets"
             self.pull = False
             if self.proto == "pull":
                 # pull exchange (rsg_dist_enable_pull): entries this rank reads, grouped by owner

@@ -203,3 +203,115 @@ def test_multi_gpu_chained_products(ngpu, precision):
             assert np.array_equal(got, r3) if precision == "d" else np.abs(got - r3).max() <= 1e-5 * np.abs(r3).max()
         finally:
             lib.rsg_spmv_multi_destroy(M)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# ONE device: a rank that exchanges with itself.  The block is a periodic 27-point stencil slab whose out-of-slab planes are
+# halo columns fed from its own boundary planes, so every exchange protocol of rsg_dist_* (flags, packets on a side stream,
+# packets pushed by the product, pull) runs through the same kernels and the same two-image / step-number logic as between
+# GPUs -- on the single-GPU box the round's end tests on.
+def _loopback_problem(nx=26, nz=20, seed=3):
+    a = host.gen_stencil27(nx, nx, nz + 2, 1, nz + 1, seed=seed)  # rows of planes [1, nz+1), global columns of nz+2 planes
+    plane = nx * nx
+    m = a.m
+    assert m == nz * plane
+    hbase = (m + 31) // 32 * 32
+    cols = a.colidx.astype(np.int64) - a.base
+    new = cols - plane                                   # own planes -> local numbering
+    below, above = cols < plane, cols >= (nz + 1) * plane
+    # periodic wrap: plane 0 is fed from the slab's LAST plane, plane nz+1 from its FIRST one; send list = [first plane | last plane]
+    new[above] = hbase + (cols[above] - (nz + 1) * plane)            # halo slot [0, plane): the first plane
+    new[below] = hbase + plane + cols[below]                         # halo slot [plane, 2 plane): the last plane
+    n_ext = hbase + 2 * plane
+    blk = host.CSR(m, n_ext, a.stored, (a.rowptr - a.base).astype(np.int32), new.astype(np.int32), a.values, 0)
+    send = np.concatenate([np.arange(plane), np.arange(m - plane, m)]).astype(np.int32)
+    return blk, hbase, send, plane
+
+
+def _loopback_reference(blk, hbase, send, x_local):
+    x_ext = np.zeros(blk.n)
+    x_ext[:blk.m] = x_local
+    x_ext[hbase:hbase + len(send)] = x_local[send]
+    return orc.spmv(blk, x_ext, "d")
+
+
+@pytest.mark.parametrize("proto", ["flags", "packets", "packets-fused", "pull"])
+def test_single_device_loopback_exchange(proto):
+    from respasol_b200.gpu import DeviceCSR, Handle
+    dev = torch.device("cuda", 0)
+    blk, hbase, send, plane = _loopback_problem()
+    h = Handle(0)
+    try:
+        A = DeviceCSR(blk, "d", dev)
+        stride = (blk.n + 31) // 32 * 32
+        ximg = torch.zeros(2 * stride, dtype=torch.float64, device=dev)
+        flags = torch.zeros(128, dtype=torch.int32, device=dev)
+        send_d = torch.from_numpy(send).to(dev)
+        img = [ximg[p * stride:] for p in range(2)]
+        slots = [[img[p].data_ptr() + 8 * hbase] for p in range(2)]          # this rank's own halo: "peer 0" is the rank itself
+        pflags = [[flags[32 * p:].data_ptr()] for p in range(2)]
+        d = h.dist_create(A, [t.data_ptr() for t in img], hbase, send_d, slots, pflags, [0], [len(send)],
+                          [flags[32 * p:].data_ptr() for p in range(2)], 1)
+        keep = []
+        if proto.startswith("packets"):
+            pk = torch.zeros(2 * 2 * plane * 2, dtype=torch.float64, device=dev)  # 2 images x 2 plane packets of 16 bytes
+            keep.append(pk)
+            mine = [pk.data_ptr() + 16 * 2 * plane * p for p in range(2)]
+            assert h.dist_enable_packets(d, mine, [[mine[0]], [mine[1]]], side_stream=(proto == "packets"))
+        elif proto == "pull":
+            col = torch.from_numpy((hbase + np.arange(len(send))).astype(np.int32)).to(dev)
+            keep += [col]
+            assert h.dist_enable_pull(d, col, send_d, [[img[0].data_ptr()], [img[1].data_ptr()]], [flags[96:].data_ptr()], [0], [len(send)],
+                                      flags[96:].data_ptr(), flags[97:].data_ptr())
+        y = torch.zeros(blk.m, dtype=torch.float64, device=dev)
+        rng = np.random.default_rng(11)
+        for it in range(7):                                   # both images, step numbers 1..7, x new every step
+            x = rng.standard_normal(blk.m)
+            xd = torch.from_numpy(x).to(dev)
+            nxt = h.lib.rsg_dist_x(d)
+            target = img[0] if nxt == img[0].data_ptr() else img[1]
+            assert nxt in (img[0].data_ptr(), img[1].data_ptr())
+            target[:blk.m].copy_(xd)
+            h.dist_step(d, y)
+            h.synchronize()
+            assert np.array_equal(y.cpu().numpy(), _loopback_reference(blk, hbase, send, x)), (proto, it)
+        for it in range(40):                                  # back to back, no host sync in between
+            h.dist_step(d, y)
+        h.synchronize()
+        assert np.array_equal(y.cpu().numpy(), _loopback_reference(blk, hbase, send, x)), proto
+        assert h.info("SPMV_ALGO_USED") == 8
+        h.dist_destroy(d)
+    finally:
+        h.close()
+
+
+def test_single_device_packets_that_never_arrive_time_out():
+    """the product's halo tiles poll packets nobody sends (the push goes to another buffer): RSG_DEPENDENCY_TIMEOUT, no hang"""
+    from respasol_b200.gpu import DeviceCSR, Handle, RsgError
+    dev = torch.device("cuda", 0)
+    blk, hbase, send, plane = _loopback_problem(nx=16, nz=8)
+    h = Handle(0)
+    try:
+        A = DeviceCSR(blk, "d", dev)
+        stride = (blk.n + 31) // 32 * 32
+        ximg = torch.zeros(2 * stride, dtype=torch.float64, device=dev)
+        flags = torch.zeros(128, dtype=torch.int32, device=dev)
+        send_d = torch.from_numpy(send).to(dev)
+        img = [ximg[p * stride:] for p in range(2)]
+        d = h.dist_create(A, [t.data_ptr() for t in img], hbase, send_d, [[img[p].data_ptr() + 8 * hbase] for p in range(2)],
+                          [[flags[32 * p:].data_ptr()] for p in range(2)], [0], [len(send)], [flags[32 * p:].data_ptr() for p in range(2)], 1)
+        pk = torch.zeros(2 * 2 * plane * 2, dtype=torch.float64, device=dev)
+        elsewhere = torch.zeros(2 * 2 * plane * 2, dtype=torch.float64, device=dev)
+        mine = [pk.data_ptr() + 16 * 2 * plane * p for p in range(2)]
+        lost = [elsewhere.data_ptr() + 16 * 2 * plane * p for p in range(2)]
+        assert h.dist_enable_packets(d, mine, [[lost[0]], [lost[1]]], side_stream=True)
+        h.set_option("WAIT_SPINS", 2000)
+        y = torch.zeros(blk.m, dtype=torch.float64, device=dev)
+        h.dist_step(d, y)
+        with pytest.raises(RsgError) as ei:
+            h.synchronize()
+        assert ei.value.status == 7
+        h.set_option("WAIT_SPINS", 0)
+        h.dist_destroy(d)
+    finally:
+        h.close()

@@ -26,7 +26,7 @@ def main():
     ap.add_argument("--steps", type=int, default=400)
     ap.add_argument("--combos", default="")
     ap.add_argument("--modes", default="full,plain,fuse_only,wait_only")
-    ap.add_argument("--proto", default="packets", choices=["pull", "packets", "packets-fused", "flags"])
+    ap.add_argument("--proto", default="auto", choices=["auto", "pull", "packets", "packets-fused", "flags"])
     ap.add_argument("--packets", type=int, default=1, help="1: {value, step} packet exchange (rsg_dist_enable_packets); 0: arrival flags")
     args = ap.parse_args()
     world, rank, lr = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])

@@ -30,7 +30,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--planes", type=int, default=17)
     ap.add_argument("--steps", type=int, default=301)
-    ap.add_argument("--proto", default="packets", choices=["pull", "packets", "packets-fused", "flags"])
+    ap.add_argument("--proto", default="auto", choices=["auto", "pull", "packets", "packets-fused", "flags"])
     ap.add_argument("--packets", type=int, default=1)
     ap.add_argument("--opts", default="SPMV_PDL=2")
     ap.add_argument("--plain", type=int, default=0, help="1: trace the plain product (no exchange) instead")
