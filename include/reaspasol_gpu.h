@@ -284,7 +284,8 @@ int rsg_dist_step(rsg_dist_t dist, void *y);
  * entry travels as {value, step number} in ONE 16-byte store (fp32 x: 8 bytes) and the halo tiles unpack their x window out of
  * the packets, polling the step number inside each entry -- no fence + counter + flag hop between the data and its consumer,
  * which is what bounds a product of a few microseconds (8 GPUs on config 5).  local_packets: this rank's 2 packet buffers
- * (image 0, 1), (n_ext - halo_start) packets each, ZERO-filled by the caller, peer-mapped; peer_packets: 2*npeers DEVICE
+ * (image 0, 1), (n_ext - halo_start) packets each, ZERO-filled by the caller (the fill COMPLETE, not merely queued on another stream: the
+ * call writes marks into them on the handle's stream), peer-mapped; peer_packets: 2*npeers DEVICE
  * pointers, image-major like peer_slots: where entry 0 of this rank's send list lands in peer q's buffer.  ONLY for
  * exchange patterns in which every rank also reads from every rank it sends to (stencils, structurally symmetric matrices):
  * that mutual dependency keeps a rank from running two steps ahead of a reader -- the job the arrival flags did, which are

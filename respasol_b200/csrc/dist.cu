@@ -316,6 +316,7 @@ int rsg_dist_step(rsg_dist_t d, void *y)
     if (!d || (d->m > 0 && !y)) return RSG_BAD_ARG;
     rsg_context *h = d->h;
     DevGuard g(h->device);
+    if (d->epoch >= 0x7ffffff0) return RSG_UNSUPPORTED; // step numbers are compared as ints (and 0 / -1 mean "padding" / "pending" in a packet)
     const int p = d->epoch & 1; // step e = epoch + 1 uses image (e - 1) & 1
     d->epoch += 1;
     // timing experiments only (tools/dist_trace.py; the results are wrong): RSG_OPT_SPMV_X_HINT bit 8 = nobody waits for / unpacks
@@ -831,6 +832,7 @@ int rsg_spmv_multi_create(int ngpu, const int *devices, char precision, int m, i
                 (void)cudaGetLastError(); rc = RSG_ALLOC_FAILED;
             }
         }
+        for (int r = 0; r < P && rc == RSG_OK; ++r) { cudaSetDevice(M->dev[(size_t)r]); cudaDeviceSynchronize(); } // the zero fill precedes every mark
         for (int r = 0; r < P && rc == RSG_OK; ++r) {
             cudaSetDevice(M->dev[(size_t)r]);
             std::vector<void *> peer((size_t)(2 * P), nullptr);

@@ -310,6 +310,7 @@ class RowBlockSpmv:
                 per_image = self.P * plan.width
                 pk = symm_mem.empty(2 * per_image * 2, dtype=dtype, device=device)  # a packet = 2 elements
                 pk.zero_()
+                torch.cuda.synchronize(device)  # the zero fill precedes the marks rsg_dist_enable_packets writes on the handle's stream
                 self.symm_pk = symm_mem.rendezvous(pk, group)
                 self.pk = pk
                 pptrs = list(self.symm_pk.buffer_ptrs)
