@@ -87,6 +87,7 @@ struct LongSplit {
     double *part;     // one 8-byte slot per segment
     int *cnt;         // arrivals per long row (reset by the last arrival)
     int nseg;
+    unsigned long long *trace; // debug (rsg_debug_trace): 4 x %globaltimer per CTA, as in the window kernel (bit 63 of word 3: segment CTA)
 };
 
 // ------------------------------------------------------------------ SpMV plan
@@ -102,6 +103,7 @@ struct SpmvPlan {
     // statistics
     int nnz = 0;           // stored entries, rowptr[m]-rowptr[0]
     int first = 0;         // rowptr[0]-base (non-zero for a row-slab view into a larger CSR)
+    bool scattered = false; // neighbouring rows read unrelated x lines (scatter statistic > 0.5): the tile kernel stages products
     int max_row = 0;
     int algo = 0;          // resolved rsg_spmv_algo
     int variant = 0;       // resolved tile/CTA shape

@@ -383,7 +383,7 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
         const int blocks = std::min((m + 255) / 256, h->sm_count * 8);
         row_stats_kernel<<<blocks, 256, 0, st>>>(m, rowptr, h->scratch_i);
         h->launches++;
-        if (colidx && (h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_AUTO || h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_WINDOW)) {
+        if (colidx && (h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_AUTO || h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_WINDOW || h->opts[RSG_OPT_SPMV_ALGO] == RSG_SPMV_TILE)) {
             const int groups = std::min((m + 31) / 32, 4096);
             scatter_stats_kernel<<<(groups * 32 + 255) / 256, 256, 0, st>>>(m, base, groups, rowptr, colidx, h->scratch_i);
             h->launches++;
@@ -396,6 +396,7 @@ int spmv_get_plan(rsg_context *h, int m, int n, int nnz_hint, int base, const in
     RSG_CUDA_TRY(cudaStreamSynchronize(st));
     p.max_row = h->pinned_i[0];
     const double scatter = h->pinned_i[4] > 0 ? (double)h->pinned_i[3] / h->pinned_i[4] : 0.0; // x lines per row, neighbouring rows
+    p.scattered = scatter > 0.5;
     p.first = h->pinned_i[1] - base;
     p.nnz = h->pinned_i[2] - h->pinned_i[1];
     if (p.nnz < 0 || p.first < 0) return RSG_BAD_ARG;

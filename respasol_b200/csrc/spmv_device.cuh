@@ -340,6 +340,13 @@ __device__ __forceinline__ void halo_flag_wait(const int *flags, int n, int epoc
     }
 }
 
+__device__ __forceinline__ unsigned long long global_ns() // (rsg_debug_trace)
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // Programmatic dependent launch (PTX griddepcontrol; no-ops in a kernel that was launched without the attribute)
 __device__ __forceinline__ void grid_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
@@ -537,7 +544,9 @@ __device__ __forceinline__ TX row_dot_lean2(const TV *s_val, const int *s_col, i
     return s;
 }
 
-template <typename TV, typename TX, int THREADS, int B, bool COH = false>
+// LIMIT > 0: rows longer than LIMIT entries are left to reduce_rows_long (a thread walking a 64-entry row of a power-law
+// matrix alone needs eight dependent rounds of gathers and is what its CTA -- and the tail of the product -- waits for)
+template <typename TV, typename TX, int THREADS, int B, bool COH = false, int LIMIT = 0>
 __device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
                                                   int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
                                                   TX alpha, TX beta)
@@ -550,8 +559,15 @@ __device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_
         for (int i = threadIdx.x; i < nrows; i += 2 * THREADS) {
             const int i2 = i + THREADS;
             const int k0 = s_rp[i] - sb, e0 = s_rp[i + 1] - sb;
-            const bool two = i2 < nrows;
-            const int k1 = two ? s_rp[i2] - sb : 0, e1 = two ? s_rp[i2 + 1] - sb : 0;
+            bool two = i2 < nrows;
+            int k1 = two ? s_rp[i2] - sb : 0, e1 = two ? s_rp[i2 + 1] - sb : 0;
+            if (LIMIT > 0) {
+                if (two && e1 - k1 > LIMIT) { two = false; k1 = e1 = 0; }
+                if (e0 - k0 > LIMIT) { // only the second row (if any) is this thread's
+                    if (two) store_y(y, row_glob + i2, row_dot_lean2<TV, TX, 1, B, COH>(s_val, s_col, k1, e1, xb), alpha, beta);
+                    continue;
+                }
+            }
             if (e0 - k0 <= B && e1 - k1 <= B) {
                 TX xv0[B], xv1[B];
 #pragma unroll
@@ -575,8 +591,89 @@ __device__ __forceinline__ void reduce_rows_lean2(const TV *s_val, const int *s_
         return;
     }
     for (int i = threadIdx.x; i < nrows; i += THREADS) {
+        if (LIMIT > 0 && s_rp[i + 1] - s_rp[i] > LIMIT) continue;
         const TX s = row_dot_lean2<TV, TX, 1, B, COH>(s_val, s_col, s_rp[i] - sb, s_rp[i + 1] - sb, xb);
         store_y(y, row_glob + i, s, alpha, beta);
+    }
+}
+
+// The rows reduce_rows_lean2<..., LIMIT> left out: G lanes each (every group scans its share of the tile's rows)
+template <typename TV, typename TX, int THREADS, int G, int B, bool COH, int LIMIT>
+__device__ __forceinline__ void reduce_rows_long(const TV *s_val, const int *s_col, const int *s_rp, int sb, int nrows,
+                                                 int row_glob, const TX *__restrict__ x, int base, TX *__restrict__ y,
+                                                 TX alpha, TX beta)
+{
+    constexpr int GROUPS = THREADS / G;
+    const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+    const TX *xb = x - base;
+    const int iters = (nrows + GROUPS - 1) / GROUPS;
+    for (int it = 0; it < iters; ++it) {
+        const int i = it * GROUPS + gid;
+        const bool lg = i < nrows && s_rp[i + 1] - s_rp[i] > LIMIT;
+        if (!__any_sync(0xffffffffu, lg)) continue;
+        TX s = 0;
+        if (lg) s = row_dot_lean2<TV, TX, G, B, COH>(s_val, s_col, s_rp[i] - sb + lane, s_rp[i + 1] - sb, xb);
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lg && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
+    }
+}
+
+// Product staging for scattered matrices: the CTA turns the staged values into products a_k * x[col_k] IN PLACE, every thread
+// taking entries tid, tid + THREADS, ... with eight gathers in flight -- ONE round of gathers for the whole tile, whatever its row
+// lengths (thread-per-row needs a dependent round per eight entries of its longest row: 3.5 us median per tile on config 4,
+// of which the arithmetic is nothing).  The row sums are then shared-memory additions in stored order: the same bits as
+// multiply-then-add in a thread (the library is compiled without contraction).  Needs sizeof(TV) == sizeof(TX).
+template <typename TV, typename TX, int THREADS, bool COH>
+__device__ __forceinline__ void stage_products(TV *s_val, const int *s_col, int kb, int ke, const TX *__restrict__ x, int base)
+{
+    static_assert(sizeof(TV) == sizeof(TX), "products are staged in place");
+    const TX *xb = x - base;
+    asm volatile("" : "+l"(xb));
+    int k = kb + (int)threadIdx.x;
+    for (; k + 7 * THREADS < ke; k += 8 * THREADS) {
+        TX xv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) xv[u] = ld_xg<COH>(xb + s_col[k + u * THREADS]);
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s_val[k + u * THREADS] = (TV)((TX)s_val[k + u * THREADS] * xv[u]);
+    }
+    {
+        TX xv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) xv[u] = (k + u * THREADS < ke) ? ld_xg<COH>(xb + s_col[k + u * THREADS]) : (TX)0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+            if (k + u * THREADS < ke) s_val[k + u * THREADS] = (TV)((TX)s_val[k + u * THREADS] * xv[u]);
+    }
+}
+
+// rows of staged products: thread per row up to LIMIT entries (stored order), G lanes per longer row
+template <typename TV, typename TX, int THREADS, int G, int LIMIT>
+__device__ __forceinline__ void sum_staged_rows(const TV *s_val, const int *s_rp, int sb, int nrows, int row_glob, TX *__restrict__ y,
+                                                TX alpha, TX beta, bool any_long)
+{
+    for (int i = threadIdx.x; i < nrows; i += THREADS) {
+        const int k0 = s_rp[i] - sb, e = s_rp[i + 1] - sb;
+        if (e - k0 > LIMIT) continue;
+        TX s = 0;
+        for (int k = k0; k < e; ++k) s += (TX)s_val[k];
+        store_y(y, row_glob + i, s, alpha, beta);
+    }
+    if (!any_long) return;
+    constexpr int GROUPS = THREADS / G;
+    const int gid = threadIdx.x / G, lane = threadIdx.x % G;
+    const int iters = (nrows + GROUPS - 1) / GROUPS;
+    for (int it = 0; it < iters; ++it) {
+        const int i = it * GROUPS + gid;
+        const bool lg = i < nrows && s_rp[i + 1] - s_rp[i] > LIMIT;
+        if (!__any_sync(0xffffffffu, lg)) continue;
+        TX s = 0;
+        if (lg)
+            for (int k = s_rp[i] - sb + lane, e = s_rp[i + 1] - sb; k < e; k += G) s += (TX)s_val[k];
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lg && lane == 0) store_y(y, row_glob + i, s, alpha, beta);
     }
 }
 

@@ -105,9 +105,26 @@ __device__ __forceinline__ void tile_reduce(unsigned char *sp, const PipeMeta &m
         }
         const int *rp = s_rp + cur;
         switch (g) {
-        case 1: // thread per row: unpredicated whole batches (8 gathers per batch for fp64 x, 16 for fp32)
-            reduce_rows_lean2<TV, TX, NC, (sizeof(TX) == 4 ? 16 : 8), COH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+        case 1: { // thread per row: unpredicated whole batches (8 gathers per batch for fp64 x, 16 for fp32)
+            constexpr int BB = sizeof(TX) == 4 ? 16 : 8;
+            if (sizeof(TV) == sizeof(TX) && (reduce_opt & 0xff) == 0 && ((reduce_opt >> 17) & 1)) {
+                // scattered columns (plan: SpmvPlan::scatter): one round of gathers for the whole tile, products staged in place
+                if constexpr (sizeof(TV) == sizeof(TX)) {
+                    stage_products<TV, TX, NC, COH>(s_val, s_col, rp[0] - sb, rp[nrows] - sb, x, base);
+                    __syncthreads();
+                    sum_staged_rows<TV, TX, NC, 8, 32>(s_val, rp, sb, nrows, r0 + cur, y, alpha, beta, mt.maxlen > 32);
+                }
+                break;
+            }
+            if ((reduce_opt & 0xff) == 0 && mt.maxlen > 2 * BB) {
+                // chosen by the tile's statistics (not forced): rows of more than two batches go to eight lanes each afterwards
+                reduce_rows_lean2<TV, TX, NC, BB, COH, 2 * BB>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+                reduce_rows_long<TV, TX, NC, 8, BB, COH, 2 * BB>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+            } else {
+                reduce_rows_lean2<TV, TX, NC, BB, COH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta);
+            }
             break;
+        }
         case 2: reduce_rows_lean2g<TV, TX, NC, 2, 8, COH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
         case 4: reduce_rows_lean<TV, TX, NC, 4, COH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
         case 8: reduce_rows_lean<TV, TX, NC, 8, COH>(s_val, s_col, rp, sb, nrows, r0 + cur, x, base, y, alpha, beta); break;
@@ -142,6 +159,8 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
     // this grid is here; this grid reads only pattern data (descriptor, row pointers, colidx -- the plan is keyed on the
     // pattern) and, if promised static, the values before grid_dependency_wait()
     if (!(COH && fuse.pull) || (int)blockIdx.x < fuse.ctas) grid_launch_dependents(); // (pull exchange: see spmv_window.cu)
+    unsigned long long *tr = ls.trace ? ls.trace + 4 * (size_t)blockIdx.x : nullptr;
+    if (tr && tid == 0) tr[0] = global_ns();
     if (COH && (int)blockIdx.x < fuse.ctas) {
         // ---- fused exchange: these CTAs are dispatched first; they publish this rank's boundary entries of x
         // to the peers (plain stores into P2P-mapped memory over NVLink) while the tiles behind them multiply
@@ -160,21 +179,41 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
             halo_flag_wait(wait_flags, wait_n, wait_epoch, err_flag, max_spins);
             __syncthreads();
         }
+        if (tr && tid == 0) tr[1] = global_ns();
         const int4 sg = ls.seg[seg_id];
         const TX tot = cta_row_sum<TV, TX, THREADS, 1, true, 0, COH>(sg.y, sg.z, colidx, values, x, base, reinterpret_cast<TX *>(smem_raw),
                                                                      make_evict_first_policy());
+        if (tr && tid == 0) tr[2] = global_ns();
+        __shared__ int s_lastseg;
         if (tid == 0) {
             const int2 lr = ls.lrow[sg.w];
             *reinterpret_cast<volatile TX *>(ls.part + seg_id) = tot; // one 8-byte slot per segment, whatever TX is
             __threadfence();
-            if (atomicAdd(ls.cnt + sg.w, 1) == lr.y - 1) {
-                __threadfence();
+            s_lastseg = atomicAdd(ls.cnt + sg.w, 1) == lr.y - 1;
+        }
+        __syncthreads();
+        if (s_lastseg) {
+            // the last segment of the row to arrive adds the partial sums -- the whole CTA, in an order fixed by the segment
+            // count alone (thread t takes partials t, t + THREADS, ...; then lanes, then warps): deterministic, and one round of
+            // loads instead of a thread walking ~100 partials one L2 round trip at a time (measured: up to 5-8 us, the end of
+            // the product on config 4)
+            __threadfence();
+            const int2 lr = ls.lrow[sg.w];
+            TX acc = 0;
+            for (int i = tid; i < lr.y; i += THREADS) acc += *reinterpret_cast<volatile TX *>(ls.part + lr.x + i);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xffffffffu, acc, o);
+            TX *red = reinterpret_cast<TX *>(smem_raw);
+            if ((tid & 31) == 0) red[tid >> 5] = acc;
+            __syncthreads();
+            if (tid == 0) {
                 TX sum = 0;
-                for (int i = 0; i < lr.y; ++i) sum += *reinterpret_cast<volatile TX *>(ls.part + lr.x + i);
+                for (int wv = 0; wv < THREADS / 32; ++wv) sum += red[wv];
                 store_y(y, sg.x, sum, alpha, beta);
                 ls.cnt[sg.w] = 0;
             }
         }
+        if (tr && tid == 0) tr[3] = global_ns() | (1ull << 63);
         return;
     }
     const int tile_id = seg_id - ls.nseg;
@@ -207,6 +246,7 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
     }
     grid_dependency_wait(); // x, y and (unless promised static) the values: what earlier work of the stream may have written
     if (COH && fuse.pull) grid_launch_dependents();
+    if (tr && tid == 0) tr[1] = global_ns();
     if (tid == 0 && mt.nr > 0 && qe > sb && !early_values)
         bulk_g2s(smem_raw + Stage::val_off, values + sb, (uint32_t)(qe - sb) * (uint32_t)sizeof(TV), &s_full, spol);
     if (must_wait) {
@@ -217,8 +257,10 @@ spmv_tile_kernel(int base, const int *__restrict__ rp0, const int *__restrict__ 
         if (mt.nr <= 0) return;
     }
     mbar_wait(&s_full, 0);
+    if (tr && tid == 0) tr[2] = global_ns();
     tile_reduce<TV, TX, THREADS, CAPE, Stage, COH>(smem_raw, mt, base, colidx, values, x, y, alpha, beta, reduce_opt, spol, &s_aux,
                                                    ls.nseg > 0);
+    if (tr && tid == 0) tr[3] = global_ns();
 }
 
 // rows longer than `cape` -> list[] = (row, zero-based start, zero-based end, 0), count in *counter (may exceed cap)
@@ -432,8 +474,13 @@ static int tile_launch_one(rsg_context *h, const SpmvPlan *p, const TV *values, 
     // entry, so with few threads walking many entries it outlasts the whole product (measured: 32 CTAs x 9 entries per
     // thread, one at a time = 18 us for a 14 us product)
     if (fuse.ctas > 0) fuse.ctas = std::max(1, std::min(1024, (fuse.nsend + 4 * THREADS - 1) / (4 * THREADS)));
-    LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg};
-    const int ropt = h->opts[RSG_OPT_SPMV_REDUCE] | (p->lanes_hint == 2 ? 1 << 16 : 0);
+    LongSplit ls = {p->seg, p->lrow, p->seg_part, p->seg_cnt, p->nseg, nullptr};
+    if (h->trace && h->trace_ctas >= p->nblk + fuse.ctas + p->nseg) {
+        ls.trace = h->trace + (size_t)(h->trace_parity & 1) * 4 * (size_t)h->trace_ctas;
+        h->trace_parity ^= 1;
+    }
+    const int ropt = h->opts[RSG_OPT_SPMV_REDUCE] | (p->lanes_hint == 2 ? 1 << 16 : 0) |
+                     ((p->scattered && h->opts[RSG_OPT_SPMV_X_HINT] != 2) ? 1 << 17 : 0); // X_HINT 2: A/B switch of the product staging
     int pdl = h->opts[RSG_OPT_SPMV_PDL]; // see spmv_window.cu / the header
     if (pdl != 1) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
@@ -566,7 +613,7 @@ extern "C" int spmv_csr_d_noalloc(int m, int n, int nnz, int base, const int *ro
     pipe_rowptr_copy_kernel<<<(rp0_len + 255) / 256, 256, 0, st>>>(m, rp0_len, base, rowptr, rp0);
     HaloFuse fuse;
     std::memset(&fuse, 0, sizeof(fuse));
-    LongSplit ls = {nullptr, nullptr, nullptr, nullptr, 0}; // rows longer than a stage are reduced CTA-per-row inside their tile
+    LongSplit ls = {nullptr, nullptr, nullptr, nullptr, 0, nullptr}; // rows longer than a stage are reduced CTA-per-row inside their tile
     const int ropt = lanes == 2 ? 1 << 16 : 0;
     constexpr int MINB = TileResidency<double, THREADS, CAPE, ROWS>::value;
     spmv_tile_kernel<double, double, THREADS, CAPE, ROWS, MINB, false>

@@ -51,12 +51,7 @@ struct WinArgs {
     unsigned long long *trace; // debug (rsg_debug_trace): 4 x %globaltimer per CTA -- entry, dependency resolved, data staged, done
 };
 
-__device__ __forceinline__ unsigned long long global_ns()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
+
 
 // -------------------------------------------------------------------------------- row reductions
 template <typename TV, typename TX>
