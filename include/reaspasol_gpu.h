@@ -76,7 +76,10 @@ typedef enum {
                                    3 chain: one CTA walks the levels, a block barrier per level (narrow levels) */
     RSG_OPT_ILU0_ALGO = 6,      /* 0 auto, 1 sync-free flags, 2 level-scheduled launches */
     RSG_OPT_SPMV_X_PERSIST = 7, /* 1: pin x in L2 with an access-policy window on the stream */
-    RSG_OPT_SPMV_X_HINT = 8,    /* tile kernel plan: 4 = never size tiles for two lanes per row (A/B); other values unused */
+    RSG_OPT_SPMV_X_HINT = 8,    /* A/B and timing switches (0 = default): 4 = tile plan never sized for two lanes per row; 2 = tile kernel
+                                   without product staging on scattered patterns; bits 8 / 16 / 32 / 64 / 128 = rsg_dist_step timing
+                                   experiments of tools/dist_trace.py (no halo wait / no push / never plain launches / fewer or more
+                                   push CTAs) -- bits 8 and 16 give WRONG results, never set them outside a timing run */
     RSG_OPT_SPMV_ROWS_PER_THREAD = 9, /* tile kernel: tile size in rows per thread (0 = 1) */
     RSG_OPT_SPMV_CTAS_PER_SM = 10,    /* unused since the persistent kernel was retired */
     RSG_OPT_TRSV_BATCH = 11,    /* sync-free solves: solution entries polled per round trip (1,2,4,8,16; 0 = default) */
