@@ -12,7 +12,11 @@
 //                     caller's cuts), halo relabelling, peer access (cudaDeviceEnablePeerAccess), one handle + one
 //                     rsg_dist per device, one host thread per device issuing its steps.  bin/test_spmv --gpus N.
 //
-// Protocol (unchanged from round 1, now in one place): step e uses image p = (e-1) & 1.  A rank's launch first stores
+// Three exchange protocols share the two-image scheme below (DESIGN.md 6 has the measurements behind the choice):
+//   flags    (rsg_dist_create alone)        push CTAs inside the product's grid, fence, counter, arrival flags; blocks >= 12 M entries
+//   packets  (+ rsg_dist_enable_packets)    {value, step} packets from a side-stream kernel, unpacked by the halo tiles; short products
+//   pull     (+ rsg_dist_enable_pull)       the product's first CTAs fetch the halo from the owners' x; any pattern, no remote store
+// Protocol of the flags form (unchanged from round 1, now in one place): step e uses image p = (e-1) & 1.  A rank's launch first stores
 // its boundary entries of image p into the readers' image-p halo slots and releases e to their flags; tiles that read
 // halo columns (and, always, the last tile) acquire flags[p][i] >= e from every neighbour.  A rank therefore never runs
 // more than one step ahead of a neighbour, which is what makes two images enough.
