@@ -130,3 +130,29 @@ def test_p2p_slot_offsets_and_readers():
     c = p0.remapped.colidx.astype(np.int64)
     halo_cols = np.unique(c[c >= p0.halo_base])
     assert halo_cols.min() >= offs[0][0] and halo_cols.max() < offs[0][0] + w
+
+
+def test_exchange_pattern_symmetry_decides_the_packet_protocol():
+    """The packet exchange is only safe when every rank reads from every rank it sends to (that mutual dependency is what keeps a
+    rank from running two steps ahead of a reader): HaloPlan.symmetric, identical on all ranks."""
+    from respasol_b200 import host
+    from respasol_b200.dist import PACKETS_BELOW_ENTRIES, HaloPlan
+    full = host.gen_stencil27(5, 5, 9, seed=0)
+    starts = np.array([0, 75, 150, 225])
+    plans = [HaloPlan(full.rows(starts[r], starts[r + 1]), starts, r) for r in range(3)]
+    needs = [p.need for p in plans]
+    assert all(p.finish(needs).symmetric for p in plans)
+    # an upwind pattern: rank r reads only from rank r - 1 (rank 0 feeds, reads nothing)
+    n, band = 300, 40
+    rp = np.zeros(n + 1, dtype=np.int32)
+    rp[1:] = np.cumsum(np.where(np.arange(n) < band, 1, 2))
+    ci = np.concatenate([[r] if r < band else [r - band, r] for r in range(n)]).astype(np.int32)
+    up = host.CSR(n, n, int(rp[-1]), rp, ci, np.ones(int(rp[-1])), 0)
+    starts = np.array([0, 100, 200, 300])
+    plans = [HaloPlan(up.rows(starts[r], starts[r + 1]), starts, r) for r in range(3)]
+    needs = [p.need for p in plans]
+    assert not any(p.finish(needs).symmetric for p in plans)
+    assert [p.readers for p in plans] == [[1], [2], []]
+    assert PACKETS_BELOW_ENTRIES == 12_000_000  # the same threshold as kDistPdlMinEntries in csrc/dist.cu
+    src = open(__file__.replace("tests/test_dist_cpu.py", "respasol_b200/csrc/dist.cu")).read()
+    assert "kDistPdlMinEntries = 12000000" in src
