@@ -279,9 +279,10 @@ int rsg_dist_create(rsg_handle_t handle, char precision, int m, int n_ext, int n
                     const int *colidx, const void *values, void *const *x_images, int halo_start, int nsend,
                     const int *send_idx, int npeers, void *const *peer_slots, int *const *peer_flags, const int *peer_lo,
                     const int *peer_hi, const int *const *wait_flags, int nwait, rsg_dist_t *dist);
-/* y = A_block * x: ONE kernel launch on the handle's stream -- its first CTAs push this rank's boundary entries of x
- * (image of this step) into the peers' slots and release the step number to their flags, its halo tiles (and always its
- * last tile) acquire the neighbours' flags before they read x.  Asynchronous. */
+/* y = A_block * x.  With the arrival flags rsg_dist_create sets up: ONE kernel launch on the handle's stream -- its first CTAs
+ * push this rank's boundary entries of x (image of this step) into the peers' slots and release the step number to their
+ * flags, its halo tiles (and always its last tile) acquire the neighbours' flags before they read x.  After
+ * rsg_dist_enable_packets / rsg_dist_enable_pull: see there.  Asynchronous. */
 int rsg_dist_step(rsg_dist_t dist, void *y);
 /* Packet exchange for a context made by rsg_dist_create (window-kernel blocks; RSG_UNSUPPORTED otherwise): every boundary
  * entry travels as {value, step number} in ONE 16-byte store (fp32 x: 8 bytes) and the halo tiles unpack their x window out of
