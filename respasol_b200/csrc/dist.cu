@@ -241,6 +241,7 @@ int rsg_dist_enable_packets(rsg_dist_t d, void *const *local_packets, void *cons
         // programmatic overlap (measured: 14.15 us with and without).
         int lo_prio = 0, hi_prio = 0;
         cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio);
+        if (const char *env = getenv("RSG_DIST_SIDE_PRIORITY")) if (!std::strcmp(env, "normal")) hi_prio = 0; // (A/B)
         if (!d->side && cudaStreamCreateWithPriority(&d->side, cudaStreamNonBlocking, hi_prio) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
         if (!d->x_ready && cudaEventCreateWithFlags(&d->x_ready, cudaEventDisableTiming) != cudaSuccess) { (void)cudaGetLastError(); return RSG_CUDA_ERROR; }
         d->pk_side = true;
