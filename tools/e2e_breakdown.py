@@ -75,10 +75,12 @@ def main():
     out["d2h_us"] = wall(d2h, args.reps)
     out["h2d_and_d2h_concurrent_us"] = wall(both, args.reps)
     h = Handle(0)
-    for direct in (1, 0, 2):
+    modes = [int(v) for v in os.environ.get("E2E_MODES", "1,0,2").split(",")]
+    chunk_list = [int(v) for v in os.environ.get("E2E_CHUNKS", "1,2,4,6,8,12,16,32").split(",")]  # negative: uniform chunks (A/B of the taper)
+    for direct in modes:
         h.set_option("HOST_Y_DIRECT", direct if direct < 2 else 0)
         h.set_option("HOST_GRAPH", 2 if direct < 2 else 0)
-        for chunks in (1, 2, 4, 6, 8, 12, 16, 32):
+        for chunks in chunk_list:
             h.set_option("HOST_CHUNKS", chunks)
             mat = h.matrix_upload(a, "d")
             xn, yn = xh.numpy(), yh.numpy()
