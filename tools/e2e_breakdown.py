@@ -76,7 +76,7 @@ def main():
     out["h2d_and_d2h_concurrent_us"] = wall(both, args.reps)
     h = Handle(0)
     modes = [int(v) for v in os.environ.get("E2E_MODES", "1,0,2").split(",")]
-    chunk_list = [int(v) for v in os.environ.get("E2E_CHUNKS", "1,2,4,6,8,12,16,32").split(",")]  # negative: uniform chunks (A/B of the taper)
+    chunk_list = [int(v) for v in os.environ.get("E2E_CHUNKS", "1,2,4,6,8,12,16,32").split(",")]
     for direct in modes:
         h.set_option("HOST_Y_DIRECT", direct if direct < 2 else 0)
         h.set_option("HOST_GRAPH", 2 if direct < 2 else 0)
