@@ -640,7 +640,7 @@ def run_ours(args):
             traffic = json.load(f).get("spmv_window_fp64_c2_bytes_per_launch" if world == 1 else None)
     my_bytes = float(spmv_bytes(a.stored, a.m, a.m if world > 1 else a.n, "d"))
     achieved = my_bytes / (per_launch_ms * 1e-3) * 1e-9  # this GPU's launch: its rows, its slice of x
-    kname = {8: "spmv_window_kernel<double,double,128,4>", 7: "spmv_tile_kernel<double,double,128,2304,512,7,%s>" % ("true" if world > 1 else "false"),
+    kname = {8: "spmv_window_kernel<double,double,%s,4,%s>" % ("64" if world > 4 else "128", "true" if world > 4 else "false"), 7: "spmv_tile_kernel<double,double,128,2304,512,7,%s>" % ("true" if world > 1 else "false"),
              3: "spmv_vector_kernel<double,double>"}.get(algo_used, "algo %d" % algo_used)
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "algorithmic_bytes_per_launch": my_bytes,
