@@ -49,3 +49,42 @@ def test_product_never_imports_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 src = open(os.path.join(dirpath, fn), errors="ignore").read()
                 assert "liboracle" not in src and "import orc" not in src and "orc_" not in src, fn
+
+
+def _enum(name):
+    """{identifier: value} of a typedef enum in the header (explicit values, or counting up from the previous one)"""
+    text = open(os.path.join(ROOT, "include", "reaspasol_gpu.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    body = re.search(r"typedef enum \{([^}]*)\}\s*%s;" % name, text).group(1)
+    out, nxt = {}, 0
+    for item in filter(None, (s.strip() for s in body.split(","))):
+        ident, _, val = item.partition("=")
+        nxt = int(val.strip(), 0) if val.strip() else nxt
+        out[ident.strip()] = nxt
+        nxt += 1
+    return out
+
+
+def test_python_option_tables_mirror_the_header_enums():
+    from respasol_b200 import gpu
+    opts = _enum("rsg_option")
+    assert {("RSG_OPT_" + k): v for k, v in gpu.OPT.items()} == {k: v for k, v in opts.items() if k != "RSG_OPT_COUNT_"}
+    assert opts["RSG_OPT_COUNT_"] == max(gpu.OPT.values()) + 1
+    algos = _enum("rsg_spmv_algo")
+    for k, v in gpu.ALGO.items():
+        assert algos["RSG_SPMV_" + k.upper()] == v, k
+    status = _enum("rsg_status")
+    lib = _lib.gpu_lib()
+    for k, v in status.items():
+        assert lib.rsg_status_string(v) != b"unknown status", k
+    assert lib.rsg_status_string(max(status.values()) + 1) == b"unknown status"
+
+
+def test_noalloc_scratch_size_stated_in_the_header():
+    text = open(os.path.join(ROOT, "include", "reaspasol_gpu.h")).read()
+    rows = 1 << int(re.search(r"#define RSG_NOALLOC_MAX_ROWS \(1 << (\d+)\)", text).group(1))
+    tiles = 1 << int(re.search(r"#define RSG_NOALLOC_MAX_TILES \(1 << (\d+)\)", text).group(1))
+    stated = int(re.search(r"#define RSG_NOALLOC_SCRATCH_BYTES (\d+)", text).group(1))
+    desc = 16 * (tiles + 1 + 15)
+    rp = (4 * (((rows + 1 + 3) & ~3) + 4) + 255) & ~255
+    assert stated == desc + rp and stated < 8 << 20  # (the .cu static_asserts the same equality)
