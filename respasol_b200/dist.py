@@ -113,6 +113,24 @@ class HaloPlan:
         self.interior = self._interior_run(a, off)
         return self
 
+    def pull_lists(self):
+        """The pull exchange's view of the halo (rsg_dist_enable_pull): for every entry this rank reads from another rank, grouped
+        by owner -- the halo column it lands in and its index in the owner's x; owner o's entries are [lo[o], hi[o])."""
+        rs = self.row_starts
+        cols, idxs, lo, hi = [], [], [], []
+        n = 0
+        for o in range(self.P):
+            lo.append(n)
+            if o != self.rank:
+                mine = self.need[(self.need >= rs[o]) & (self.need < rs[o + 1])] - rs[o]
+                pos = np.searchsorted(self.send_idx[o], mine)
+                cols.append(self.halo_base + o * self.width + pos)
+                idxs.append(mine)
+                n += len(mine)
+            hi.append(n)
+        cat = (lambda v: np.concatenate(v).astype(np.int32)) if cols else (lambda v: np.zeros(0, np.int32))
+        return cat(cols), cat(idxs), lo, hi
+
     @staticmethod
     def _interior_run(a, off):
         """[r0, r1): the longest run of consecutive rows without an off-block column."""
@@ -281,20 +299,9 @@ class RowBlockSpmv:
             self.pull = False
             if self.proto == "pull":
                 # pull exchange (rsg_dist_enable_pull): entries this rank reads, grouped by owner
-                rs = self.row_starts
-                cols, idxs, lo, hi = [], [], [], []
-                n = 0
-                for o in range(self.P):
-                    lo.append(n)
-                    if o != self.rank:
-                        mine = plan.need[(plan.need >= rs[o]) & (plan.need < rs[o + 1])] - rs[o]
-                        pos = np.searchsorted(plan.send_idx[o], mine)
-                        cols.append(plan.halo_base + o * plan.width + pos)
-                        idxs.append(mine)
-                        n += len(mine)
-                    hi.append(n)
-                self.pull_col = torch.from_numpy(np.concatenate(cols).astype(np.int32) if cols else np.zeros(0, np.int32)).to(device)
-                self.pull_idx = torch.from_numpy(np.concatenate(idxs).astype(np.int32) if idxs else np.zeros(0, np.int32)).to(device)
+                pcol, pidx, lo, hi = plan.pull_lists()
+                self.pull_col = torch.from_numpy(pcol).to(device)
+                self.pull_idx = torch.from_numpy(pidx).to(device)
                 base = nimg * 32
                 peer_x = [[(ptrs[q] + p * stride * esz) if hi[q] > lo[q] else 0 for q in range(self.P)] for p in range(2)]
                 peer_ready = [(fptrs[q] + 4 * base) if q in nb[self.rank] else 0 for q in range(self.P)]

@@ -156,3 +156,30 @@ def test_exchange_pattern_symmetry_decides_the_packet_protocol():
     assert PACKETS_BELOW_ENTRIES == 12_000_000  # the same threshold as kDistPdlMinEntries in csrc/dist.cu
     src = open(__file__.replace("tests/test_dist_cpu.py", "respasol_b200/csrc/dist.cu")).read()
     assert "kDistPdlMinEntries = 12000000" in src
+
+
+def test_pull_lists_fetch_exactly_what_the_relabelled_columns_read():
+    """HaloPlan.pull_lists (the pull exchange's setup): filling the halo of x_ext with owner_x[idx] at `col` for every listed entry
+    gives the same product as the global one -- on a stencil (contiguous boundary planes) and on a scattered pattern."""
+    import orc
+    from respasol_b200 import host
+    from respasol_b200.dist import HaloPlan
+    for full in (host.gen_stencil27(6, 5, 12, seed=1), host.gen_powerlaw(900, 2.2, 16, 2, 300, 4)):
+        P = 3
+        starts = np.array([0, full.m // 3 & ~3, 2 * full.m // 3 & ~3, full.m])
+        plans = [HaloPlan(full.rows(starts[r], starts[r + 1]), starts, r) for r in range(P)]
+        needs = [p.need for p in plans]
+        x = orc.dlarnv(full.n) - 0.5
+        ref = orc.spmv(full, x, "d")
+        for r, p in enumerate(plans):
+            p.finish(needs)
+            col, idx, lo, hi = p.pull_lists()
+            assert len(col) == len(idx) == p.recv_entries and lo[0] == 0 and hi[-1] == len(col)
+            x_ext = np.zeros(p.n_ext)
+            x_ext[:p.n_local] = x[starts[r]:starts[r + 1]]
+            for o in range(P):
+                assert o != r or hi[o] == lo[o]
+                sl = slice(lo[o], hi[o])
+                assert np.all(col[sl] >= p.halo_base + o * p.width) and np.all(col[sl] < p.halo_base + (o + 1) * p.width)
+                x_ext[col[sl]] = x[starts[o] + idx[sl]]
+            assert np.array_equal(orc.spmv(p.remapped, x_ext, "d"), ref[starts[r]:starts[r + 1]]), r
